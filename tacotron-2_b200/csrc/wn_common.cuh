@@ -1,0 +1,96 @@
+// wn_common.cuh - internal types shared by the kernels and the C-ABI layer of libwavenet_b200.so.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/wavenet_b200.h"
+#include "../../include/wn_math.h"
+
+// Device-side view of the model in the "generic" layout: every matrix is [K][N] row-major exactly as TensorFlow
+// stores/linearises it (modules.py:238-251: row = tap*C_in + ci, tap 0 = oldest sample), biases always present
+// (zeros when hparams.use_bias is off).  Residual layers are laid out with one common stride.
+struct WnModelDev {
+    int L, R, G, S, O, ksize, H, cin, gin, in_ch, NZ;
+    int input_type, legacy, residual_legacy;
+    float log_scale_min, log_scale_min_gauss;
+    int dil[WN_MAX_LAYERS];
+    int qlen[WN_MAX_LAYERS];       // ring slots per layer = (k-1)*d + 1   (wavenet.py:815)
+    long long qoff[WN_MAX_LAYERS]; // float offset of layer l's ring inside one utterance's ring block
+    long long ring_per_utt;        // floats
+    const float *first_w, *first_b;
+    const float *layers;           // base of layer 0
+    long long layer_stride;        // floats
+    int off_conv_w, off_conv_b, off_cin_w, off_cin_b, off_gin_w, off_gin_b, off_out_w, off_out_b, off_skip_w,
+        off_skip_b;
+    const float *h1_w, *h1_b, *h2_w, *h2_b;
+    const float *emb;              // [n_speakers][gin] or nullptr
+};
+
+struct WnUpLayerDev {
+    const float *w, *b;
+    int scale;
+};
+
+struct WnHostTensor {
+    std::vector<float> data;
+    std::vector<int64_t> shape;
+};
+
+struct WnPipePlan;  // wn_loop_pipe.cu
+
+struct wn_handle {
+    wn_config cfg;
+    int device = 0, sm_count = 0;
+    bool finalized = false;
+    std::string err;
+    std::map<std::string, WnHostTensor> host_w;
+    WnModelDev m;
+    float *d_blob = nullptr;  // all generic-layout weights
+    size_t blob_floats = 0;
+    WnUpLayerDev up[WN_MAX_UPSAMPLE];
+    int n_up = 0;
+    // scratch (grown on demand, owned by the handle)
+    float *d_ring = nullptr;  size_t ring_floats = 0;
+    float *d_cup = nullptr;   size_t cup_floats = 0;
+    float *d_tmp0 = nullptr, *d_tmp1 = nullptr; size_t tmp_floats = 0;
+    float *d_gemb = nullptr;  size_t gemb_floats = 0;
+    // host-call staging
+    float *d_in_c = nullptr, *d_in_noise = nullptr, *d_in_teacher = nullptr, *d_out_audio = nullptr,
+          *d_out_raw = nullptr;
+    int32_t *d_in_g = nullptr;
+    size_t in_c_n = 0, in_noise_n = 0, in_teacher_n = 0, out_audio_n = 0, out_raw_n = 0, in_g_n = 0;
+    WnPipePlan *pipe = nullptr;
+    int engine = WN_ENGINE_GENERIC;
+    int64_t launches = 0;
+    int64_t n_params = 0;
+};
+
+#define WN_CUDA_TRY(h, expr)                                                                   \
+    do {                                                                                       \
+        cudaError_t e__ = (expr);                                                              \
+        if (e__ != cudaSuccess) {                                                              \
+            (h)->err = std::string(#expr) + ": " + cudaGetErrorString(e__);                    \
+            return WN_ERR_CUDA;                                                                \
+        }                                                                                      \
+    } while (0)
+
+// kernels / launchers implemented in the other translation units --------------------------------------------
+int wn_launch_upsample(wn_handle *h, const float *c, int B, int Tc, float *c_up, cudaStream_t st);
+int wn_launch_loop_generic(wn_handle *h, const float *c_up, const float *g_emb, const float *noise,
+                           const float *teacher, int inputs_mode, int B, int T, float *audio, float *raw,
+                           cudaStream_t st);
+int wn_launch_step_full(wn_handle *h, const float *x, const float *c_up, const float *g_emb, int B, int T,
+                        float *raw, cudaStream_t st);
+// pipelined persistent engine (wn_loop_pipe.cu)
+int wn_pipe_plan(wn_handle *h);   // decides whether the model fits; builds packed weights; 0 = usable
+void wn_pipe_free(wn_handle *h);
+void wn_pipe_fill_info(wn_handle *h, wn_info *info);
+int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int B, int T,
+                        float *audio, float *raw, cudaStream_t st);
+
+int wn_ensure(wn_handle *h, float **p, size_t *cur, size_t need);

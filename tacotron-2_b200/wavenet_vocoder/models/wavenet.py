@@ -1,0 +1,176 @@
+"""WaveNet vocoder model object - host-side mirror of the reference's ``WaveNet`` class
+(``code/wavenet_vocoder/models/wavenet.py:86-923``) for the synthesis path only.
+
+Same constructor checks, attribute names (``receptive_field``, ``tower_y_hat``, ``tower_y_hat_eval``,
+``tower_synth_upsampled_local_features``) and method names (``initialize``, ``incremental``, ``step``) as the
+reference, but eager: the reference builds a TF graph over placeholders and runs it later through a session, here
+the calls take numpy arrays and run the sm_100a kernels of libwavenet_b200.so immediately.  Training members
+(``add_loss``, ``add_optimizer``, EMA) are out of scope (disabled in this fork).
+
+The random draws the reference takes inside its ``tf.while_loop`` (gaussian.py:49, mixture.py:91,104, wavenet.py:865)
+are an explicit ``noise`` input here so the output is a pure function of (weights, c, noise, teacher).
+"""
+import numpy as np
+
+from hparams import get_hop_size, validate_wavenet_hparams
+from infolog import log
+from wavenet_vocoder import util
+from wavenet_vocoder import weights as wn_weights
+from wavenet_vocoder._native import NativeWaveNet
+from wavenet_vocoder.util import is_mulaw, is_mulaw_quantize, is_scalar_input
+
+receptive_field_size = wn_weights.receptive_field_size
+
+
+def make_noise(hp, T, B, rng):
+	"""Draws for T steps of B utterances in the layout the kernels consume, [T, B, NZ]."""
+	if is_scalar_input(hp.input_type):
+		if hp.out_channels == 2:
+			return rng.standard_normal((T, B, 1), dtype=np.float32)
+		K = hp.out_channels // 3
+		return rng.uniform(1e-5, 1. - 1e-5, (T, B, K + 1)).astype(np.float32)
+	return rng.uniform(0., 1., (T, B, 1)).astype(np.float32)
+
+
+class WaveNet(object):
+	"""Tacotron-2 Wavenet Vocoder model (synthesis path)."""
+
+	def __init__(self, hparams, init=False, engine='auto'):
+		self._hparams = hparams
+		validate_wavenet_hparams(hparams)	#wavenet.py:93-97 + models/__init__.py:6-9 + the late assert of :800, eagerly
+		self.scalar_input = is_scalar_input(hparams.input_type)
+		self.receptive_field = receptive_field_size(hparams.layers, hparams.stacks, hparams.kernel_size)
+		self._engine = engine
+		self._native = None
+		self._rng = np.random.default_rng(hparams.get('wavenet_synthesis_seed'))
+		self.tower_y_hat = []
+		self.tower_y_hat_eval = []
+		self.tower_synth_upsampled_local_features = []
+		self.variables = None
+
+	#Sanity check functions (wavenet.py:637-647)
+	def has_speaker_embedding(self):
+		return self._hparams.gin_channels > 0 and self._hparams.use_speaker_embedding
+
+	def local_conditioning_enabled(self):
+		return self._hparams.cin_channels > 0
+
+	def global_conditioning_enabled(self):
+		return self._hparams.gin_channels > 0
+
+	# ---- weights ("restore") ------------------------------------------------------------------------
+	def load_weights(self, weights):
+		"""weights: dict name -> array in TF layouts (wavenet_vocoder/weights.py).  Uploads to the current CUDA device."""
+		wn_weights.check_weights(self._hparams, weights)
+		if self._native is not None:
+			self._native.close()
+		self._native = NativeWaveNet(self._hparams, weights, engine=self._engine)
+		self.variables = list(weights.keys())
+		info = self._native.info()
+		log('Initialized Wavenet model. Dimensions (? = dynamic shape): ')
+		log('  Receptive Field:           ({} samples / {:.1f} ms)'.format(self.receptive_field,
+			self.receptive_field / self._hparams.sample_rate * 1000.))
+		log('  WaveNet Parameters:        {:.3f} Million.'.format(info['n_params'] / 1000000))
+		log('  Engine:                    {} ({} SMs)'.format(info['engine'], info['sm_count']))
+		return self
+
+	@property
+	def native(self):
+		if self._native is None:
+			raise RuntimeError('WaveNet weights not loaded: call load_weights() (Synthesizer.load does it)')
+		return self._native
+
+	def set_seed(self, seed):
+		self._rng = np.random.default_rng(seed)
+
+	# ---- wavenet.py:218-473, synthesis branch only ---------------------------------------------------
+	def initialize(self, y, c, g, input_lengths, x=None, synthesis_length=None, test_inputs=None, split_infos=None,
+			noise=None, want_raw=True):
+		"""Synthesis branch of the reference's initialize() (y is None, x is None): c [B, Tc, num_mels] normalised
+		local conditions, g [B, 1] speaker ids or None, test_inputs [B, T, 1] teacher-forcing waveform or None.
+		Fills tower_y_hat ([B, T] waveform), tower_y_hat_eval (raw per-step parameters) and
+		tower_synth_upsampled_local_features like the reference (one tower: utterances shard across processes)."""
+		hp = self._hparams
+		if y is not None or x is not None:
+			raise NotImplementedError('training / evaluation towers are out of scope (disabled in the reference fork)')
+		if c is None:
+			raise NotImplementedError('synthesis without local conditioning needs synthesis_length; use incremental()')
+		c = np.asarray(c, np.float32)
+		if c.ndim != 3:
+			raise ValueError('Expected 3 dimension shape [batch_size(1), time_length, {}] for local condition features '
+				'but found {}'.format(hp.cin_channels, c.shape))	#wavenet.py:414-417
+		B, Tc, _ = c.shape
+		T = Tc * get_hop_size(hp)	#wavenet.py:419-423
+		teacher = None
+		if test_inputs is not None:
+			teacher = np.asarray(test_inputs, np.float32).reshape(B, -1)
+			if teacher.shape[1] < T:
+				teacher = np.pad(teacher, [(0, 0), (0, T - teacher.shape[1])])
+			teacher = teacher[:, :T]
+		if noise is None:
+			noise = make_noise(hp, T, B, self._rng)
+		res = self.native.synthesize_host(c, noise, g_ids=g, teacher=teacher, want_raw=want_raw)
+		audio, raw = res if want_raw else (res, None)
+		self.tower_y_hat = [audio]
+		if raw is not None:
+			#scalar input: [B, O, T]; mulaw-quantize: [B, T, C]  (wavenet.py:904-908)
+			self.tower_y_hat_eval = [raw if is_mulaw_quantize(hp.input_type) else np.transpose(raw, [0, 2, 1])]
+		self.tower_synth_upsampled_local_features = [None]	#materialised on request by upsample()
+		return audio
+
+	def upsample(self, c):
+		"""The conditioning network alone (wavenet.py:781-803): c [B, Tc, 80] -> [B, 80, T] like
+		upsampled_local_features."""
+		import torch
+		c = np.ascontiguousarray(c, np.float32)
+		B, Tc, M = c.shape
+		T = Tc * get_hop_size(self._hparams)
+		dc = torch.from_numpy(c).cuda()
+		out = torch.empty((B, T, M), dtype=torch.float32, device='cuda')
+		self.native.upsample(dc, B, Tc, out, stream=torch.cuda.current_stream().cuda_stream)
+		torch.cuda.synchronize()
+		return out.permute(0, 2, 1).contiguous().cpu().numpy()
+
+	def incremental(self, initial_input=None, c=None, g=None, time_length=100, test_inputs=None, softmax=True,
+			quantize=True, log_scale_min=-7.0, log_scale_min_gauss=-7.0, noise=None):
+		"""Reference signature (wavenet.py:724).  c here is [B, cin, Tc] (channels first, as the reference passes it);
+		returns generated samples [B, C, T] (scalar input: C=1; mulaw-quantize: one-hot C=quantize_channels).
+		initial_input / softmax / log_scale_* are accepted for signature compatibility: the start frame is the
+		reference's silence frame and the scale floors come from hparams, exactly as initialize() passes them."""
+		hp = self._hparams
+		if c is None:
+			raise NotImplementedError('local conditioning is required by this build (both shipped configs use it)')
+		c_btc = np.ascontiguousarray(np.transpose(np.asarray(c, np.float32), [0, 2, 1]))
+		audio = self.initialize(None, c_btc, g, None, test_inputs=test_inputs, noise=noise)
+		B = audio.shape[0]
+		if is_mulaw_quantize(hp.input_type):
+			cls = util.mulaw_quantize(audio, hp.quantize_channels)
+			return np.transpose(np.eye(hp.quantize_channels, dtype=np.float32)[cls], [0, 2, 1])
+		if is_mulaw(hp.input_type):
+			return util.mulaw(audio, hp.quantize_channels).astype(np.float32).reshape(B, 1, -1)
+		return audio.reshape(B, 1, -1)
+
+	def step(self, x, c=None, g=None, softmax=False):
+		"""Teacher-forced full-sequence pass (wavenet.py:650-721), dropout off.  x [B, C_in, T] (scalar: C_in = 1;
+		mulaw-quantize: one-hot), c [B, cin, Tc] -> [B, out_channels, T]."""
+		import torch
+		hp = self._hparams
+		x = np.asarray(x, np.float32)
+		B, Cin, T = x.shape
+		xin = x[:, 0, :] if self.scalar_input else np.argmax(x, axis=1).astype(np.float32)
+		c_btc = np.ascontiguousarray(np.transpose(np.asarray(c, np.float32), [0, 2, 1]))
+		Tc = c_btc.shape[1]
+		if Tc * get_hop_size(hp) != T:
+			raise ValueError('upsampled conditioning length {} != input length {} (wavenet.py:697)'.format(
+				Tc * get_hop_size(hp), T))
+		dx = torch.from_numpy(np.ascontiguousarray(xin)).cuda()
+		dc = torch.from_numpy(c_btc).cuda()
+		dg = None if g is None else torch.from_numpy(np.asarray(g, np.int32).reshape(B)).cuda()
+		raw = torch.empty((B, T, hp.out_channels), dtype=torch.float32, device='cuda')
+		self.native.step_full(dx, dc, B, Tc, raw, g_ids=dg, stream=torch.cuda.current_stream().cuda_stream)
+		torch.cuda.synchronize()
+		out = raw.permute(0, 2, 1).contiguous().cpu().numpy()
+		if softmax:
+			e = np.exp(out - out.max(axis=1, keepdims=True))
+			out = e / e.sum(axis=1, keepdims=True)
+		return out

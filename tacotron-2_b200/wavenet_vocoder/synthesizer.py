@@ -1,0 +1,113 @@
+"""``Synthesizer`` - the drop-in boundary of the hot path (reference ``code/wavenet_vocoder/synthesizer.py``).
+
+Same ``load(checkpoint_path, hparams, model_name)`` / ``synthesize(mel_spectrograms, speaker_ids, basenames,
+out_dir, log_dir)`` contract: a list of un-normalised ``[frames, num_mels]`` mels in, peak-normalised int16 wav files
+out.  Where the reference does one ``session.run`` on a TF graph (:97) this does one ``wn_synthesize_host`` call into
+libwavenet_b200.so.  Differences, all stated in DESIGN.md: weights come from an ``.npz`` weight table or
+``random:<seed>`` (TF-checkpoint import is a "next" row); PNG plots are skipped (no matplotlib here,
+out of scope); an optional ``seed`` makes the draws reproducible (the reference's are unseeded).
+"""
+import os
+
+import numpy as np
+
+from datasets.audio import get_hop_size, save_wavenet_wav
+from infolog import log
+from wavenet_vocoder import weights as wn_weights
+from wavenet_vocoder.models import create_model
+from wavenet_vocoder.models.wavenet import make_noise
+
+
+def _interp(feats, in_range):
+	#rescales from [-max, max] (or [0, max]) to [0, 1]  (feeder.py:426-428)
+	return (feats - in_range[0]) / (in_range[1] - in_range[0])
+
+
+def _pad_inputs(x, maxlen, _pad=0):
+	return np.pad(x, [(0, maxlen - len(x)), (0, 0)], mode='constant', constant_values=_pad)
+
+
+def resolve_weights(checkpoint_path, hparams):
+	"""'random:<seed>[:kind]' -> deterministic random init; '*.npz' -> weight table; anything else is a TF checkpoint,
+	which this build cannot read yet."""
+	if isinstance(checkpoint_path, dict):
+		return checkpoint_path
+	if checkpoint_path is None or str(checkpoint_path).startswith('random'):
+		parts = str(checkpoint_path or 'random').split(':')
+		seed = int(parts[1]) if len(parts) > 1 and parts[1] else hparams.wavenet_random_seed
+		kind = parts[2] if len(parts) > 2 else 'tf-init'
+		return wn_weights.init_weights(hparams, seed=seed, kind=kind)
+	if str(checkpoint_path).endswith('.npz') and os.path.exists(checkpoint_path):
+		return wn_weights.load_weights(checkpoint_path)
+	raise RuntimeError('Failed to load checkpoint at {} (expected an .npz weight table or random:<seed>; '
+		'TensorFlow checkpoints are not readable by this build)'.format(checkpoint_path))
+
+
+class Synthesizer:
+	def load(self, checkpoint_path, hparams, model_name='WaveNet', engine='auto'):
+		log('Constructing model: {}'.format(model_name))
+		self._hparams = hparams
+		self.synth_debug = hparams.wavenet_synth_debug
+		self.model = create_model(model_name, hparams, engine=engine)
+		log('Loading checkpoint: {}'.format(checkpoint_path))
+		self.model.load_weights(resolve_weights(checkpoint_path, hparams))
+		self._rng = np.random.default_rng(hparams.get('wavenet_synthesis_seed'))
+		return self
+
+	def prepare_batch(self, mel_spectrograms):
+		"""synthesizer.py:56-70: true lengths, clip, pad with the range minimum, stack, rescale to [0, 1]."""
+		hp = self._hparams
+		audio_lengths = [len(x) * get_hop_size(hp) for x in mel_spectrograms]
+		maxlen = max([len(x) for x in mel_spectrograms])
+		T2_output_range = (-hp.max_abs_value, hp.max_abs_value) if hp.symmetric_mels else (0, hp.max_abs_value)
+		if hp.clip_for_wavenet:
+			mel_spectrograms = [np.clip(x, T2_output_range[0], T2_output_range[1]) for x in mel_spectrograms]
+		c_batch = np.stack([_pad_inputs(x, maxlen, _pad=T2_output_range[0]) for x in mel_spectrograms]).astype(np.float32)
+		if hp.normalize_for_wavenet:
+			c_batch = _interp(c_batch, T2_output_range).astype(np.float32)
+		return c_batch, audio_lengths
+
+	def synthesize(self, mel_spectrograms, speaker_ids, basenames, out_dir, log_dir, seed=None, noise=None,
+			return_wavs=False):
+		hp = self._hparams
+		local_cond, global_cond = self._check_conditions()
+		if not local_cond:
+			raise NotImplementedError('synthesis without local conditioning is not wired (both shipped configs use mels)')
+
+		if self.synth_debug:	#synthesizer.py:51-53
+			assert len(hp.wavenet_debug_mels) == len(hp.wavenet_debug_wavs)
+			mel_spectrograms = [np.load(mel_file) for mel_file in hp.wavenet_debug_mels]
+
+		c_batch, audio_lengths = self.prepare_batch(mel_spectrograms)
+		g = None if (speaker_ids is None or not global_cond) else np.asarray(speaker_ids, dtype=np.int32).reshape(len(c_batch), 1)
+
+		teacher = None
+		if self.synth_debug:	#synthesizer.py:83-94 teacher forcing with the target waveforms
+			test_wavs = [np.load(debug_wav).reshape(-1, 1) for debug_wav in hp.wavenet_debug_wavs]
+			max_test_len = max([len(x) for x in test_wavs])
+			teacher = np.stack([_pad_inputs(x, max_test_len) for x in test_wavs]).astype(np.float32)
+
+		B, Tc = c_batch.shape[0], c_batch.shape[1]
+		T = Tc * get_hop_size(hp)
+		if noise is None:
+			rng = self._rng if seed is None else np.random.default_rng(seed)
+			noise = make_noise(hp, T, B, rng)
+
+		#Generate wavs and clip extra padding to select Real speech parts  (synthesizer.py:97-104)
+		generated = self.model.initialize(None, c_batch, g, None, test_inputs=teacher, noise=noise, want_raw=False)
+		generated_wavs = [wav[:length] for wav, length in zip(generated, audio_lengths)]
+		if return_wavs:
+			return generated_wavs
+
+		audio_filenames = []
+		for i, generated_wav in enumerate(generated_wavs):
+			#Save wav to disk (plots of the reference, :115-125, are out of scope)
+			audio_filename = os.path.join(out_dir, 'wavenet-audio-{}.wav'.format(basenames[i]))
+			save_wavenet_wav(generated_wav, audio_filename, sr=hp.sample_rate, inv_preemphasize=hp.preemphasize, k=hp.preemphasis)
+			audio_filenames.append(audio_filename)
+		return audio_filenames
+
+	def _check_conditions(self):
+		local_condition = self._hparams.cin_channels > 0
+		global_condition = self._hparams.gin_channels > 0
+		return local_condition, global_condition
