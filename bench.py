@@ -1,0 +1,341 @@
+"""bench.py - audio samples/s and real-time factor of WaveNet incremental (fast-wavenet) synthesis on B200.
+
+  python bench.py --gpus N --steps K --warmup W            (N>1: launched by torch.distributed.run, one rank per GPU)
+  python bench.py --impl reference ...                     (the CPU arm: the oracle port on the host cores)
+
+A "step" is one pass of the hot path over one batch of synthetic utterances: upsampling network + the autoregressive
+loop + decode (wn_synthesize), random-init weights (seed 5339, 'tf-init'), synthetic mels and noise.
+Workload: BASELINE.json configs[1] - default_22k hparams, 64 utterances x 5 s (401 frames -> 110 275 samples each)
+PER GPU (weak scaling: utterances are independent, every rank synthesises its own 64 and rank 0 gathers the audio).
+`--workload c3` runs configs[2] instead: 256 utterances x 10 s sharded over the ranks (strong scaling).
+
+One JSON line on stdout (rank 0).  `value` is device-resident (inputs in HBM before the timed region, CUDA events on
+the launch stream, max over ranks); `e2e` goes through the host-buffer C-ABI call wn_synthesize_host (pinned host
+buffers, H2D + D2H inside the timed region).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, 'tacotron-2_b200')):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+SAMPLE_RATE = 22050
+METRIC = 'audio samples/sec (real-time factor = value / 22050), WaveNet incremental synthesis'
+UNIT = 'samples/s'
+WORKLOADS = {
+    # name: (utterances, frames, weak scaling?)
+    'c2': (64, 401, True),    # BASELINE.json configs[1]: batch 64 x 5 s on 1 B200 (per GPU when N > 1)
+    'c3': (256, 802, False),  # configs[2]: 256 x 10 s sharded over the ranks
+    'c1': (1, 81, True),      # configs[0]: batch 1 x 1 s
+    'tiny': (8, 8, True),     # development only
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=3)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS))
+    ap.add_argument('--engine', default='auto', choices=['auto', 'generic', 'pipeline'])
+    ap.add_argument('--hparams', default='default_22k', choices=['default_22k', 'paper'])
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-e2e', action='store_true')
+    return ap.parse_args()
+
+
+def get_hparams(name):
+    import hparams as hp_mod
+    if name == 'paper':
+        import paper_hparams
+        return paper_hparams.hparams.copy()
+    return hp_mod.default_22k()
+
+
+def synth_inputs(hp, utt_ids, Tc, with_noise=True):
+    """Synthetic normalised mels [B, Tc, 80] (seed 1234+u per utterance) and Gaussian / uniform noise [T, B, NZ]."""
+    from wavenet_vocoder.models.wavenet import make_noise
+    B = len(utt_ids)
+    c = np.empty((B, Tc, hp.num_mels), np.float32)
+    for i, u in enumerate(utt_ids):
+        mel = np.random.default_rng(1234 + u).uniform(-4, 4, (Tc, hp.num_mels)).astype(np.float32)
+        c[i] = (np.clip(mel, -4, 4) + 4) / 8
+    T = Tc * hp.hop_size
+    noise = make_noise(hp, T, B, np.random.default_rng(2024 + utt_ids[0])) if with_noise else None
+    return c, noise
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port (C restatement, OpenMP over utterances) on the box's host cores
+# ---------------------------------------------------------------------------------------------------------------
+def cpu_sample(hp, weights, cores, frames=None):
+    """One bounded sample of the workload: `cores` utterances x `frames` frames through upsample + loop.
+    Returns (samples, seconds)."""
+    from oracle.c_oracle import COracle
+    frames = frames or 24   # 24 frames = 6 600 samples/utterance, ~5 s per core at ~1.3 k samples/s/core
+    co = COracle(hp, weights)
+    c, noise = synth_inputs(hp, list(range(cores)), frames)
+    t0 = time.perf_counter()
+    co.synthesize(c, noise=noise, nthreads=cores)
+    dt = time.perf_counter() - t0
+    return cores * frames * hp.hop_size, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    from wavenet_vocoder import weights as W
+    hp = get_hparams(args.hparams)
+    weights = W.init_weights(hp, seed=5339, kind='tf-init')
+    cores = os.cpu_count() or 1
+    B, Tc, weak = WORKLOADS[args.workload]
+    for _ in range(args.warmup):
+        cpu_sample(hp, weights, cores, frames=2)
+    n_tot, t_tot = 0, 0.0
+    for _ in range(args.steps):
+        n, dt = cpu_sample(hp, weights, cores)
+        n_tot += n
+        t_tot += dt
+    v = n_tot / t_tot
+    sample = '{} utterances x 24 frames ({} samples) per step, C oracle port with OpenMP over utterances'.format(cores, cores * 24 * hp.hop_size)
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': v, 'unit': UNIT, 'rtf': v / SAMPLE_RATE, 'n_gpus': args.gpus,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * t_tot / args.steps, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': workload_config(args, hp, B, Tc, args.gpus),
+        'cpu_baseline': {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample,
+                         'note': 'the reference is TensorFlow-1.x Python and cannot run on this box; this is the CPU '
+                                 'restatement of its math (oracle/c/wn_oracle.c)'},
+        'e2e': {'value': v, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, hp, B, Tc, n_gpus):
+    weak = WORKLOADS[args.workload][2]
+    return {
+        'workload': 'WaveNet incremental synthesis, {} hparams (L{} R{} G{} S{} out{} {}), {} utterances x {:.1f} s '
+                    '({} frames -> {} samples){}'.format(
+                        args.hparams, hp.layers, hp.residual_channels, hp.gate_channels, hp.skip_out_channels,
+                        hp.out_channels, hp.upsample_type, B, Tc * hp.hop_size / hp.sample_rate, Tc, Tc * hp.hop_size,
+                        ' per GPU' if weak else ' total, sharded over the ranks'),
+        'baseline_config': {'c2': 'configs[1]', 'c3': 'configs[2]', 'c1': 'configs[0]'}.get(args.workload, 'dev'),
+        'utterances_per_gpu': B if weak else B // n_gpus, 'frames': Tc, 'samples_per_utterance': Tc * hp.hop_size,
+        'weights': 'random-init seed 5339 (tf-init)', 'parallelism': 'dp{} (utterances, no data-path collective; final gather)'.format(n_gpus),
+        'l2': 'inputs+scratch larger than L2 (upsampled conditioning {:.2f} GB per pass) and an L2 flush between steps'.format(
+            (B if weak else B // n_gpus) * Tc * hp.hop_size * hp.num_mels * 4 / 1e9),
+    }
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# clocks during the timed region (B200_PROFILING.md recipe)
+# ---------------------------------------------------------------------------------------------------------------
+class ClockSampler(object):
+    Q = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.gpu), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '200'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(',')])
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, power, reasons = [], [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); smax.append(float(r[2])); power.append(float(r[3]))
+                for n, v in zip(names, r[5:9]):
+                    if v.lower().startswith('active'):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {'sm_mhz': float(np.median(sm)) if sm else None, 'sm_max_mhz': max(smax) if smax else None,
+                'power_w_max': max(power) if power else None, 'samples': len(sm), 'reasons': sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from wavenet_vocoder import weights as W
+    from wavenet_vocoder._native import NativeWaveNet
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    assert torch.cuda.is_available(), 'bench.py --impl ours needs a B200 (there is no CPU path)'
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
+    n_gpus = world
+
+    hp = get_hparams(args.hparams)
+    B_total, Tc, weak = WORKLOADS[args.workload]
+    B = B_total if weak else B_total // world
+    utt0 = rank * B
+    T = Tc * hp.hop_size
+    weights = W.init_weights(hp, seed=5339, kind='tf-init')
+    net = NativeWaveNet(hp, weights, engine=args.engine)
+    info0 = net.info()
+    stream = torch.cuda.current_stream()
+    sp = stream.cuda_stream
+
+    # synthetic inputs, resident in HBM before the timed region
+    c_np, noise_np = synth_inputs(hp, list(range(utt0, utt0 + B)), Tc)
+    d_c = torch.from_numpy(c_np).cuda()
+    d_noise = torch.from_numpy(noise_np).cuda()
+    d_audio = torch.empty((B, T), dtype=torch.float32, device='cuda')
+    gathered = [torch.empty_like(d_audio) for _ in range(world)] if (world > 1 and rank == 0) else None
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device='cuda')  # 256 MB > 126 MB L2
+
+    def one_step():
+        net.synthesize(d_c, B, Tc, d_noise, d_audio, stream=sp)
+        if world > 1:   # the final gather of the path (synthesizer.py:100-101): audio of every rank onto rank 0
+            dist.gather(d_audio, gathered, dst=0)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        one_step()
+    barrier()
+    assert bool(torch.isfinite(d_audio).all()), 'non-finite audio'
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = net.info()['kernel_launches']
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    loop_ms, up_ms = [], []
+    barrier()
+    for s, e in ev:
+        flush.fill_(1.0)           # L2 flush, outside the event pair
+        s.record(stream)
+        one_step()
+        e.record(stream)
+        e.synchronize()
+        inf = net.info()
+        loop_ms.append(inf['last_loop_ms'])
+        up_ms.append(inf['last_upsample_ms'])
+    barrier()
+    total_ms = sum(s.elapsed_time(e) for s, e in ev)
+    launches = net.info()['kernel_launches'] - launches0 + args.steps   # + the flush fill kernels are torch's, not ours
+    launches -= args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([total_ms], dtype=torch.float64, device='cuda')
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    samples_per_step = B * T * world
+    value = samples_per_step * args.steps / (total_ms / 1e3)
+
+    # e2e: the host-buffer C-ABI call (pinned host memory; H2D of mels+noise and D2H of audio inside the timed region)
+    e2e = None
+    if not args.no_e2e:
+        h_c = torch.from_numpy(c_np).pin_memory()
+        h_noise = torch.from_numpy(noise_np).pin_memory()
+        h_audio = torch.empty((B, T), dtype=torch.float32).pin_memory()
+        net.synthesize_host(h_c.numpy(), h_noise.numpy(), audio_out=h_audio.numpy(), stream=sp)  # warm-up (staging buffers)
+        n_e2e = max(1, min(args.steps, 3))
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            net.synthesize_host(h_c.numpy(), h_noise.numpy(), audio_out=h_audio.numpy(), stream=sp)
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device='cuda')
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {'value': samples_per_step * n_e2e / float(dt.item()), 'unit': UNIT,
+               'h2d_bytes_per_step': int(c_np.nbytes + noise_np.nbytes), 'd2h_bytes_per_step': int(B * T * 4),
+               'steps': n_e2e, 'api': 'wn_synthesize_host (libwavenet_b200.so C ABI), pinned host buffers'}
+        assert bool(np.isfinite(h_audio.numpy()).all())
+
+    if rank == 0:
+        info = net.info()
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+        except Exception:
+            pass
+        hbm_peak = peaks.get('hbm_gbs', 6650.0)
+        peak_src = 'measured (MEASURED_PEAKS.json)' if 'hbm_gbs' in peaks else 'fallback (B200_PROFILING.md)'
+        lm = float(np.mean(loop_ms))
+        alg_bytes = float(info['bytes_per_sample']) * B * T
+        achieved = alg_bytes / (lm / 1e3) / 1e9
+        roofline = {
+            'kernel': 'autoregressive loop kernel ({} engine)'.format(info['engine']), 'bound': 'hbm',
+            'achieved': achieved, 'peak': hbm_peak, 'unit': 'GB/s', 'frac': achieved / hbm_peak, 'traffic': None,
+            'peak_source': peak_src, 'algorithmic_bytes_per_launch': alg_bytes,
+            'bytes_per_sample': int(info['bytes_per_sample']), 'kernel_ms': lm, 'upsample_ms': float(np.mean(up_ms)),
+            'us_per_step': 1e3 * lm / T, 'fp32_tflops': info['flops_per_sample'] * B * T / (lm / 1e3) / 1e12,
+            'upsample_gbs': B * T * hp.num_mels * 4 * (1 + 1.0 / hp.hop_size) / (float(np.mean(up_ms)) / 1e3) / 1e9,
+            'note': 'the loop is bound by serial step latency (us_per_step), not by bytes or flops; see DESIGN.md',
+        }
+        line = {
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'rtf': value / SAMPLE_RATE, 'n_gpus': n_gpus,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': total_ms / args.steps, 'higher_is_better': True,
+            'scaling': 'weak' if weak else 'strong', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': workload_config(args, hp, B_total, Tc, n_gpus), 'engine': info['engine'],
+            'clocks': clocks, 'gpu_launches': int(launches), 'roofline': roofline,
+        }
+        if e2e is not None:
+            line['e2e'] = e2e
+        if not args.no_cpu_baseline and world == 1:
+            cores = os.cpu_count() or 1
+            n, dt = cpu_sample(hp, weights, cores)
+            line['cpu_baseline'] = {
+                'value': n / dt, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                'sample': '{} utterances x 24 frames ({} samples), C oracle port (oracle/c/wn_oracle.c), OpenMP over '
+                          'utterances, upsample included'.format(cores, n)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

@@ -73,6 +73,8 @@ typedef struct wn_info {
     int32_t pipeline_ctas, pipeline_ctas_per_layer, pipeline_group_size;
     int32_t sm_count;
     int64_t kernel_launches;      /* kernels launched by this handle so far (for the bench's gpu_launches) */
+    float last_upsample_ms;       /* CUDA-event duration of the upsampling net in the last completed wn_synthesize (-1: n/a) */
+    float last_loop_ms;           /* CUDA-event duration of the loop kernel in the last completed wn_synthesize (-1: n/a) */
 } wn_info;
 
 typedef struct wn_handle wn_handle;

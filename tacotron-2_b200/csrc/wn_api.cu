@@ -330,10 +330,19 @@ extern "C" int wn_synthesize(wn_handle *h, const float *c, const int32_t *g_ids,
     cudaStream_t st = (cudaStream_t)stream;
     const int T = Tc * (h->cfg.cin_channels > 0 ? h->cfg.hop_size : 1);
     const float *c_up, *g_emb;
+    if (!h->ev[0])
+        for (int i = 0; i < 3; ++i) WN_CUDA_TRY(h, cudaEventCreate(&h->ev[i]));
+    h->ev_valid = false;
+    WN_CUDA_TRY(h, cudaEventRecord(h->ev[0], st));
     rc = prep_conditioning(h, c, g_ids, B, Tc, c_up_out, &c_up, &g_emb, st);
     if (rc) return rc;
-    if (h->engine == WN_ENGINE_PIPELINE) return wn_launch_loop_pipe(h, c_up, noise, teacher, B, T, audio, raw, st);
-    return wn_launch_loop_generic(h, c_up, g_emb, noise, teacher, 0, B, T, audio, raw, st);
+    WN_CUDA_TRY(h, cudaEventRecord(h->ev[1], st));
+    if (h->engine == WN_ENGINE_PIPELINE) rc = wn_launch_loop_pipe(h, c_up, noise, teacher, B, T, audio, raw, st);
+    else rc = wn_launch_loop_generic(h, c_up, g_emb, noise, teacher, 0, B, T, audio, raw, st);
+    if (rc) return rc;
+    WN_CUDA_TRY(h, cudaEventRecord(h->ev[2], st));
+    h->ev_valid = true;
+    return WN_OK;
 }
 
 extern "C" int wn_step_full(wn_handle *h, const float *x, const float *c, const int32_t *g_ids, int B, int Tc,
@@ -407,6 +416,11 @@ extern "C" int wn_query(wn_handle *h, wn_info *info) {
     info->engine = h->engine;
     info->sm_count = h->sm_count;
     info->kernel_launches = h->launches;
+    info->last_upsample_ms = info->last_loop_ms = -1.0f;
+    if (h->ev_valid && cudaEventQuery(h->ev[2]) == cudaSuccess) {
+        cudaEventElapsedTime(&info->last_upsample_ms, h->ev[0], h->ev[1]);
+        cudaEventElapsedTime(&info->last_loop_ms, h->ev[1], h->ev[2]);
+    }
     wn_pipe_fill_info(h, info);
     return WN_OK;
 }
@@ -416,6 +430,8 @@ extern "C" const char *wn_last_error(wn_handle *h) { return h ? h->err.c_str() :
 extern "C" void wn_destroy(wn_handle *h) {
     if (!h) return;
     wn_pipe_free(h);
+    for (int i = 0; i < 3; ++i)
+        if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     float *bufs[] = {h->d_blob, h->d_ring, h->d_cup, h->d_tmp0, h->d_tmp1, h->d_gemb, h->d_in_c, h->d_in_noise,
                      h->d_in_teacher, h->d_out_audio, h->d_out_raw, (float *)h->d_in_g};
     for (float *p : bufs)

@@ -67,6 +67,8 @@ struct wn_handle {
     WnPipePlan *pipe = nullptr;
     int engine = WN_ENGINE_GENERIC;
     int64_t launches = 0;
+    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};  // before upsample / before loop / after loop
+    bool ev_valid = false;
     int64_t n_params = 0;
 };
 

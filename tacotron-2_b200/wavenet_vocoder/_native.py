@@ -48,7 +48,8 @@ class WnInfo(C.Structure):
 		('receptive_field', C.c_int32), ('n_params', C.c_int64), ('flops_per_sample', C.c_int64),
 		('bytes_per_sample', C.c_int64), ('weight_bytes', C.c_int64), ('engine', C.c_int32),
 		('pipeline_ctas', C.c_int32), ('pipeline_ctas_per_layer', C.c_int32), ('pipeline_group_size', C.c_int32),
-		('sm_count', C.c_int32), ('kernel_launches', C.c_int64)]
+		('sm_count', C.c_int32), ('kernel_launches', C.c_int64),
+		('last_upsample_ms', C.c_float), ('last_loop_ms', C.c_float)]
 
 
 _lib = None
