@@ -390,7 +390,7 @@ extern "C" int wn_synthesize_host(wn_handle *h, const float *c, const int32_t *g
     WN_CUDA_TRY(h, cudaMemcpyAsync(audio, h->d_out_audio, sizeof(float) * n_a, cudaMemcpyDeviceToHost, st));
     if (raw) WN_CUDA_TRY(h, cudaMemcpyAsync(raw, h->d_out_raw, sizeof(float) * n_a * cfg.out_channels, cudaMemcpyDeviceToHost, st));
     WN_CUDA_TRY(h, cudaStreamSynchronize(st));
-    return WN_OK;
+    return wn_pipe_check_abort(h);
 }
 
 extern "C" int wn_query(wn_handle *h, wn_info *info) {

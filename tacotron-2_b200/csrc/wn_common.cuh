@@ -92,6 +92,7 @@ int wn_launch_step_full(wn_handle *h, const float *x, const float *c_up, const f
 int wn_pipe_plan(wn_handle *h);   // decides whether the model fits; builds packed weights; 0 = usable
 void wn_pipe_free(wn_handle *h);
 void wn_pipe_fill_info(wn_handle *h, wn_info *info);
+int wn_pipe_check_abort(wn_handle *h);  // after a stream sync: WN_ERR_WATCHDOG if the persistent kernel bailed out
 int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int B, int T,
                         float *audio, float *raw, cudaStream_t st);
 

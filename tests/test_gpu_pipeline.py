@@ -1,0 +1,112 @@
+"""The pipelined persistent engine (csrc/wn_loop_pipe.cu) through the C ABI: because it keeps the fixed fma order of
+the C oracle, every comparison here is BIT-EXACT over the whole utterance, free running and teacher forced, for every
+split of the network over CTAs (P), group size (NU) and utterances-per-thread (UT)."""
+import os
+
+import numpy as np
+import pytest
+
+import common
+from oracle import wavenet_oracle as O
+from oracle.c_oracle import COracle
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
+
+
+def _variants():
+    v = common.small_variants()
+    out = {k: v[k] for k in ('gauss_subpixel', 'mol_2d_nolegacy', 'subpixel_no_nninit_odd')}
+    out['mulaw_scalar'] = common.small(input_type='mulaw', quantize_channels=256)
+    return out
+
+
+def _net(hp, w, **env):
+    from wavenet_vocoder._native import NativeWaveNet
+    old = {k: os.environ.get(k) for k in env}
+    try:
+        for k, val in env.items():
+            os.environ[k] = str(val)
+        net = NativeWaveNet(hp, w, engine='pipeline')
+    finally:
+        for k, val in old.items():
+            if val is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = val
+    assert net.info()['engine'] == 'pipeline'
+    return net
+
+
+def _check(net, hp, w, B, Tc):
+    T = Tc * hp.hop_size
+    c, nz = common.cond_for(hp, B, Tc), common.noise_for(hp, T, B)
+    teacher = common.teacher_for(hp, B, T)
+    co = COracle(hp, w)
+    audio, raw = net.synthesize_host(c, nz, want_raw=True)
+    a_c, _, raw_c, _ = co.synthesize(c, noise=nz)
+    assert np.array_equal(raw[:, 0], raw_c[:, 0]), 'first step differs'
+    bad = np.where(np.any(raw != raw_c, axis=(0, 2)))[0]
+    assert bad.size == 0, 'free-running raw params differ first at step {}'.format(bad[:1])
+    assert np.array_equal(audio, a_c)
+    audio, raw = net.synthesize_host(c, nz, teacher=teacher, want_raw=True)
+    a_c, _, raw_c, _ = co.synthesize(c, noise=nz, teacher=teacher)
+    assert np.array_equal(raw, raw_c) and np.array_equal(audio, a_c)
+    return raw
+
+
+@pytest.mark.parametrize('name', list(_variants()))
+@pytest.mark.parametrize('B', [1, 3, 9])
+def test_pipeline_small_variants_bit_exact(name, B):
+    hp = _variants()[name]
+    w = common.weights_for(hp)
+    net = _net(hp, w)
+    raw = _check(net, hp, w, B, 4)
+    if B == 3:  # and the 1e-3 relative criterion against the op-for-op numpy oracle
+        T = 4 * hp.hop_size
+        c, nz, teacher = common.cond_for(hp, B, 4), common.noise_for(hp, T, B), common.teacher_for(hp, B, T)
+        _, raw_np = O.WaveNetOracle(hp, w).incremental(c=c, noise=nz, test_inputs=teacher)
+        assert np.all(common.rel_close(raw, np.transpose(raw_np, [0, 2, 1])))
+
+
+@pytest.mark.parametrize('env', [dict(WN_PIPE_P=2), dict(WN_PIPE_P=3), dict(WN_PIPE_NU=8, WN_PIPE_UT=2),
+                                 dict(WN_PIPE_NU=2), dict(WN_PIPE_P=7, WN_PIPE_NU=6, WN_PIPE_UT=2)])
+def test_pipeline_plans_bit_exact(env):
+    hp = common.small()
+    w = common.weights_for(hp)
+    _check(_net(hp, w, **env), hp, w, 7, 3)
+
+
+def test_pipeline_default_config_bit_exact():
+    """default_22k (L20 R128 G256 S128): 6 utterances x 4 frames, whole utterance bit-exact vs the C oracle."""
+    hp = common.default_22k()
+    w = common.weights_for(hp)
+    net = _net(hp, w)
+    info = net.info()
+    assert info['pipeline_ctas'] == 80 and info['pipeline_ctas_per_layer'] == 4
+    _check(net, hp, w, 6, 4)
+
+
+def test_pipeline_repeated_calls_and_long_dilation_history():
+    """Two calls on one handle (mailboxes are re-armed) and T > receptive field so every ring wraps (512*2+1 slots)."""
+    hp = common.default_22k()
+    w = common.weights_for(hp)
+    net = _net(hp, w)
+    B, Tc = 4, 17  # 4675 steps > 4093
+    T = Tc * hp.hop_size
+    c, nz = common.cond_for(hp, B, Tc), common.noise_for(hp, T, B)
+    a1 = net.synthesize_host(c, nz)
+    a2 = net.synthesize_host(c, nz)
+    a_c = COracle(hp, w).synthesize(c, noise=nz)[0]
+    assert np.array_equal(a1, a_c) and np.array_equal(a2, a_c)
+
+
+def test_auto_engine_picks_pipeline_and_falls_back():
+    from wavenet_vocoder._native import NativeWaveNet
+    hp = common.small()
+    assert NativeWaveNet(hp, common.weights_for(hp), engine='auto').info()['engine'] == 'pipeline'
+    hq = common.small_variants()['mulaw_quantize']
+    assert NativeWaveNet(hq, common.weights_for(hq), engine='auto').info()['engine'] == 'generic'
+    hp_paper = common.paper()  # fp32 weights of the paper config do not fit shared memory -> generic
+    assert NativeWaveNet(hp_paper, common.weights_for(hp_paper), engine='auto').info()['engine'] == 'generic'
+    with pytest.raises(ValueError, match='pipeline engine unavailable'):
+        NativeWaveNet(hq, common.weights_for(hq), engine='pipeline')
