@@ -22,7 +22,7 @@ extern "C" {
 
 #define WN_MAX_LAYERS 64
 #define WN_MAX_UPSAMPLE 8
-#define WN_ABI_VERSION 1
+#define WN_ABI_VERSION 2
 
 typedef enum {
     WN_OK = 0,
@@ -61,6 +61,10 @@ typedef struct wn_config {
     int32_t gin_channels;         /* <= 0 disables global conditioning */
     int32_t use_speaker_embedding, n_speakers;
     int32_t engine;               /* wn_engine; AUTO picks the pipelined persistent kernel when the model fits it */
+    int32_t ksplit;               /* fp32 summation order of the out / skip 1x1s: number of contiguous blocks of the gated
+                                     channels summed separately and then added up (DESIGN.md "Arithmetic").  0 = the
+                                     pipelined engine's CTAs-per-layer (1 when only the generic engine applies).  Both
+                                     engines honour it, so a fixed value makes results independent of the engine. */
 } wn_config;
 
 typedef struct wn_info {
@@ -70,6 +74,7 @@ typedef struct wn_info {
     int64_t bytes_per_sample;     /* algorithmic bytes/sample with resident weights */
     int64_t weight_bytes;
     int32_t engine;               /* engine wn_synthesize will use */
+    int32_t ksplit;               /* the value in effect (see wn_config.ksplit); a CPU checker must use the same */
     int32_t pipeline_ctas, pipeline_ctas_per_layer, pipeline_group_size;
     int32_t sm_count;
     int64_t kernel_launches;      /* kernels launched by this handle so far (for the bench's gpu_launches) */

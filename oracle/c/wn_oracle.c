@@ -9,18 +9,59 @@
 
 #include "../../include/wn_math.h"
 
-/* y[n] = (sum_k x[k] * W[k][n], sequential fma chain) (+ b[n]).  This is tf.matmul + tf.nn.bias_add
- * (modules.py:295-297) with the accumulation order fixed. */
-static void matvec(const float *x, int K, const float *W, const float *b, int N, float *y) {
-    /* k outer / n inner: each y[n] still sees the same sequential-k fma chain, but rows of W stream contiguously */
-    for (int n = 0; n < N; ++n) y[n] = 0.0f;
+/* ---- the fixed ("canonical") accumulation orders shared with the CUDA kernels ("Arithmetic") -------
+ * TensorFlow does not define the reduction order of tf.matmul, so any fixed order is a valid restatement of
+ * modules.py:295-297; these are the orders the sm_100a kernels use, which makes kernel and checker bit-comparable.
+ *
+ * dot16: the K products are dealt to 16 partial sums by groups of four (element k belongs to partial (k/4) % 16),
+ * each partial is a sequential fma chain in ascending k, and the partials are added as a balanced binary tree
+ * (neighbours first: ((p0+p1)+(p2+p3)) + ...).  On the GPU the 16 partials live in 16 lanes of a warp and the tree
+ * is an xor-butterfly of shuffles.  rows[k] points at row k of a [K][N] matrix (TensorFlow layout).
+ */
+#define WNO_LANES 16
+static void dot16_rows(const float *x, int K, const float *const *rows, int N, const float *bias, float *y,
+                       float *scratch /* [16][N] */) {
+    memset(scratch, 0, sizeof(float) * (size_t)WNO_LANES * N);
     for (int k = 0; k < K; ++k) {
+        float *p = scratch + (size_t)((k >> 2) % WNO_LANES) * N;
         const float xk = x[k];
-        const float *Wk = W + (size_t)k * N;
-        for (int n = 0; n < N; ++n) y[n] = fmaf(xk, Wk[n], y[n]);
+        const float *Wk = rows[k];
+        for (int n = 0; n < N; ++n) p[n] = fmaf(xk, Wk[n], p[n]);
     }
-    if (b)
-        for (int n = 0; n < N; ++n) y[n] = y[n] + b[n];
+    for (int s = 1; s < WNO_LANES; s <<= 1)
+        for (int j = 0; j < WNO_LANES; j += 2 * s) {
+            float *a = scratch + (size_t)j * N;
+            const float *b = scratch + (size_t)(j + s) * N;
+            for (int n = 0; n < N; ++n) a[n] = a[n] + b[n];
+        }
+    for (int n = 0; n < N; ++n) y[n] = scratch[n] + (bias ? bias[n] : 0.0f);
+}
+
+static void dot16(const float *x, int K, const float *W, int N, const float *bias, float *y, float *scratch,
+                  const float **rows /* [K] scratch */) {
+    for (int k = 0; k < K; ++k) rows[k] = W + (size_t)k * N;
+    dot16_rows(x, K, rows, N, bias, y, scratch);
+}
+
+/* blocked: the K inputs are cut into `nsplit` contiguous blocks [K*p/nsplit, K*(p+1)/nsplit); each block is one
+ * sequential fma chain starting from 0, the block sums are added in ascending p, then the bias.  On the GPU every
+ * block is computed by a different CTA (the one that owns those gate channels) and the consumer adds them up. */
+static void dot_blocked(const float *x, int K, const float *W, int N, const float *bias, int nsplit, float *y,
+                        float *scratch /* [N] */) {
+    if (nsplit < 1) nsplit = 1;
+    for (int p = 0; p < nsplit; ++p) {
+        const int k0 = (int)((long long)K * p / nsplit), k1 = (int)((long long)K * (p + 1) / nsplit);
+        float *acc = p == 0 ? y : scratch;
+        for (int n = 0; n < N; ++n) acc[n] = 0.0f;
+        for (int k = k0; k < k1; ++k) {
+            const float xk = x[k];
+            const float *Wk = W + (size_t)k * N;
+            for (int n = 0; n < N; ++n) acc[n] = fmaf(xk, Wk[n], acc[n]);
+        }
+        if (p > 0)
+            for (int n = 0; n < N; ++n) y[n] = y[n] + scratch[n];
+    }
+    for (int n = 0; n < N; ++n) y[n] = y[n] + (bias ? bias[n] : 0.0f);
 }
 
 static inline float act(float y, int kind, float alpha) {
@@ -198,13 +239,40 @@ static int run_utterance(const wno_config *cfg, const wno_weights *w, const floa
         qtot += (size_t)qlen[l] * R;
     }
     float *queues = (float *)calloc(qtot ? qtot : 1, sizeof(float));
-    float *x = (float *)malloc(sizeof(float) * R), *taps = (float *)malloc(sizeof(float) * (size_t)k * R);
-    float *pre = (float *)malloc(sizeof(float) * G), *cc = (float *)malloc(sizeof(float) * G);
+    /* gate pre-activation = ONE dot16 over the concatenation [older taps (k-1)*R | c(t) cin | g gin | x(t) R] against
+     * the matching rows of the dilated conv / cin 1x1 / gin 1x1 kernels, plus the sum of their biases
+     * ((b_conv + b_cin) + b_gin), i.e. modules.py:294-297 + :497-508 with one fixed reduction order. */
+    const int cinu = (cin > 0 && c_up) ? cin : 0, ginu = (gin > 0 && g_emb) ? gin : 0;
+    const int Kcat = k * R + cinu + ginu;
+    const int Nmax = (G > S ? G : S) > O ? (G > S ? G : S) : O;
+    const int Kmax = Kcat > S ? Kcat : S;
+    float *x = (float *)malloc(sizeof(float) * R), *xcat = (float *)malloc(sizeof(float) * (size_t)Kcat);
+    float *pre = (float *)malloc(sizeof(float) * G), *bsum = (float *)malloc(sizeof(float) * (size_t)L * G);
     float *z = (float *)malloc(sizeof(float) * H), *o = (float *)malloc(sizeof(float) * R);
     float *s = (float *)malloc(sizeof(float) * S), *skips = (float *)malloc(sizeof(float) * S);
     float *h1 = (float *)malloc(sizeof(float) * S), *out = (float *)malloc(sizeof(float) * (O > 0 ? O : 1));
     float *e = (float *)malloc(sizeof(float) * (O > 0 ? O : 1));
-    if (!queues || !x || !taps || !pre || !cc || !z || !o || !s || !skips || !h1 || !out || !e) return -2;
+    float *scratch = (float *)malloc(sizeof(float) * (size_t)WNO_LANES * Nmax);
+    const float **rows = (const float **)malloc(sizeof(float *) * (size_t)L * Kmax);
+    if (!queues || !x || !xcat || !pre || !bsum || !z || !o || !s || !skips || !h1 || !out || !e || !scratch || !rows)
+        return -2;
+    for (int l = 0; l < L; ++l) {
+        const float **rw = rows + (size_t)l * Kmax;
+        int q = 0;
+        for (int i = 0; i < (k - 1) * R; ++i) rw[q++] = w->conv_w[l] + (size_t)i * G;
+        for (int i = 0; i < cinu; ++i) rw[q++] = w->cin_w[l] + (size_t)i * G;
+        for (int i = 0; i < ginu; ++i) rw[q++] = w->gin_w[l] + (size_t)i * G;
+        for (int i = (k - 1) * R; i < k * R; ++i) rw[q++] = w->conv_w[l] + (size_t)i * G;
+        for (int n = 0; n < G; ++n) {
+            float bs = w->conv_b[l] ? w->conv_b[l][n] : 0.0f;
+            if (cinu) bs = bs + (w->cin_b[l] ? w->cin_b[l][n] : 0.0f);
+            if (ginu) bs = bs + (w->gin_b[l] ? w->gin_b[l][n] : 0.0f);
+            bsum[(size_t)l * G + n] = bs;
+        }
+    }
+    const float **hrows = (const float **)malloc(sizeof(float *) * (size_t)(S > 0 ? S : 1));
+    if (!hrows) return -2;
+    const int nsplit = cfg->ksplit > 0 ? cfg->ksplit : 1;
 
     /* initial input (wavenet.py:433-445): raw 0.0, mulaw mulaw(0)=0.0, mulaw-quantize class int((0+1)/2*255)=127 */
     float cur_scalar = 0.0f;
@@ -212,42 +280,35 @@ static int run_utterance(const wno_config *cfg, const wno_weights *w, const floa
 
     for (int t = 0; t < T; ++t) {
         /* first_conv.incremental_step (wavenet.py:826) */
-        if (quant) {
-            for (int n = 0; n < R; ++n) {
-                float acc = w->first_w[(size_t)cur_class * R + n]; /* one-hot row select == the fma chain over zeros */
-                x[n] = w->first_b ? acc + w->first_b[n] : acc;
-            }
-        } else {
-            matvec(&cur_scalar, 1, w->first_w, w->first_b, R, x);
+        for (int n = 0; n < R; ++n) {
+            float acc = quant ? w->first_w[(size_t)cur_class * R + n]   /* one-hot row select */
+                              : fmaf(cur_scalar, w->first_w[n], 0.0f);
+            x[n] = acc + (w->first_b ? w->first_b[n] : 0.0f);
         }
         for (int l = 0; l < L; ++l) {
             const int d = cfg->dilations[l];
             float *q = queues + qoff[l];
-            /* CausalConv1D incremental (modules.py:273-297) */
+            float *older = xcat, *cur = xcat + (size_t)(k - 1) * R + cinu + ginu;
+            /* CausalConv1D incremental (modules.py:273-297): taps x(t-(k-1)d) ... x(t-d), x(t) */
             if (shiftqueue) {
                 memmove(q, q + R, sizeof(float) * (size_t)(qlen[l] - 1) * R);
                 memcpy(q + (size_t)(qlen[l] - 1) * R, x, sizeof(float) * R);
-                for (int j = 0; j < k; ++j) memcpy(taps + (size_t)j * R, q + (size_t)j * d * R, sizeof(float) * R);
+                for (int j = 0; j < k - 1; ++j) memcpy(older + (size_t)j * R, q + (size_t)j * d * R, sizeof(float) * R);
             } else {
                 memcpy(q + (size_t)(t % qlen[l]) * R, x, sizeof(float) * R);
-                for (int j = 0; j < k; ++j) {
+                for (int j = 0; j < k - 1; ++j) {
                     int tt = t - (k - 1 - j) * d;
-                    if (tt >= 0) memcpy(taps + (size_t)j * R, q + (size_t)(tt % qlen[l]) * R, sizeof(float) * R);
-                    else memset(taps + (size_t)j * R, 0, sizeof(float) * R);
+                    if (tt >= 0) memcpy(older + (size_t)j * R, q + (size_t)(tt % qlen[l]) * R, sizeof(float) * R);
+                    else memset(older + (size_t)j * R, 0, sizeof(float) * R);
                 }
             }
-            matvec(taps, k * R, w->conv_w[l], w->conv_b[l], G, pre);
-            if (cin > 0 && c_up) { /* modules.py:497-501 */
-                matvec(c_up + (size_t)t * cin, cin, w->cin_w[l], w->cin_b[l], G, cc);
-                for (int n = 0; n < G; ++n) pre[n] = pre[n] + cc[n];
-            }
-            if (gin > 0 && g_emb) { /* modules.py:504-508 */
-                matvec(g_emb, gin, w->gin_w[l], w->gin_b[l], G, cc);
-                for (int n = 0; n < G; ++n) pre[n] = pre[n] + cc[n];
-            }
+            if (cinu) memcpy(xcat + (size_t)(k - 1) * R, c_up + (size_t)t * cin, sizeof(float) * cin);
+            if (ginu) memcpy(xcat + (size_t)(k - 1) * R + cinu, g_emb, sizeof(float) * gin);
+            memcpy(cur, x, sizeof(float) * R);
+            dot16_rows(xcat, Kcat, rows + (size_t)l * Kmax, G, bsum + (size_t)l * G, pre, scratch);
             for (int n = 0; n < H; ++n) z[n] = wn_tanhf(pre[n]) * wn_sigmoidf(pre[H + n]); /* :494, :510 */
-            matvec(z, H, w->skip_w[l], w->skip_b[l], S, s);                                /* :512 */
-            matvec(z, H, w->out_w[l], w->out_b[l], R, o);                                  /* :515 */
+            dot_blocked(z, H, w->skip_w[l], S, w->skip_b[l], nsplit, s, scratch);          /* :512 */
+            dot_blocked(z, H, w->out_w[l], R, w->out_b[l], nsplit, o, scratch);            /* :515 */
             for (int n = 0; n < R; ++n) {                                                  /* :517-520 */
                 float v = o[n] + x[n];
                 x[n] = cfg->residual_legacy ? v * WN_SQRT_HALF : v;
@@ -263,9 +324,9 @@ static int run_utterance(const wno_config *cfg, const wno_weights *w, const floa
         }
         /* head (wavenet.py:840-844) */
         for (int n = 0; n < S; ++n) skips[n] = skips[n] > 0.0f ? skips[n] : 0.0f;
-        matvec(skips, S, w->head1_w, w->head1_b, S, h1);
+        dot16(skips, S, w->head1_w, S, w->head1_b, h1, scratch, hrows);
         for (int n = 0; n < S; ++n) h1[n] = h1[n] > 0.0f ? h1[n] : 0.0f;
-        matvec(h1, S, w->head2_w, w->head2_b, O, out);
+        dot16(h1, S, w->head2_w, O, w->head2_b, out, scratch, hrows);
         if (raw) memcpy(raw + (size_t)t * O, out, sizeof(float) * O);
         /* sampling (wavenet.py:850-869) */
         const float *nz = noise ? noise + (size_t)t * noise_stride : NULL;
@@ -282,8 +343,8 @@ static int run_utterance(const wno_config *cfg, const wno_weights *w, const floa
             cur_class = teacher ? (int)teacher[t] : cls;
         }
     }
-    free(queues); free(x); free(taps); free(pre); free(cc); free(z); free(o); free(s); free(skips); free(h1);
-    free(out); free(e);
+    free(queues); free(x); free(xcat); free(pre); free(bsum); free(z); free(o); free(s); free(skips); free(h1);
+    free(out); free(e); free(scratch); free((void *)rows); free((void *)hrows);
     return 0;
 }
 

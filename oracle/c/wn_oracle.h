@@ -1,7 +1,7 @@
 /* TEST INFRASTRUCTURE - plain-C restatement of the WaveNet incremental synthesis path (parity unpinned for the
- * TF numerics, see oracle/wavenet_oracle.py).  Same math as the numpy oracle, but every dot product is a
- * sequential float32 fma chain over k (then one separate bias add) and every transcendental comes from
- * include/wn_math.h, which is exactly what the fp32 CUDA kernels do - so kernel and checker can be compared
+ * TF numerics, see oracle/wavenet_oracle.py).  Same math as the numpy oracle, but every dot product is reduced in
+ * one fixed order of float32 fma / add operations (wn_oracle.c: dot16, dot_blocked) and every transcendental comes
+ * from include/wn_math.h, which is exactly what the fp32 CUDA kernels do - so kernel and checker can be compared
  * bit for bit on free-running audio.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
  * --impl reference legs may load this library.
  */
@@ -26,6 +26,7 @@ typedef struct {
     int32_t upsample_type, upsample_activation, n_upsample, freq_axis_kernel_size, hop_size;
     int32_t upsample_scales[WNO_MAX_UPSAMPLE];
     float leaky_alpha;
+    int32_t ksplit; /* blocks of the out / skip 1x1 reductions (= CTAs per layer of the CUDA plan, wn_info.ksplit); <= 1: one block */
 } wno_config;
 
 /* TF layouts, C-contiguous: conv kernels [k*C_in][C_out] (row = tap*C_in + ci, tap 0 oldest; modules.py:238-251). */

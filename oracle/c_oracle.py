@@ -26,7 +26,7 @@ class Config(C.Structure):
         ('dilations', C.c_int32 * MAX_LAYERS),
         ('upsample_type', C.c_int32), ('upsample_activation', C.c_int32), ('n_upsample', C.c_int32),
         ('freq_axis_kernel_size', C.c_int32), ('hop_size', C.c_int32),
-        ('upsample_scales', C.c_int32 * MAX_UP), ('leaky_alpha', C.c_float)]
+        ('upsample_scales', C.c_int32 * MAX_UP), ('leaky_alpha', C.c_float), ('ksplit', C.c_int32)]
 
 
 class Weights(C.Structure):
@@ -68,7 +68,9 @@ def _hop(hp):
 class COracle(object):
     """Same inputs as oracle.wavenet_oracle.WaveNetOracle (hp + weight dict in TF layouts)."""
 
-    def __init__(self, hp, weights):
+    def __init__(self, hp, weights, ksplit=1):
+        """ksplit: number of blocks of the out / skip 1x1 reductions - pass NativeWaveNet.info()['ksplit'] to mirror
+        the CUDA plan bit for bit (the value only changes the fp32 summation order)."""
         self.hp = hp
         self._keep = []
         cfg = Config()
@@ -99,6 +101,7 @@ class COracle(object):
         for i, s in enumerate(hp.upsample_scales[:MAX_UP]):
             cfg.upsample_scales[i] = s
         cfg.leaky_alpha = hp.leaky_alpha
+        cfg.ksplit = int(ksplit)
         self.cfg = cfg
 
         w = Weights()

@@ -206,19 +206,42 @@ extern "C" int wn_finalize(wn_handle *h) {
         return it == h->host_w.end() ? nullptr : it->second.data.data();
     };
     BlobBuilder bb;
+    auto r4 = [](int v) { return (v + 3) & ~3; };
+    m.Kcat = m.ksize * m.R + m.cin + m.gin;
+    m.KcatPad = r4(m.Kcat);
+    m.Spad = r4(m.S);
+    // transposed copy of a TensorFlow [K][N] matrix: out[n][k], rows padded with zeros to Kpad
+    auto transposed = [](const float *w, int K, int N, int Kpad) {
+        std::vector<float> t((size_t)N * Kpad, 0.0f);
+        for (int k = 0; k < K; ++k)
+            for (int n = 0; n < N; ++n) t[(size_t)n * Kpad + k] = w[(size_t)k * N + n];
+        return t;
+    };
     size_t o_first_w = bb.add(W("input_convolution/kernel"), (size_t)m.in_ch * m.R);
     size_t o_first_b = bb.add(W("input_convolution/bias"), m.R);
     size_t o_layers = 0, stride = 0;
     for (int l = 0; l < m.L; ++l) {
         std::string p = "ResidualConv1DGLU_" + std::to_string(l) + "/residual_block_";
-        size_t base = bb.add(W(p + "causal_conv/kernel"), (size_t)m.ksize * m.R * m.G);
+        // gate pre-activation matrix over the concatenated input [older taps | c | g | x(t)] (DESIGN.md "Arithmetic")
+        const float *cw = W(p + "causal_conv/kernel"), *iw = W(p + "cin_conv/kernel"), *gw = W(p + "gin_conv/kernel");
+        const float *cb = W(p + "causal_conv/bias"), *ib = W(p + "cin_conv/bias"), *gb = W(p + "gin_conv/bias");
+        std::vector<float> cat((size_t)m.G * m.KcatPad, 0.0f), bsum(m.G, 0.0f);
+        const int n_old = (m.ksize - 1) * m.R;
+        for (int n = 0; n < m.G; ++n) {
+            float *row = cat.data() + (size_t)n * m.KcatPad;
+            for (int k = 0; k < n_old; ++k) row[k] = cw[(size_t)k * m.G + n];
+            for (int k = 0; k < m.cin; ++k) row[n_old + k] = iw[(size_t)k * m.G + n];
+            for (int k = 0; k < m.gin; ++k) row[n_old + m.cin + k] = gw[(size_t)k * m.G + n];
+            for (int k = 0; k < m.R; ++k) row[n_old + m.cin + m.gin + k] = cw[(size_t)(n_old + k) * m.G + n];
+            float bs = cb ? cb[n] : 0.0f;
+            if (m.cin > 0) bs = bs + (ib ? ib[n] : 0.0f);
+            if (m.gin > 0) bs = bs + (gb ? gb[n] : 0.0f);
+            bsum[n] = bs;
+        }
+        size_t base = bb.add(cat.data(), cat.size());
         if (l == 0) o_layers = base;
-        m.off_conv_w = 0;
-        m.off_conv_b = (int)(bb.add(W(p + "causal_conv/bias"), m.G) - base);
-        m.off_cin_w = (int)(bb.add(W(p + "cin_conv/kernel"), (size_t)m.cin * m.G) - base);
-        m.off_cin_b = (int)(bb.add(W(p + "cin_conv/bias"), m.G) - base);
-        m.off_gin_w = (int)(bb.add(W(p + "gin_conv/kernel"), (size_t)m.gin * m.G) - base);
-        m.off_gin_b = (int)(bb.add(W(p + "gin_conv/bias"), m.G) - base);
+        m.off_cat_w = 0;
+        m.off_bsum = (int)(bb.add(bsum.data(), m.G) - base);
         m.off_out_w = (int)(bb.add(W(p + "out_conv/kernel"), (size_t)m.H * m.R) - base);
         m.off_out_b = (int)(bb.add(W(p + "out_conv/bias"), m.R) - base);
         m.off_skip_w = (int)(bb.add(W(p + "skip_conv/kernel"), (size_t)m.H * m.S) - base);
@@ -226,9 +249,11 @@ extern "C" int wn_finalize(wn_handle *h) {
         bb.add(nullptr, 0);
         if (l == 0) stride = bb.v.size() - base;
     }
-    size_t o_h1w = bb.add(W("final_convolution_1/kernel"), (size_t)m.S * m.S);
+    std::vector<float> h1t = transposed(W("final_convolution_1/kernel"), m.S, m.S, m.Spad);
+    std::vector<float> h2t = transposed(W("final_convolution_2/kernel"), m.S, m.O, m.Spad);
+    size_t o_h1w = bb.add(h1t.data(), h1t.size());
     size_t o_h1b = bb.add(W("final_convolution_1/bias"), m.S);
-    size_t o_h2w = bb.add(W("final_convolution_2/kernel"), (size_t)m.S * m.O);
+    size_t o_h2w = bb.add(h2t.data(), h2t.size());
     size_t o_h2b = bb.add(W("final_convolution_2/bias"), m.O);
     size_t o_emb = 0;
     const bool has_emb = c.gin_channels > 0 && c.use_speaker_embedding;
@@ -267,9 +292,12 @@ extern "C" int wn_finalize(wn_handle *h) {
         h->up[i].scale = c.upsample_scales[i];
     }
     // engine selection: the pipelined persistent kernel when the model fits it, else the generic kernel
+    // ksplit (summation order of the out / skip 1x1s): the caller's value, else the pipeline plan's CTAs per layer
     h->engine = WN_ENGINE_GENERIC;
+    m.ksplit = c.ksplit > 0 ? c.ksplit : 1;
+    if (c.ksplit > m.H) return fail(h, WN_ERR_INVALID, "ksplit exceeds gate_channels / 2");
     if (c.engine != WN_ENGINE_GENERIC) {
-        int prc = wn_pipe_plan(h);
+        int prc = wn_pipe_plan(h);   // honours cfg.ksplit > 0, else picks its own split and reports it in m.ksplit
         if (prc == 0) h->engine = WN_ENGINE_PIPELINE;
         else if (c.engine == WN_ENGINE_PIPELINE) return fail(h, WN_ERR_INVALID, "pipeline engine unavailable: " + h->err);
         else h->err.clear();
@@ -414,6 +442,7 @@ extern "C" int wn_query(wn_handle *h, wn_info *info) {
         info->weight_bytes = h->n_params * 4;
     }
     info->engine = h->engine;
+    info->ksplit = h->finalized ? h->m.ksplit : 0;
     info->sm_count = h->sm_count;
     info->kernel_launches = h->launches;
     info->last_upsample_ms = info->last_loop_ms = -1.0f;

@@ -11,12 +11,16 @@
 #include "../../include/wavenet_b200.h"
 #include "../../include/wn_math.h"
 
-// Device-side view of the model in the "generic" layout: every matrix is [K][N] row-major exactly as TensorFlow
-// stores/linearises it (modules.py:238-251: row = tap*C_in + ci, tap 0 = oldest sample), biases always present
+// Device-side view of the model in the "generic" layout.  Matrices reduced with dot16 (the gate pre-activation over
+// the concatenated input [older taps | c | g | x(t)], the two head 1x1s) are stored TRANSPOSED, [N][Kpad] with Kpad a
+// multiple of 4 and zero padding, so that the 16 lanes of one output read 256 contiguous bytes; the out / skip 1x1s
+// (blocked sequential chains, one thread per output) stay [K][N] as TensorFlow stores them.  Biases always present
 // (zeros when hparams.use_bias is off).  Residual layers are laid out with one common stride.
 struct WnModelDev {
     int L, R, G, S, O, ksize, H, cin, gin, in_ch, NZ;
     int input_type, legacy, residual_legacy;
+    int ksplit;                    // blocks of the out / skip reductions (DESIGN.md "Arithmetic")
+    int Kcat, KcatPad, Spad;       // Kcat = ksize*R + cin + gin
     float log_scale_min, log_scale_min_gauss;
     int dil[WN_MAX_LAYERS];
     int qlen[WN_MAX_LAYERS];       // ring slots per layer = (k-1)*d + 1   (wavenet.py:815)
@@ -25,9 +29,8 @@ struct WnModelDev {
     const float *first_w, *first_b;
     const float *layers;           // base of layer 0
     long long layer_stride;        // floats
-    int off_conv_w, off_conv_b, off_cin_w, off_cin_b, off_gin_w, off_gin_b, off_out_w, off_out_b, off_skip_w,
-        off_skip_b;
-    const float *h1_w, *h1_b, *h2_w, *h2_b;
+    int off_cat_w, off_bsum, off_out_w, off_out_b, off_skip_w, off_skip_b;
+    const float *h1_w, *h1_b, *h2_w, *h2_b;   // h1_w [S][Spad], h2_w [O][Spad] (transposed)
     const float *emb;              // [n_speakers][gin] or nullptr
 };
 

@@ -1,40 +1,62 @@
 // wn_loop_generic.cu - "generic" engine of the autoregressive loop (wavenet.py:805-911): one CTA per utterance,
-// the whole time loop inside ONE kernel launch, weights streamed from L2 in their TensorFlow [K][N] layout,
-// dilation ring buffers in global memory, sampling fused, noise read from the caller's buffer.
+// the whole time loop inside ONE kernel launch, weights streamed from L2, dilation ring buffers in global memory,
+// sampling fused, noise read from the caller's buffer.
 //
 // This engine accepts every configuration the reference's hparams allow (any R/G/S/L/kernel_size, scalar or
 // one-hot input, Gaussian / mixture-of-logistics / categorical heads, local and global conditioning).  It is the
 // correctness anchor and the fall-back for models whose weights do not fit the shared memory of the pipelined
 // persistent engine (wn_loop_pipe.cu), which is the fast path.
 //
-// Arithmetic: every dot product is a sequential fp32 fma chain over k followed by ONE bias add, every
-// transcendental comes from include/wn_math.h - the exact order oracle/c/wn_oracle.c uses, so free-running
-// audio can be compared bit for bit.
+// Arithmetic: the fixed fp32 orders of DESIGN.md "Arithmetic" (dot16 for the gate pre-activation and the head,
+// blocked sequential chains for the out / skip 1x1s), every transcendental from include/wn_math.h - the exact
+// operations oracle/c/wn_oracle.c performs, so free-running audio can be compared bit for bit.
 #include "wn_common.cuh"
 
 namespace {
 
-// y[n] = bias[n] + sum_k x[k] * W[k][n]; x in shared memory (broadcast), W rows coalesced over n.
-__device__ __forceinline__ float dot_col(const float *__restrict__ xs, int K, const float *__restrict__ W, int N, int n) {
+constexpr int GEN_THREADS = 512;
+constexpr int LANES = 16;   // partial sums per dot16
+
+// dot16 of xs[0..K) (shared memory, zero padded to a multiple of 4) with row n of Wt ([N][Kpad], global), for the
+// outputs n = nb + group.  Every thread of the CTA calls it with the same trip count (shuffles are warp-wide).
+// Lane j owns the float4 chunks c = j, j+16, ... ; the xor butterfly adds neighbours first, which is the tree of
+// wn_oracle.c:dot16.  Returns the full sum on every lane of the group.
+__device__ __forceinline__ float dot16_lane(const float *xs, int K, int Kpad, const float *__restrict__ Wt, int n,
+                                            bool valid, int lane) {
     float acc = 0.0f;
-    const float *wp = W + n;
-    int k = 0;
-    for (; k + 8 <= K; k += 8) {
-        float w0 = __ldg(wp + (long long)(k + 0) * N), w1 = __ldg(wp + (long long)(k + 1) * N);
-        float w2 = __ldg(wp + (long long)(k + 2) * N), w3 = __ldg(wp + (long long)(k + 3) * N);
-        float w4 = __ldg(wp + (long long)(k + 4) * N), w5 = __ldg(wp + (long long)(k + 5) * N);
-        float w6 = __ldg(wp + (long long)(k + 6) * N), w7 = __ldg(wp + (long long)(k + 7) * N);
-        acc = __fmaf_rn(xs[k + 0], w0, acc);
-        acc = __fmaf_rn(xs[k + 1], w1, acc);
-        acc = __fmaf_rn(xs[k + 2], w2, acc);
-        acc = __fmaf_rn(xs[k + 3], w3, acc);
-        acc = __fmaf_rn(xs[k + 4], w4, acc);
-        acc = __fmaf_rn(xs[k + 5], w5, acc);
-        acc = __fmaf_rn(xs[k + 6], w6, acc);
-        acc = __fmaf_rn(xs[k + 7], w7, acc);
+    if (valid) {
+        const float4 *w4 = reinterpret_cast<const float4 *>(Wt + (long long)n * Kpad);
+        const float4 *x4 = reinterpret_cast<const float4 *>(xs);
+        const int nfull = K >> 2;
+        for (int c = lane; c < nfull; c += LANES) {
+            const float4 wv = __ldg(w4 + c);
+            const float4 xv = x4[c];
+            acc = __fmaf_rn(xv.x, wv.x, acc);
+            acc = __fmaf_rn(xv.y, wv.y, acc);
+            acc = __fmaf_rn(xv.z, wv.z, acc);
+            acc = __fmaf_rn(xv.w, wv.w, acc);
+        }
+        if ((K & 3) && (nfull % LANES) == lane) {   // ragged tail chunk: only the elements below K
+            const float *wr = Wt + (long long)n * Kpad;
+            for (int k = nfull * 4; k < K; ++k) acc = __fmaf_rn(xs[k], __ldg(wr + k), acc);
+        }
     }
-    for (; k < K; ++k) acc = __fmaf_rn(xs[k], __ldg(wp + (long long)k * N), acc);
+#pragma unroll
+    for (int s = 1; s < LANES; s <<= 1) acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, s));
     return acc;
+}
+
+// blocked sequential chains (wn_oracle.c:dot_blocked): y = ((o_0 + o_1) + ...) + b, o_p over k in [K*p/P, K*(p+1)/P).
+__device__ __forceinline__ float dot_blocked_col(const float *__restrict__ zs, int K, const float *__restrict__ W,
+                                                 int N, int n, int nsplit, float bias) {
+    float y = 0.0f;
+    for (int p = 0; p < nsplit; ++p) {
+        const int k0 = (int)((long long)K * p / nsplit), k1 = (int)((long long)K * (p + 1) / nsplit);
+        float acc = 0.0f;
+        for (int k = k0; k < k1; ++k) acc = __fmaf_rn(zs[k], __ldg(W + (long long)k * N + n), acc);
+        y = p == 0 ? acc : __fadd_rn(y, acc);
+    }
+    return __fadd_rn(y, bias);
 }
 
 __device__ float sample_gaussian(const WnModelDev &m, const float *out, float eps) {  // gaussian.py:39-52
@@ -75,28 +97,29 @@ __device__ int sample_categorical(const float *logits, int C, float u, float *e)
     return C - 1;
 }
 
-// grid = B utterances, block = NT threads.  Dynamic shared memory carved below.
-__global__ void wn_loop_generic_kernel(const WnModelDev m, const float *__restrict__ c_up,
-                                       const float *__restrict__ g_emb, const float *__restrict__ noise,
-                                       const float *__restrict__ teacher, int inputs_mode, int B, int T,
-                                       float *__restrict__ rings,
-                                       float *__restrict__ audio, float *__restrict__ raw) {
-    extern __shared__ float sm[];
+__device__ __forceinline__ int round4(int v) { return (v + 3) & ~3; }
+
+// grid = B utterances, block = GEN_THREADS.  Dynamic shared memory carved below.
+__global__ void __launch_bounds__(GEN_THREADS) wn_loop_generic_kernel(
+    const WnModelDev m, const float *__restrict__ c_up, const float *__restrict__ g_emb,
+    const float *__restrict__ noise, const float *__restrict__ teacher, int inputs_mode, int B, int T,
+    float *__restrict__ rings, float *__restrict__ audio, float *__restrict__ raw) {
+    extern __shared__ __align__(16) float sm[];
     const int tid = threadIdx.x, NT = blockDim.x, b = blockIdx.x;
+    const int lane = tid & (LANES - 1), group = tid / LANES, ngroups = NT / LANES;
     const int R = m.R, G = m.G, S = m.S, O = m.O, H = m.H, ks = m.ksize;
-    float *x = sm;                 // [R]   current residual-stream vector
-    float *taps = x + R;           // [ks*R]
-    float *pre = taps + ks * R;    // [G]
-    float *z = pre + G;            // [H]
-    float *skips = z + H;          // [S]
-    float *h1 = skips + S;         // [S]
-    float *outv = h1 + S;          // [O]
-    float *ev = outv + O;          // [O]   categorical scratch
-    float *cond = ev + O;          // [cin]
-    float *gv = cond + (m.cin > 0 ? m.cin : 0);  // [gin]
-    float *fb = gv + (m.gin > 0 ? m.gin : 0);    // [2]: fb[0] next scalar input, fb[1] next class
+    float *x = sm;                            // [round4(R)]  current residual-stream vector
+    float *xcat = x + round4(R);              // [KcatPad]    older taps | c(t) | g | x(t)
+    float *pre = xcat + m.KcatPad;            // [round4(G)]
+    float *z = pre + round4(G);               // [round4(H)]
+    float *skips = z + round4(H);             // [Spad]
+    float *h1 = skips + m.Spad;               // [Spad]
+    float *outv = h1 + m.Spad;                // [round4(O)]
+    float *ev = outv + round4(O);             // [round4(O)]  categorical scratch
+    float *fb = ev + round4(O);               // [4]: fb[0] next scalar input, fb[1] next class
     const bool quant = m.input_type == WN_INPUT_MULAW_QUANTIZE;
     float *ring = rings + (long long)b * m.ring_per_utt;
+    const int o_cond = (ks - 1) * R, o_g = o_cond + m.cin, o_cur = o_g + m.gin;
 
     if (tid == 0) {  // wavenet.py:433-445: raw/mulaw 0.0; class int((0+1)/2*255)=127
         fb[0] = 0.0f;
@@ -104,7 +127,10 @@ __global__ void wn_loop_generic_kernel(const WnModelDev m, const float *__restri
         // inputs_mode (WaveNet.step semantics, wavenet.py:650-721): teacher[t] IS the network input of step t
         if (inputs_mode) fb[0] = fb[1] = teacher[(long long)b * T];
     }
-    for (int i = tid; i < m.gin; i += NT) gv[i] = g_emb ? g_emb[(long long)b * m.gin + i] : 0.0f;
+    for (int i = tid; i < m.KcatPad; i += NT) xcat[i] = 0.0f;
+    for (int i = tid; i < 2 * m.Spad; i += NT) skips[i] = 0.0f;   // skips and h1 (padding must stay zero)
+    __syncthreads();
+    for (int i = tid; i < m.gin; i += NT) xcat[o_g + i] = g_emb ? g_emb[(long long)b * m.gin + i] : 0.0f;
     __syncthreads();
 
     for (int t = 0; t < T; ++t) {
@@ -115,8 +141,7 @@ __global__ void wn_loop_generic_kernel(const WnModelDev m, const float *__restri
             else acc = __fmaf_rn(fb[0], __ldg(m.first_w + n), 0.0f);
             x[n] = __fadd_rn(acc, __ldg(m.first_b + n));
         }
-        if (m.cin > 0)
-            for (int i = tid; i < m.cin; i += NT) cond[i] = __ldg(c_up + ((long long)b * T + t) * m.cin + i);
+        for (int i = tid; i < m.cin; i += NT) xcat[o_cond + i] = __ldg(c_up + ((long long)b * T + t) * m.cin + i);
         __syncthreads();
 
         for (int l = 0; l < m.L; ++l) {
@@ -127,20 +152,15 @@ __global__ void wn_loop_generic_kernel(const WnModelDev m, const float *__restri
             for (int i = tid; i < ks * R; i += NT) {
                 const int j = i / R, n = i - j * R;
                 const int tt = t - (ks - 1 - j) * d;
-                float v;
-                if (j == ks - 1) { v = x[n]; rq[(long long)(t % ql) * R + n] = v; }
-                else v = tt >= 0 ? rq[(long long)(tt % ql) * R + n] : 0.0f;
-                taps[i] = v;
+                if (j == ks - 1) { const float v = x[n]; rq[(long long)(t % ql) * R + n] = v; xcat[o_cur + n] = v; }
+                else xcat[i] = tt >= 0 ? rq[(long long)(tt % ql) * R + n] : 0.0f;
             }
             __syncthreads();
-            // ---- dilated conv + conditioning 1x1s (modules.py:294-297, :497-508) --------------------------
-            for (int n = tid; n < G; n += NT) {
-                float a = __fadd_rn(dot_col(taps, ks * R, lw + m.off_conv_w, G, n), __ldg(lw + m.off_conv_b + n));
-                if (m.cin > 0)
-                    a = __fadd_rn(a, __fadd_rn(dot_col(cond, m.cin, lw + m.off_cin_w, G, n), __ldg(lw + m.off_cin_b + n)));
-                if (m.gin > 0)
-                    a = __fadd_rn(a, __fadd_rn(dot_col(gv, m.gin, lw + m.off_gin_w, G, n), __ldg(lw + m.off_gin_b + n)));
-                pre[n] = a;
+            // ---- gate pre-activation: one dot16 over [taps | c | g | x(t)] (modules.py:294-297, :497-508) ----
+            for (int nb = 0; nb < G; nb += ngroups) {
+                const int n = nb + group;
+                const float a = dot16_lane(xcat, m.Kcat, m.KcatPad, lw + m.off_cat_w, n, n < G, lane);
+                if (lane == 0 && n < G) pre[n] = __fadd_rn(a, __ldg(lw + m.off_bsum + n));
             }
             __syncthreads();
             for (int n = tid; n < H; n += NT) z[n] = __fmul_rn(wn_tanhf(pre[n]), wn_sigmoidf(pre[H + n]));  // :510
@@ -148,7 +168,7 @@ __global__ void wn_loop_generic_kernel(const WnModelDev m, const float *__restri
             // ---- skip and residual 1x1s (modules.py:512-520, wavenet.py:833-836) ---------------------------
             for (int n = tid; n < S + R; n += NT) {
                 if (n < S) {
-                    float s = __fadd_rn(dot_col(z, H, lw + m.off_skip_w, S, n), __ldg(lw + m.off_skip_b + n));
+                    float s = dot_blocked_col(z, H, lw + m.off_skip_w, S, n, m.ksplit, __ldg(lw + m.off_skip_b + n));
                     if (l == 0) skips[n] = s;
                     else {
                         float v = __fadd_rn(skips[n], s);
@@ -156,7 +176,7 @@ __global__ void wn_loop_generic_kernel(const WnModelDev m, const float *__restri
                     }
                 } else {
                     const int r = n - S;
-                    float o = __fadd_rn(dot_col(z, H, lw + m.off_out_w, R, r), __ldg(lw + m.off_out_b + r));
+                    float o = dot_blocked_col(z, H, lw + m.off_out_w, R, r, m.ksplit, __ldg(lw + m.off_out_b + r));
                     float v = __fadd_rn(o, x[r]);
                     x[r] = m.residual_legacy ? __fmul_rn(v, WN_SQRT_HALF) : v;
                 }
@@ -166,15 +186,20 @@ __global__ void wn_loop_generic_kernel(const WnModelDev m, const float *__restri
         // ---- head (wavenet.py:840-844) ---------------------------------------------------------------------
         for (int n = tid; n < S; n += NT) skips[n] = skips[n] > 0.0f ? skips[n] : 0.0f;
         __syncthreads();
-        for (int n = tid; n < S; n += NT) {
-            float v = __fadd_rn(dot_col(skips, S, m.h1_w, S, n), __ldg(m.h1_b + n));
-            h1[n] = v > 0.0f ? v : 0.0f;
+        for (int nb = 0; nb < S; nb += ngroups) {
+            const int n = nb + group;
+            const float a = dot16_lane(skips, S, m.Spad, m.h1_w, n, n < S, lane);
+            if (lane == 0 && n < S) { const float v = __fadd_rn(a, __ldg(m.h1_b + n)); h1[n] = v > 0.0f ? v : 0.0f; }
         }
         __syncthreads();
-        for (int n = tid; n < O; n += NT) {
-            float v = __fadd_rn(dot_col(h1, S, m.h2_w, O, n), __ldg(m.h2_b + n));
-            outv[n] = v;
-            if (raw) raw[((long long)b * T + t) * O + n] = v;  // wavenet.py:847
+        for (int nb = 0; nb < O; nb += ngroups) {
+            const int n = nb + group;
+            const float a = dot16_lane(h1, S, m.Spad, m.h2_w, n, n < O, lane);
+            if (lane == 0 && n < O) {
+                const float v = __fadd_rn(a, __ldg(m.h2_b + n));
+                outv[n] = v;
+                if (raw) raw[((long long)b * T + t) * O + n] = v;  // wavenet.py:847
+            }
         }
         __syncthreads();
         // ---- sampling + feedback (wavenet.py:850-878) ----------------------------------------------------------
@@ -207,16 +232,12 @@ int wn_launch_loop_generic(wn_handle *h, const float *c_up, const float *g_emb, 
     const WnModelDev &m = h->m;
     if (wn_ensure(h, &h->d_ring, &h->ring_floats, (size_t)B * (size_t)m.ring_per_utt)) return WN_ERR_NOMEM;
     WN_CUDA_TRY(h, cudaMemsetAsync(h->d_ring, 0, sizeof(float) * (size_t)B * (size_t)m.ring_per_utt, st));
-    int need = m.G > m.R + m.S ? m.G : m.R + m.S;
-    int nt = ((need + 31) / 32) * 32;
-    if (nt > 1024) nt = 1024;
-    if (nt < 64) nt = 64;
-    size_t smem = sizeof(float) * (size_t)(m.R + m.ksize * m.R + m.G + m.H + 2 * m.S + 2 * m.O +
-                                           (m.cin > 0 ? m.cin : 0) + (m.gin > 0 ? m.gin : 0) + 4);
+    auto r4 = [](int v) { return (v + 3) & ~3; };
+    size_t smem = sizeof(float) * (size_t)(r4(m.R) + m.KcatPad + r4(m.G) + r4(m.H) + 2 * m.Spad + 2 * r4(m.O) + 4);
     if (smem > 48 * 1024)
         WN_CUDA_TRY(h, cudaFuncSetAttribute(wn_loop_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    wn_loop_generic_kernel<<<B, nt, smem, st>>>(m, c_up, g_emb, noise, teacher, inputs_mode, B, T, h->d_ring,
-                                                audio, raw);
+    wn_loop_generic_kernel<<<B, GEN_THREADS, smem, st>>>(m, c_up, g_emb, noise, teacher, inputs_mode, B, T, h->d_ring,
+                                                         audio, raw);
     h->launches++;
     WN_CUDA_TRY(h, cudaGetLastError());
     return WN_OK;

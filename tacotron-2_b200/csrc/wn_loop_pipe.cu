@@ -1,66 +1,80 @@
 // wn_loop_pipe.cu - the pipelined persistent engine of the autoregressive loop (wavenet.py:805-911) for sm_100a.
 //
 // One cooperative launch runs the whole utterance batch for all T steps.  The network is laid out ACROSS the SMs:
-//   * every residual layer l is owned by P CTAs ("layer CTAs", one per SM); CTA (l,p) keeps ITS slice of the layer's
-//     weights resident in shared memory for the whole launch: the rows of the dilated conv + cin 1x1 that produce gate
-//     channels [h0,h1) (both the tanh and the sigmoid half, so gating is local), and the rows of the residual / skip
-//     1x1s that produce output channels [r0,r1) / [s0,s1);
-//   * NH "head CTAs" own the two head 1x1s, the first (input) 1x1 and the sampler.
+//   * every residual layer l is owned by P CTAs ("layer CTAs", one per SM).  CTA (l,p) keeps ITS slice of the layer's
+//     weights resident in shared memory for the whole launch: the rows of the gate pre-activation matrix (dilated conv +
+//     cin 1x1 over the concatenated input [x(t-2d) | x(t-d) | c(t) | x(t)]) that produce gate channels [h0,h1) - the tanh
+//     and the sigmoid half, so gating is local - and the COLUMNS [h0,h1) of the residual-out / skip 1x1s;
+//   * NH "head CTAs" own the two head 1x1s and the sampler.
 // Utterances travel through that pipeline in groups of NU.  All stages walk the same schedule (t major, group minor),
 // so while layer 7 works on group 3 layer 6 works on group 4: the serial chain of one group costs ~(L+1) stage
 // latencies per sample, but all SMs stay busy on different groups.  The only feedback edge is sample(t) -> input(t+1).
 //
-// Hand-off between CTAs never uses a barrier or a separate flag: every float travels as an 8-byte {value, tag} word
-// (tag = t+1) written with one 64-bit store and polled with 64-bit loads by the consumer ("LL" protocol), so a value
-// is usable the moment it lands in L2.  Three kinds of mailboxes, all in global memory (L2 resident when small):
-//   X[l]  the input vector of layer l, [group][slot][u][R].  It has 2*d_l+1 slots and so doubles as the dilation
-//         ring buffer: taps x(t-d), x(t-2d) are re-read from older slots (modules.py:285-292 without the queue shift);
-//   Z[l]  the gated activations of layer l, exchanged between the P CTAs of the layer (each needs all of z);
-//   S[l]  the running skip sum after layer l, slice p -> slice p of layer l+1, and the full vector to the head.
-// Everything that does not depend on x_l(t) - the two older taps, the conditioning 1x1 - is prefetched into registers
-// one work item ahead and accumulated before x_l(t) arrives, so the per-layer critical path is one K=R fma chain,
-// the gate, the z exchange and one K=G/2 chain.
+// ONE hand-off per layer.  The P CTAs of a layer never talk to each other: each one gates its own channels and then
+// multiplies them with its column block of the out / skip 1x1s, which yields a PARTIAL sum for every output channel
+// (split-K).  The partial sums travel to all P CTAs of layer l+1, which add them up in a fixed order (p = 0, 1, ...),
+// add the bias and the residual input, and so each rebuild the full x_{l+1}(t) they need.  The running skip sum is
+// carried along the same edges (slice p of it by the CTAs (.,p)) and reaches the head with the last layer's partials.
 //
-// Arithmetic is the same fixed order as wn_loop_generic.cu and oracle/c/wn_oracle.c (sequential fp32 fma chains over
-// k, one bias add, include/wn_math.h), so results are bit-identical to both.
+// Hand-off never uses a barrier or a separate flag: every float travels as an 8-byte {value, tag} word (tag = t+1)
+// written with 128-bit stores and polled with 128-bit loads by the consumer ("LL" protocol), so a value is usable
+// the moment it lands in L2.  Mailboxes are double buffered on t&1 (no CTA can be more than one step ahead of another:
+// step t+1 cannot start before the head sampled step t, which needs every CTA's step-t output).
+// The dilation history x_l(t-d), x_l(t-2d) lives in a per-CTA ring in global memory (plain floats, written by the CTA
+// itself right after it rebuilt x_l(t)); it is read one work item ahead into registers, together with the
+// conditioning column c(t), and the part of the gate pre-activation that only needs those is computed BEFORE x_l(t)
+// arrives, so the per-layer critical path is: poll -> K=R slice of the dot -> gate -> K=H/P chain -> store.
+//
+// Arithmetic is the fixed order of DESIGN.md "Arithmetic" (dot16 / blocked chains with ksplit = P), identical in
+// wn_loop_generic.cu and oracle/c/wn_oracle.c, so results are bit-identical to both.
 //
 // Scope: scalar input (raw / mulaw), Gaussian or mixture-of-logistics head, kernel_size 3, local conditioning on,
-// global conditioning off, fp32 weights that fit shared memory (the default config uses 165 KB per layer CTA).
+// global conditioning off, fp32 weights that fit shared memory (default config: 163 KB per layer CTA at P = 4).
 // Anything else runs on the generic engine.
 #include <cooperative_groups.h>
 
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
 
 #include "wn_common.cuh"
 
 namespace {
 
 constexpr int PIPE_THREADS = 256;
+constexpr int LANES = 16;            // partial sums per dot16
+constexpr int MAX_P = 8;             // CTAs per layer
 constexpr int MAX_PF = 4;            // 16-byte prefetch loads per thread for the two older taps
-constexpr unsigned SPIN_LIMIT = 1u << 24;
+constexpr unsigned SPIN_LIMIT = 1u << 22;
 
 struct PipeCta {
     int role;                        // 0 layer, 1 head
     int l, p;                        // layer / slice (head: index of the head CTA in l)
-    int h0, hn, r0, rn, s0, sn;      // gate / residual / skip channel slices owned
+    int h0, hn, r0, rn, s0, sn;      // gate-channel / residual / skip slices owned
     long long blob;                  // float offset of this CTA's packed weights
+    long long ring;                  // float offset of this CTA's private dilation ring
 };
 
 struct PipeParams {
     // model
-    int L, R, G, S, O, H, cin, NZ, input_type, legacy, residual_legacy;
+    int L, R, H, S, O, cin, NZ, input_type, legacy, residual_legacy;
     float log_scale_min, log_scale_min_gauss;
     int dil[WN_MAX_LAYERS], depth[WN_MAX_LAYERS];
-    long long xoff[WN_MAX_LAYERS];   // uint64 offset of X[l] inside xbuf
     // plan
     int P, NH, NU, NG;
-    int hmax, rmax, smax;            // largest slice sizes (uniform smem layout)
-    int KC, KCs, KI, KIs, KH, KHs, KS, KSs;   // chain lengths (padded to 4) and padded row strides
+    int hq, hk;                      // gate channels per CTA padded: hq rows per half (even), hk = K of the partial chains (mult. of 4)
+    int NR, NQ;                      // gate rows per CTA (2*hq, multiple of 4) and row quads
+    int KC, KC4, C0;                 // concatenated K (3R + cin), in chunks, and the chunks that precede x(t)
+    int smax;                        // largest skip slice
     int layer_blob_floats, head_blob_floats;
     const float *blobs;
     const PipeCta *ctas;
-    unsigned long long *xbuf, *zbuf, *sbuf;
+    float *rings;
+    unsigned long long *op, *xr, *sp, *rs, *in;   // mailboxes (see the host side for sizes)
+    long long op_sz, xr_sz, sp_sz, rs_sz;          // words per consumer stage
     int *abort_flag;
+    long long *stats;                // optional [CTA][8] clock64 counters (WN_PIPE_STATS), else nullptr
     // call
     const float *c_up, *noise, *teacher;
     float *audio, *raw;
@@ -70,50 +84,24 @@ struct PipeParams {
 __device__ __forceinline__ unsigned long long pack_ll(float v, unsigned tag) {
     return ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v);
 }
-__device__ __forceinline__ void st_ll(unsigned long long *p, float v, unsigned tag) {
-    *(volatile unsigned long long *)p = pack_ll(v, tag);
+__device__ __forceinline__ void st_ll2(unsigned long long *p, float v0, float v1, unsigned tag) {   // 16-byte aligned
+    const unsigned long long a = pack_ll(v0, tag), b = pack_ll(v1, tag);
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
 }
 __device__ __forceinline__ void ld_ll2(const unsigned long long *p, unsigned long long &a, unsigned long long &b) {
-    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p));
-}
-__device__ __forceinline__ unsigned long long ld_ll1(const unsigned long long *p) {
-    return *(const volatile unsigned long long *)p;
-}
-__device__ __forceinline__ void ldcg2(const unsigned long long *p, unsigned long long &a, unsigned long long &b) {
-    asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p));
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
 }
 __device__ __forceinline__ float ll_val(unsigned long long w) { return __uint_as_float((unsigned)(w & 0xffffffffu)); }
 __device__ __forceinline__ unsigned ll_tag(unsigned long long w) { return (unsigned)(w >> 32); }
 
-// Poll `npairs` consecutive {value,tag} words starting at src until all carry `tag`.  The words form rows of
-// `rowlen` (even) values; value i goes to dst[(i / rowlen) * dstride + i % rowlen] (shared memory).  Each thread owns
-// 16-byte chunks.  Returns nonzero if the watchdog fired (a peer CTA never delivered: never expected).
-__device__ __forceinline__ int poll_block(const unsigned long long *src, int npairs, unsigned tag, float *dst,
-                                          int rowlen, int dstride, int *abort_flag) {
-    int bad = 0;
-    for (int i = threadIdx.x * 2; i < npairs; i += PIPE_THREADS * 2) {
-        unsigned long long a, b;
-        unsigned spins = 0;
-        for (;;) {
-            ld_ll2(src + i, a, b);
-            if (ll_tag(a) == tag && ll_tag(b) == tag) break;
-            if ((++spins & 0x3ffu) == 0) {
-                if (*(volatile int *)abort_flag) { bad = 1; break; }
-                if (spins > SPIN_LIMIT) { atomicExch(abort_flag, 1); bad = 1; break; }
-            }
-        }
-        const int row = i / rowlen, col = i - row * rowlen;
-        dst[row * dstride + col] = ll_val(a);
-        dst[row * dstride + col + 1] = ll_val(b);
-    }
-    return bad;
-}
-
-__device__ __forceinline__ int poll_one(const unsigned long long *src, unsigned tag, float &v, int *abort_flag) {
+// Poll one pair of {value,tag} words until both carry `tag`.  Returns nonzero if the watchdog fired.
+__device__ __forceinline__ int poll_pair(const unsigned long long *src, unsigned tag, float &v0, float &v1,
+                                         int *abort_flag) {
     unsigned spins = 0;
     for (;;) {
-        unsigned long long a = ld_ll1(src);
-        if (ll_tag(a) == tag) { v = ll_val(a); return 0; }
+        unsigned long long a, b;
+        ld_ll2(src, a, b);
+        if (ll_tag(a) == tag && ll_tag(b) == tag) { v0 = ll_val(a); v1 = ll_val(b); return 0; }
         if ((++spins & 0x3ffu) == 0) {
             if (*(volatile int *)abort_flag) return 1;
             if (spins > SPIN_LIMIT) { atomicExch(abort_flag, 1); return 1; }
@@ -121,42 +109,134 @@ __device__ __forceinline__ int poll_one(const unsigned long long *src, unsigned 
     }
 }
 
-// acc += sum_{k<K} x[k] * w[k], sequential, 4 at a time (K % 4 == 0, 16-byte aligned shared memory)
-template <int UT>
-__device__ __forceinline__ void chain(float (&acc)[UT], const float *w, const float *x, int xstride, int K) {
-    const float4 *w4 = reinterpret_cast<const float4 *>(w);
-#pragma unroll 4
-    for (int k4 = 0; k4 < K / 4; ++k4) {
-        const float4 wv = w4[k4];
+__device__ __forceinline__ int round4(int v) { return (v + 3) & ~3; }
+
+// ---- the fp32 inner products ---------------------------------------------------------------------------------
+// Operands in shared memory are "k-major": xs[k][NU] (utterances fastest), so one 16-byte load brings the same k
+// for 4 utterances.  Weights are row-major [row][K].
+//
+// mac_lane: the thread owns a tile of 4 rows x NU utterances and the float4 chunks c = first, first+16, ... < c_end of K
+// (lane = c % 16): acc[i*NU+u] += sum_e w[4q+i][4c+e] * xs[4c+e][u], e ascending, c ascending - one partial of dot16.
+template <int NU>
+__device__ __forceinline__ void mac_lane(float (&acc)[4 * NU], const float4 *__restrict__ w4 /* row 4q, chunk 0 */,
+                                         int KC4, const float *__restrict__ xs, int c_first, int c_end) {
+#pragma unroll 2
+    for (int c = c_first; c < c_end; c += LANES) {
+        float4 w[4];
 #pragma unroll
-        for (int j = 0; j < UT; ++j) {
-            const float4 xv = reinterpret_cast<const float4 *>(x + j * xstride)[k4];
-            acc[j] = __fmaf_rn(xv.x, wv.x, acc[j]);
-            acc[j] = __fmaf_rn(xv.y, wv.y, acc[j]);
-            acc[j] = __fmaf_rn(xv.z, wv.z, acc[j]);
-            acc[j] = __fmaf_rn(xv.w, wv.w, acc[j]);
+        for (int i = 0; i < 4; ++i) w[i] = w4[i * KC4 + c];
+        const float *xk = xs + (size_t)c * 4 * NU;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            float xv[NU];
+            if (NU == 2) {
+                const float2 t = *reinterpret_cast<const float2 *>(xk + e * NU);
+                xv[0] = t.x; xv[1] = t.y;
+            } else {
+#pragma unroll
+                for (int u4 = 0; u4 < NU / 4; ++u4) {
+                    const float4 t = *reinterpret_cast<const float4 *>(xk + e * NU + u4 * 4);
+                    xv[u4 * 4 + 0] = t.x; xv[u4 * 4 + 1] = t.y; xv[u4 * 4 + 2] = t.z; xv[u4 * 4 + 3] = t.w;
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float wv = e == 0 ? w[i].x : (e == 1 ? w[i].y : (e == 2 ? w[i].z : w[i].w));
+#pragma unroll
+                for (int u = 0; u < NU; ++u) acc[i * NU + u] = __fmaf_rn(xv[u], wv, acc[i * NU + u]);
+            }
         }
     }
 }
 
-__device__ float pipe_sample_gaussian(const PipeParams &P, const float *out, float eps) {  // gaussian.py:39-52
+// Butterfly of the 16 lanes' partials: neighbours first (the tree of wn_oracle.c:dot16).  While a lane holds more
+// than one value each step also halves what it keeps (the lane with the mask bit set keeps the upper half), so
+// the whole reduction of NV values costs NV-1 shuffles instead of 4*NV.  On return the lane holds NV/16 (at least
+// 1) finished sums in a[0..]; the original index of a[i] is i + reduce16_base<NV>(lane).
+template <int NV>
+__device__ __forceinline__ void reduce16(float (&a)[NV], int lane) {
+    int cnt = NV;
+#pragma unroll
+    for (int m = 1; m < LANES; m <<= 1) {
+        if (cnt >= 2) {
+            const int half = cnt / 2;
+            const bool up = (lane & m) != 0;
+#pragma unroll
+            for (int i = 0; i < NV / 2; ++i) {
+                if (i < half) {
+                    const float send = up ? a[i] : a[i + half];
+                    const float keep = up ? a[i + half] : a[i];
+                    a[i] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, m));
+                }
+            }
+            cnt = half;
+        } else {
+            a[0] = __fadd_rn(a[0], __shfl_xor_sync(0xffffffffu, a[0], m));
+        }
+    }
+}
+template <int NV>
+__device__ __forceinline__ int reduce16_base(int lane) {
+    int cnt = NV, base = 0;
+#pragma unroll
+    for (int m = 1; m < LANES; m <<= 1) {
+        if (cnt >= 2) { cnt /= 2; if (lane & m) base += cnt; }
+    }
+    return base;
+}
+
+// chain_tile: 4 rows x NU utterances, K sequential in-thread (the blocked chains of the out / skip 1x1s).
+// w4t is chunk-major: w4t[c * nrows + row] holds W[row][4c..4c+3]; the thread's rows are row0 + i*rstride.
+template <int NU>
+__device__ __forceinline__ void chain_tile(float (&acc)[4 * NU], const float4 *__restrict__ w4t, int nrows, int row0,
+                                           int rstride, const float *__restrict__ zs, int K4) {
+    for (int c = 0; c < K4; ++c) {
+        float4 w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) w[i] = w4t[c * nrows + row0 + i * rstride];
+        const float *zk = zs + (size_t)c * 4 * NU;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            float zv[NU];
+            if (NU == 2) {
+                const float2 t = *reinterpret_cast<const float2 *>(zk + e * NU);
+                zv[0] = t.x; zv[1] = t.y;
+            } else {
+#pragma unroll
+                for (int u4 = 0; u4 < NU / 4; ++u4) {
+                    const float4 t = *reinterpret_cast<const float4 *>(zk + e * NU + u4 * 4);
+                    zv[u4 * 4 + 0] = t.x; zv[u4 * 4 + 1] = t.y; zv[u4 * 4 + 2] = t.z; zv[u4 * 4 + 3] = t.w;
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float wv = e == 0 ? w[i].x : (e == 1 ? w[i].y : (e == 2 ? w[i].z : w[i].w));
+#pragma unroll
+                for (int u = 0; u < NU; ++u) acc[i * NU + u] = __fmaf_rn(zv[u], wv, acc[i * NU + u]);
+            }
+        }
+    }
+}
+
+__device__ float pipe_sample_gaussian(const PipeParams &P, const float *out, int ostride, float eps) {  // gaussian.py:39-52
     float mean = out[0];
-    float ls = out[1] > P.log_scale_min_gauss ? out[1] : P.log_scale_min_gauss;
+    float ls = out[ostride] > P.log_scale_min_gauss ? out[ostride] : P.log_scale_min_gauss;
     float x = __fadd_rn(mean, __fmul_rn(wn_expf(ls), eps));
     x = x > -1.0f ? x : -1.0f;
     return x < 1.0f ? x : 1.0f;
 }
 
-__device__ float pipe_sample_mol(const PipeParams &P, const float *out, const float *u) {  // mixture.py:76-107
+__device__ float pipe_sample_mol(const PipeParams &P, const float *out, int ostride, const float *u) {  // mixture.py:76-107
     const int K = P.O / 3;
     int best = 0;
     float bestv = 0.0f;
     for (int k = 0; k < K; ++k) {
-        float v = __fsub_rn(out[k], wn_logf(-wn_logf(u[k])));
+        float v = __fsub_rn(out[k * ostride], wn_logf(-wn_logf(u[k])));
         if (k == 0 || v > bestv) { bestv = v; best = k; }
     }
-    float mean = out[K + best];
-    float ls = out[2 * K + best] > P.log_scale_min ? out[2 * K + best] : P.log_scale_min;
+    float mean = out[(K + best) * ostride];
+    float lsr = out[(2 * K + best) * ostride];
+    float ls = lsr > P.log_scale_min ? lsr : P.log_scale_min;
     float u2 = u[K];
     float lg = __fsub_rn(wn_logf(u2), wn_logf(__fsub_rn(1.0f, u2)));
     float x = __fadd_rn(mean, __fmul_rn(wn_expf(ls), lg));
@@ -164,284 +244,404 @@ __device__ float pipe_sample_mol(const PipeParams &P, const float *out, const fl
     return x < 1.0f ? x : 1.0f;
 }
 
-__device__ __forceinline__ int round4(int v) { return (v + 3) & ~3; }
-
-
 // ---------------------------------------------------------------------------------------------------------------
-// layer CTA: owns slice p of residual layer l  (ResidualConv1DGLU.incremental_step, modules.py:468-521)
+// layer CTA: owns gate channels [h0,h1) of residual layer l  (ResidualConv1DGLU.incremental_step, modules.py:468-521)
 // ---------------------------------------------------------------------------------------------------------------
-template <int UT>
+template <int NU>
 __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) {
+    constexpr int NV = 4 * NU, NP = NU / 2;          // accumulators per thread; utterance pairs per group
     const int tid = threadIdx.x;
-    const int R = P.R, H = P.H, NU = P.NU, NG = P.NG, T = P.T, l = me.l;
-    const int hn = me.hn, rn = me.rn, sn = me.sn, hmax = P.hmax, rmax = P.rmax;
+    const int R = P.R, S = P.S, NG = P.NG, T = P.T, l = me.l, PP = P.P;
+    const int hn = me.hn, hq = P.hq, hk = P.hk, NR = P.NR, KC = P.KC, KC4 = P.KC4, C0 = P.C0;
     const int d = P.dil[l], depth = P.depth[l];
-    const int NUT = NU / UT;
+    const bool last = (l == P.L - 1);
     // ---- shared memory carve-up (weights first: identical to the packed blob) ------------------------------
-    float *Wc = smem;                                   // [2*hmax][KCs]   dilated conv rows (tanh rows, then sigmoid rows)
-    float *Wci = Wc + 2 * hmax * P.KCs;                 // [2*hmax][KIs]   cin 1x1 rows
-    float *Wos = Wci + 2 * hmax * P.KIs;                // [rmax+smax][KHs] residual-out rows, then skip rows
-    float *bconv = Wos + (rmax + P.smax) * P.KHs;       // [round4(2*hmax)]
-    float *bcin = bconv + round4(2 * hmax);
-    float *bos = bcin + round4(2 * hmax);               // [round4(rmax+smax)]
-    float *xt = smem + P.layer_blob_floats;             // [NU][3R]  tap0 | tap1 | tap2 (= x_l(t))
-    float *cond = xt + NU * 3 * R;                      // [NU][KI]
-    float *pre = cond + NU * P.KI;                      // [NU][2*hmax]
-    float *zf = pre + round4(NU * 2 * hmax);            // [NU][KH]
+    float *Wcat = smem;                                  // [NR][KC]      gate rows: tanh rows [0,hn), sigmoid rows [hq,hq+hn)
+    float *Wos = Wcat + (size_t)NR * KC;                 // [hk/4][R+S][4] columns [h0,h1) of out (rows 0..R) and skip (rows R..R+S)
+    float *bsum = Wos + (size_t)(R + S) * hk;            // [NR]
+    float *bpo = bsum + NR;                              // [R]           out-conv bias of layer l-1
+    float *bps = bpo + R;                                // [round4(smax)] skip-conv bias of layer l-1, my slice
+    float *fw = bps + round4(P.smax);                    // [R] first conv (layer 0 only)
+    float *fb = fw + R;                                  // [R]
+    float *xc = smem + P.layer_blob_floats;              // [KC][NU]      x(t-2d) | x(t-d) | c(t) | x(t), k-major
+    float *pre = xc + (size_t)KC * NU;                   // [NR][NU]
+    float *zs = pre + (size_t)NR * NU;                   // [hk][NU]
     {
         const float4 *src = reinterpret_cast<const float4 *>(P.blobs + me.blob);
         float4 *dst = reinterpret_cast<float4 *>(smem);
         for (int i = tid; i < P.layer_blob_floats / 4; i += PIPE_THREADS) dst[i] = __ldg(src + i);
-        for (int i = tid; i < NU * (3 * R + P.KI + P.KH) + round4(NU * 2 * hmax); i += PIPE_THREADS) xt[i] = 0.0f;
+        for (int i = tid; i < (KC + NR + hk) * NU; i += PIPE_THREADS) xc[i] = 0.0f;
     }
     __syncthreads();
 
-    unsigned long long *X = P.xbuf + P.xoff[l];
-    unsigned long long *Xn = (l + 1 < P.L) ? P.xbuf + P.xoff[l + 1] : nullptr;
-    const int depth_n = (l + 1 < P.L) ? P.depth[l + 1] : 1;
-    unsigned long long *Z = P.zbuf + (long long)l * NG * NU * H;
-    unsigned long long *Sout = P.sbuf + (long long)l * NG * NU * P.S;
-    const unsigned long long *Sin = (l > 0) ? P.sbuf + (long long)(l - 1) * NG * NU * P.S : nullptr;
+    float *ring = P.rings + (size_t)me.ring * NG * R * NU;   // [NG][depth][R][NU]; me.ring counts ring slots
+    const int o_cur = 2 * R + P.cin;
+    // consumer-side mailboxes of this layer (stage l) and producer-side ones (stage l+1)
+    const unsigned long long *op_in = P.op + (long long)l * P.op_sz, *xr_in = P.xr + (long long)l * P.xr_sz;
+    const unsigned long long *sp_in = P.sp + (long long)l * P.sp_sz, *rs_in = P.rs + (long long)l * P.rs_sz;
+    unsigned long long *op_out = P.op + (long long)(l + 1) * P.op_sz, *xr_out = P.xr + (long long)(l + 1) * P.xr_sz;
+    unsigned long long *sp_out = P.sp + (long long)(l + 1) * P.sp_sz, *rs_out = P.rs + (long long)(l + 1) * P.rs_sz;
 
-    // my work items (at most one of each per thread, checked by the plan)
-    const int n_pre = 2 * hn * NUT, n_os = (rn + sn) * NUT;
-    const bool has_pre = tid < n_pre, has_os = tid < n_os;
-    const int pj = has_pre ? tid % (2 * hn) : 0, put = has_pre ? tid / (2 * hn) : 0;
-    const int prow = pj < hn ? pj : hmax + (pj - hn);
-    const int oj = has_os ? tid % (rn + sn) : 0, out_ut = has_os ? tid / (rn + sn) : 0;
-    const bool is_out = oj < rn;
-    const int orow = is_out ? oj : rmax + (oj - rn);
+    // ---- thread roles -------------------------------------------------------------------------------------
+    const int lane = tid & (LANES - 1), q = tid / LANES;   // dot16: row quad q, partial `lane`
+    const bool has_q = q < P.NQ;
+    const bool warp_has_q = (tid / 32) * 2 < P.NQ;
+    const float4 *wq = reinterpret_cast<const float4 *>(Wcat) + (size_t)(has_q ? 4 * q : 0) * KC4;
+    const int c1_first = C0 + ((lane - C0) % LANES + LANES) % LANES;   // first chunk >= C0 owned by this lane
+    const int rbase = reduce16_base<NV>(lane);
+    const int NT2 = (R + S) / 4;                            // threads of the blocked chains (4 rows each)
+    const bool has_t2 = tid < NT2;
+    const int NT2r = (NT2 + 31) & ~31;
+    const int hbase = (NT2r <= PIPE_THREADS - 64) ? NT2r : 0;   // threads [hbase, 256) carry the skip sum meanwhile
+    const int hthreads = PIPE_THREADS - hbase;
 
     // ---- register prefetch of the older taps and the conditioning column of the NEXT work item -------------
-    const int n_tap16 = NU * R;          // 16-byte chunks: 2 taps * NU * R/2
-    const int n_c16 = NU * P.KI / 4;
-    unsigned long long pfa[MAX_PF], pfb[MAX_PF];
-    float4 pfc = make_float4(0.f, 0.f, 0.f, 0.f);
-    int pf_t = 0;
-    int bad = 0;
+    const int n_tap16 = 2 * R * NU / 4;                     // float4 loads for both taps
+    const int n_c16 = NU * (P.cin / 4);
+    float4 pft[MAX_PF], pfc;
     auto prefetch = [&](int g, int t) {
-        pf_t = t;
 #pragma unroll
         for (int k = 0; k < MAX_PF; ++k) {
-            const int q = tid + k * PIPE_THREADS;
-            pfa[k] = 0ull; pfb[k] = 0ull;
-            if (q < n_tap16) {
-                const int half = n_tap16 / 2;
-                const int tap = q / half, rem = q - tap * half;
-                const int u = rem / (R / 2), r = (rem - u * (R / 2)) * 2;
+            const int qf = tid + k * PIPE_THREADS;
+            pft[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (qf < n_tap16) {
+                const int per = n_tap16 / 2;
+                const int tap = qf / per, rem = qf - tap * per;
                 const int tt = t - (2 - tap) * d;
-                if (tt >= 0) ldcg2(X + ((long long)(g * depth + tt % depth) * NU + u) * R + r, pfa[k], pfb[k]);
+                if (tt >= 0)
+                    pft[k] = __ldcg(reinterpret_cast<const float4 *>(ring + (size_t)(g * depth + tt % depth) * R * NU) + rem);
             }
         }
         pfc = make_float4(0.f, 0.f, 0.f, 0.f);
         if (tid < n_c16) {
-            const int u = tid / (P.KI / 4), c4 = tid - u * (P.KI / 4);
+            const int u = tid / (P.cin / 4), c4 = tid - u * (P.cin / 4);
             const int b = g * NU + u;
-            if (b < P.B && c4 * 4 < P.cin)
-                pfc = __ldg(reinterpret_cast<const float4 *>(P.c_up + ((long long)b * T + t) * P.cin) + c4);
+            if (b < P.B) pfc = __ldg(reinterpret_cast<const float4 *>(P.c_up + ((long long)b * T + t) * P.cin) + c4);
         }
     };
     auto commit = [&]() {
 #pragma unroll
         for (int k = 0; k < MAX_PF; ++k) {
-            const int q = tid + k * PIPE_THREADS;
-            if (q < n_tap16) {
-                const int half = n_tap16 / 2;
-                const int tap = q / half, rem = q - tap * half;
-                const int u = rem / (R / 2), r = (rem - u * (R / 2)) * 2;
-                const int tt = pf_t - (2 - tap) * d;
-                // a tap read ahead of time must carry the tag of its own step; anything else is a protocol bug
-                if (tt >= 0 && (ll_tag(pfa[k]) != (unsigned)tt + 1u || ll_tag(pfb[k]) != (unsigned)tt + 1u)) {
-                    atomicExch(P.abort_flag, 2);
-                    bad = 1;
-                }
-                *reinterpret_cast<float2 *>(xt + u * 3 * R + tap * R + r) = make_float2(ll_val(pfa[k]), ll_val(pfb[k]));
-            }
+            const int qf = tid + k * PIPE_THREADS;
+            if (qf < n_tap16) reinterpret_cast<float4 *>(xc)[qf] = pft[k];
         }
-        if (tid < n_c16) reinterpret_cast<float4 *>(cond)[tid] = pfc;
+        if (tid < n_c16) {
+            const int u = tid / (P.cin / 4), c4 = tid - u * (P.cin / 4);
+            float *dst = xc + (size_t)(2 * R + 4 * c4) * NU + u;
+            dst[0] = pfc.x; dst[NU] = pfc.y; dst[2 * NU] = pfc.z; dst[3 * NU] = pfc.w;
+        }
     };
 
+    float acc[NV];
+    auto phase0 = [&]() {   // everything that does not need x_l(t): taps t-2d, t-d and the conditioning column
+#pragma unroll
+        for (int i = 0; i < NV; ++i) acc[i] = 0.0f;
+        if (has_q) mac_lane<NU>(acc, wq, KC4, xc, lane, C0);
+    };
+
+    int bad = 0;
+    long long st_c[6] = {0, 0, 0, 0, 0, 0};
+    const bool do_stats = P.stats != nullptr && tid == 0;
+    const long long st_begin = clock64();
+
     prefetch(0, 0);
+    commit();
+    __syncthreads();
+    phase0();
+
     const long long n_items = (long long)T * NG;
     int t = 0, g = 0;
     for (long long it = 0; it < n_items; ++it) {
         const unsigned tag = (unsigned)t + 1u;
-        commit();
-        if (__syncthreads_or(bad)) return;                                                           // (A)
+        const long long slot_g = (long long)(t & 1) * NG + g;
+        const long long c0 = do_stats ? clock64() : 0;
+        // ---- D: wait for the inputs of (t, g) and rebuild x_l(t) ----------------------------------------------
+        for (int task = tid; task < R * NP; task += PIPE_THREADS) {
+            const int r = task / NP, up = task - r * NP;
+            float x0, x1;
+            if (l == 0) {   // first_conv.incremental_step (wavenet.py:826) on the value the head fed back
+                float s0, s1;
+                bad |= poll_pair(P.in + slot_g * NU + 2 * up, tag, s0, s1, P.abort_flag);
+                x0 = __fadd_rn(__fmaf_rn(s0, fw[r], 0.0f), fb[r]);
+                x1 = __fadd_rn(__fmaf_rn(s1, fw[r], 0.0f), fb[r]);
+            } else {        // out 1x1 of layer l-1: partial sums in ascending p, bias, residual (modules.py:515-520)
+                unsigned long long wa[MAX_P + 1], wb[MAX_P + 1];
+                const unsigned long long *src[MAX_P + 1];
+#pragma unroll
+                for (int pp = 0; pp < MAX_P; ++pp)
+                    src[pp] = op_in + ((slot_g * PP + (pp < PP ? pp : 0)) * R + r) * NU + 2 * up;
+                src[MAX_P] = xr_in + (slot_g * R + r) * NU + 2 * up;
+                unsigned pending = ((1u << PP) - 1u) | (1u << MAX_P);
+                unsigned spins = 0;
+                while (pending) {
+#pragma unroll
+                    for (int pp = 0; pp <= MAX_P; ++pp)
+                        if (pending & (1u << pp)) ld_ll2(src[pp], wa[pp], wb[pp]);
+#pragma unroll
+                    for (int pp = 0; pp <= MAX_P; ++pp)
+                        if ((pending & (1u << pp)) && ll_tag(wa[pp]) == tag && ll_tag(wb[pp]) == tag) pending &= ~(1u << pp);
+                    if (pending && (++spins & 0x3ffu) == 0) {
+                        if (*(volatile int *)P.abort_flag) { bad = 1; break; }
+                        if (spins > SPIN_LIMIT) { atomicExch(P.abort_flag, 1); bad = 1; break; }
+                    }
+                }
+                float y0 = ll_val(wa[0]), y1 = ll_val(wb[0]);
+#pragma unroll
+                for (int pp = 1; pp < MAX_P; ++pp)
+                    if (pp < PP) { y0 = __fadd_rn(y0, ll_val(wa[pp])); y1 = __fadd_rn(y1, ll_val(wb[pp])); }
+                y0 = __fadd_rn(y0, bpo[r]); y1 = __fadd_rn(y1, bpo[r]);
+                y0 = __fadd_rn(y0, ll_val(wa[MAX_P])); y1 = __fadd_rn(y1, ll_val(wb[MAX_P]));
+                x0 = P.residual_legacy ? __fmul_rn(y0, WN_SQRT_HALF) : y0;
+                x1 = P.residual_legacy ? __fmul_rn(y1, WN_SQRT_HALF) : y1;
+            }
+            *reinterpret_cast<float2 *>(xc + (size_t)(o_cur + r) * NU + 2 * up) = make_float2(x0, x1);
+            __stcg(reinterpret_cast<float2 *>(ring + ((size_t)(g * depth + t % depth) * R + r) * NU + 2 * up),
+                   make_float2(x0, x1));
+        }
+        if (__syncthreads_or(bad)) return;                                                           // (1)
+        const long long c1 = do_stats ? clock64() : 0;
+        // the residual input x_l(t), slice [r0,r1), travels with the partial sums (the consumer adds it)
+        if (!last)
+            for (int task = tid; task < me.rn * NP; task += PIPE_THREADS) {
+                const int r = me.r0 + task / NP, up = task % NP;
+                const float2 v = *reinterpret_cast<const float2 *>(xc + (size_t)(o_cur + r) * NU + 2 * up);
+                st_ll2(xr_out + (slot_g * R + r) * NU + 2 * up, v.x, v.y, tag);
+            }
         int g2 = g + 1, t2 = t;
         if (g2 == NG) { g2 = 0; t2 = t + 1; }
-        // the next item's older taps were delivered in earlier items - except with a single group and d = 1, where
-        // tap t+1-d is the x_l(t) this item is about to receive: then the read-ahead is issued after the poll below
-        const bool early_pf = NG > 1;
-        if (early_pf && t2 < T) prefetch(g2, t2);
-        // ---- phase 0: everything that does not need x_l(t): taps t-2d, t-d and the cin 1x1 ----------------
-        float acc[UT], cacc[UT];
+        if (t2 < T) prefetch(g2, t2);   // ring slots of (t2 - d, g2) were written in an earlier item or just above
+        // ---- E: current tap, tree reduction, bias (modules.py:294-297, :497-501) ----------------------------
+        if (warp_has_q) {   // warp-uniform: the butterfly shuffles need every lane of the warp
+            if (has_q) mac_lane<NU>(acc, wq, KC4, xc, c1_first, KC4);
+            reduce16<NV>(acc, lane);
+            if (has_q) {
 #pragma unroll
-        for (int j = 0; j < UT; ++j) acc[j] = cacc[j] = 0.0f;
-        if (has_pre) {
-            chain<UT>(acc, Wc + prow * P.KCs, xt + put * UT * 3 * R, 3 * R, 2 * R);
-            chain<UT>(cacc, Wci + prow * P.KIs, cond + put * UT * P.KI, P.KI, P.KI);
-        }
-        // ---- wait for x_l(t) of this group (from layer l-1, or from the head for l = 0) ---------------------
-        bad |= poll_block(X + (long long)(g * depth + t % depth) * NU * R, NU * R, tag, xt + 2 * R, R, 3 * R, P.abort_flag);
-        if (__syncthreads_or(bad)) return;                                                           // (B)
-        if (!early_pf && t2 < T) prefetch(g2, t2);
-        // ---- phase 1: current tap, biases, conditioning add (modules.py:294-297, :497-501) -----------------
-        if (has_pre) {
-            chain<UT>(acc, Wc + prow * P.KCs + 2 * R, xt + put * UT * 3 * R + 2 * R, 3 * R, R);
-#pragma unroll
-            for (int j = 0; j < UT; ++j)
-                pre[(put * UT + j) * 2 * hmax + prow] =
-                    __fadd_rn(__fadd_rn(acc[j], bconv[prow]), __fadd_rn(cacc[j], bcin[prow]));
-        }
-        __syncthreads();                                                                             // (C)
-        // ---- gate (modules.py:510) and publish my z channels to the P CTAs of this layer -------------------
-        if (tid < hn * NU) {
-            const int j = tid % hn, u = tid / hn;
-            const float zv = __fmul_rn(wn_tanhf(pre[u * 2 * hmax + j]), wn_sigmoidf(pre[u * 2 * hmax + hmax + j]));
-            st_ll(Z + ((long long)g * NU + u) * H + me.h0 + j, zv, tag);
-        }
-        bad |= poll_block(Z + (long long)g * NU * H, NU * H, tag, zf, H, P.KH, P.abort_flag);
-        if (__syncthreads_or(bad)) return;                                                           // (D)
-        // ---- phase 2: residual-out rows -> x_{l+1}(t); skip rows -> running skip sum (modules.py:512-520) --
-        if (has_os) {
-            float a2[UT];
-#pragma unroll
-            for (int j = 0; j < UT; ++j) a2[j] = 0.0f;
-            chain<UT>(a2, Wos + orow * P.KHs, zf + out_ut * UT * P.KH, P.KH, P.KH);
-#pragma unroll
-            for (int j = 0; j < UT; ++j) {
-                const int u = out_ut * UT + j;
-                const float v = __fadd_rn(a2[j], bos[orow]);
-                if (is_out) {
-                    if (Xn) {
-                        const int r = me.r0 + oj;
-                        const float s2 = __fadd_rn(v, xt[u * 3 * R + 2 * R + r]);
-                        const float xn = P.residual_legacy ? __fmul_rn(s2, WN_SQRT_HALF) : s2;
-                        st_ll(Xn + ((long long)(g * depth_n + t % depth_n) * NU + u) * R + r, xn, tag);
-                    }
-                } else {
-                    const int sc = me.s0 + (oj - rn);
-                    float sk = v;                                          // wavenet.py:833-836
-                    if (Sin) {
-                        float prev;
-                        bad |= poll_one(Sin + ((long long)g * NU + u) * P.S + sc, tag, prev, P.abort_flag);
-                        const float s2 = __fadd_rn(prev, v);
-                        sk = P.legacy ? __fmul_rn(s2, WN_SQRT_HALF) : s2;
-                    }
-                    st_ll(Sout + ((long long)g * NU + u) * P.S + sc, sk, tag);
+                for (int i = 0; i < (NV >= LANES ? NV / LANES : 1); ++i) {
+                    const int v = rbase + i, row = 4 * q + v / NU, u = v % NU;
+                    pre[(size_t)row * NU + u] = __fadd_rn(acc[i], bsum[row]);
                 }
             }
         }
-        if (++g == NG) { g = 0; ++t; }
+        __syncthreads();                                                                             // (2)
+        const long long c2 = do_stats ? clock64() : 0;
+        // ---- F: gate (modules.py:510) --------------------------------------------------------------------------
+        for (int i = tid; i < hn * NU; i += PIPE_THREADS) {
+            const int j = i / NU, u = i - j * NU;
+            zs[(size_t)j * NU + u] = __fmul_rn(wn_tanhf(pre[(size_t)j * NU + u]), wn_sigmoidf(pre[(size_t)(hq + j) * NU + u]));
+        }
+        __syncthreads();                                                                             // (3)
+        const long long c3 = do_stats ? clock64() : 0;
+        // ---- G: my column block of the out / skip 1x1s -> partial sums for layer l+1 / the head ---------------
+        if (has_t2) {
+            float a2[NV];
+#pragma unroll
+            for (int i = 0; i < NV; ++i) a2[i] = 0.0f;
+            chain_tile<NU>(a2, reinterpret_cast<const float4 *>(Wos), R + S, tid, NT2, zs, hk / 4);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int row = tid + i * NT2;
+                unsigned long long *dst;
+                if (row < R) {
+                    if (last) continue;
+                    dst = op_out + ((slot_g * PP + me.p) * R + row) * NU;
+                } else {
+                    dst = sp_out + ((slot_g * PP + me.p) * S + (row - R)) * NU;
+                }
+#pragma unroll
+                for (int up = 0; up < NP; ++up) st_ll2(dst + 2 * up, a2[i * NU + 2 * up], a2[i * NU + 2 * up + 1], tag);
+            }
+        }
+        // ---- H: running skip sum through layer l-1, my slice (wavenet.py:833-836), sent to (l+1, p) / the head ---
+        if (l >= 1 && tid >= hbase) {
+            for (int task = tid - hbase; task < me.sn * NP; task += hthreads) {
+                const int cl = task / NP, up = task - cl * NP, c = me.s0 + cl;
+                float s0 = 0.f, s1 = 0.f;
+#pragma unroll 1
+                for (int pp = 0; pp < PP; ++pp) {
+                    float v0, v1;
+                    bad |= poll_pair(sp_in + ((slot_g * PP + pp) * S + c) * NU + 2 * up, tag, v0, v1, P.abort_flag);
+                    if (pp == 0) { s0 = v0; s1 = v1; } else { s0 = __fadd_rn(s0, v0); s1 = __fadd_rn(s1, v1); }
+                }
+                s0 = __fadd_rn(s0, bps[cl]); s1 = __fadd_rn(s1, bps[cl]);
+                if (l >= 2) {
+                    float v0, v1;
+                    bad |= poll_pair(rs_in + (slot_g * S + c) * NU + 2 * up, tag, v0, v1, P.abort_flag);
+                    s0 = __fadd_rn(v0, s0); s1 = __fadd_rn(v1, s1);
+                    if (P.legacy) { s0 = __fmul_rn(s0, WN_SQRT_HALF); s1 = __fmul_rn(s1, WN_SQRT_HALF); }
+                }
+                st_ll2(rs_out + (slot_g * S + c) * NU + 2 * up, s0, s1, tag);
+            }
+        }
+        const long long c4 = do_stats ? clock64() : 0;
+        // ---- next item: older taps + conditioning into shared memory, then its x(t)-independent part ------------
+        if (t2 < T) commit();
+        if (__syncthreads_or(bad)) return;                                                           // (4)
+        if (t2 < T) phase0();
+        if (do_stats) {
+            const long long c5 = clock64();
+            st_c[0] += c1 - c0; st_c[1] += c2 - c1; st_c[2] += c3 - c2; st_c[3] += c4 - c3; st_c[4] += c5 - c4;
+        }
+        g = g2; t = t2;
+    }
+    if (do_stats) {
+        long long *o = P.stats + (long long)blockIdx.x * 8;
+        for (int i = 0; i < 5; ++i) o[i] = st_c[i];
+        o[5] = clock64() - st_begin; o[6] = n_items; o[7] = 0;
     }
 }
 
 
+// 1 row x NU utterances, chunks c = c_first, c_first+16, ... (one partial of dot16) - the small second head 1x1
+template <int NU>
+__device__ __forceinline__ void mac_lane1(float (&acc)[NU], const float4 *__restrict__ w4, const float *__restrict__ xs,
+                                          int c_first, int c_end) {
+    for (int c = c_first; c < c_end; c += LANES) {
+        const float4 w = w4[c];
+        const float *xk = xs + (size_t)c * 4 * NU;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float wv = e == 0 ? w.x : (e == 1 ? w.y : (e == 2 ? w.z : w.w));
+#pragma unroll
+            for (int u = 0; u < NU; ++u) acc[u] = __fmaf_rn(xk[e * NU + u], wv, acc[u]);
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
-// head CTA: relu -> 1x1 -> relu -> 1x1 (wavenet.py:840-844), sampler (:850-859), feedback + first 1x1 (:826, :877)
-// for the groups g = me.l, me.l + NH, ...
+// head CTA: last skip accumulation, relu -> 1x1 -> relu -> 1x1 (wavenet.py:833-844), sampler (:850-859) and the
+// feedback value (:877) for the groups g = me.l, me.l + NH, ...
 // ---------------------------------------------------------------------------------------------------------------
+template <int NU>
 __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
+    constexpr int NV = 4 * NU, NP = NU / 2;
     const int tid = threadIdx.x;
-    const int R = P.R, S = P.S, O = P.O, NU = P.NU, NG = P.NG, T = P.T;
-    float *W1 = smem;                          // [S][KSs]
-    float *W2 = W1 + S * P.KSs;                // [O][KSs]
-    float *b1 = W2 + O * P.KSs;                // [round4(S)]
-    float *b2 = b1 + round4(S);                // [round4(O)]
-    float *fw = b2 + round4(O);                // [round4(R)]
-    float *fb = fw + round4(R);                // [round4(R)]
-    float *sk = smem + P.head_blob_floats;     // [NU][KS]
-    float *h1 = sk + NU * P.KS;                // [NU][KS]
-    float *outv = h1 + NU * P.KS;              // [NU][round4(O)]
-    float *nin = outv + NU * round4(O);        // [NU]
+    const int S = P.S, O = P.O, NG = P.NG, T = P.T, PP = P.P, L = P.L;
+    const int S4 = S / 4;
+    float *W1 = smem;                          // [S][S]   row n = output channel (transposed TF kernel)
+    float *W2 = W1 + (size_t)S * S;            // [O][S]
+    float *b1 = W2 + (size_t)O * S;            // [S]
+    float *b2 = b1 + S;                        // [round4(O)]
+    float *bsl = b2 + round4(O);               // [S]      skip-conv bias of the last layer
+    float *hs = smem + P.head_blob_floats;     // [S][NU]  relu(skips), k-major
+    float *h1 = hs + (size_t)S * NU;           // [S][NU]
+    float *outv = h1 + (size_t)S * NU;         // [O][NU]
     {
         const float4 *src = reinterpret_cast<const float4 *>(P.blobs + me.blob);
         float4 *dst = reinterpret_cast<float4 *>(smem);
         for (int i = tid; i < P.head_blob_floats / 4; i += PIPE_THREADS) dst[i] = __ldg(src + i);
-        for (int i = tid; i < NU * (2 * P.KS + round4(O)) + NU; i += PIPE_THREADS) sk[i] = 0.0f;
     }
     __syncthreads();
-    unsigned long long *X0 = P.xbuf + P.xoff[0];
-    const int depth0 = P.depth[0];
-    const unsigned long long *Sl = P.sbuf + (long long)(P.L - 1) * NG * NU * S;
+    const unsigned long long *sp_in = P.sp + (long long)L * P.sp_sz, *rs_in = P.rs + (long long)L * P.rs_sz;
+    const int lane = tid & (LANES - 1), q16 = tid / LANES;
+    const int rbase4 = reduce16_base<NV>(lane), rbase1 = reduce16_base<NU>(lane);
 
-    // initial input (wavenet.py:433-445): raw 0.0, mulaw mulaw(0) = 0.0 -> x_0(0) = first_conv(0)
+    // initial input (wavenet.py:433-445): raw 0.0, mulaw mulaw(0) = 0.0
     for (int g = me.l; g < NG; g += P.NH)
-        for (int i = tid; i < R * NU; i += PIPE_THREADS) {
-            const int r = i % R, u = i / R;
-            const float x0 = __fadd_rn(__fmaf_rn(0.0f, fw[r], 0.0f), fb[r]);
-            st_ll(X0 + ((long long)(g * depth0 + 0) * NU + u) * R + r, x0, 1u);
-        }
+        if (tid < NP) st_ll2(P.in + ((long long)0 * NG + g) * NU + 2 * tid, 0.0f, 0.0f, 1u);
 
     int bad = 0;
+    long long st_c[2] = {0, 0};
+    const bool do_stats = P.stats != nullptr && tid == 0;
+    const long long st_begin = clock64();
     for (int t = 0; t < T; ++t) {
         const unsigned tag = (unsigned)t + 1u;
         for (int g = me.l; g < NG; g += P.NH) {
-            bad |= poll_block(Sl + (long long)g * NU * S, NU * S, tag, sk, S, P.KS, P.abort_flag);
-            if (__syncthreads_or(bad)) return;
-            for (int i = tid; i < S * NU; i += PIPE_THREADS) {       // relu -> final_convolution_1 -> relu
-                const int n = i % S, u = i / S;
-                const float4 *w4 = reinterpret_cast<const float4 *>(W1 + n * P.KSs);
-                const float4 *x4 = reinterpret_cast<const float4 *>(sk + u * P.KS);
-                float acc = 0.0f;
-#pragma unroll 4
-                for (int k4 = 0; k4 < P.KS / 4; ++k4) {
-                    const float4 wv = w4[k4];
-                    float4 xv = x4[k4];
-                    xv.x = xv.x > 0.f ? xv.x : 0.f; xv.y = xv.y > 0.f ? xv.y : 0.f;
-                    xv.z = xv.z > 0.f ? xv.z : 0.f; xv.w = xv.w > 0.f ? xv.w : 0.f;
-                    acc = __fmaf_rn(xv.x, wv.x, acc);
-                    acc = __fmaf_rn(xv.y, wv.y, acc);
-                    acc = __fmaf_rn(xv.z, wv.z, acc);
-                    acc = __fmaf_rn(xv.w, wv.w, acc);
+            const long long slot_g = (long long)(t & 1) * NG + g;
+            const long long c0 = do_stats ? clock64() : 0;
+            // ---- skips = (skips_{L-2} + s_{L-1}) * sqrt(.5); relu ----------------------------------------------
+            for (int task = tid; task < S * NP; task += PIPE_THREADS) {
+                const int c = task / NP, up = task - c * NP;
+                float s0 = 0.f, s1 = 0.f;
+#pragma unroll 1
+                for (int pp = 0; pp < PP; ++pp) {
+                    float v0, v1;
+                    bad |= poll_pair(sp_in + ((slot_g * PP + pp) * S + c) * NU + 2 * up, tag, v0, v1, P.abort_flag);
+                    if (pp == 0) { s0 = v0; s1 = v1; } else { s0 = __fadd_rn(s0, v0); s1 = __fadd_rn(s1, v1); }
                 }
-                const float v = __fadd_rn(acc, b1[n]);
-                h1[u * P.KS + n] = v > 0.0f ? v : 0.0f;
+                s0 = __fadd_rn(s0, bsl[c]); s1 = __fadd_rn(s1, bsl[c]);
+                if (L >= 2) {
+                    float v0, v1;
+                    bad |= poll_pair(rs_in + (slot_g * S + c) * NU + 2 * up, tag, v0, v1, P.abort_flag);
+                    s0 = __fadd_rn(v0, s0); s1 = __fadd_rn(v1, s1);
+                    if (P.legacy) { s0 = __fmul_rn(s0, WN_SQRT_HALF); s1 = __fmul_rn(s1, WN_SQRT_HALF); }
+                }
+                *reinterpret_cast<float2 *>(hs + (size_t)c * NU + 2 * up) =
+                    make_float2(s0 > 0.f ? s0 : 0.f, s1 > 0.f ? s1 : 0.f);
+            }
+            if (__syncthreads_or(bad)) return;
+            const long long c1 = do_stats ? clock64() : 0;
+            // ---- final_convolution_1 + relu: dot16, 4 rows x NU per thread -------------------------------------
+            for (int qb = 0; qb < S4; qb += PIPE_THREADS / LANES) {
+                const int q = qb + q16;
+                float acc[NV];
+#pragma unroll
+                for (int i = 0; i < NV; ++i) acc[i] = 0.0f;
+                if (q < S4) mac_lane<NU>(acc, reinterpret_cast<const float4 *>(W1) + (size_t)4 * q * S4, S4, hs, lane, S4);
+                reduce16<NV>(acc, lane);
+                if (q < S4) {
+#pragma unroll
+                    for (int i = 0; i < (NV >= LANES ? NV / LANES : 1); ++i) {
+                        const int v = rbase4 + i, row = 4 * q + v / NU, u = v % NU;
+                        const float y = __fadd_rn(acc[i], b1[row]);
+                        h1[(size_t)row * NU + u] = y > 0.0f ? y : 0.0f;
+                    }
+                }
             }
             __syncthreads();
-            for (int i = tid; i < O * NU; i += PIPE_THREADS) {       // final_convolution_2
-                const int n = i % O, u = i / O;
-                float acc1[1] = {0.0f};
-                chain<1>(acc1, W2 + n * P.KSs, h1 + u * P.KS, P.KS, P.KS);
-                const float v = __fadd_rn(acc1[0], b2[n]);
-                outv[u * round4(O) + n] = v;
-                const int b = g * NU + u;
-                if (P.raw && b < P.B) P.raw[((long long)b * T + t) * O + n] = v;   // wavenet.py:847
+            // ---- final_convolution_2: dot16, 1 row x NU per 16 lanes ----------------------------------------------
+            for (int nb = 0; nb < O; nb += PIPE_THREADS / LANES) {
+                const int n = nb + q16;
+                float acc[NU];
+#pragma unroll
+                for (int u = 0; u < NU; ++u) acc[u] = 0.0f;
+                if (n < O) mac_lane1<NU>(acc, reinterpret_cast<const float4 *>(W2) + (size_t)n * S4, h1, lane, S4);
+                reduce16<NU>(acc, lane);
+                if (n < O) {
+#pragma unroll
+                    for (int i = 0; i < (NU >= LANES ? NU / LANES : 1); ++i) {
+                        const int u = rbase1 + i;
+                        const float y = __fadd_rn(acc[i], b2[n]);
+                        outv[(size_t)n * NU + u] = y;
+                        const int b = g * NU + u;
+                        if (P.raw && b < P.B && (lane >> (NU == 2 ? 1 : (NU == 4 ? 2 : 3))) == 0)
+                            P.raw[((long long)b * T + t) * O + n] = y;                     // wavenet.py:847
+                    }
+                }
             }
             __syncthreads();
-            if (tid < NU) {                                           // sampling + feedback
+            // ---- sampling + feedback ------------------------------------------------------------------------------
+            if (tid < 32) {
                 const int u = tid, b = g * NU + u;
                 float nxt = 0.0f;
-                if (b < P.B) {
+                if (u < NU && b < P.B) {
                     const float *nz = P.noise + ((long long)t * P.B + b) * P.NZ;
-                    const float *o = outv + u * round4(O);
-                    const float smp = (O == 2) ? pipe_sample_gaussian(P, o, nz[0]) : pipe_sample_mol(P, o, nz);
+                    const float smp = (O == 2) ? pipe_sample_gaussian(P, outv + u, NU, nz[0])
+                                               : pipe_sample_mol(P, outv + u, NU, nz);
                     P.audio[(long long)b * T + t] = P.input_type == WN_INPUT_MULAW ? wn_inv_mulawf(smp) : smp;
                     nxt = P.teacher ? P.teacher[(long long)b * T + t] : smp;
                 }
-                nin[u] = nxt;
+                const float other = __shfl_down_sync(0xffffffffu, nxt, 1);
+                if (u < NU && !(u & 1) && t + 1 < T)
+                    st_ll2(P.in + ((long long)((t + 1) & 1) * NG + g) * NU + u, nxt, other, tag + 1u);
             }
-            __syncthreads();
-            if (t + 1 < T) {
-                const int slot = (t + 1) % depth0;
-                for (int i = tid; i < R * NU; i += PIPE_THREADS) {   // first_conv.incremental_step of step t+1
-                    const int r = i % R, u = i / R;
-                    const float x0 = __fadd_rn(__fmaf_rn(nin[u], fw[r], 0.0f), fb[r]);
-                    st_ll(X0 + ((long long)(g * depth0 + slot) * NU + u) * R + r, x0, tag + 1u);
-                }
-            }
+            if (do_stats) { st_c[0] += c1 - c0; st_c[1] += clock64() - c1; }
         }
+    }
+    if (do_stats) {
+        long long *o = P.stats + (long long)blockIdx.x * 8;
+        o[0] = st_c[0]; o[1] = st_c[1]; o[2] = o[3] = o[4] = 0;
+        o[5] = clock64() - st_begin; o[6] = T; o[7] = 1;
     }
 }
 
-template <int UT>
+template <int NU>
 __global__ void __launch_bounds__(PIPE_THREADS, 1) wn_loop_pipe_kernel(const PipeParams P) {
     extern __shared__ __align__(16) float pipe_smem[];
     const PipeCta me = P.ctas[blockIdx.x];
-    if (me.role == 0) layer_role<UT>(P, me, pipe_smem);
-    else head_role(P, me, pipe_smem);
+    if (me.role == 0) layer_role<NU>(P, me, pipe_smem);
+    else head_role<NU>(P, me, pipe_smem);
 }
+
 
 }  // namespace
 
@@ -453,20 +653,22 @@ struct WnPipePlan {
     int max_heads = 16;
     float *d_blobs = nullptr;
     PipeCta *d_ctas = nullptr;
-    unsigned long long *d_mail = nullptr;   // xbuf | zbuf | sbuf
+    unsigned long long *d_mail = nullptr;   // op | xr | sp | rs | in
     size_t mail_words = 0;
+    float *d_rings = nullptr;
+    size_t ring_floats = 0;
+    long long ring_slots = 0;        // sum over layer CTAs of their ring depth
     int *d_abort = nullptr;
     int *h_abort = nullptr;          // pinned mirror, copied after every launch
+    long long *d_stats = nullptr;    // WN_PIPE_STATS=<file>: per-CTA clock64 counters, dumped after each synchronised call
+    int stats_ctas = 0;
     size_t smem_bytes = 0;
-    int UT = 1;
 };
 
 static int env_int(const char *name, int dflt) {
     const char *v = getenv(name);
     return (v && *v) ? atoi(v) : dflt;
 }
-
-static int pad_stride(int K) { return ((K / 4) % 2 == 1) ? K : K + 4; }   // (stride/4) odd: conflict-free LDS.128 across rows
 static int r4(int v) { return (v + 3) & ~3; }
 
 void wn_pipe_free(wn_handle *h) {
@@ -475,8 +677,10 @@ void wn_pipe_free(wn_handle *h) {
     if (pl->d_blobs) cudaFree(pl->d_blobs);
     if (pl->d_ctas) cudaFree(pl->d_ctas);
     if (pl->d_mail) cudaFree(pl->d_mail);
+    if (pl->d_rings) cudaFree(pl->d_rings);
     if (pl->d_abort) cudaFree(pl->d_abort);
     if (pl->h_abort) cudaFreeHost(pl->h_abort);
+    if (pl->d_stats) cudaFree(pl->d_stats);
     delete pl;
     h->pipe = nullptr;
 }
@@ -488,117 +692,155 @@ void wn_pipe_fill_info(wn_handle *h, wn_info *info) {
     info->pipeline_group_size = h->pipe->prm.NU;
 }
 
+static const void *pipe_kernel(int NU) {
+    switch (NU) {
+        case 2: return (const void *)wn_loop_pipe_kernel<2>;
+        case 4: return (const void *)wn_loop_pipe_kernel<4>;
+        default: return (const void *)wn_loop_pipe_kernel<8>;
+    }
+}
+
+// Fills the geometry that follows from (model, P, NU); returns the dynamic shared memory the kernel needs, 0 if the
+// split does not fit the thread roles.
+static size_t pipe_geometry(const WnModelDev &m, PipeParams &p) {
+    auto lo = [&](int n, int q) { return (int)((long long)n * q / p.P); };
+    int hmax = 0;
+    p.smax = 0;
+    for (int q = 0; q < p.P; ++q) {
+        hmax = std::max(hmax, lo(m.H, q + 1) - lo(m.H, q));
+        p.smax = std::max(p.smax, lo(m.S, q + 1) - lo(m.S, q));
+    }
+    p.hq = (hmax + 1) & ~1;
+    p.hk = r4(hmax);
+    p.NR = 2 * p.hq;
+    p.NQ = p.NR / 4;
+    p.KC = 3 * m.R + m.cin;
+    p.KC4 = p.KC / 4;
+    p.C0 = (2 * m.R + m.cin) / 4;
+    if (p.NQ * LANES > PIPE_THREADS || (m.R + m.S) / 4 > PIPE_THREADS) return 0;
+    if (p.NU * (m.cin / 4) > PIPE_THREADS || 2 * m.R * p.NU / 4 > MAX_PF * PIPE_THREADS) return 0;
+    p.layer_blob_floats = p.NR * p.KC + (m.R + m.S) * p.hk + p.NR + m.R + r4(p.smax) + 2 * m.R;
+    p.head_blob_floats = m.S * m.S + m.O * m.S + m.S + r4(m.O) + m.S;
+    const size_t layer_smem = sizeof(float) * ((size_t)p.layer_blob_floats + (size_t)(p.KC + p.NR + p.hk) * p.NU);
+    const size_t head_smem = sizeof(float) * ((size_t)p.head_blob_floats + (size_t)(2 * m.S + r4(m.O)) * p.NU);
+    return std::max(layer_smem, head_smem);
+}
+
 int wn_pipe_plan(wn_handle *h) {
     const wn_config &c = h->cfg;
-    const WnModelDev &m = h->m;
+    WnModelDev &m = h->m;
     auto no = [&](const std::string &why) { h->err = why; return -1; };
     if (c.input_type == WN_INPUT_MULAW_QUANTIZE) return no("one-hot (mulaw-quantize) input runs on the generic engine");
     if (m.ksize != 3) return no("kernel_size != 3 runs on the generic engine");
     if (m.cin <= 0 || m.cin % 4) return no("needs local conditioning with cin_channels % 4 == 0");
     if (m.gin > 0) return no("global conditioning runs on the generic engine");
-    if (m.R % 4 || m.S % 4 || m.H % 4) return no("channel counts must be multiples of 4");
+    if (m.R % 4 || m.S % 4) return no("residual / skip channel counts must be multiples of 4");
     WnPipePlan *pl = new WnPipePlan();
     PipeParams &p = pl->prm;
     memset(&p, 0, sizeof(p));
-    p.L = m.L; p.R = m.R; p.G = m.G; p.S = m.S; p.O = m.O; p.H = m.H; p.cin = m.cin; p.NZ = m.NZ;
+    p.L = m.L; p.R = m.R; p.H = m.H; p.S = m.S; p.O = m.O; p.cin = m.cin; p.NZ = m.NZ;
     p.input_type = m.input_type; p.legacy = m.legacy; p.residual_legacy = m.residual_legacy;
     p.log_scale_min = m.log_scale_min; p.log_scale_min_gauss = m.log_scale_min_gauss;
     for (int l = 0; l < m.L; ++l) { p.dil[l] = m.dil[l]; p.depth[l] = 2 * m.dil[l] + 1; }
-    p.P = env_int("WN_PIPE_P", 4);
-    p.NU = env_int("WN_PIPE_NU", 4);
-    pl->UT = env_int("WN_PIPE_UT", 1);
     auto bail = [&](const std::string &why) { delete pl; h->err = why; return -1; };
-    if (p.P < 1 || p.P > m.H || p.P > m.R || p.P > m.S) return bail("bad WN_PIPE_P");
-    if (pl->UT != 1 && pl->UT != 2) return bail("WN_PIPE_UT must be 1 or 2");
-    if (p.NU < 1 || p.NU % pl->UT) return bail("WN_PIPE_NU must be a multiple of WN_PIPE_UT");
-    auto lo = [&](int n, int q) { return (int)((long long)n * q / p.P); };
-    p.hmax = p.rmax = p.smax = 0;
-    for (int q = 0; q < p.P; ++q) {
-        p.hmax = std::max(p.hmax, lo(m.H, q + 1) - lo(m.H, q));
-        p.rmax = std::max(p.rmax, lo(m.R, q + 1) - lo(m.R, q));
-        p.smax = std::max(p.smax, lo(m.S, q + 1) - lo(m.S, q));
-    }
-    const int NUT = p.NU / pl->UT;
-    if (2 * p.hmax * NUT > PIPE_THREADS || (p.rmax + p.smax) * NUT > PIPE_THREADS || p.hmax * p.NU > PIPE_THREADS)
-        return bail("slice x group does not fit 256 threads (raise WN_PIPE_P or lower WN_PIPE_NU)");
-    if (p.NU * m.R > MAX_PF * PIPE_THREADS) return bail("tap prefetch does not fit (NU * R > 1024)");
-    p.KC = 3 * m.R; p.KCs = pad_stride(p.KC);
-    p.KI = r4(m.cin); p.KIs = pad_stride(p.KI);
-    p.KH = m.H; p.KHs = pad_stride(p.KH);
-    p.KS = m.S; p.KSs = pad_stride(p.KS);
-    if (p.NU * p.KI / 4 > PIPE_THREADS) return bail("conditioning prefetch does not fit");
-    p.layer_blob_floats = 2 * p.hmax * p.KCs + 2 * p.hmax * p.KIs + (p.rmax + p.smax) * p.KHs + 2 * r4(2 * p.hmax) +
-                          r4(p.rmax + p.smax);
-    p.head_blob_floats = m.S * p.KSs + m.O * p.KSs + r4(m.S) + r4(m.O) + 2 * r4(m.R);
-    const size_t layer_smem = sizeof(float) * ((size_t)p.layer_blob_floats + (size_t)p.NU * (3 * m.R + p.KI + p.KH) + r4(p.NU * 2 * p.hmax));
-    const size_t head_smem = sizeof(float) * ((size_t)p.head_blob_floats + (size_t)p.NU * (2 * p.KS + r4(m.O)) + p.NU);
-    pl->smem_bytes = std::max(layer_smem, head_smem);
+    p.NU = env_int("WN_PIPE_NU", 4);
+    if (p.NU != 2 && p.NU != 4 && p.NU != 8) return bail("WN_PIPE_NU must be 2, 4 or 8");
     int max_optin = 0;
     cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
-    if (pl->smem_bytes > (size_t)max_optin)
-        return bail("fp32 weight slice (" + std::to_string(pl->smem_bytes) + " B) exceeds shared memory per CTA (" +
-                    std::to_string(max_optin) + " B)");
-    if (m.L * p.P + 1 > h->sm_count) return bail("more layer CTAs than SMs");
-    pl->max_heads = std::min(16, h->sm_count - m.L * p.P);
+    // CTAs per layer: the caller's ksplit (it fixes the summation order), else WN_PIPE_P, else the widest split that
+    // leaves SMs for the head CTAs
+    auto feasible = [&](int P) {
+        if (P < 1 || P > MAX_P || P > m.H || P > m.S || P > m.R) return false;
+        if (m.L * P + 1 > h->sm_count) return false;
+        p.P = P;
+        const size_t smem = pipe_geometry(m, p);
+        return smem > 0 && smem <= (size_t)max_optin;
+    };
+    int P = c.ksplit > 0 ? c.ksplit : env_int("WN_PIPE_P", 0);
+    if (P > 0) {
+        if (!feasible(P)) return bail("split over " + std::to_string(P) + " CTAs per layer does not fit (shared memory " +
+                                      std::to_string(max_optin) + " B, " + std::to_string(h->sm_count) + " SMs)");
+    } else {
+        const int want_heads = 8;
+        for (P = std::min(MAX_P, std::max(1, (h->sm_count - want_heads) / m.L)); P >= 1; --P)
+            if (feasible(P)) break;
+        if (P < 1)
+            for (P = MAX_P; P >= 1; --P)
+                if (feasible(P)) break;
+        if (P < 1) return bail("fp32 weight slices do not fit shared memory for any split");
+    }
+    p.P = P;
+    pl->smem_bytes = pipe_geometry(m, p);
+    pl->max_heads = std::min(32, h->sm_count - m.L * p.P);
+    m.ksplit = p.P;
 
     // ---- pack weights: one blob per layer CTA in its shared-memory layout, one head blob ---------------------
+    auto lo = [&](int n, int q) { return (int)((long long)n * q / p.P); };
     auto Wt = [&](const std::string &n) -> const float * {
         auto it = h->host_w.find(n);
         return it == h->host_w.end() ? nullptr : it->second.data.data();
     };
+    const int G = 2 * m.H, R = m.R, S = m.S;
     std::vector<float> blobs((size_t)m.L * p.P * p.layer_blob_floats + p.head_blob_floats, 0.0f);
     std::vector<PipeCta> ctas;
+    long long ring_slots = 0;
     for (int l = 0; l < m.L; ++l) {
         std::string pre = "ResidualConv1DGLU_" + std::to_string(l) + "/residual_block_";
         const float *cw = Wt(pre + "causal_conv/kernel"), *cb = Wt(pre + "causal_conv/bias");
         const float *iw = Wt(pre + "cin_conv/kernel"), *ib = Wt(pre + "cin_conv/bias");
-        const float *ow = Wt(pre + "out_conv/kernel"), *ob = Wt(pre + "out_conv/bias");
-        const float *sw = Wt(pre + "skip_conv/kernel"), *sb = Wt(pre + "skip_conv/bias");
+        const float *ow = Wt(pre + "out_conv/kernel"), *sw = Wt(pre + "skip_conv/kernel");
+        std::string prv = "ResidualConv1DGLU_" + std::to_string(l - 1) + "/residual_block_";
+        const float *pob = l > 0 ? Wt(prv + "out_conv/bias") : nullptr, *psb = l > 0 ? Wt(prv + "skip_conv/bias") : nullptr;
+        const float *f = Wt("input_convolution/kernel"), *fbb = Wt("input_convolution/bias");
         for (int q = 0; q < p.P; ++q) {
             PipeCta ct;
+            memset(&ct, 0, sizeof(ct));
             ct.role = 0; ct.l = l; ct.p = q;
             ct.h0 = lo(m.H, q); ct.hn = lo(m.H, q + 1) - ct.h0;
-            ct.r0 = lo(m.R, q); ct.rn = lo(m.R, q + 1) - ct.r0;
-            ct.s0 = lo(m.S, q); ct.sn = lo(m.S, q + 1) - ct.s0;
+            ct.r0 = lo(R, q); ct.rn = lo(R, q + 1) - ct.r0;
+            ct.s0 = lo(S, q); ct.sn = lo(S, q + 1) - ct.s0;
             ct.blob = (long long)(l * p.P + q) * p.layer_blob_floats;
+            ct.ring = ring_slots;
+            ring_slots += p.depth[l];
             float *b = blobs.data() + ct.blob;
-            float *Wc = b, *Wci = Wc + 2 * p.hmax * p.KCs, *Wos = Wci + 2 * p.hmax * p.KIs;
-            float *bconv = Wos + (p.rmax + p.smax) * p.KHs, *bcin = bconv + r4(2 * p.hmax), *bos = bcin + r4(2 * p.hmax);
+            float *Wcat = b, *Wos = Wcat + (size_t)p.NR * p.KC, *bsum = Wos + (size_t)(R + S) * p.hk, *bpo = bsum + p.NR,
+                  *bps = bpo + R, *fw = bps + r4(p.smax), *fbv = fw + R;
             for (int half = 0; half < 2; ++half)
                 for (int j = 0; j < ct.hn; ++j) {
-                    const int row = half * p.hmax + j, col = half * m.H + ct.h0 + j;   // modules.py:494 split order
-                    for (int k = 0; k < 3 * m.R; ++k) Wc[row * p.KCs + k] = cw[(size_t)k * m.G + col];
-                    for (int k = 0; k < m.cin; ++k) Wci[row * p.KIs + k] = iw[(size_t)k * m.G + col];
-                    bconv[row] = cb ? cb[col] : 0.0f;
-                    bcin[row] = ib ? ib[col] : 0.0f;
+                    const int row = half * p.hq + j, col = half * m.H + ct.h0 + j;   // modules.py:494 split order
+                    float *w = Wcat + (size_t)row * p.KC;
+                    for (int k = 0; k < 2 * R; ++k) w[k] = cw[(size_t)k * G + col];
+                    for (int k = 0; k < m.cin; ++k) w[2 * R + k] = iw[(size_t)k * G + col];
+                    for (int k = 0; k < R; ++k) w[2 * R + m.cin + k] = cw[(size_t)(2 * R + k) * G + col];
+                    bsum[row] = (cb ? cb[col] : 0.0f) + (ib ? ib[col] : 0.0f);
                 }
-            for (int j = 0; j < ct.rn; ++j) {
-                for (int k = 0; k < m.H; ++k) Wos[j * p.KHs + k] = ow[(size_t)k * m.R + ct.r0 + j];
-                bos[j] = ob ? ob[ct.r0 + j] : 0.0f;
-            }
-            for (int j = 0; j < ct.sn; ++j) {
-                for (int k = 0; k < m.H; ++k) Wos[(p.rmax + j) * p.KHs + k] = sw[(size_t)k * m.S + ct.s0 + j];
-                bos[p.rmax + j] = sb ? sb[ct.s0 + j] : 0.0f;
-            }
+            for (int row = 0; row < R + S; ++row)
+                for (int k = 0; k < ct.hn; ++k) {
+                    const float v = row < R ? ow[(size_t)(ct.h0 + k) * R + row] : sw[(size_t)(ct.h0 + k) * S + (row - R)];
+                    Wos[((size_t)(k / 4) * (R + S) + row) * 4 + (k % 4)] = v;
+                }
+            for (int r = 0; r < R; ++r) { bpo[r] = pob ? pob[r] : 0.0f; fw[r] = f[r]; fbv[r] = fbb ? fbb[r] : 0.0f; }
+            for (int j = 0; j < ct.sn; ++j) bps[j] = psb ? psb[ct.s0 + j] : 0.0f;
             ctas.push_back(ct);
         }
     }
+    pl->ring_slots = ring_slots;
     {
         const long long hb = (long long)m.L * p.P * p.layer_blob_floats;
         float *b = blobs.data() + hb;
-        float *W1 = b, *W2 = W1 + m.S * p.KSs, *b1 = W2 + m.O * p.KSs, *b2 = b1 + r4(m.S), *fw = b2 + r4(m.O), *fb = fw + r4(m.R);
+        float *W1 = b, *W2 = W1 + (size_t)S * S, *b1 = W2 + (size_t)m.O * S, *b2 = b1 + S, *bsl = b2 + r4(m.O);
         const float *w1 = Wt("final_convolution_1/kernel"), *bb1 = Wt("final_convolution_1/bias");
         const float *w2 = Wt("final_convolution_2/kernel"), *bb2 = Wt("final_convolution_2/bias");
-        const float *f = Wt("input_convolution/kernel"), *fbb = Wt("input_convolution/bias");
-        for (int n = 0; n < m.S; ++n) {
-            for (int k = 0; k < m.S; ++k) W1[n * p.KSs + k] = w1[(size_t)k * m.S + n];
+        const float *lsb = Wt("ResidualConv1DGLU_" + std::to_string(m.L - 1) + "/residual_block_skip_conv/bias");
+        for (int n = 0; n < S; ++n) {
+            for (int k = 0; k < S; ++k) W1[(size_t)n * S + k] = w1[(size_t)k * S + n];
             b1[n] = bb1 ? bb1[n] : 0.0f;
+            bsl[n] = lsb ? lsb[n] : 0.0f;
         }
         for (int n = 0; n < m.O; ++n) {
-            for (int k = 0; k < m.S; ++k) W2[n * p.KSs + k] = w2[(size_t)k * m.O + n];
+            for (int k = 0; k < S; ++k) W2[(size_t)n * S + k] = w2[(size_t)k * m.O + n];
             b2[n] = bb2 ? bb2[n] : 0.0f;
         }
-        for (int r = 0; r < m.R; ++r) { fw[r] = f[r]; fb[r] = fbb ? fbb[r] : 0.0f; }
         for (int j = 0; j < pl->max_heads; ++j) {
             PipeCta ct;
             memset(&ct, 0, sizeof(ct));
@@ -621,8 +863,7 @@ int wn_pipe_plan(wn_handle *h) {
     p.blobs = pl->d_blobs;
     p.ctas = pl->d_ctas;
     p.abort_flag = pl->d_abort;
-    auto kern = pl->UT == 2 ? wn_loop_pipe_kernel<2> : wn_loop_pipe_kernel<1>;
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem_bytes) != cudaSuccess) {
+    if (cudaFuncSetAttribute(pipe_kernel(p.NU), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem_bytes) != cudaSuccess) {
         wn_pipe_free(h);
         h->err = std::string("pipeline engine: ") + cudaGetErrorString(cudaGetLastError());
         return -1;
@@ -633,9 +874,24 @@ int wn_pipe_plan(wn_handle *h) {
 int wn_pipe_check_abort(wn_handle *h) {   // call after the stream has been synchronised
     if (!h->pipe || !h->pipe->h_abort) return WN_OK;
     const int code = *h->pipe->h_abort;
+    if (h->pipe->d_stats && h->pipe->stats_ctas > 0 && getenv("WN_PIPE_STATS")) {   // development aid
+        std::vector<long long> st((size_t)h->pipe->stats_ctas * 8);
+        if (cudaMemcpy(st.data(), h->pipe->d_stats, st.size() * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess) {
+            FILE *f = fopen(getenv("WN_PIPE_STATS"), "a");
+            if (f) {
+                const PipeParams &q = h->pipe->prm;
+                fprintf(f, "# pipe stats: L=%d P=%d NU=%d ctas=%d  cols: cta role wait+combine ph1 gate ph2+skip commit+ph0 total items\n",
+                        q.L, q.P, q.NU, h->pipe->stats_ctas);
+                for (int i = 0; i < h->pipe->stats_ctas; ++i)
+                    fprintf(f, "%d %lld %lld %lld %lld %lld %lld %lld %lld\n", i, st[i * 8 + 7], st[i * 8 + 0], st[i * 8 + 1],
+                            st[i * 8 + 2], st[i * 8 + 3], st[i * 8 + 4], st[i * 8 + 5], st[i * 8 + 6]);
+                fclose(f);
+            }
+        }
+        h->pipe->stats_ctas = 0;
+    }
     if (code == 0) return WN_OK;
-    h->err = code == 2 ? "pipeline engine: stale dilation tap (protocol error)"
-                       : "pipeline engine: watchdog - a CTA waited too long for a peer";
+    h->err = "pipeline engine: watchdog - a CTA waited too long for a peer";
     return WN_ERR_WATCHDOG;
 }
 
@@ -648,11 +904,12 @@ int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, con
     p.NH = std::min(p.NG, pl->max_heads);
     p.B = B; p.T = T;
     p.c_up = c_up; p.noise = noise; p.teacher = teacher; p.audio = audio; p.raw = raw;
-    // mailboxes: X (per layer, ring depth 2d+1) | Z | S, all 8-byte {value, tag} words, zeroed (tag 0 = empty)
-    size_t words = 0;
-    for (int l = 0; l < p.L; ++l) { p.xoff[l] = (long long)words; words += (size_t)p.NG * p.depth[l] * p.NU * p.R; }
-    const size_t zoff = words; words += (size_t)p.L * p.NG * p.NU * p.H;
-    const size_t soff = words; words += (size_t)p.L * p.NG * p.NU * p.S;
+    // mailboxes, 8-byte {value, tag} words, zeroed (tag 0 = empty), double buffered on t&1, one set per consumer stage
+    // (layers 0..L-1, head = L):  op [2][NG][P][R][NU] | xr [2][NG][R][NU] | sp [2][NG][P][S][NU] | rs [2][NG][S][NU]
+    const long long slots = 2ll * p.NG * p.NU;
+    p.op_sz = slots * p.P * p.R; p.xr_sz = slots * p.R; p.sp_sz = slots * p.P * p.S; p.rs_sz = slots * p.S;
+    const size_t stages = (size_t)p.L + 1;
+    const size_t words = stages * (size_t)(p.op_sz + p.xr_sz + p.sp_sz + p.rs_sz) + (size_t)slots;
     if (pl->mail_words < words) {
         if (pl->d_mail) cudaFree(pl->d_mail);
         pl->d_mail = nullptr; pl->mail_words = 0;
@@ -660,14 +917,30 @@ int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, con
         if (e != cudaSuccess) { h->err = std::string("pipeline mailboxes: ") + cudaGetErrorString(e); return WN_ERR_NOMEM; }
         pl->mail_words = words;
     }
-    p.xbuf = pl->d_mail; p.zbuf = pl->d_mail + zoff; p.sbuf = pl->d_mail + soff;
+    p.op = pl->d_mail; p.xr = p.op + stages * p.op_sz; p.sp = p.xr + stages * p.xr_sz; p.rs = p.sp + stages * p.sp_sz;
+    p.in = p.rs + stages * p.rs_sz;
+    // private dilation rings of the layer CTAs: [CTA][NG][2d+1][R][NU] floats (never read before written: no memset)
+    const size_t ring_floats = (size_t)pl->ring_slots * p.NG * p.R * p.NU;
+    if (pl->ring_floats < ring_floats) {
+        if (pl->d_rings) cudaFree(pl->d_rings);
+        pl->d_rings = nullptr; pl->ring_floats = 0;
+        cudaError_t e = cudaMalloc((void **)&pl->d_rings, ring_floats * sizeof(float));
+        if (e != cudaSuccess) { h->err = std::string("pipeline rings: ") + cudaGetErrorString(e); return WN_ERR_NOMEM; }
+        pl->ring_floats = ring_floats;
+    }
+    p.rings = pl->d_rings;
     WN_CUDA_TRY(h, cudaMemsetAsync(pl->d_mail, 0, words * 8, st));
     WN_CUDA_TRY(h, cudaMemsetAsync(pl->d_abort, 0, sizeof(int), st));
     const int grid = p.L * p.P + p.NH;
+    p.stats = nullptr;
+    if (getenv("WN_PIPE_STATS")) {
+        if (!pl->d_stats) cudaMalloc((void **)&pl->d_stats, sizeof(long long) * 8 * 512);
+        if (pl->d_stats) { cudaMemsetAsync(pl->d_stats, 0, sizeof(long long) * 8 * 512, st); p.stats = pl->d_stats; pl->stats_ctas = grid; }
+    }
     void *args[] = {&p};
-    const void *kern = pl->UT == 2 ? (const void *)wn_loop_pipe_kernel<2> : (const void *)wn_loop_pipe_kernel<1>;
-    WN_CUDA_TRY(h, cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(PIPE_THREADS), args, pl->smem_bytes, st));
+    WN_CUDA_TRY(h, cudaLaunchCooperativeKernel(pipe_kernel(p.NU), dim3(grid), dim3(PIPE_THREADS), args, pl->smem_bytes, st));
     h->launches++;
     WN_CUDA_TRY(h, cudaMemcpyAsync(pl->h_abort, pl->d_abort, sizeof(int), cudaMemcpyDeviceToHost, st));
     return WN_OK;
 }
+

@@ -13,7 +13,7 @@ from wavenet_vocoder.util import is_scalar_input
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'libwavenet_b200.so')
 
-WN_ABI_VERSION = 1
+WN_ABI_VERSION = 2
 MAX_UP = 8
 INPUT_TYPES = {'raw': 0, 'mulaw': 1, 'mulaw-quantize': 2}
 UP_TYPES = {'SubPixel': 0, '2D': 1, '1D': 2, 'Resize': 3, 'NearestNeighbor': 4}
@@ -40,13 +40,13 @@ class WnConfig(C.Structure):
 		('n_upsample_scales', C.c_int32), ('upsample_scales', C.c_int32 * MAX_UP),
 		('freq_axis_kernel_size', C.c_int32), ('leaky_alpha', C.c_float), ('nn_init', C.c_int32),
 		('hop_size', C.c_int32), ('gin_channels', C.c_int32), ('use_speaker_embedding', C.c_int32),
-		('n_speakers', C.c_int32), ('engine', C.c_int32)]
+		('n_speakers', C.c_int32), ('engine', C.c_int32), ('ksplit', C.c_int32)]
 
 
 class WnInfo(C.Structure):
 	_fields_ = [
 		('receptive_field', C.c_int32), ('n_params', C.c_int64), ('flops_per_sample', C.c_int64),
-		('bytes_per_sample', C.c_int64), ('weight_bytes', C.c_int64), ('engine', C.c_int32),
+		('bytes_per_sample', C.c_int64), ('weight_bytes', C.c_int64), ('engine', C.c_int32), ('ksplit', C.c_int32),
 		('pipeline_ctas', C.c_int32), ('pipeline_ctas_per_layer', C.c_int32), ('pipeline_group_size', C.c_int32),
 		('sm_count', C.c_int32), ('kernel_launches', C.c_int64),
 		('last_upsample_ms', C.c_float), ('last_loop_ms', C.c_float)]
@@ -95,7 +95,7 @@ def load_library(path=None):
 	return lib
 
 
-def config_from_hparams(hp, engine='auto'):
+def config_from_hparams(hp, engine='auto', ksplit=0):
 	cfg = WnConfig()
 	cfg.abi_version = WN_ABI_VERSION
 	cfg.input_type = INPUT_TYPES[hp.input_type]
@@ -122,6 +122,7 @@ def config_from_hparams(hp, engine='auto'):
 	cfg.use_speaker_embedding = int(hp.use_speaker_embedding)
 	cfg.n_speakers = hp.n_speakers if hp.n_speakers is not None else 0
 	cfg.engine = ENGINES[engine]
+	cfg.ksplit = int(ksplit)
 	return cfg
 
 
@@ -139,11 +140,11 @@ def _ptr(x):
 class NativeWaveNet(object):
 	"""One model on the current CUDA device (one wn_handle)."""
 
-	def __init__(self, hp, weights, engine='auto'):
+	def __init__(self, hp, weights, engine='auto', ksplit=0):
 		self.lib = load_library()
 		self.hp = hp
 		self._h = C.c_void_p()
-		cfg = config_from_hparams(hp, engine)
+		cfg = config_from_hparams(hp, engine, ksplit)
 		rc = self.lib.wn_create(C.byref(cfg), C.byref(self._h))
 		if rc != 0:
 			msg = self.lib.wn_last_error(None).decode()

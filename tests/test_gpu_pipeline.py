@@ -41,7 +41,7 @@ def _check(net, hp, w, B, Tc):
     T = Tc * hp.hop_size
     c, nz = common.cond_for(hp, B, Tc), common.noise_for(hp, T, B)
     teacher = common.teacher_for(hp, B, T)
-    co = COracle(hp, w)
+    co = COracle(hp, w, ksplit=net.info()['ksplit'])   # the plan's CTAs per layer fix the summation order
     audio, raw = net.synthesize_host(c, nz, want_raw=True)
     a_c, _, raw_c, _ = co.synthesize(c, noise=nz)
     assert np.array_equal(raw[:, 0], raw_c[:, 0]), 'first step differs'
@@ -68,8 +68,8 @@ def test_pipeline_small_variants_bit_exact(name, B):
         assert np.all(common.rel_close(raw, np.transpose(raw_np, [0, 2, 1])))
 
 
-@pytest.mark.parametrize('env', [dict(WN_PIPE_P=2), dict(WN_PIPE_P=3), dict(WN_PIPE_NU=8, WN_PIPE_UT=2),
-                                 dict(WN_PIPE_NU=2), dict(WN_PIPE_P=7, WN_PIPE_NU=6, WN_PIPE_UT=2)])
+@pytest.mark.parametrize('env', [dict(WN_PIPE_P=1), dict(WN_PIPE_P=2), dict(WN_PIPE_P=3), dict(WN_PIPE_NU=8),
+                                 dict(WN_PIPE_NU=2), dict(WN_PIPE_P=7, WN_PIPE_NU=8), dict(WN_PIPE_P=5, WN_PIPE_NU=2)])
 def test_pipeline_plans_bit_exact(env):
     hp = common.small()
     w = common.weights_for(hp)
@@ -82,8 +82,34 @@ def test_pipeline_default_config_bit_exact():
     w = common.weights_for(hp)
     net = _net(hp, w)
     info = net.info()
-    assert info['pipeline_ctas'] == 80 and info['pipeline_ctas_per_layer'] == 4
+    assert info['pipeline_ctas'] == 20 * info['pipeline_ctas_per_layer'] and info['ksplit'] == info['pipeline_ctas_per_layer']
     _check(net, hp, w, 6, 4)
+
+
+@pytest.mark.parametrize('P', [4, 7])
+def test_pipeline_default_config_plans(P):
+    hp = common.default_22k()
+    w = common.weights_for(hp)
+    net = _net(hp, w, WN_PIPE_P=P)
+    assert net.info()['ksplit'] == P
+    _check(net, hp, w, 5, 3)
+
+
+def test_generic_and_pipeline_agree_for_the_same_ksplit():
+    """wn_config.ksplit pins the summation order: the two engines then return identical bits."""
+    from wavenet_vocoder._native import NativeWaveNet
+    hp = common.small()
+    w = common.weights_for(hp)
+    B, Tc = 5, 3
+    T = Tc * hp.hop_size
+    c, nz = common.cond_for(hp, B, Tc), common.noise_for(hp, T, B)
+    a_p, r_p = NativeWaveNet(hp, w, engine='pipeline', ksplit=3).synthesize_host(c, nz, want_raw=True)
+    gen = NativeWaveNet(hp, w, engine='generic', ksplit=3)
+    assert gen.info()['ksplit'] == 3
+    a_g, r_g = gen.synthesize_host(c, nz, want_raw=True)
+    assert np.array_equal(a_p, a_g) and np.array_equal(r_p, r_g)
+    a_1 = NativeWaveNet(hp, w, engine='generic').synthesize_host(c, nz)
+    assert np.allclose(a_1[:, :50], a_g[:, :50], atol=1e-4)   # a different order, the same function
 
 
 def test_pipeline_repeated_calls_and_long_dilation_history():
@@ -96,7 +122,7 @@ def test_pipeline_repeated_calls_and_long_dilation_history():
     c, nz = common.cond_for(hp, B, Tc), common.noise_for(hp, T, B)
     a1 = net.synthesize_host(c, nz)
     a2 = net.synthesize_host(c, nz)
-    a_c = COracle(hp, w).synthesize(c, noise=nz)[0]
+    a_c = COracle(hp, w, ksplit=net.info()['ksplit']).synthesize(c, noise=nz)[0]
     assert np.array_equal(a1, a_c) and np.array_equal(a2, a_c)
 
 
