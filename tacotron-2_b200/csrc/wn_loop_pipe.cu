@@ -45,7 +45,7 @@ namespace {
 constexpr int PIPE_THREADS = 256;
 constexpr int LANES = 16;            // partial sums per dot16
 constexpr int MAX_P = 8;             // CTAs per layer
-constexpr int MAX_PF = 4;            // 16-byte prefetch loads per thread for the two older taps
+constexpr int MAX_PF = 2;            // 16-byte prefetch loads per thread for the two older taps
 constexpr unsigned SPIN_LIMIT = 1u << 22;
 
 struct PipeCta {
@@ -112,40 +112,87 @@ __device__ __forceinline__ int poll_pair(const unsigned long long *src, unsigned
 __device__ __forceinline__ int round4(int v) { return (v + 3) & ~3; }
 
 // ---- the fp32 inner products ---------------------------------------------------------------------------------
-// Operands in shared memory are "k-major": xs[k][NU] (utterances fastest), so one 16-byte load brings the same k
-// for 4 utterances.  Weights are row-major [row][K].
+// dot16 operands in shared memory: element k = 4c+e of utterance u sits at xs_pos(k, u) = ((e*NU/4 + u/4)*K4 + c)*4 + u%4,
+// i.e. one 16-byte word holds the same k for 4 utterances and, for fixed e, the words of consecutive chunks c are
+// contiguous - the 16 lanes of a dot16 (lane = c % 16) then read 256 contiguous bytes, free of bank conflicts.
+// Weights are row-major [row][K].
 //
-// mac_lane: the thread owns a tile of 4 rows x NU utterances and the float4 chunks c = first, first+16, ... < c_end of K
-// (lane = c % 16): acc[i*NU+u] += sum_e w[4q+i][4c+e] * xs[4c+e][u], e ascending, c ascending - one partial of dot16.
+// All multiply-adds are issued as FFMA2 (fma.rn.f32x2: two independent IEEE round-to-nearest fp32 fmas per
+// instruction, the form in which sm_100 reaches its fp32 peak): the pair is two UTTERANCES of the same output, the
+// weight is the scalar broadcast operand.  Each lane of each fma is exactly fmaf(), so the bits equal the oracle's.
 template <int NU>
-__device__ __forceinline__ void mac_lane(float (&acc)[4 * NU], const float4 *__restrict__ w4 /* row 4q, chunk 0 */,
-                                         int KC4, const float *__restrict__ xs, int c_first, int c_end) {
-#pragma unroll 2
-    for (int c = c_first; c < c_end; c += LANES) {
-        float4 w[4];
+__device__ __forceinline__ int xs_pos(int k, int u, int K4) {
+    return (((k & 3) * (NU / 4) + (u >> 2)) * K4 + (k >> 2)) * 4 + (u & 3);
+}
+
+__device__ __forceinline__ float2 ffma2(float2 a, float w, float2 c) {
+    float2 d;
+    const float2 ww = make_float2(w, w);   // ptxas folds the duplicate into FFMA2's scalar-broadcast operand
+    asm("fma.rn.f32x2 %0, %1, %2, %3;"
+        : "=l"(*reinterpret_cast<unsigned long long *>(&d))
+        : "l"(*reinterpret_cast<const unsigned long long *>(&a)),
+          "l"(*reinterpret_cast<const unsigned long long *>(&ww)),
+          "l"(*reinterpret_cast<const unsigned long long *>(&c)));
+    return d;
+}
+
+template <int NU, int ROWS>
+struct MacOps {
+    float4 w[ROWS];
+    float4 x[NU];   // [e][u4]
+};
+
+template <int NU, int ROWS>
+__device__ __forceinline__ void mac_fma(float2 (&acc)[ROWS * NU / 2], const MacOps<NU, ROWS> &o) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) w[i] = w4[i * KC4 + c];
-        const float *xk = xs + (size_t)c * 4 * NU;
+    for (int e = 0; e < 4; ++e) {
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            float xv[NU];
-            if (NU == 2) {
-                const float2 t = *reinterpret_cast<const float2 *>(xk + e * NU);
-                xv[0] = t.x; xv[1] = t.y;
-            } else {
+        for (int i = 0; i < ROWS; ++i) {
+            const float wv = e == 0 ? o.w[i].x : (e == 1 ? o.w[i].y : (e == 2 ? o.w[i].z : o.w[i].w));
 #pragma unroll
-                for (int u4 = 0; u4 < NU / 4; ++u4) {
-                    const float4 t = *reinterpret_cast<const float4 *>(xk + e * NU + u4 * 4);
-                    xv[u4 * 4 + 0] = t.x; xv[u4 * 4 + 1] = t.y; xv[u4 * 4 + 2] = t.z; xv[u4 * 4 + 3] = t.w;
-                }
-            }
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float wv = e == 0 ? w[i].x : (e == 1 ? w[i].y : (e == 2 ? w[i].z : w[i].w));
-#pragma unroll
-                for (int u = 0; u < NU; ++u) acc[i * NU + u] = __fmaf_rn(xv[u], wv, acc[i * NU + u]);
+            for (int u4 = 0; u4 < NU / 4; ++u4) {
+                const float4 t = o.x[e * (NU / 4) + u4];
+                acc[i * (NU / 2) + 2 * u4] = ffma2(make_float2(t.x, t.y), wv, acc[i * (NU / 2) + 2 * u4]);
+                acc[i * (NU / 2) + 2 * u4 + 1] = ffma2(make_float2(t.z, t.w), wv, acc[i * (NU / 2) + 2 * u4 + 1]);
             }
         }
+    }
+}
+
+// mac_lane: the thread owns a tile of ROWS rows x NU utterances and the float4 chunks c = c_first, c_first+16, ... < c_end
+// of K (lane = c % 16): acc[row i][utt u] += sum_e w[i][4c+e] * xs[4c+e][u], e ascending, c ascending - one partial
+// of dot16.  Loads of the next chunk are issued before the fmas of the current one (register double buffer).
+template <int NU, int ROWS>
+__device__ __forceinline__ void mac_lane(float2 (&acc)[ROWS * NU / 2], const float4 *__restrict__ w4 /* first row, chunk 0 */,
+                                         int KC4, const float *__restrict__ xs, int c_first, int c_end) {
+    const float4 *x4 = reinterpret_cast<const float4 *>(xs);
+    auto load = [&](MacOps<NU, ROWS> &o, int c) {
+#pragma unroll
+        for (int i = 0; i < ROWS; ++i) o.w[i] = w4[i * KC4 + c];
+#pragma unroll
+        for (int j = 0; j < NU; ++j) o.x[j] = x4[j * KC4 + c];
+    };
+    int c = c_first;
+    if (c >= c_end) return;
+    if (ROWS * NU > 16) {   // large tiles: one operand buffer (registers)
+        for (; c < c_end; c += LANES) {
+            MacOps<NU, ROWS> a;
+            load(a, c);
+            mac_fma<NU, ROWS>(acc, a);
+        }
+        return;
+    }
+    MacOps<NU, ROWS> a, b;
+    load(a, c);
+    for (;;) {
+        const int c1 = c + LANES;
+        if (c1 < c_end) load(b, c1);
+        mac_fma<NU, ROWS>(acc, a);
+        if (c1 >= c_end) break;
+        c = c1 + LANES;
+        if (c < c_end) load(a, c);
+        mac_fma<NU, ROWS>(acc, b);
+        if (c >= c_end) break;
     }
 }
 
@@ -184,37 +231,38 @@ __device__ __forceinline__ int reduce16_base(int lane) {
     }
     return base;
 }
+// float2 accumulators (row i, utterance pair) -> flat values v = i*NU + u for reduce16
+template <int NV>
+__device__ __forceinline__ void unpack2(const float2 (&acc)[NV / 2], float (&a)[NV]) {
+#pragma unroll
+    for (int i = 0; i < NV / 2; ++i) { a[2 * i] = acc[i].x; a[2 * i + 1] = acc[i].y; }
+}
 
-// chain_tile: 4 rows x NU utterances, K sequential in-thread (the blocked chains of the out / skip 1x1s).
+// chain_tile: ROWS rows x NU utterances, K sequential in-thread (the blocked chains of the out / skip 1x1s).
 // w4t is chunk-major: w4t[c * nrows + row] holds W[row][4c..4c+3]; the thread's rows are row0 + i*rstride.
-template <int NU>
-__device__ __forceinline__ void chain_tile(float (&acc)[4 * NU], const float4 *__restrict__ w4t, int nrows, int row0,
+// zs is k-major [k][NU]; every lane reads the same words (broadcast).
+template <int NU, int ROWS>
+__device__ __forceinline__ void chain_tile(float2 (&acc)[ROWS * NU / 2], const float4 *__restrict__ w4t, int nrows, int row0,
                                            int rstride, const float *__restrict__ zs, int K4) {
-    for (int c = 0; c < K4; ++c) {
-        float4 w[4];
+    const float4 *z4 = reinterpret_cast<const float4 *>(zs);
+    auto load = [&](MacOps<NU, ROWS> &o, int c) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) w[i] = w4t[c * nrows + row0 + i * rstride];
-        const float *zk = zs + (size_t)c * 4 * NU;
+        for (int i = 0; i < ROWS; ++i) o.w[i] = w4t[c * nrows + row0 + i * rstride];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            float zv[NU];
-            if (NU == 2) {
-                const float2 t = *reinterpret_cast<const float2 *>(zk + e * NU);
-                zv[0] = t.x; zv[1] = t.y;
-            } else {
-#pragma unroll
-                for (int u4 = 0; u4 < NU / 4; ++u4) {
-                    const float4 t = *reinterpret_cast<const float4 *>(zk + e * NU + u4 * 4);
-                    zv[u4 * 4 + 0] = t.x; zv[u4 * 4 + 1] = t.y; zv[u4 * 4 + 2] = t.z; zv[u4 * 4 + 3] = t.w;
-                }
-            }
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float wv = e == 0 ? w[i].x : (e == 1 ? w[i].y : (e == 2 ? w[i].z : w[i].w));
-#pragma unroll
-                for (int u = 0; u < NU; ++u) acc[i * NU + u] = __fmaf_rn(zv[u], wv, acc[i * NU + u]);
-            }
-        }
+        for (int j = 0; j < NU; ++j) o.x[j] = z4[c * NU + j];
+    };
+    if (K4 <= 0) return;
+    MacOps<NU, ROWS> a, b;
+    load(a, 0);
+    int c = 0;
+    for (;;) {
+        if (c + 1 < K4) load(b, c + 1);
+        mac_fma<NU, ROWS>(acc, a);
+        if (c + 1 >= K4) break;
+        c += 2;
+        if (c < K4) load(a, c);
+        mac_fma<NU, ROWS>(acc, b);
+        if (c >= K4) break;
     }
 }
 
@@ -244,6 +292,27 @@ __device__ float pipe_sample_mol(const PipeParams &P, const float *out, int ostr
     return x < 1.0f ? x : 1.0f;
 }
 
+// Poll up to MAX_P+1 pairs of {value,tag} words at once (all loads in flight together, re-issued only for the
+// ones still pending) until every selected pair carries `tag`.  mask bit i selects src[i].
+__device__ __forceinline__ int poll_set(const unsigned long long *const (&src)[MAX_P + 1], unsigned mask, unsigned tag,
+                                        unsigned long long (&wa)[MAX_P + 1], unsigned long long (&wb)[MAX_P + 1],
+                                        int *abort_flag) {
+    unsigned pending = mask, spins = 0;
+    while (pending) {
+#pragma unroll
+        for (int i = 0; i <= MAX_P; ++i)
+            if (pending & (1u << i)) ld_ll2(src[i], wa[i], wb[i]);
+#pragma unroll
+        for (int i = 0; i <= MAX_P; ++i)
+            if ((pending & (1u << i)) && ll_tag(wa[i]) == tag && ll_tag(wb[i]) == tag) pending &= ~(1u << i);
+        if (pending && (++spins & 0x3ffu) == 0) {
+            if (*(volatile int *)abort_flag) return 1;
+            if (spins > SPIN_LIMIT) { atomicExch(abort_flag, 1); return 1; }
+        }
+    }
+    return 0;
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // layer CTA: owns gate channels [h0,h1) of residual layer l  (ResidualConv1DGLU.incremental_step, modules.py:468-521)
 // ---------------------------------------------------------------------------------------------------------------
@@ -263,7 +332,7 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
     float *bps = bpo + R;                                // [round4(smax)] skip-conv bias of layer l-1, my slice
     float *fw = bps + round4(P.smax);                    // [R] first conv (layer 0 only)
     float *fb = fw + R;                                  // [R]
-    float *xc = smem + P.layer_blob_floats;              // [KC][NU]      x(t-2d) | x(t-d) | c(t) | x(t), k-major
+    float *xc = smem + P.layer_blob_floats;              // [KC x NU]     x(t-2d) | x(t-d) | c(t) | x(t) in xs_pos order
     float *pre = xc + (size_t)KC * NU;                   // [NR][NU]
     float *zs = pre + (size_t)NR * NU;                   // [hk][NU]
     {
@@ -274,73 +343,83 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
     }
     __syncthreads();
 
-    float *ring = P.rings + (size_t)me.ring * NG * R * NU;   // [NG][depth][R][NU]; me.ring counts ring slots
-    const int o_cur = 2 * R + P.cin;
+    float *ring = P.rings + (size_t)me.ring * NG * R * NU;   // [NG][depth][R x NU]; me.ring counts ring slots
+    const int o_cur4 = (2 * R + P.cin) / 4, R4 = R / 4;
     // consumer-side mailboxes of this layer (stage l) and producer-side ones (stage l+1)
     const unsigned long long *op_in = P.op + (long long)l * P.op_sz, *xr_in = P.xr + (long long)l * P.xr_sz;
     const unsigned long long *sp_in = P.sp + (long long)l * P.sp_sz, *rs_in = P.rs + (long long)l * P.rs_sz;
     unsigned long long *op_out = P.op + (long long)(l + 1) * P.op_sz, *xr_out = P.xr + (long long)(l + 1) * P.xr_sz;
     unsigned long long *sp_out = P.sp + (long long)(l + 1) * P.sp_sz, *rs_out = P.rs + (long long)(l + 1) * P.rs_sz;
 
-    // ---- thread roles -------------------------------------------------------------------------------------
+    // ---- thread roles (everything that only depends on tid is computed once, outside the time loop) -------
     const int lane = tid & (LANES - 1), q = tid / LANES;   // dot16: row quad q, partial `lane`
     const bool has_q = q < P.NQ;
     const bool warp_has_q = (tid / 32) * 2 < P.NQ;
     const float4 *wq = reinterpret_cast<const float4 *>(Wcat) + (size_t)(has_q ? 4 * q : 0) * KC4;
     const int c1_first = C0 + ((lane - C0) % LANES + LANES) % LANES;   // first chunk >= C0 owned by this lane
     const int rbase = reduce16_base<NV>(lane);
-    const int NT2 = (R + S) / 4;                            // threads of the blocked chains (4 rows each)
+    const int NT2 = (R + S) / 2;                            // threads of the blocked chains (2 rows each)
     const bool has_t2 = tid < NT2;
     const int NT2r = (NT2 + 31) & ~31;
     const int hbase = (NT2r <= PIPE_THREADS - 64) ? NT2r : 0;   // threads [hbase, 256) carry the skip sum meanwhile
     const int hthreads = PIPE_THREADS - hbase;
-
-    // ---- register prefetch of the older taps and the conditioning column of the NEXT work item -------------
+    // D task of this thread (first loop trip): mailbox row m (e-major: m = (r%4)*R/4 + r/4), utterance pair up
+    const int d_m = tid / NP, d_up = tid - d_m * NP, d_e = d_m / R4, d_cr = d_m - d_e * R4;
+    // prefetch / commit slots
     const int n_tap16 = 2 * R * NU / 4;                     // float4 loads for both taps
     const int n_c16 = NU * (P.cin / 4);
+    int pf_tap[MAX_PF], pf_rem[MAX_PF], pf_dst[MAX_PF];
+#pragma unroll
+    for (int k = 0; k < MAX_PF; ++k) {
+        const int qf = tid + k * PIPE_THREADS, per = n_tap16 / 2;
+        pf_tap[k] = -1; pf_rem[k] = 0; pf_dst[k] = 0;
+        if (qf < n_tap16) {   // a ring slot is [e*NU/4 + u/4][R/4][4]: segment `seg` of tap `tap` -> chunks tap*R/4.. of xc
+            pf_tap[k] = qf / per;
+            pf_rem[k] = qf - pf_tap[k] * per;
+            const int seg = pf_rem[k] / R4, cr = pf_rem[k] - seg * R4;
+            pf_dst[k] = seg * KC4 + pf_tap[k] * R4 + cr;
+        }
+    }
+    const int pc_u = tid / (P.cin / 4), pc_c4 = tid - pc_u * (P.cin / 4);
+
+    // ---- register prefetch of the older taps and the conditioning column of the NEXT work item -------------
     float4 pft[MAX_PF], pfc;
     auto prefetch = [&](int g, int t) {
 #pragma unroll
         for (int k = 0; k < MAX_PF; ++k) {
-            const int qf = tid + k * PIPE_THREADS;
             pft[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (qf < n_tap16) {
-                const int per = n_tap16 / 2;
-                const int tap = qf / per, rem = qf - tap * per;
-                const int tt = t - (2 - tap) * d;
+            if (pf_tap[k] >= 0) {
+                const int tt = t - (2 - pf_tap[k]) * d;
                 if (tt >= 0)
-                    pft[k] = __ldcg(reinterpret_cast<const float4 *>(ring + (size_t)(g * depth + tt % depth) * R * NU) + rem);
+                    pft[k] = __ldcg(reinterpret_cast<const float4 *>(ring + (size_t)(g * depth + tt % depth) * R * NU) + pf_rem[k]);
             }
         }
         pfc = make_float4(0.f, 0.f, 0.f, 0.f);
         if (tid < n_c16) {
-            const int u = tid / (P.cin / 4), c4 = tid - u * (P.cin / 4);
-            const int b = g * NU + u;
-            if (b < P.B) pfc = __ldg(reinterpret_cast<const float4 *>(P.c_up + ((long long)b * T + t) * P.cin) + c4);
+            const int b = g * NU + pc_u;
+            if (b < P.B) pfc = __ldg(reinterpret_cast<const float4 *>(P.c_up + ((long long)b * T + t) * P.cin) + pc_c4);
         }
     };
     auto commit = [&]() {
 #pragma unroll
-        for (int k = 0; k < MAX_PF; ++k) {
-            const int qf = tid + k * PIPE_THREADS;
-            if (qf < n_tap16) reinterpret_cast<float4 *>(xc)[qf] = pft[k];
-        }
+        for (int k = 0; k < MAX_PF; ++k)
+            if (pf_tap[k] >= 0) reinterpret_cast<float4 *>(xc)[pf_dst[k]] = pft[k];
         if (tid < n_c16) {
-            const int u = tid / (P.cin / 4), c4 = tid - u * (P.cin / 4);
-            float *dst = xc + (size_t)(2 * R + 4 * c4) * NU + u;
-            dst[0] = pfc.x; dst[NU] = pfc.y; dst[2 * NU] = pfc.z; dst[3 * NU] = pfc.w;
+            const int k = 2 * R + 4 * pc_c4;
+            xc[xs_pos<NU>(k, pc_u, KC4)] = pfc.x; xc[xs_pos<NU>(k + 1, pc_u, KC4)] = pfc.y;
+            xc[xs_pos<NU>(k + 2, pc_u, KC4)] = pfc.z; xc[xs_pos<NU>(k + 3, pc_u, KC4)] = pfc.w;
         }
     };
 
-    float acc[NV];
+    float2 acc[NV / 2];
     auto phase0 = [&]() {   // everything that does not need x_l(t): taps t-2d, t-d and the conditioning column
 #pragma unroll
-        for (int i = 0; i < NV; ++i) acc[i] = 0.0f;
-        if (has_q) mac_lane<NU>(acc, wq, KC4, xc, lane, C0);
+        for (int i = 0; i < NV / 2; ++i) acc[i] = make_float2(0.0f, 0.0f);
+        if (has_q) mac_lane<NU, 4>(acc, wq, KC4, xc, lane, C0);
     };
 
     int bad = 0;
-    long long st_c[6] = {0, 0, 0, 0, 0, 0};
+    long long st_c[6] = {0, 0, 0, 0, 0, 0}, st_d[6] = {0, 0, 0, 0, 0, 0};
     const bool do_stats = P.stats != nullptr && tid == 0;
     const long long st_begin = clock64();
 
@@ -356,8 +435,12 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
         const long long slot_g = (long long)(t & 1) * NG + g;
         const long long c0 = do_stats ? clock64() : 0;
         // ---- D: wait for the inputs of (t, g) and rebuild x_l(t) ----------------------------------------------
+        // mailbox rows are stored e-major (position m = (r%4)*R/4 + r/4), so that consecutive threads read
+        // consecutive mailbox words AND write consecutive words of xc and of the ring
         for (int task = tid; task < R * NP; task += PIPE_THREADS) {
-            const int r = task / NP, up = task - r * NP;
+            int m = d_m, up = d_up, e = d_e, cr = d_cr;
+            if (task != tid) { m = task / NP; up = task - m * NP; e = m / R4; cr = m - e * R4; }
+            const int r = 4 * cr + e;
             float x0, x1;
             if (l == 0) {   // first_conv.incremental_step (wavenet.py:826) on the value the head fed back
                 float s0, s1;
@@ -369,22 +452,9 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
                 const unsigned long long *src[MAX_P + 1];
 #pragma unroll
                 for (int pp = 0; pp < MAX_P; ++pp)
-                    src[pp] = op_in + ((slot_g * PP + (pp < PP ? pp : 0)) * R + r) * NU + 2 * up;
-                src[MAX_P] = xr_in + (slot_g * R + r) * NU + 2 * up;
-                unsigned pending = ((1u << PP) - 1u) | (1u << MAX_P);
-                unsigned spins = 0;
-                while (pending) {
-#pragma unroll
-                    for (int pp = 0; pp <= MAX_P; ++pp)
-                        if (pending & (1u << pp)) ld_ll2(src[pp], wa[pp], wb[pp]);
-#pragma unroll
-                    for (int pp = 0; pp <= MAX_P; ++pp)
-                        if ((pending & (1u << pp)) && ll_tag(wa[pp]) == tag && ll_tag(wb[pp]) == tag) pending &= ~(1u << pp);
-                    if (pending && (++spins & 0x3ffu) == 0) {
-                        if (*(volatile int *)P.abort_flag) { bad = 1; break; }
-                        if (spins > SPIN_LIMIT) { atomicExch(P.abort_flag, 1); bad = 1; break; }
-                    }
-                }
+                    src[pp] = op_in + ((slot_g * PP + (pp < PP ? pp : 0)) * R + m) * NU + 2 * up;
+                src[MAX_P] = xr_in + (slot_g * R + m) * NU + 2 * up;
+                bad |= poll_set(src, ((1u << PP) - 1u) | (1u << MAX_P), tag, wa, wb, P.abort_flag);
                 float y0 = ll_val(wa[0]), y1 = ll_val(wb[0]);
 #pragma unroll
                 for (int pp = 1; pp < MAX_P; ++pp)
@@ -394,79 +464,85 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
                 x0 = P.residual_legacy ? __fmul_rn(y0, WN_SQRT_HALF) : y0;
                 x1 = P.residual_legacy ? __fmul_rn(y1, WN_SQRT_HALF) : y1;
             }
-            *reinterpret_cast<float2 *>(xc + (size_t)(o_cur + r) * NU + 2 * up) = make_float2(x0, x1);
-            __stcg(reinterpret_cast<float2 *>(ring + ((size_t)(g * depth + t % depth) * R + r) * NU + 2 * up),
-                   make_float2(x0, x1));
+            // the residual input x_l(t), slice [r0,r1), travels with the partial sums (the consumer adds it)
+            if (!last && r >= me.r0 && r < me.r0 + me.rn) st_ll2(xr_out + (slot_g * R + m) * NU + 2 * up, x0, x1, tag);
+            const int seg = e * (NU / 4) + (up >> 1);
+            *reinterpret_cast<float2 *>(xc + (size_t)(seg * KC4 + o_cur4 + cr) * 4 + 2 * (up & 1)) = make_float2(x0, x1);
+            __stcg(reinterpret_cast<float2 *>(ring + (size_t)(g * depth + t % depth) * R * NU +
+                                              (size_t)(seg * R4 + cr) * 4 + 2 * (up & 1)), make_float2(x0, x1));
         }
         if (__syncthreads_or(bad)) return;                                                           // (1)
         const long long c1 = do_stats ? clock64() : 0;
-        // the residual input x_l(t), slice [r0,r1), travels with the partial sums (the consumer adds it)
-        if (!last)
-            for (int task = tid; task < me.rn * NP; task += PIPE_THREADS) {
-                const int r = me.r0 + task / NP, up = task % NP;
-                const float2 v = *reinterpret_cast<const float2 *>(xc + (size_t)(o_cur + r) * NU + 2 * up);
-                st_ll2(xr_out + (slot_g * R + r) * NU + 2 * up, v.x, v.y, tag);
-            }
         int g2 = g + 1, t2 = t;
         if (g2 == NG) { g2 = 0; t2 = t + 1; }
         if (t2 < T) prefetch(g2, t2);   // ring slots of (t2 - d, g2) were written in an earlier item or just above
+        const long long e0 = do_stats ? clock64() : 0;
         // ---- E: current tap, tree reduction, bias (modules.py:294-297, :497-501) ----------------------------
         if (warp_has_q) {   // warp-uniform: the butterfly shuffles need every lane of the warp
-            if (has_q) mac_lane<NU>(acc, wq, KC4, xc, c1_first, KC4);
-            reduce16<NV>(acc, lane);
+            if (has_q) mac_lane<NU, 4>(acc, wq, KC4, xc, c1_first, KC4);
+            const long long e1 = do_stats ? clock64() : 0;
+            float a[NV];
+            unpack2<NV>(acc, a);
+            reduce16<NV>(a, lane);
             if (has_q) {
 #pragma unroll
                 for (int i = 0; i < (NV >= LANES ? NV / LANES : 1); ++i) {
                     const int v = rbase + i, row = 4 * q + v / NU, u = v % NU;
-                    pre[(size_t)row * NU + u] = __fadd_rn(acc[i], bsum[row]);
+                    pre[(size_t)row * NU + u] = __fadd_rn(a[i], bsum[row]);
                 }
             }
+            if (do_stats) { const long long e2 = clock64(); st_d[0] += e0 - c1; st_d[1] += e1 - e0; st_d[2] += e2 - e1; }
         }
         __syncthreads();                                                                             // (2)
         const long long c2 = do_stats ? clock64() : 0;
-        // ---- F: gate (modules.py:510) --------------------------------------------------------------------------
-        for (int i = tid; i < hn * NU; i += PIPE_THREADS) {
-            const int j = i / NU, u = i - j * NU;
-            zs[(size_t)j * NU + u] = __fmul_rn(wn_tanhf(pre[(size_t)j * NU + u]), wn_sigmoidf(pre[(size_t)(hq + j) * NU + u]));
+        // ---- F: gate (modules.py:510): even lane tanh, odd lane sigmoid, one shuffle -------------------------
+        for (int base = 0; base < 2 * hn * NU; base += PIPE_THREADS) {
+            const int i = base + tid, v = i >> 1;
+            float a = 0.0f;
+            if (i < 2 * hn * NU) a = (i & 1) ? wn_sigmoidf(pre[(size_t)hq * NU + v]) : wn_tanhf(pre[v]);
+            const float o = __shfl_xor_sync(0xffffffffu, a, 1);
+            if (i < 2 * hn * NU && !(i & 1)) zs[v] = __fmul_rn(a, o);
         }
         __syncthreads();                                                                             // (3)
         const long long c3 = do_stats ? clock64() : 0;
         // ---- G: my column block of the out / skip 1x1s -> partial sums for layer l+1 / the head ---------------
         if (has_t2) {
-            float a2[NV];
+            float2 a2[NU];
 #pragma unroll
-            for (int i = 0; i < NV; ++i) a2[i] = 0.0f;
-            chain_tile<NU>(a2, reinterpret_cast<const float4 *>(Wos), R + S, tid, NT2, zs, hk / 4);
+            for (int i = 0; i < NU; ++i) a2[i] = make_float2(0.0f, 0.0f);
+            chain_tile<NU, 2>(a2, reinterpret_cast<const float4 *>(Wos), R + S, tid, NT2, zs, hk / 4);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < 2; ++i) {
                 const int row = tid + i * NT2;
                 unsigned long long *dst;
                 if (row < R) {
                     if (last) continue;
-                    dst = op_out + ((slot_g * PP + me.p) * R + row) * NU;
+                    dst = op_out + ((slot_g * PP + me.p) * R + (row & 3) * R4 + (row >> 2)) * NU;
                 } else {
                     dst = sp_out + ((slot_g * PP + me.p) * S + (row - R)) * NU;
                 }
 #pragma unroll
-                for (int up = 0; up < NP; ++up) st_ll2(dst + 2 * up, a2[i * NU + 2 * up], a2[i * NU + 2 * up + 1], tag);
+                for (int up = 0; up < NP; ++up) st_ll2(dst + 2 * up, a2[i * NP + up].x, a2[i * NP + up].y, tag);
             }
         }
         // ---- H: running skip sum through layer l-1, my slice (wavenet.py:833-836), sent to (l+1, p) / the head ---
         if (l >= 1 && tid >= hbase) {
             for (int task = tid - hbase; task < me.sn * NP; task += hthreads) {
                 const int cl = task / NP, up = task - cl * NP, c = me.s0 + cl;
-                float s0 = 0.f, s1 = 0.f;
-#pragma unroll 1
-                for (int pp = 0; pp < PP; ++pp) {
-                    float v0, v1;
-                    bad |= poll_pair(sp_in + ((slot_g * PP + pp) * S + c) * NU + 2 * up, tag, v0, v1, P.abort_flag);
-                    if (pp == 0) { s0 = v0; s1 = v1; } else { s0 = __fadd_rn(s0, v0); s1 = __fadd_rn(s1, v1); }
-                }
+                unsigned long long wa[MAX_P + 1], wb[MAX_P + 1];
+                const unsigned long long *src[MAX_P + 1];
+#pragma unroll
+                for (int pp = 0; pp < MAX_P; ++pp)
+                    src[pp] = sp_in + ((slot_g * PP + (pp < PP ? pp : 0)) * S + c) * NU + 2 * up;
+                src[MAX_P] = rs_in + (slot_g * S + c) * NU + 2 * up;
+                bad |= poll_set(src, ((1u << PP) - 1u) | (l >= 2 ? (1u << MAX_P) : 0u), tag, wa, wb, P.abort_flag);
+                float s0 = ll_val(wa[0]), s1 = ll_val(wb[0]);
+#pragma unroll
+                for (int pp = 1; pp < MAX_P; ++pp)
+                    if (pp < PP) { s0 = __fadd_rn(s0, ll_val(wa[pp])); s1 = __fadd_rn(s1, ll_val(wb[pp])); }
                 s0 = __fadd_rn(s0, bps[cl]); s1 = __fadd_rn(s1, bps[cl]);
                 if (l >= 2) {
-                    float v0, v1;
-                    bad |= poll_pair(rs_in + (slot_g * S + c) * NU + 2 * up, tag, v0, v1, P.abort_flag);
-                    s0 = __fadd_rn(v0, s0); s1 = __fadd_rn(v1, s1);
+                    s0 = __fadd_rn(ll_val(wa[MAX_P]), s0); s1 = __fadd_rn(ll_val(wb[MAX_P]), s1);
                     if (P.legacy) { s0 = __fmul_rn(s0, WN_SQRT_HALF); s1 = __fmul_rn(s1, WN_SQRT_HALF); }
                 }
                 st_ll2(rs_out + (slot_g * S + c) * NU + 2 * up, s0, s1, tag);
@@ -475,8 +551,11 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
         const long long c4 = do_stats ? clock64() : 0;
         // ---- next item: older taps + conditioning into shared memory, then its x(t)-independent part ------------
         if (t2 < T) commit();
+        const long long f0 = do_stats ? clock64() : 0;
         if (__syncthreads_or(bad)) return;                                                           // (4)
+        const long long f1 = do_stats ? clock64() : 0;
         if (t2 < T) phase0();
+        if (do_stats) { st_d[3] += f0 - c4; st_d[4] += f1 - f0; st_d[5] += clock64() - f1; }
         if (do_stats) {
             const long long c5 = clock64();
             st_c[0] += c1 - c0; st_c[1] += c2 - c1; st_c[2] += c3 - c2; st_c[3] += c4 - c3; st_c[4] += c5 - c4;
@@ -484,26 +563,10 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
         g = g2; t = t2;
     }
     if (do_stats) {
-        long long *o = P.stats + (long long)blockIdx.x * 8;
+        long long *o = P.stats + (long long)blockIdx.x * 16;
         for (int i = 0; i < 5; ++i) o[i] = st_c[i];
         o[5] = clock64() - st_begin; o[6] = n_items; o[7] = 0;
-    }
-}
-
-
-// 1 row x NU utterances, chunks c = c_first, c_first+16, ... (one partial of dot16) - the small second head 1x1
-template <int NU>
-__device__ __forceinline__ void mac_lane1(float (&acc)[NU], const float4 *__restrict__ w4, const float *__restrict__ xs,
-                                          int c_first, int c_end) {
-    for (int c = c_first; c < c_end; c += LANES) {
-        const float4 w = w4[c];
-        const float *xk = xs + (size_t)c * 4 * NU;
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const float wv = e == 0 ? w.x : (e == 1 ? w.y : (e == 2 ? w.z : w.w));
-#pragma unroll
-            for (int u = 0; u < NU; ++u) acc[u] = __fmaf_rn(xk[e * NU + u], wv, acc[u]);
-        }
+        for (int i = 0; i < 6; ++i) o[8 + i] = st_d[i];
     }
 }
 
@@ -522,8 +585,8 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
     float *b1 = W2 + (size_t)O * S;            // [S]
     float *b2 = b1 + S;                        // [round4(O)]
     float *bsl = b2 + round4(O);               // [S]      skip-conv bias of the last layer
-    float *hs = smem + P.head_blob_floats;     // [S][NU]  relu(skips), k-major
-    float *h1 = hs + (size_t)S * NU;           // [S][NU]
+    float *hs = smem + P.head_blob_floats;     // [S x NU] relu(skips), xs_pos order
+    float *h1 = hs + (size_t)S * NU;           // [S x NU] xs_pos order
     float *outv = h1 + (size_t)S * NU;         // [O][NU]
     {
         const float4 *src = reinterpret_cast<const float4 *>(P.blobs + me.blob);
@@ -540,7 +603,7 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
         if (tid < NP) st_ll2(P.in + ((long long)0 * NG + g) * NU + 2 * tid, 0.0f, 0.0f, 1u);
 
     int bad = 0;
-    long long st_c[2] = {0, 0};
+    long long st_c[4] = {0, 0, 0, 0};
     const bool do_stats = P.stats != nullptr && tid == 0;
     const long long st_begin = clock64();
     for (int t = 0; t < T; ++t) {
@@ -548,24 +611,33 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
         for (int g = me.l; g < NG; g += P.NH) {
             const long long slot_g = (long long)(t & 1) * NG + g;
             const long long c0 = do_stats ? clock64() : 0;
+            // the sampler's inputs do not depend on the network: fetch them while the skip sums are still in flight
+            float nz0 = 0.0f, tch = 0.0f;
+            if (tid < NU && g * NU + tid < P.B) {
+                const long long b = g * NU + tid;
+                if (O == 2) nz0 = __ldg(P.noise + ((long long)t * P.B + b) * P.NZ);
+                if (P.teacher) tch = __ldg(P.teacher + b * T + t);
+            }
             // ---- skips = (skips_{L-2} + s_{L-1}) * sqrt(.5); relu ----------------------------------------------
             for (int task = tid; task < S * NP; task += PIPE_THREADS) {
                 const int c = task / NP, up = task - c * NP;
-                float s0 = 0.f, s1 = 0.f;
-#pragma unroll 1
-                for (int pp = 0; pp < PP; ++pp) {
-                    float v0, v1;
-                    bad |= poll_pair(sp_in + ((slot_g * PP + pp) * S + c) * NU + 2 * up, tag, v0, v1, P.abort_flag);
-                    if (pp == 0) { s0 = v0; s1 = v1; } else { s0 = __fadd_rn(s0, v0); s1 = __fadd_rn(s1, v1); }
-                }
+                unsigned long long wa[MAX_P + 1], wb[MAX_P + 1];
+                const unsigned long long *src[MAX_P + 1];
+#pragma unroll
+                for (int pp = 0; pp < MAX_P; ++pp)
+                    src[pp] = sp_in + ((slot_g * PP + (pp < PP ? pp : 0)) * S + c) * NU + 2 * up;
+                src[MAX_P] = rs_in + (slot_g * S + c) * NU + 2 * up;
+                bad |= poll_set(src, ((1u << PP) - 1u) | (L >= 2 ? (1u << MAX_P) : 0u), tag, wa, wb, P.abort_flag);
+                float s0 = ll_val(wa[0]), s1 = ll_val(wb[0]);
+#pragma unroll
+                for (int pp = 1; pp < MAX_P; ++pp)
+                    if (pp < PP) { s0 = __fadd_rn(s0, ll_val(wa[pp])); s1 = __fadd_rn(s1, ll_val(wb[pp])); }
                 s0 = __fadd_rn(s0, bsl[c]); s1 = __fadd_rn(s1, bsl[c]);
                 if (L >= 2) {
-                    float v0, v1;
-                    bad |= poll_pair(rs_in + (slot_g * S + c) * NU + 2 * up, tag, v0, v1, P.abort_flag);
-                    s0 = __fadd_rn(v0, s0); s1 = __fadd_rn(v1, s1);
+                    s0 = __fadd_rn(ll_val(wa[MAX_P]), s0); s1 = __fadd_rn(ll_val(wb[MAX_P]), s1);
                     if (P.legacy) { s0 = __fmul_rn(s0, WN_SQRT_HALF); s1 = __fmul_rn(s1, WN_SQRT_HALF); }
                 }
-                *reinterpret_cast<float2 *>(hs + (size_t)c * NU + 2 * up) =
+                *reinterpret_cast<float2 *>(hs + xs_pos<NU>(c, 2 * up, S4)) =
                     make_float2(s0 > 0.f ? s0 : 0.f, s1 > 0.f ? s1 : 0.f);
             }
             if (__syncthreads_or(bad)) return;
@@ -573,63 +645,68 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
             // ---- final_convolution_1 + relu: dot16, 4 rows x NU per thread -------------------------------------
             for (int qb = 0; qb < S4; qb += PIPE_THREADS / LANES) {
                 const int q = qb + q16;
-                float acc[NV];
+                float2 acc[NV / 2];
 #pragma unroll
-                for (int i = 0; i < NV; ++i) acc[i] = 0.0f;
-                if (q < S4) mac_lane<NU>(acc, reinterpret_cast<const float4 *>(W1) + (size_t)4 * q * S4, S4, hs, lane, S4);
-                reduce16<NV>(acc, lane);
+                for (int i = 0; i < NV / 2; ++i) acc[i] = make_float2(0.0f, 0.0f);
+                if (q < S4) mac_lane<NU, 4>(acc, reinterpret_cast<const float4 *>(W1) + (size_t)4 * q * S4, S4, hs, lane, S4);
+                float a[NV];
+                unpack2<NV>(acc, a);
+                reduce16<NV>(a, lane);
                 if (q < S4) {
 #pragma unroll
                     for (int i = 0; i < (NV >= LANES ? NV / LANES : 1); ++i) {
                         const int v = rbase4 + i, row = 4 * q + v / NU, u = v % NU;
-                        const float y = __fadd_rn(acc[i], b1[row]);
-                        h1[(size_t)row * NU + u] = y > 0.0f ? y : 0.0f;
+                        const float y = __fadd_rn(a[i], b1[row]);
+                        h1[xs_pos<NU>(row, u, S4)] = y > 0.0f ? y : 0.0f;
                     }
                 }
             }
             __syncthreads();
+            const long long c2 = do_stats ? clock64() : 0;
             // ---- final_convolution_2: dot16, 1 row x NU per 16 lanes ----------------------------------------------
             for (int nb = 0; nb < O; nb += PIPE_THREADS / LANES) {
                 const int n = nb + q16;
-                float acc[NU];
+                float2 acc[NP];
 #pragma unroll
-                for (int u = 0; u < NU; ++u) acc[u] = 0.0f;
-                if (n < O) mac_lane1<NU>(acc, reinterpret_cast<const float4 *>(W2) + (size_t)n * S4, h1, lane, S4);
-                reduce16<NU>(acc, lane);
+                for (int u = 0; u < NP; ++u) acc[u] = make_float2(0.0f, 0.0f);
+                if (n < O) mac_lane<NU, 1>(acc, reinterpret_cast<const float4 *>(W2) + (size_t)n * S4, S4, h1, lane, S4);
+                float a[NU];
+                unpack2<NU>(acc, a);
+                reduce16<NU>(a, lane);
                 if (n < O) {
 #pragma unroll
                     for (int i = 0; i < (NU >= LANES ? NU / LANES : 1); ++i) {
                         const int u = rbase1 + i;
-                        const float y = __fadd_rn(acc[i], b2[n]);
+                        const float y = __fadd_rn(a[i], b2[n]);
                         outv[(size_t)n * NU + u] = y;
                         const int b = g * NU + u;
-                        if (P.raw && b < P.B && (lane >> (NU == 2 ? 1 : (NU == 4 ? 2 : 3))) == 0)
+                        if (P.raw && b < P.B && (lane >> (NU == 4 ? 2 : 3)) == 0)   // one of the lanes holding this sum
                             P.raw[((long long)b * T + t) * O + n] = y;                     // wavenet.py:847
                     }
                 }
             }
             __syncthreads();
+            const long long c3 = do_stats ? clock64() : 0;
             // ---- sampling + feedback ------------------------------------------------------------------------------
             if (tid < 32) {
                 const int u = tid, b = g * NU + u;
                 float nxt = 0.0f;
                 if (u < NU && b < P.B) {
-                    const float *nz = P.noise + ((long long)t * P.B + b) * P.NZ;
-                    const float smp = (O == 2) ? pipe_sample_gaussian(P, outv + u, NU, nz[0])
-                                               : pipe_sample_mol(P, outv + u, NU, nz);
+                    const float smp = (O == 2) ? pipe_sample_gaussian(P, outv + u, NU, nz0)
+                                               : pipe_sample_mol(P, outv + u, NU, P.noise + ((long long)t * P.B + b) * P.NZ);
                     P.audio[(long long)b * T + t] = P.input_type == WN_INPUT_MULAW ? wn_inv_mulawf(smp) : smp;
-                    nxt = P.teacher ? P.teacher[(long long)b * T + t] : smp;
+                    nxt = P.teacher ? tch : smp;
                 }
                 const float other = __shfl_down_sync(0xffffffffu, nxt, 1);
                 if (u < NU && !(u & 1) && t + 1 < T)
                     st_ll2(P.in + ((long long)((t + 1) & 1) * NG + g) * NU + u, nxt, other, tag + 1u);
             }
-            if (do_stats) { st_c[0] += c1 - c0; st_c[1] += clock64() - c1; }
+            if (do_stats) { st_c[0] += c1 - c0; st_c[1] += c2 - c1; st_c[2] += c3 - c2; st_c[3] += clock64() - c3; }
         }
     }
     if (do_stats) {
-        long long *o = P.stats + (long long)blockIdx.x * 8;
-        o[0] = st_c[0]; o[1] = st_c[1]; o[2] = o[3] = o[4] = 0;
+        long long *o = P.stats + (long long)blockIdx.x * 16;
+        o[0] = st_c[0]; o[1] = st_c[1]; o[2] = st_c[2]; o[3] = st_c[3]; o[4] = 0;
         o[5] = clock64() - st_begin; o[6] = T; o[7] = 1;
     }
 }
@@ -693,11 +770,7 @@ void wn_pipe_fill_info(wn_handle *h, wn_info *info) {
 }
 
 static const void *pipe_kernel(int NU) {
-    switch (NU) {
-        case 2: return (const void *)wn_loop_pipe_kernel<2>;
-        case 4: return (const void *)wn_loop_pipe_kernel<4>;
-        default: return (const void *)wn_loop_pipe_kernel<8>;
-    }
+    return NU == 4 ? (const void *)wn_loop_pipe_kernel<4> : (const void *)wn_loop_pipe_kernel<8>;
 }
 
 // Fills the geometry that follows from (model, P, NU); returns the dynamic shared memory the kernel needs, 0 if the
@@ -717,7 +790,7 @@ static size_t pipe_geometry(const WnModelDev &m, PipeParams &p) {
     p.KC = 3 * m.R + m.cin;
     p.KC4 = p.KC / 4;
     p.C0 = (2 * m.R + m.cin) / 4;
-    if (p.NQ * LANES > PIPE_THREADS || (m.R + m.S) / 4 > PIPE_THREADS) return 0;
+    if (p.NQ * LANES > PIPE_THREADS || (m.R + m.S) / 2 > PIPE_THREADS) return 0;
     if (p.NU * (m.cin / 4) > PIPE_THREADS || 2 * m.R * p.NU / 4 > MAX_PF * PIPE_THREADS) return 0;
     p.layer_blob_floats = p.NR * p.KC + (m.R + m.S) * p.hk + p.NR + m.R + r4(p.smax) + 2 * m.R;
     p.head_blob_floats = m.S * m.S + m.O * m.S + m.S + r4(m.O) + m.S;
@@ -744,7 +817,7 @@ int wn_pipe_plan(wn_handle *h) {
     for (int l = 0; l < m.L; ++l) { p.dil[l] = m.dil[l]; p.depth[l] = 2 * m.dil[l] + 1; }
     auto bail = [&](const std::string &why) { delete pl; h->err = why; return -1; };
     p.NU = env_int("WN_PIPE_NU", 4);
-    if (p.NU != 2 && p.NU != 4 && p.NU != 8) return bail("WN_PIPE_NU must be 2, 4 or 8");
+    if (p.NU != 4 && p.NU != 8) return bail("WN_PIPE_NU must be 4 or 8");
     int max_optin = 0;
     cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
     // CTAs per layer: the caller's ksplit (it fixes the summation order), else WN_PIPE_P, else the widest split that
@@ -875,7 +948,7 @@ int wn_pipe_check_abort(wn_handle *h) {   // call after the stream has been sync
     if (!h->pipe || !h->pipe->h_abort) return WN_OK;
     const int code = *h->pipe->h_abort;
     if (h->pipe->d_stats && h->pipe->stats_ctas > 0 && getenv("WN_PIPE_STATS")) {   // development aid
-        std::vector<long long> st((size_t)h->pipe->stats_ctas * 8);
+        std::vector<long long> st((size_t)h->pipe->stats_ctas * 16);
         if (cudaMemcpy(st.data(), h->pipe->d_stats, st.size() * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess) {
             FILE *f = fopen(getenv("WN_PIPE_STATS"), "a");
             if (f) {
@@ -883,8 +956,9 @@ int wn_pipe_check_abort(wn_handle *h) {   // call after the stream has been sync
                 fprintf(f, "# pipe stats: L=%d P=%d NU=%d ctas=%d  cols: cta role wait+combine ph1 gate ph2+skip commit+ph0 total items\n",
                         q.L, q.P, q.NU, h->pipe->stats_ctas);
                 for (int i = 0; i < h->pipe->stats_ctas; ++i)
-                    fprintf(f, "%d %lld %lld %lld %lld %lld %lld %lld %lld\n", i, st[i * 8 + 7], st[i * 8 + 0], st[i * 8 + 1],
-                            st[i * 8 + 2], st[i * 8 + 3], st[i * 8 + 4], st[i * 8 + 5], st[i * 8 + 6]);
+                    fprintf(f, "%d %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld\n", i, st[i * 16 + 7], st[i * 16 + 0],
+                            st[i * 16 + 1], st[i * 16 + 2], st[i * 16 + 3], st[i * 16 + 4], st[i * 16 + 5], st[i * 16 + 6],
+                            st[i * 16 + 8], st[i * 16 + 9], st[i * 16 + 10], st[i * 16 + 11], st[i * 16 + 12], st[i * 16 + 13]);
                 fclose(f);
             }
         }
@@ -934,8 +1008,8 @@ int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, con
     const int grid = p.L * p.P + p.NH;
     p.stats = nullptr;
     if (getenv("WN_PIPE_STATS")) {
-        if (!pl->d_stats) cudaMalloc((void **)&pl->d_stats, sizeof(long long) * 8 * 512);
-        if (pl->d_stats) { cudaMemsetAsync(pl->d_stats, 0, sizeof(long long) * 8 * 512, st); p.stats = pl->d_stats; pl->stats_ctas = grid; }
+        if (!pl->d_stats) cudaMalloc((void **)&pl->d_stats, sizeof(long long) * 16 * 512);
+        if (pl->d_stats) { cudaMemsetAsync(pl->d_stats, 0, sizeof(long long) * 16 * 512, st); p.stats = pl->d_stats; pl->stats_ctas = grid; }
     }
     void *args[] = {&p};
     WN_CUDA_TRY(h, cudaLaunchCooperativeKernel(pipe_kernel(p.NU), dim3(grid), dim3(PIPE_THREADS), args, pl->smem_bytes, st));

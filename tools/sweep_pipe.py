@@ -23,11 +23,14 @@ def summarize_stats(path, clock_mhz=1965.0):
     if len(lay):
         items = lay[:, 8].mean()
         per = lay[:, 2:8].mean(axis=0) / items / clock_mhz   # us per item
-        out.append('layer CTAs us/item: commit+ph0 {:.2f} wait_x {:.2f} ph1 {:.2f} gate+wait_z {:.2f} ph2 {:.2f} | total {:.2f}'.format(*per))
+        out.append('layer CTAs us/item: wait+combine {:.2f} ph1+reduce {:.2f} gate {:.2f} ph2+skip {:.2f} commit+ph0 {:.2f} | total {:.2f}'.format(*per))
+        if lay.shape[1] >= 15:
+            per2 = lay[:, 9:15].mean(axis=0) / items / clock_mhz
+            out.append('   thread 0 detail: prefetch-issue {:.2f} mac(ph1) {:.2f} reduce+store {:.2f} | commit {:.2f} sync4 {:.2f} ph0 {:.2f}'.format(*per2))
     if len(head):
         items = head[:, 8].mean()
-        per = head[:, [2, 3, 7]].mean(axis=0) / items / clock_mhz
-        out.append('head CTAs us/step: wait_s {:.2f} work {:.2f} | total {:.2f}'.format(*per))
+        per = head[:, [2, 3, 4, 5, 7]].mean(axis=0) / items / clock_mhz
+        out.append('head CTAs us/step: wait+combine {:.2f} conv1 {:.2f} conv2 {:.2f} sample {:.2f} | total {:.2f}'.format(*per))
     return out
 
 
