@@ -60,7 +60,7 @@ struct wn_handle {
     // scratch (grown on demand, owned by the handle)
     float *d_ring = nullptr;  size_t ring_floats = 0;
     float *d_cup = nullptr;   size_t cup_floats = 0;
-    float *d_tmp0 = nullptr, *d_tmp1 = nullptr; size_t tmp_floats = 0;
+    float *d_tmp0 = nullptr, *d_tmp1 = nullptr; size_t tmp_floats = 0, tmp1_floats = 0;
     float *d_gemb = nullptr;  size_t gemb_floats = 0;
     // host-call staging
     float *d_in_c = nullptr, *d_in_noise = nullptr, *d_in_teacher = nullptr, *d_out_audio = nullptr,

@@ -245,9 +245,7 @@ int wn_launch_upsample(wn_handle *h, const float *c, int B, int Tc, float *c_up,
     }
     if (max_mid > 0) {
         if (wn_ensure(h, &h->d_tmp0, &h->tmp_floats, max_mid)) return WN_ERR_NOMEM;
-        size_t dummy = 0;
-        if (h->d_tmp1) { cudaFree(h->d_tmp1); h->d_tmp1 = nullptr; }
-        if (wn_ensure(h, &h->d_tmp1, &dummy, h->tmp_floats)) return WN_ERR_NOMEM;
+        if (h->n_up > 2 && wn_ensure(h, &h->d_tmp1, &h->tmp1_floats, max_mid)) return WN_ERR_NOMEM;   // ping-pong partner
     }
     const float *src = c;
     int W = Tc;
