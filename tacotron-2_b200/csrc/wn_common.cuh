@@ -11,6 +11,9 @@
 #include "../../include/wavenet_b200.h"
 #include "../../include/wn_math.h"
 
+// Partial sums per "dot" reduction of the canonical fp32 order (DESIGN.md "Arithmetic"); oracle/c/wn_oracle.c: WNO_LANES.
+#define WN_DOT_LANES 16
+
 // Device-side view of the model in the "generic" layout.  Matrices reduced with dot16 (the gate pre-activation over
 // the concatenated input [older taps | c | g | x(t)], the two head 1x1s) are stored TRANSPOSED, [N][Kpad] with Kpad a
 // multiple of 4 and zero padding, so that the 16 lanes of one output read 256 contiguous bytes; the out / skip 1x1s

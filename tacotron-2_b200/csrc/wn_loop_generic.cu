@@ -15,7 +15,7 @@
 namespace {
 
 constexpr int GEN_THREADS = 512;
-constexpr int LANES = 16;   // partial sums per dot16
+constexpr int LANES = WN_DOT_LANES;   // partial sums per dot reduction
 
 // dot16 of xs[0..K) (shared memory, zero padded to a multiple of 4) with row n of Wt ([N][Kpad], global), for the
 // outputs n = nb + group.  Every thread of the CTA calls it with the same trip count (shuffles are warp-wide).

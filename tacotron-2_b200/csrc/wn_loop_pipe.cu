@@ -42,8 +42,9 @@
 
 namespace {
 
-constexpr int PIPE_THREADS = 256;
-constexpr int LANES = 16;            // partial sums per dot16
+constexpr int PIPE_THREADS = 256;     // threads of one TEAM; a CTA runs TEAMS teams that share the resident weights
+constexpr int TEAMS = 1;              // and work on different utterance groups (g % TEAMS), out of phase with each other
+constexpr int LANES = WN_DOT_LANES;            // partial sums per dot16
 constexpr int MAX_P = 8;             // CTAs per layer
 constexpr int MAX_PF = 2;            // 16-byte prefetch loads per thread for the two older taps
 constexpr unsigned SPIN_LIMIT = 1u << 22;
@@ -71,8 +72,10 @@ struct PipeParams {
     const float *blobs;
     const PipeCta *ctas;
     float *rings;
-    unsigned long long *op, *xr, *sp, *rs, *in;   // mailboxes (see the host side for sizes)
-    long long op_sz, xr_sz, sp_sz, rs_sz;          // words per consumer stage
+    // mailboxes: one block per consumer stage (layers 0..L-1, head = L): op | xr | sp | rs (see the host side); `in`
+    // carries the sample fed back from the head to layer 0
+    unsigned long long *mail, *in;
+    long long stage_sz, xr_off, sp_off, rs_off;    // words
     int *abort_flag;
     long long *stats;                // optional [CTA][8] clock64 counters (WN_PIPE_STATS), else nullptr
     // call
@@ -86,10 +89,10 @@ __device__ __forceinline__ unsigned long long pack_ll(float v, unsigned tag) {
 }
 __device__ __forceinline__ void st_ll2(unsigned long long *p, float v0, float v1, unsigned tag) {   // 16-byte aligned
     const unsigned long long a = pack_ll(v0, tag), b = pack_ll(v1, tag);
-    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
+    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
 }
 __device__ __forceinline__ void ld_ll2(const unsigned long long *p, unsigned long long &a, unsigned long long &b) {
-    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
 }
 __device__ __forceinline__ float ll_val(unsigned long long w) { return __uint_as_float((unsigned)(w & 0xffffffffu)); }
 __device__ __forceinline__ unsigned ll_tag(unsigned long long w) { return (unsigned)(w >> 32); }
@@ -110,6 +113,20 @@ __device__ __forceinline__ int poll_pair(const unsigned long long *src, unsigned
 }
 
 __device__ __forceinline__ int round4(int v) { return (v + 3) & ~3; }
+
+// Barriers of one team (named barrier 1 + team, PIPE_THREADS participants): the teams never wait for each other.
+__device__ __forceinline__ void team_sync(int team) {
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + team), "r"(PIPE_THREADS) : "memory");
+}
+__device__ __forceinline__ int team_sync_or(int team, int v) {
+    int out;
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\tsetp.ne.s32 q, %1, 0;\n\tbar.red.or.pred p, %2, %3, q;\n\tselp.s32 %0, 1, 0, p;\n\t}"
+        : "=r"(out)
+        : "r"(v), "r"(1 + team), "r"(PIPE_THREADS)
+        : "memory");
+    return out;
+}
 
 // ---- the fp32 inner products ---------------------------------------------------------------------------------
 // dot16 operands in shared memory: element k = 4c+e of utterance u sits at xs_pos(k, u) = ((e*NU/4 + u/4)*K4 + c)*4 + u%4,
@@ -316,45 +333,57 @@ __device__ __forceinline__ int poll_set(const unsigned long long *const (&src)[M
 // ---------------------------------------------------------------------------------------------------------------
 // layer CTA: owns gate channels [h0,h1) of residual layer l  (ResidualConv1DGLU.incremental_step, modules.py:468-521)
 // ---------------------------------------------------------------------------------------------------------------
-template <int NU>
+// RT / CT: residual (= skip) channels and conditioning channels as compile-time constants (0 = read them from P): with
+// constants every index computation below folds into shifts and immediates, which the compiler rematerialises instead
+// of keeping ~40 loop-invariant registers alive.
+template <int NU, int RT, int CT, bool STATS>
 __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) {
     constexpr int NV = 4 * NU, NP = NU / 2;          // accumulators per thread; utterance pairs per group
-    const int tid = threadIdx.x;
-    const int R = P.R, S = P.S, NG = P.NG, T = P.T, l = me.l, PP = P.P;
-    const int hn = me.hn, hq = P.hq, hk = P.hk, NR = P.NR, KC = P.KC, KC4 = P.KC4, C0 = P.C0;
+    const int tid = threadIdx.x % PIPE_THREADS, team = threadIdx.x / PIPE_THREADS;
+    const int R = RT ? RT : P.R, S = RT ? RT : P.S, cin = CT ? CT : P.cin;
+    const int NG = P.NG, T = P.T, l = me.l, PP = P.P;
+    const int KC = 3 * R + cin, KC4 = KC / 4, C0 = (2 * R + cin) / 4;
+    const int hn = me.hn, hq = P.hq, hk = P.hk, NR = P.NR;
     const int d = P.dil[l], depth = P.depth[l];
     const bool last = (l == P.L - 1);
     // ---- shared memory carve-up (weights first: identical to the packed blob) ------------------------------
-    float *Wcat = smem;                                  // [NR][KC]      gate rows: tanh rows [0,hn), sigmoid rows [hq,hq+hn)
+    float *Wcat = smem;                                  // [NR][KC]      gate rows: row 2j = tanh half, 2j+1 = sigmoid half of channel h0+j
     float *Wos = Wcat + (size_t)NR * KC;                 // [hk/4][R+S][4] columns [h0,h1) of out (rows 0..R) and skip (rows R..R+S)
     float *bsum = Wos + (size_t)(R + S) * hk;            // [NR]
     float *bpo = bsum + NR;                              // [R]           out-conv bias of layer l-1
     float *bps = bpo + R;                                // [round4(smax)] skip-conv bias of layer l-1, my slice
     float *fw = bps + round4(P.smax);                    // [R] first conv (layer 0 only)
     float *fb = fw + R;                                  // [R]
-    float *xc = smem + P.layer_blob_floats;              // [KC x NU]     x(t-2d) | x(t-d) | c(t) | x(t) in xs_pos order
+    float *xc = smem + P.layer_blob_floats + (size_t)team * (KC + NR + hk) * NU;   // per team:
+                                                         // [KC x NU]     x(t-2d) | x(t-d) | c(t) | x(t) in xs_pos order
     float *pre = xc + (size_t)KC * NU;                   // [NR][NU]
     float *zs = pre + (size_t)NR * NU;                   // [hk][NU]
     {
         const float4 *src = reinterpret_cast<const float4 *>(P.blobs + me.blob);
         float4 *dst = reinterpret_cast<float4 *>(smem);
-        for (int i = tid; i < P.layer_blob_floats / 4; i += PIPE_THREADS) dst[i] = __ldg(src + i);
+        for (int i = threadIdx.x; i < P.layer_blob_floats / 4; i += PIPE_THREADS * TEAMS) dst[i] = __ldg(src + i);
         for (int i = tid; i < (KC + NR + hk) * NU; i += PIPE_THREADS) xc[i] = 0.0f;
     }
     __syncthreads();
+    if (team >= NG) return;   // fewer groups than teams
 
     float *ring = P.rings + (size_t)me.ring * NG * R * NU;   // [NG][depth][R x NU]; me.ring counts ring slots
-    const int o_cur4 = (2 * R + P.cin) / 4, R4 = R / 4;
-    // consumer-side mailboxes of this layer (stage l) and producer-side ones (stage l+1)
-    const unsigned long long *op_in = P.op + (long long)l * P.op_sz, *xr_in = P.xr + (long long)l * P.xr_sz;
-    const unsigned long long *sp_in = P.sp + (long long)l * P.sp_sz, *rs_in = P.rs + (long long)l * P.rs_sz;
-    unsigned long long *op_out = P.op + (long long)(l + 1) * P.op_sz, *xr_out = P.xr + (long long)(l + 1) * P.xr_sz;
-    unsigned long long *sp_out = P.sp + (long long)(l + 1) * P.sp_sz, *rs_out = P.rs + (long long)(l + 1) * P.rs_sz;
+    const int o_cur4 = (2 * R + cin) / 4, R4 = R / 4;
+    // consumer-side mailboxes of this layer (stage l); the producer-side ones (stage l+1) follow at + stage_sz
+    unsigned long long *const mbox = P.mail + (long long)l * P.stage_sz;
+#define op_in (mbox)
+#define xr_in (mbox + P.xr_off)
+#define sp_in (mbox + P.sp_off)
+#define rs_in (mbox + P.rs_off)
+#define op_out (mbox + P.stage_sz)
+#define xr_out (mbox + P.stage_sz + P.xr_off)
+#define sp_out (mbox + P.stage_sz + P.sp_off)
+#define rs_out (mbox + P.stage_sz + P.rs_off)
 
     // ---- thread roles (everything that only depends on tid is computed once, outside the time loop) -------
     const int lane = tid & (LANES - 1), q = tid / LANES;   // dot16: row quad q, partial `lane`
     const bool has_q = q < P.NQ;
-    const bool warp_has_q = (tid / 32) * 2 < P.NQ;
+    const bool warp_has_q = (tid / 32) * (32 / LANES) < P.NQ;
     const float4 *wq = reinterpret_cast<const float4 *>(Wcat) + (size_t)(has_q ? 4 * q : 0) * KC4;
     const int c1_first = C0 + ((lane - C0) % LANES + LANES) % LANES;   // first chunk >= C0 owned by this lane
     const int rbase = reduce16_base<NV>(lane);
@@ -367,7 +396,7 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
     const int d_m = tid / NP, d_up = tid - d_m * NP, d_e = d_m / R4, d_cr = d_m - d_e * R4;
     // prefetch / commit slots
     const int n_tap16 = 2 * R * NU / 4;                     // float4 loads for both taps
-    const int n_c16 = NU * (P.cin / 4);
+    const int n_c16 = NU * (cin / 4);
     int pf_tap[MAX_PF], pf_rem[MAX_PF], pf_dst[MAX_PF];
 #pragma unroll
     for (int k = 0; k < MAX_PF; ++k) {
@@ -380,24 +409,28 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
             pf_dst[k] = seg * KC4 + pf_tap[k] * R4 + cr;
         }
     }
-    const int pc_u = tid / (P.cin / 4), pc_c4 = tid - pc_u * (P.cin / 4);
+    const int pc_u = tid / (cin / 4), pc_c4 = tid - pc_u * (cin / 4);
 
     // ---- register prefetch of the older taps and the conditioning column of the NEXT work item -------------
     float4 pft[MAX_PF], pfc;
-    auto prefetch = [&](int g, int t) {
+    // `slot` = t % depth of the item being prefetched; depth = 2d+1, so (t-2d) % depth = slot+1 and (t-d) % depth =
+    // slot+d+1 (both mod depth): no division in the time loop
+    auto prefetch = [&](int g, int t, int slot) {
 #pragma unroll
         for (int k = 0; k < MAX_PF; ++k) {
             pft[k] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (pf_tap[k] >= 0) {
                 const int tt = t - (2 - pf_tap[k]) * d;
+                int sl = slot + 1 + (pf_tap[k] ? d : 0);
+                if (sl >= depth) sl -= depth;
                 if (tt >= 0)
-                    pft[k] = __ldcg(reinterpret_cast<const float4 *>(ring + (size_t)(g * depth + tt % depth) * R * NU) + pf_rem[k]);
+                    pft[k] = __ldcg(reinterpret_cast<const float4 *>(ring + (size_t)(g * depth + sl) * R * NU) + pf_rem[k]);
             }
         }
         pfc = make_float4(0.f, 0.f, 0.f, 0.f);
         if (tid < n_c16) {
             const int b = g * NU + pc_u;
-            if (b < P.B) pfc = __ldg(reinterpret_cast<const float4 *>(P.c_up + ((long long)b * T + t) * P.cin) + pc_c4);
+            if (b < P.B) pfc = __ldg(reinterpret_cast<const float4 *>(P.c_up + ((long long)b * T + t) * cin) + pc_c4);
         }
     };
     auto commit = [&]() {
@@ -420,16 +453,16 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
 
     int bad = 0;
     long long st_c[6] = {0, 0, 0, 0, 0, 0}, st_d[6] = {0, 0, 0, 0, 0, 0};
-    const bool do_stats = P.stats != nullptr && tid == 0;
-    const long long st_begin = clock64();
+    const bool do_stats = STATS && P.stats != nullptr && threadIdx.x == 0;
+    const long long st_begin = STATS ? clock64() : 0;
 
-    prefetch(0, 0);
+    prefetch(team, 0, 0);
     commit();
-    __syncthreads();
+    team_sync(team);
     phase0();
 
-    const long long n_items = (long long)T * NG;
-    int t = 0, g = 0;
+    const long long n_items = (long long)T * ((NG - team + TEAMS - 1) / TEAMS);   // this team's groups: team, team+TEAMS, ...
+    int t = 0, g = team, rslot = 0;   // rslot = t % depth
     for (long long it = 0; it < n_items; ++it) {
         const unsigned tag = (unsigned)t + 1u;
         const long long slot_g = (long long)(t & 1) * NG + g;
@@ -468,14 +501,14 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
             if (!last && r >= me.r0 && r < me.r0 + me.rn) st_ll2(xr_out + (slot_g * R + m) * NU + 2 * up, x0, x1, tag);
             const int seg = e * (NU / 4) + (up >> 1);
             *reinterpret_cast<float2 *>(xc + (size_t)(seg * KC4 + o_cur4 + cr) * 4 + 2 * (up & 1)) = make_float2(x0, x1);
-            __stcg(reinterpret_cast<float2 *>(ring + (size_t)(g * depth + t % depth) * R * NU +
+            __stcg(reinterpret_cast<float2 *>(ring + (size_t)(g * depth + rslot) * R * NU +
                                               (size_t)(seg * R4 + cr) * 4 + 2 * (up & 1)), make_float2(x0, x1));
         }
-        if (__syncthreads_or(bad)) return;                                                           // (1)
+        if (team_sync_or(team, bad)) return;                                                         // (1)
         const long long c1 = do_stats ? clock64() : 0;
-        int g2 = g + 1, t2 = t;
-        if (g2 == NG) { g2 = 0; t2 = t + 1; }
-        if (t2 < T) prefetch(g2, t2);   // ring slots of (t2 - d, g2) were written in an earlier item or just above
+        int g2 = g + TEAMS, t2 = t, rslot2 = rslot;
+        if (g2 >= NG) { g2 = team; t2 = t + 1; rslot2 = rslot + 1 == depth ? 0 : rslot + 1; }
+        if (t2 < T) prefetch(g2, t2, rslot2);   // ring slots of (t2 - d, g2) were written in an earlier item or just above
         const long long e0 = do_stats ? clock64() : 0;
         // ---- E: current tap, tree reduction, bias (modules.py:294-297, :497-501) ----------------------------
         if (warp_has_q) {   // warp-uniform: the butterfly shuffles need every lane of the warp
@@ -484,26 +517,24 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
             float a[NV];
             unpack2<NV>(acc, a);
             reduce16<NV>(a, lane);
-            if (has_q) {
+            // gate (modules.py:510).  Rows of a quad are (tanh j, sigmoid j, tanh j+1, sigmoid j+1), so the two halves of
+            // one gated value sit in lanes that differ in the bit the butterfly used for tile-row bit 0 (mask 2): every
+            // lane evaluates ONE transcendental, one shuffle brings the partner, the tanh lane stores z.
 #pragma unroll
-                for (int i = 0; i < (NV >= LANES ? NV / LANES : 1); ++i) {
-                    const int v = rbase + i, row = 4 * q + v / NU, u = v % NU;
-                    pre[(size_t)row * NU + u] = __fadd_rn(a[i], bsum[row]);
+            for (int i = 0; i < (NV >= LANES ? NV / LANES : 1); ++i) {
+                const int v = rbase + i, ti = v / NU, u = v % NU, row = 4 * q + ti;
+                float g_act = 0.0f;
+                if (has_q) {
+                    const float pv = __fadd_rn(a[i], bsum[row]);
+                    g_act = (ti & 1) ? wn_sigmoidf(pv) : wn_tanhf(pv);
                 }
+                const float o_act = __shfl_xor_sync(0xffffffffu, g_act, 2);
+                if (has_q && !(ti & 1)) zs[(size_t)(2 * q + (ti >> 1)) * NU + u] = __fmul_rn(g_act, o_act);
             }
             if (do_stats) { const long long e2 = clock64(); st_d[0] += e0 - c1; st_d[1] += e1 - e0; st_d[2] += e2 - e1; }
         }
-        __syncthreads();                                                                             // (2)
         const long long c2 = do_stats ? clock64() : 0;
-        // ---- F: gate (modules.py:510): even lane tanh, odd lane sigmoid, one shuffle -------------------------
-        for (int base = 0; base < 2 * hn * NU; base += PIPE_THREADS) {
-            const int i = base + tid, v = i >> 1;
-            float a = 0.0f;
-            if (i < 2 * hn * NU) a = (i & 1) ? wn_sigmoidf(pre[(size_t)hq * NU + v]) : wn_tanhf(pre[v]);
-            const float o = __shfl_xor_sync(0xffffffffu, a, 1);
-            if (i < 2 * hn * NU && !(i & 1)) zs[v] = __fmul_rn(a, o);
-        }
-        __syncthreads();                                                                             // (3)
+        team_sync(team);                                                                             // (3)
         const long long c3 = do_stats ? clock64() : 0;
         // ---- G: my column block of the out / skip 1x1s -> partial sums for layer l+1 / the head ---------------
         if (has_t2) {
@@ -552,7 +583,7 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
         // ---- next item: older taps + conditioning into shared memory, then its x(t)-independent part ------------
         if (t2 < T) commit();
         const long long f0 = do_stats ? clock64() : 0;
-        if (__syncthreads_or(bad)) return;                                                           // (4)
+        if (team_sync_or(team, bad)) return;                                                         // (4)
         const long long f1 = do_stats ? clock64() : 0;
         if (t2 < T) phase0();
         if (do_stats) { st_d[3] += f0 - c4; st_d[4] += f1 - f0; st_d[5] += clock64() - f1; }
@@ -560,7 +591,7 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
             const long long c5 = clock64();
             st_c[0] += c1 - c0; st_c[1] += c2 - c1; st_c[2] += c3 - c2; st_c[3] += c4 - c3; st_c[4] += c5 - c4;
         }
-        g = g2; t = t2;
+        g = g2; t = t2; rslot = rslot2;
     }
     if (do_stats) {
         long long *o = P.stats + (long long)blockIdx.x * 16;
@@ -570,14 +601,23 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
     }
 }
 
+#undef op_in
+#undef xr_in
+#undef sp_in
+#undef rs_in
+#undef op_out
+#undef xr_out
+#undef sp_out
+#undef rs_out
+
 // ---------------------------------------------------------------------------------------------------------------
 // head CTA: last skip accumulation, relu -> 1x1 -> relu -> 1x1 (wavenet.py:833-844), sampler (:850-859) and the
 // feedback value (:877) for the groups g = me.l, me.l + NH, ...
 // ---------------------------------------------------------------------------------------------------------------
-template <int NU>
+template <int NU, bool STATS>
 __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
     constexpr int NV = 4 * NU, NP = NU / 2;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x % PIPE_THREADS, team = threadIdx.x / PIPE_THREADS;
     const int S = P.S, O = P.O, NG = P.NG, T = P.T, PP = P.P, L = P.L;
     const int S4 = S / 4;
     float *W1 = smem;                          // [S][S]   row n = output channel (transposed TF kernel)
@@ -585,30 +625,32 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
     float *b1 = W2 + (size_t)O * S;            // [S]
     float *b2 = b1 + S;                        // [round4(O)]
     float *bsl = b2 + round4(O);               // [S]      skip-conv bias of the last layer
-    float *hs = smem + P.head_blob_floats;     // [S x NU] relu(skips), xs_pos order
+    float *hs = smem + P.head_blob_floats + (size_t)team * (2 * S + round4(O)) * NU;   // per team:
+                                               // [S x NU] relu(skips), xs_pos order
     float *h1 = hs + (size_t)S * NU;           // [S x NU] xs_pos order
     float *outv = h1 + (size_t)S * NU;         // [O][NU]
     {
         const float4 *src = reinterpret_cast<const float4 *>(P.blobs + me.blob);
         float4 *dst = reinterpret_cast<float4 *>(smem);
-        for (int i = tid; i < P.head_blob_floats / 4; i += PIPE_THREADS) dst[i] = __ldg(src + i);
+        for (int i = threadIdx.x; i < P.head_blob_floats / 4; i += PIPE_THREADS * TEAMS) dst[i] = __ldg(src + i);
     }
     __syncthreads();
-    const unsigned long long *sp_in = P.sp + (long long)L * P.sp_sz, *rs_in = P.rs + (long long)L * P.rs_sz;
+    const int g_first = me.l * TEAMS + team, g_step = P.NH * TEAMS;   // this team's groups
+    const unsigned long long *sp_in = P.mail + (long long)L * P.stage_sz + P.sp_off, *rs_in = sp_in - P.sp_off + P.rs_off;
     const int lane = tid & (LANES - 1), q16 = tid / LANES;
     const int rbase4 = reduce16_base<NV>(lane), rbase1 = reduce16_base<NU>(lane);
 
     // initial input (wavenet.py:433-445): raw 0.0, mulaw mulaw(0) = 0.0
-    for (int g = me.l; g < NG; g += P.NH)
+    for (int g = g_first; g < NG; g += g_step)
         if (tid < NP) st_ll2(P.in + ((long long)0 * NG + g) * NU + 2 * tid, 0.0f, 0.0f, 1u);
 
     int bad = 0;
     long long st_c[4] = {0, 0, 0, 0};
-    const bool do_stats = P.stats != nullptr && tid == 0;
+    const bool do_stats = STATS && P.stats != nullptr && threadIdx.x == 0;
     const long long st_begin = clock64();
     for (int t = 0; t < T; ++t) {
         const unsigned tag = (unsigned)t + 1u;
-        for (int g = me.l; g < NG; g += P.NH) {
+        for (int g = g_first; g < NG; g += g_step) {
             const long long slot_g = (long long)(t & 1) * NG + g;
             const long long c0 = do_stats ? clock64() : 0;
             // the sampler's inputs do not depend on the network: fetch them while the skip sums are still in flight
@@ -640,7 +682,7 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
                 *reinterpret_cast<float2 *>(hs + xs_pos<NU>(c, 2 * up, S4)) =
                     make_float2(s0 > 0.f ? s0 : 0.f, s1 > 0.f ? s1 : 0.f);
             }
-            if (__syncthreads_or(bad)) return;
+            if (team_sync_or(team, bad)) return;
             const long long c1 = do_stats ? clock64() : 0;
             // ---- final_convolution_1 + relu: dot16, 4 rows x NU per thread -------------------------------------
             for (int qb = 0; qb < S4; qb += PIPE_THREADS / LANES) {
@@ -661,7 +703,7 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
                     }
                 }
             }
-            __syncthreads();
+            team_sync(team);
             const long long c2 = do_stats ? clock64() : 0;
             // ---- final_convolution_2: dot16, 1 row x NU per 16 lanes ----------------------------------------------
             for (int nb = 0; nb < O; nb += PIPE_THREADS / LANES) {
@@ -685,7 +727,7 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
                     }
                 }
             }
-            __syncthreads();
+            team_sync(team);
             const long long c3 = do_stats ? clock64() : 0;
             // ---- sampling + feedback ------------------------------------------------------------------------------
             if (tid < 32) {
@@ -711,14 +753,13 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
     }
 }
 
-template <int NU>
-__global__ void __launch_bounds__(PIPE_THREADS, 1) wn_loop_pipe_kernel(const PipeParams P) {
+template <int NU, int RT, int CT, bool STATS>
+__global__ void __launch_bounds__(PIPE_THREADS * TEAMS, 1) wn_loop_pipe_kernel(const PipeParams P) {
     extern __shared__ __align__(16) float pipe_smem[];
     const PipeCta me = P.ctas[blockIdx.x];
-    if (me.role == 0) layer_role<NU>(P, me, pipe_smem);
-    else head_role<NU>(P, me, pipe_smem);
+    if (me.role == 0) layer_role<NU, RT, CT, STATS>(P, me, pipe_smem);
+    else head_role<NU, STATS>(P, me, pipe_smem);
 }
-
 
 }  // namespace
 
@@ -769,8 +810,12 @@ void wn_pipe_fill_info(wn_handle *h, wn_info *info) {
     info->pipeline_group_size = h->pipe->prm.NU;
 }
 
-static const void *pipe_kernel(int NU) {
-    return NU == 4 ? (const void *)wn_loop_pipe_kernel<4> : (const void *)wn_loop_pipe_kernel<8>;
+// Specialised for the shipped default block (R = S = 128, 80 mel bands), generic otherwise; the variants with the
+// clock64 counters are separate instantiations so that the production kernel carries no timing registers.
+static const void *pipe_kernel(const PipeParams &p, bool stats) {
+    const bool dflt = p.R == 128 && p.S == 128 && p.cin == 80;
+    if (stats) return dflt ? (const void *)wn_loop_pipe_kernel<4, 128, 80, true> : (const void *)wn_loop_pipe_kernel<4, 0, 0, true>;
+    return dflt ? (const void *)wn_loop_pipe_kernel<4, 128, 80, false> : (const void *)wn_loop_pipe_kernel<4, 0, 0, false>;
 }
 
 // Fills the geometry that follows from (model, P, NU); returns the dynamic shared memory the kernel needs, 0 if the
@@ -794,8 +839,8 @@ static size_t pipe_geometry(const WnModelDev &m, PipeParams &p) {
     if (p.NU * (m.cin / 4) > PIPE_THREADS || 2 * m.R * p.NU / 4 > MAX_PF * PIPE_THREADS) return 0;
     p.layer_blob_floats = p.NR * p.KC + (m.R + m.S) * p.hk + p.NR + m.R + r4(p.smax) + 2 * m.R;
     p.head_blob_floats = m.S * m.S + m.O * m.S + m.S + r4(m.O) + m.S;
-    const size_t layer_smem = sizeof(float) * ((size_t)p.layer_blob_floats + (size_t)(p.KC + p.NR + p.hk) * p.NU);
-    const size_t head_smem = sizeof(float) * ((size_t)p.head_blob_floats + (size_t)(2 * m.S + r4(m.O)) * p.NU);
+    const size_t layer_smem = sizeof(float) * ((size_t)p.layer_blob_floats + (size_t)TEAMS * (p.KC + p.NR + p.hk) * p.NU);
+    const size_t head_smem = sizeof(float) * ((size_t)p.head_blob_floats + (size_t)TEAMS * (2 * m.S + r4(m.O)) * p.NU);
     return std::max(layer_smem, head_smem);
 }
 
@@ -817,7 +862,7 @@ int wn_pipe_plan(wn_handle *h) {
     for (int l = 0; l < m.L; ++l) { p.dil[l] = m.dil[l]; p.depth[l] = 2 * m.dil[l] + 1; }
     auto bail = [&](const std::string &why) { delete pl; h->err = why; return -1; };
     p.NU = env_int("WN_PIPE_NU", 4);
-    if (p.NU != 4 && p.NU != 8) return bail("WN_PIPE_NU must be 4 or 8");
+    if (p.NU != 4) return bail("WN_PIPE_NU must be 4");
     int max_optin = 0;
     cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
     // CTAs per layer: the caller's ksplit (it fixes the summation order), else WN_PIPE_P, else the widest split that
@@ -880,7 +925,8 @@ int wn_pipe_plan(wn_handle *h) {
                   *bps = bpo + R, *fw = bps + r4(p.smax), *fbv = fw + R;
             for (int half = 0; half < 2; ++half)
                 for (int j = 0; j < ct.hn; ++j) {
-                    const int row = half * p.hq + j, col = half * m.H + ct.h0 + j;   // modules.py:494 split order
+                    // row 2j = tanh half of gate channel h0+j, row 2j+1 = its sigmoid half (modules.py:494 split order)
+                    const int row = 2 * j + half, col = half * m.H + ct.h0 + j;
                     float *w = Wcat + (size_t)row * p.KC;
                     for (int k = 0; k < 2 * R; ++k) w[k] = cw[(size_t)k * G + col];
                     for (int k = 0; k < m.cin; ++k) w[2 * R + k] = iw[(size_t)k * G + col];
@@ -936,7 +982,8 @@ int wn_pipe_plan(wn_handle *h) {
     p.blobs = pl->d_blobs;
     p.ctas = pl->d_ctas;
     p.abort_flag = pl->d_abort;
-    if (cudaFuncSetAttribute(pipe_kernel(p.NU), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem_bytes) != cudaSuccess) {
+    if (cudaFuncSetAttribute(pipe_kernel(p, false), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem_bytes) != cudaSuccess ||
+        cudaFuncSetAttribute(pipe_kernel(p, true), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem_bytes) != cudaSuccess) {
         wn_pipe_free(h);
         h->err = std::string("pipeline engine: ") + cudaGetErrorString(cudaGetLastError());
         return -1;
@@ -975,15 +1022,16 @@ int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, con
     if (!pl) { h->err = "pipeline engine not planned"; return WN_ERR_STATE; }
     PipeParams p = pl->prm;
     p.NG = (B + p.NU - 1) / p.NU;
-    p.NH = std::min(p.NG, pl->max_heads);
+    p.NH = std::min((p.NG + TEAMS - 1) / TEAMS, pl->max_heads);
     p.B = B; p.T = T;
     p.c_up = c_up; p.noise = noise; p.teacher = teacher; p.audio = audio; p.raw = raw;
     // mailboxes, 8-byte {value, tag} words, zeroed (tag 0 = empty), double buffered on t&1, one set per consumer stage
     // (layers 0..L-1, head = L):  op [2][NG][P][R][NU] | xr [2][NG][R][NU] | sp [2][NG][P][S][NU] | rs [2][NG][S][NU]
     const long long slots = 2ll * p.NG * p.NU;
-    p.op_sz = slots * p.P * p.R; p.xr_sz = slots * p.R; p.sp_sz = slots * p.P * p.S; p.rs_sz = slots * p.S;
+    const long long op_sz = slots * p.P * p.R, xr_sz = slots * p.R, sp_sz = slots * p.P * p.S, rs_sz = slots * p.S;
+    p.xr_off = op_sz; p.sp_off = op_sz + xr_sz; p.rs_off = op_sz + xr_sz + sp_sz; p.stage_sz = op_sz + xr_sz + sp_sz + rs_sz;
     const size_t stages = (size_t)p.L + 1;
-    const size_t words = stages * (size_t)(p.op_sz + p.xr_sz + p.sp_sz + p.rs_sz) + (size_t)slots;
+    const size_t words = stages * (size_t)p.stage_sz + (size_t)slots;
     if (pl->mail_words < words) {
         if (pl->d_mail) cudaFree(pl->d_mail);
         pl->d_mail = nullptr; pl->mail_words = 0;
@@ -991,8 +1039,8 @@ int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, con
         if (e != cudaSuccess) { h->err = std::string("pipeline mailboxes: ") + cudaGetErrorString(e); return WN_ERR_NOMEM; }
         pl->mail_words = words;
     }
-    p.op = pl->d_mail; p.xr = p.op + stages * p.op_sz; p.sp = p.xr + stages * p.xr_sz; p.rs = p.sp + stages * p.sp_sz;
-    p.in = p.rs + stages * p.rs_sz;
+    p.mail = pl->d_mail;
+    p.in = p.mail + stages * p.stage_sz;
     // private dilation rings of the layer CTAs: [CTA][NG][2d+1][R][NU] floats (never read before written: no memset)
     const size_t ring_floats = (size_t)pl->ring_slots * p.NG * p.R * p.NU;
     if (pl->ring_floats < ring_floats) {
@@ -1012,7 +1060,7 @@ int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, con
         if (pl->d_stats) { cudaMemsetAsync(pl->d_stats, 0, sizeof(long long) * 16 * 512, st); p.stats = pl->d_stats; pl->stats_ctas = grid; }
     }
     void *args[] = {&p};
-    WN_CUDA_TRY(h, cudaLaunchCooperativeKernel(pipe_kernel(p.NU), dim3(grid), dim3(PIPE_THREADS), args, pl->smem_bytes, st));
+    WN_CUDA_TRY(h, cudaLaunchCooperativeKernel(pipe_kernel(p, p.stats != nullptr), dim3(grid), dim3(PIPE_THREADS * TEAMS), args, pl->smem_bytes, st));
     h->launches++;
     WN_CUDA_TRY(h, cudaMemcpyAsync(pl->h_abort, pl->d_abort, sizeof(int), cudaMemcpyDeviceToHost, st));
     return WN_OK;

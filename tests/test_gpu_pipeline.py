@@ -68,8 +68,8 @@ def test_pipeline_small_variants_bit_exact(name, B):
         assert np.all(common.rel_close(raw, np.transpose(raw_np, [0, 2, 1])))
 
 
-@pytest.mark.parametrize('env', [dict(WN_PIPE_P=1), dict(WN_PIPE_P=2), dict(WN_PIPE_P=3), dict(WN_PIPE_NU=8),
-                                 dict(WN_PIPE_P=7, WN_PIPE_NU=8), dict(WN_PIPE_P=5, WN_PIPE_NU=4)])
+@pytest.mark.parametrize('env', [dict(WN_PIPE_P=1), dict(WN_PIPE_P=2), dict(WN_PIPE_P=3), 
+                                 dict(WN_PIPE_P=7), dict(WN_PIPE_P=5, WN_PIPE_NU=4)])
 def test_pipeline_plans_bit_exact(env):
     hp = common.small()
     w = common.weights_for(hp)
