@@ -191,7 +191,7 @@ __device__ __forceinline__ void mac_lane(float2 (&acc)[ROWS * NU / 2], const flo
     };
     int c = c_first;
     if (c >= c_end) return;
-    if (ROWS * NU > 16) {   // large tiles: one operand buffer (registers)
+    if (ROWS * NU > 16 || TEAMS > 1) {   // large tiles or a 128-register budget: one operand buffer
         for (; c < c_end; c += LANES) {
             MacOps<NU, ROWS> a;
             load(a, c);
@@ -311,14 +311,16 @@ __device__ float pipe_sample_mol(const PipeParams &P, const float *out, int ostr
 
 // Poll up to MAX_P+1 pairs of {value,tag} words at once (all loads in flight together, re-issued only for the
 // ones still pending) until every selected pair carries `tag`.  mask bit i selects src[i].
-__device__ __forceinline__ int poll_set(const unsigned long long *const (&src)[MAX_P + 1], unsigned mask, unsigned tag,
+// Sources: i < MAX_P -> base + i*stride (the partial sums of producer CTA i), i == MAX_P -> extra.
+__device__ __forceinline__ int poll_set(const unsigned long long *base, unsigned stride, const unsigned long long *extra,
+                                        unsigned mask, unsigned tag,
                                         unsigned long long (&wa)[MAX_P + 1], unsigned long long (&wb)[MAX_P + 1],
                                         int *abort_flag) {
     unsigned pending = mask, spins = 0;
     while (pending) {
 #pragma unroll
         for (int i = 0; i <= MAX_P; ++i)
-            if (pending & (1u << i)) ld_ll2(src[i], wa[i], wb[i]);
+            if (pending & (1u << i)) ld_ll2(i < MAX_P ? base + i * stride : extra, wa[i], wb[i]);
 #pragma unroll
         for (int i = 0; i <= MAX_P; ++i)
             if ((pending & (1u << i)) && ll_tag(wa[i]) == tag && ll_tag(wb[i]) == tag) pending &= ~(1u << i);
@@ -452,7 +454,7 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
     };
 
     int bad = 0;
-    long long st_c[6] = {0, 0, 0, 0, 0, 0}, st_d[6] = {0, 0, 0, 0, 0, 0};
+    long long st_c[5] = {0, 0, 0, 0, 0};
     const bool do_stats = STATS && P.stats != nullptr && threadIdx.x == 0;
     const long long st_begin = STATS ? clock64() : 0;
 
@@ -465,7 +467,7 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
     int t = 0, g = team, rslot = 0;   // rslot = t % depth
     for (long long it = 0; it < n_items; ++it) {
         const unsigned tag = (unsigned)t + 1u;
-        const long long slot_g = (long long)(t & 1) * NG + g;
+        const int slot_g = (t & 1) * NG + g;
         const long long c0 = do_stats ? clock64() : 0;
         // ---- D: wait for the inputs of (t, g) and rebuild x_l(t) ----------------------------------------------
         // mailbox rows are stored e-major (position m = (r%4)*R/4 + r/4), so that consecutive threads read
@@ -482,12 +484,9 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
                 x1 = __fadd_rn(__fmaf_rn(s1, fw[r], 0.0f), fb[r]);
             } else {        // out 1x1 of layer l-1: partial sums in ascending p, bias, residual (modules.py:515-520)
                 unsigned long long wa[MAX_P + 1], wb[MAX_P + 1];
-                const unsigned long long *src[MAX_P + 1];
-#pragma unroll
-                for (int pp = 0; pp < MAX_P; ++pp)
-                    src[pp] = op_in + ((slot_g * PP + (pp < PP ? pp : 0)) * R + m) * NU + 2 * up;
-                src[MAX_P] = xr_in + (slot_g * R + m) * NU + 2 * up;
-                bad |= poll_set(src, ((1u << PP) - 1u) | (1u << MAX_P), tag, wa, wb, P.abort_flag);
+                bad |= poll_set(op_in + (unsigned)((slot_g * PP * R + m) * NU + 2 * up), (unsigned)(R * NU),
+                                xr_in + (unsigned)((slot_g * R + m) * NU + 2 * up),
+                                ((1u << PP) - 1u) | (1u << MAX_P), tag, wa, wb, P.abort_flag);
                 float y0 = ll_val(wa[0]), y1 = ll_val(wb[0]);
 #pragma unroll
                 for (int pp = 1; pp < MAX_P; ++pp)
@@ -509,11 +508,9 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
         int g2 = g + TEAMS, t2 = t, rslot2 = rslot;
         if (g2 >= NG) { g2 = team; t2 = t + 1; rslot2 = rslot + 1 == depth ? 0 : rslot + 1; }
         if (t2 < T) prefetch(g2, t2, rslot2);   // ring slots of (t2 - d, g2) were written in an earlier item or just above
-        const long long e0 = do_stats ? clock64() : 0;
         // ---- E: current tap, tree reduction, bias (modules.py:294-297, :497-501) ----------------------------
         if (warp_has_q) {   // warp-uniform: the butterfly shuffles need every lane of the warp
             if (has_q) mac_lane<NU, 4>(acc, wq, KC4, xc, c1_first, KC4);
-            const long long e1 = do_stats ? clock64() : 0;
             float a[NV];
             unpack2<NV>(acc, a);
             reduce16<NV>(a, lane);
@@ -531,7 +528,6 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
                 const float o_act = __shfl_xor_sync(0xffffffffu, g_act, 2);
                 if (has_q && !(ti & 1)) zs[(size_t)(2 * q + (ti >> 1)) * NU + u] = __fmul_rn(g_act, o_act);
             }
-            if (do_stats) { const long long e2 = clock64(); st_d[0] += e0 - c1; st_d[1] += e1 - e0; st_d[2] += e2 - e1; }
         }
         const long long c2 = do_stats ? clock64() : 0;
         team_sync(team);                                                                             // (3)
@@ -561,12 +557,9 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
             for (int task = tid - hbase; task < me.sn * NP; task += hthreads) {
                 const int cl = task / NP, up = task - cl * NP, c = me.s0 + cl;
                 unsigned long long wa[MAX_P + 1], wb[MAX_P + 1];
-                const unsigned long long *src[MAX_P + 1];
-#pragma unroll
-                for (int pp = 0; pp < MAX_P; ++pp)
-                    src[pp] = sp_in + ((slot_g * PP + (pp < PP ? pp : 0)) * S + c) * NU + 2 * up;
-                src[MAX_P] = rs_in + (slot_g * S + c) * NU + 2 * up;
-                bad |= poll_set(src, ((1u << PP) - 1u) | (l >= 2 ? (1u << MAX_P) : 0u), tag, wa, wb, P.abort_flag);
+                bad |= poll_set(sp_in + (unsigned)((slot_g * PP * S + c) * NU + 2 * up), (unsigned)(S * NU),
+                                rs_in + (unsigned)((slot_g * S + c) * NU + 2 * up),
+                                ((1u << PP) - 1u) | (l >= 2 ? (1u << MAX_P) : 0u), tag, wa, wb, P.abort_flag);
                 float s0 = ll_val(wa[0]), s1 = ll_val(wb[0]);
 #pragma unroll
                 for (int pp = 1; pp < MAX_P; ++pp)
@@ -582,11 +575,8 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
         const long long c4 = do_stats ? clock64() : 0;
         // ---- next item: older taps + conditioning into shared memory, then its x(t)-independent part ------------
         if (t2 < T) commit();
-        const long long f0 = do_stats ? clock64() : 0;
         if (team_sync_or(team, bad)) return;                                                         // (4)
-        const long long f1 = do_stats ? clock64() : 0;
         if (t2 < T) phase0();
-        if (do_stats) { st_d[3] += f0 - c4; st_d[4] += f1 - f0; st_d[5] += clock64() - f1; }
         if (do_stats) {
             const long long c5 = clock64();
             st_c[0] += c1 - c0; st_c[1] += c2 - c1; st_c[2] += c3 - c2; st_c[3] += c4 - c3; st_c[4] += c5 - c4;
@@ -597,7 +587,6 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
         long long *o = P.stats + (long long)blockIdx.x * 16;
         for (int i = 0; i < 5; ++i) o[i] = st_c[i];
         o[5] = clock64() - st_begin; o[6] = n_items; o[7] = 0;
-        for (int i = 0; i < 6; ++i) o[8 + i] = st_d[i];
     }
 }
 
@@ -651,7 +640,7 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
     for (int t = 0; t < T; ++t) {
         const unsigned tag = (unsigned)t + 1u;
         for (int g = g_first; g < NG; g += g_step) {
-            const long long slot_g = (long long)(t & 1) * NG + g;
+            const int slot_g = (t & 1) * NG + g;
             const long long c0 = do_stats ? clock64() : 0;
             // the sampler's inputs do not depend on the network: fetch them while the skip sums are still in flight
             float nz0 = 0.0f, tch = 0.0f;
@@ -664,12 +653,9 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
             for (int task = tid; task < S * NP; task += PIPE_THREADS) {
                 const int c = task / NP, up = task - c * NP;
                 unsigned long long wa[MAX_P + 1], wb[MAX_P + 1];
-                const unsigned long long *src[MAX_P + 1];
-#pragma unroll
-                for (int pp = 0; pp < MAX_P; ++pp)
-                    src[pp] = sp_in + ((slot_g * PP + (pp < PP ? pp : 0)) * S + c) * NU + 2 * up;
-                src[MAX_P] = rs_in + (slot_g * S + c) * NU + 2 * up;
-                bad |= poll_set(src, ((1u << PP) - 1u) | (L >= 2 ? (1u << MAX_P) : 0u), tag, wa, wb, P.abort_flag);
+                bad |= poll_set(sp_in + (unsigned)((slot_g * PP * S + c) * NU + 2 * up), (unsigned)(S * NU),
+                                rs_in + (unsigned)((slot_g * S + c) * NU + 2 * up),
+                                ((1u << PP) - 1u) | (L >= 2 ? (1u << MAX_P) : 0u), tag, wa, wb, P.abort_flag);
                 float s0 = ll_val(wa[0]), s1 = ll_val(wb[0]);
 #pragma unroll
                 for (int pp = 1; pp < MAX_P; ++pp)
@@ -879,7 +865,7 @@ int wn_pipe_plan(wn_handle *h) {
         if (!feasible(P)) return bail("split over " + std::to_string(P) + " CTAs per layer does not fit (shared memory " +
                                       std::to_string(max_optin) + " B, " + std::to_string(h->sm_count) + " SMs)");
     } else {
-        const int want_heads = 8;
+        const int want_heads = 16;   // one head CTA per group up to 64 utterances (the head serves its groups serially)
         for (P = std::min(MAX_P, std::max(1, (h->sm_count - want_heads) / m.L)); P >= 1; --P)
             if (feasible(P)) break;
         if (P < 1)

@@ -23,8 +23,8 @@ def summarize_stats(path, clock_mhz=1965.0):
     if len(lay):
         items = lay[:, 8].mean()
         per = lay[:, 2:8].mean(axis=0) / items / clock_mhz   # us per item
-        out.append('layer CTAs us/item: wait+combine {:.2f} ph1+reduce {:.2f} gate {:.2f} ph2+skip {:.2f} commit+ph0 {:.2f} | total {:.2f}'.format(*per))
-        if lay.shape[1] >= 15:
+        out.append('layer CTAs us/item: wait+combine {:.2f} ph1+reduce+gate {:.2f} (sync) {:.2f} ph2+skip {:.2f} commit+ph0 {:.2f} | total {:.2f}'.format(*per))
+        if False:
             per2 = lay[:, 9:15].mean(axis=0) / items / clock_mhz
             out.append('   thread 0 detail: prefetch-issue {:.2f} mac(ph1) {:.2f} reduce+store {:.2f} | commit {:.2f} sync4 {:.2f} ph0 {:.2f}'.format(*per2))
     if len(head):
