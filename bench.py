@@ -299,9 +299,26 @@ def run_ours(args):
         lm = float(np.mean(loop_ms))
         alg_bytes = float(info['bytes_per_sample']) * B * T
         achieved = alg_bytes / (lm / 1e3) / 1e9
+        # DRAM traffic per launch: bytes/sample of the committed `ncu --set full` capture (same kernel, same batch, shorter
+        # utterances) scaled to this launch's sample count
+        traffic, traffic_src = None, None
+        try:
+            prof = {}
+            for ln in open(os.path.join(ROOT, 'profiles', 'r1_pipe_ncu_full_summary.csv')):
+                f = ln.strip().split(',')
+                if len(f) == 3 and f[0].startswith('dram__bytes'):
+                    prof[f[0]] = float(f[2]) * {'Gbyte': 1e9, 'Mbyte': 1e6, 'Kbyte': 1e3, 'byte': 1.0}[f[1]]
+            per_sample = (prof['dram__bytes_read.sum'] + prof['dram__bytes_write.sum']) / (64 * 1100)
+            traffic = per_sample * B * T
+            traffic_src = 'profiles/r1_pipe_ncu_full_summary.csv: {:.0f} B/sample measured at B=64, T=1100, scaled to this launch'.format(per_sample)
+        except Exception:
+            pass
+        fp32_peak = 148 * 128 * 2 * 1.965e9 / 1e12   # CUDA-core fp32 peak (FFMA2), nominal: MEASURED_PEAKS.json has no fp32 figure
         roofline = {
             'kernel': 'autoregressive loop kernel ({} engine)'.format(info['engine']), 'bound': 'hbm',
-            'achieved': achieved, 'peak': hbm_peak, 'unit': 'GB/s', 'frac': achieved / hbm_peak, 'traffic': None,
+            'achieved': achieved, 'peak': hbm_peak, 'unit': 'GB/s', 'frac': achieved / hbm_peak, 'traffic': traffic,
+            'traffic_source': traffic_src, 'fp32_peak_tflops_nominal': fp32_peak,
+            'fp32_frac_nominal': info['flops_per_sample'] * B * T / (lm / 1e3) / 1e12 / fp32_peak,
             'peak_source': peak_src, 'algorithmic_bytes_per_launch': alg_bytes,
             'bytes_per_sample': int(info['bytes_per_sample']), 'kernel_ms': lm, 'upsample_ms': float(np.mean(up_ms)),
             'us_per_step': 1e3 * lm / T, 'fp32_tflops': info['flops_per_sample'] * B * T / (lm / 1e3) / 1e12,

@@ -365,7 +365,7 @@ extern "C" int wn_synthesize(wn_handle *h, const float *c, const int32_t *g_ids,
     rc = prep_conditioning(h, c, g_ids, B, Tc, c_up_out, &c_up, &g_emb, st);
     if (rc) return rc;
     WN_CUDA_TRY(h, cudaEventRecord(h->ev[1], st));
-    if (h->engine == WN_ENGINE_PIPELINE) rc = wn_launch_loop_pipe(h, c_up, noise, teacher, B, T, audio, raw, st);
+    if (h->engine == WN_ENGINE_PIPELINE) rc = wn_launch_loop_pipe(h, c_up, noise, teacher, 0, B, T, audio, raw, st);
     else rc = wn_launch_loop_generic(h, c_up, g_emb, noise, teacher, 0, B, T, audio, raw, st);
     if (rc) return rc;
     WN_CUDA_TRY(h, cudaEventRecord(h->ev[2], st));

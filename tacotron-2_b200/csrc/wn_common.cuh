@@ -99,7 +99,7 @@ int wn_pipe_plan(wn_handle *h);   // decides whether the model fits; builds pack
 void wn_pipe_free(wn_handle *h);
 void wn_pipe_fill_info(wn_handle *h, wn_info *info);
 int wn_pipe_check_abort(wn_handle *h);  // after a stream sync: WN_ERR_WATCHDOG if the persistent kernel bailed out
-int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int B, int T,
-                        float *audio, float *raw, cudaStream_t st);
+int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int inputs_mode,
+                        int B, int T, float *audio, float *raw, cudaStream_t st);
 
 int wn_ensure(wn_handle *h, float **p, size_t *cur, size_t need);

@@ -48,6 +48,9 @@ constexpr int LANES = WN_DOT_LANES;            // partial sums per dot16
 constexpr int MAX_P = 8;             // CTAs per layer
 constexpr int MAX_PF = 2;            // 16-byte prefetch loads per thread for the two older taps
 constexpr unsigned SPIN_LIMIT = 1u << 22;
+#ifndef P_BACKOFF_NS
+#define P_BACKOFF_NS 0
+#endif
 
 struct PipeCta {
     int role;                        // 0 layer, 1 head
@@ -80,6 +83,7 @@ struct PipeParams {
     long long *stats;                // optional [CTA][8] clock64 counters (WN_PIPE_STATS), else nullptr
     // call
     const float *c_up, *noise, *teacher;
+    int inputs_mode;                 // WaveNet.step semantics: teacher[t] IS the input of step t, nothing is sampled
     float *audio, *raw;
     int B, T;
 };
@@ -105,6 +109,7 @@ __device__ __forceinline__ int poll_pair(const unsigned long long *src, unsigned
         unsigned long long a, b;
         ld_ll2(src, a, b);
         if (ll_tag(a) == tag && ll_tag(b) == tag) { v0 = ll_val(a); v1 = ll_val(b); return 0; }
+        if (P_BACKOFF_NS) __nanosleep(P_BACKOFF_NS);
         if ((++spins & 0x3ffu) == 0) {
             if (*(volatile int *)abort_flag) return 1;
             if (spins > SPIN_LIMIT) { atomicExch(abort_flag, 1); return 1; }
@@ -324,6 +329,7 @@ __device__ __forceinline__ int poll_set(const unsigned long long *base, unsigned
 #pragma unroll
         for (int i = 0; i <= MAX_P; ++i)
             if ((pending & (1u << i)) && ll_tag(wa[i]) == tag && ll_tag(wb[i]) == tag) pending &= ~(1u << i);
+        if (pending && P_BACKOFF_NS) __nanosleep(P_BACKOFF_NS);
         if (pending && (++spins & 0x3ffu) == 0) {
             if (*(volatile int *)abort_flag) return 1;
             if (spins > SPIN_LIMIT) { atomicExch(abort_flag, 1); return 1; }
@@ -631,7 +637,15 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
 
     // initial input (wavenet.py:433-445): raw 0.0, mulaw mulaw(0) = 0.0
     for (int g = g_first; g < NG; g += g_step)
-        if (tid < NP) st_ll2(P.in + ((long long)0 * NG + g) * NU + 2 * tid, 0.0f, 0.0f, 1u);
+        if (tid < NP) {
+            float i0 = 0.0f, i1 = 0.0f;
+            if (P.inputs_mode) {   // WaveNet.step (wavenet.py:650-721): the first input is x[0]
+                const int b0 = g * NU + 2 * tid;
+                if (b0 < P.B) i0 = P.teacher[(long long)b0 * T];
+                if (b0 + 1 < P.B) i1 = P.teacher[(long long)(b0 + 1) * T];
+            }
+            st_ll2(P.in + ((long long)0 * NG + g) * NU + 2 * tid, i0, i1, 1u);
+        }
 
     int bad = 0;
     long long st_c[4] = {0, 0, 0, 0};
@@ -646,8 +660,8 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
             float nz0 = 0.0f, tch = 0.0f;
             if (tid < NU && g * NU + tid < P.B) {
                 const long long b = g * NU + tid;
-                if (O == 2) nz0 = __ldg(P.noise + ((long long)t * P.B + b) * P.NZ);
-                if (P.teacher) tch = __ldg(P.teacher + b * T + t);
+                if (O == 2 && P.noise) nz0 = __ldg(P.noise + ((long long)t * P.B + b) * P.NZ);
+                if (P.teacher) tch = P.inputs_mode ? (t + 1 < T ? __ldg(P.teacher + b * T + t + 1) : 0.0f) : __ldg(P.teacher + b * T + t);
             }
             // ---- skips = (skips_{L-2} + s_{L-1}) * sqrt(.5); relu ----------------------------------------------
             for (int task = tid; task < S * NP; task += PIPE_THREADS) {
@@ -719,7 +733,9 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
             if (tid < 32) {
                 const int u = tid, b = g * NU + u;
                 float nxt = 0.0f;
-                if (u < NU && b < P.B) {
+                if (u < NU && b < P.B && P.inputs_mode) {
+                    nxt = tch;
+                } else if (u < NU && b < P.B) {
                     const float smp = (O == 2) ? pipe_sample_gaussian(P, outv + u, NU, nz0)
                                                : pipe_sample_mol(P, outv + u, NU, P.noise + ((long long)t * P.B + b) * P.NZ);
                     P.audio[(long long)b * T + t] = P.input_type == WN_INPUT_MULAW ? wn_inv_mulawf(smp) : smp;
@@ -1002,15 +1018,15 @@ int wn_pipe_check_abort(wn_handle *h) {   // call after the stream has been sync
     return WN_ERR_WATCHDOG;
 }
 
-int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int B, int T,
-                        float *audio, float *raw, cudaStream_t st) {
+int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int inputs_mode,
+                        int B, int T, float *audio, float *raw, cudaStream_t st) {
     WnPipePlan *pl = h->pipe;
     if (!pl) { h->err = "pipeline engine not planned"; return WN_ERR_STATE; }
     PipeParams p = pl->prm;
     p.NG = (B + p.NU - 1) / p.NU;
     p.NH = std::min((p.NG + TEAMS - 1) / TEAMS, pl->max_heads);
     p.B = B; p.T = T;
-    p.c_up = c_up; p.noise = noise; p.teacher = teacher; p.audio = audio; p.raw = raw;
+    p.c_up = c_up; p.noise = noise; p.teacher = teacher; p.audio = audio; p.raw = raw; p.inputs_mode = inputs_mode;
     // mailboxes, 8-byte {value, tag} words, zeroed (tag 0 = empty), double buffered on t&1, one set per consumer stage
     // (layers 0..L-1, head = L):  op [2][NG][P][R][NU] | xr [2][NG][R][NU] | sp [2][NG][P][S][NU] | rs [2][NG][S][NU]
     const long long slots = 2ll * p.NG * p.NU;

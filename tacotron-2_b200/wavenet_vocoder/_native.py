@@ -11,7 +11,7 @@ import numpy as np
 from wavenet_vocoder.util import is_scalar_input
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libwavenet_b200.so')
+LIB_PATH = os.environ.get('WN_B200_LIB') or os.path.join(_HERE, 'libwavenet_b200.so')   # override: development builds
 
 WN_ABI_VERSION = 2
 MAX_UP = 8

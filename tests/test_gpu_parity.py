@@ -113,7 +113,8 @@ def test_generic_engine_default_config_c1_prefix():
     assert np.all(common.rel_close(raw[:, :550], np.transpose(raw_np, [0, 2, 1])[:, :550]))
 
 
-def test_step_full_matches_oracle_step():
+@pytest.mark.parametrize('engine', ['generic', 'pipeline'])
+def test_step_full_matches_oracle_step(engine):
     hp = common.small()
     w = common.weights_for(hp)
     B, Tc = 2, 4
@@ -121,7 +122,7 @@ def test_step_full_matches_oracle_step():
     c = common.cond_for(hp, B, Tc)
     x = common.teacher_for(hp, B, T)
     from wavenet_vocoder.models import create_model
-    model = create_model('WaveNet', hp, engine='generic')
+    model = create_model('WaveNet', hp, engine=engine)
     model.load_weights(w)
     y = model.step(x[:, None, :], c=np.transpose(c, [0, 2, 1]))
     want = O.WaveNetOracle(hp, w).step(x[:, None, :], c=np.transpose(c, [0, 2, 1]))
