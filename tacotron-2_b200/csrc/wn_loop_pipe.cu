@@ -44,6 +44,7 @@ namespace {
 
 constexpr int PIPE_THREADS = 256;     // threads of one TEAM; a CTA runs TEAMS teams that share the resident weights
 constexpr int TEAMS = 1;              // and work on different utterance groups (g % TEAMS), out of phase with each other
+static_assert(TEAMS == 1, "the layer role runs one team per CTA");
 constexpr int LANES = WN_DOT_LANES;            // partial sums per dot16
 constexpr int MAX_P = 8;             // CTAs per layer
 constexpr int MAX_PF = 2;            // 16-byte prefetch loads per thread for the two older taps
@@ -75,10 +76,11 @@ struct PipeParams {
     const float *blobs;
     const PipeCta *ctas;
     float *rings;
-    // mailboxes: one block per consumer stage (layers 0..L-1, head = L): op | xr | sp | rs (see the host side); `in`
-    // carries the sample fed back from the head to layer 0
+    // mailboxes: one block per consumer stage (layers 0..L-1, head = L): x | rs (see the host side); `in` carries the
+    // sample fed back from the head to layer 0
     unsigned long long *mail, *in;
-    long long stage_sz, xr_off, sp_off, rs_off;    // words
+    long long stage_sz, rs_off;      // words
+    int rmax, RO;                    // largest residual slice; rows of one source in the exchange inbox (rmax + smax)
     int *abort_flag;
     long long *stats;                // optional [CTA][8] clock64 counters (WN_PIPE_STATS), else nullptr
     // call
@@ -115,6 +117,34 @@ __device__ __forceinline__ int poll_pair(const unsigned long long *src, unsigned
             if (spins > SPIN_LIMIT) { atomicExch(abort_flag, 1); return 1; }
         }
     }
+}
+
+// ---- thread-block cluster / distributed shared memory (the P CTAs of a layer form one cluster) ------------------
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ unsigned mapa_u32(unsigned addr, unsigned rank) {   // my shared address -> the same variable of CTA `rank`
+    unsigned r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+// 16-byte store into a peer's shared memory that also counts 16 bytes on the peer's mbarrier (release at cluster scope)
+__device__ __forceinline__ void st_async4(unsigned raddr, float4 v, unsigned rmbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%1, %2, %3, %4}, [%5];"
+                 ::"r"(raddr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(rmbar) : "memory");
+}
+__device__ __forceinline__ void mbar_init(unsigned a, unsigned n) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(a), "r"(n) : "memory");
+}
+__device__ __forceinline__ void mbar_expect(unsigned a, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(a), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ int mbar_try(unsigned a, unsigned parity) {
+    unsigned ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+    return (int)ok;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
 __device__ __forceinline__ int round4(int v) { return (v + 3) & ~3; }
@@ -314,30 +344,6 @@ __device__ float pipe_sample_mol(const PipeParams &P, const float *out, int ostr
     return x < 1.0f ? x : 1.0f;
 }
 
-// Poll up to MAX_P+1 pairs of {value,tag} words at once (all loads in flight together, re-issued only for the
-// ones still pending) until every selected pair carries `tag`.  mask bit i selects src[i].
-// Sources: i < MAX_P -> base + i*stride (the partial sums of producer CTA i), i == MAX_P -> extra.
-__device__ __forceinline__ int poll_set(const unsigned long long *base, unsigned stride, const unsigned long long *extra,
-                                        unsigned mask, unsigned tag,
-                                        unsigned long long (&wa)[MAX_P + 1], unsigned long long (&wb)[MAX_P + 1],
-                                        int *abort_flag) {
-    unsigned pending = mask, spins = 0;
-    while (pending) {
-#pragma unroll
-        for (int i = 0; i <= MAX_P; ++i)
-            if (pending & (1u << i)) ld_ll2(i < MAX_P ? base + i * stride : extra, wa[i], wb[i]);
-#pragma unroll
-        for (int i = 0; i <= MAX_P; ++i)
-            if ((pending & (1u << i)) && ll_tag(wa[i]) == tag && ll_tag(wb[i]) == tag) pending &= ~(1u << i);
-        if (pending && P_BACKOFF_NS) __nanosleep(P_BACKOFF_NS);
-        if (pending && (++spins & 0x3ffu) == 0) {
-            if (*(volatile int *)abort_flag) return 1;
-            if (spins > SPIN_LIMIT) { atomicExch(abort_flag, 1); return 1; }
-        }
-    }
-    return 0;
-}
-
 // ---------------------------------------------------------------------------------------------------------------
 // layer CTA: owns gate channels [h0,h1) of residual layer l  (ResidualConv1DGLU.incremental_step, modules.py:468-521)
 // ---------------------------------------------------------------------------------------------------------------
@@ -347,45 +353,50 @@ __device__ __forceinline__ int poll_set(const unsigned long long *base, unsigned
 template <int NU, int RT, int CT, bool STATS>
 __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) {
     constexpr int NV = 4 * NU, NP = NU / 2;          // accumulators per thread; utterance pairs per group
+    constexpr int XT = 4;                            // exchange tasks per thread at most (checked by the plan)
     const int tid = threadIdx.x % PIPE_THREADS, team = threadIdx.x / PIPE_THREADS;
     const int R = RT ? RT : P.R, S = RT ? RT : P.S, cin = CT ? CT : P.cin;
     const int NG = P.NG, T = P.T, l = me.l, PP = P.P;
     const int KC = 3 * R + cin, KC4 = KC / 4, C0 = (2 * R + cin) / 4;
-    const int hn = me.hn, hq = P.hq, hk = P.hk, NR = P.NR;
+    const int hk = P.hk, NR = P.NR;
     const int d = P.dil[l], depth = P.depth[l];
     const bool last = (l == P.L - 1);
     // ---- shared memory carve-up (weights first: identical to the packed blob) ------------------------------
     float *Wcat = smem;                                  // [NR][KC]      gate rows: row 2j = tanh half, 2j+1 = sigmoid half of channel h0+j
     float *Wos = Wcat + (size_t)NR * KC;                 // [hk/4][R+S][4] columns [h0,h1) of out (rows 0..R) and skip (rows R..R+S)
     float *bsum = Wos + (size_t)(R + S) * hk;            // [NR]
-    float *bpo = bsum + NR;                              // [R]           out-conv bias of layer l-1
-    float *bps = bpo + R;                                // [round4(smax)] skip-conv bias of layer l-1, my slice
+    float *bpo = bsum + NR;                              // [R]           out-conv bias of this layer
+    float *bps = bpo + R;                                // [round4(smax)] skip-conv bias of this layer, my slice
     float *fw = bps + round4(P.smax);                    // [R] first conv (layer 0 only)
     float *fb = fw + R;                                  // [R]
-    float *xc = smem + P.layer_blob_floats + (size_t)team * (KC + NR + hk) * NU;   // per team:
-                                                         // [KC x NU]     x(t-2d) | x(t-d) | c(t) | x(t) in xs_pos order
-    float *pre = xc + (size_t)KC * NU;                   // [NR][NU]
+    float *xc = smem + P.layer_blob_floats;              // [KC x NU]     x(t-2d) | x(t-d) | c(t) | x(t) in xs_pos order
+    float *pre = xc + (size_t)KC * NU;                   // [NR][NU]      (unused: the gate is fused into the reduction)
     float *zs = pre + (size_t)NR * NU;                   // [hk][NU]
+    float *part = zs + (size_t)hk * NU;                  // [2][P][RO][NU] inbox of the intra-layer exchange (written by the
+                                                         //               cluster peers with st.async), double buffered on the item parity
+    unsigned long long *mbar = reinterpret_cast<unsigned long long *>(part + (size_t)2 * PP * P.RO * NU);   // [2]
     {
         const float4 *src = reinterpret_cast<const float4 *>(P.blobs + me.blob);
         float4 *dst = reinterpret_cast<float4 *>(smem);
         for (int i = threadIdx.x; i < P.layer_blob_floats / 4; i += PIPE_THREADS * TEAMS) dst[i] = __ldg(src + i);
         for (int i = tid; i < (KC + NR + hk) * NU; i += PIPE_THREADS) xc[i] = 0.0f;
+        if (threadIdx.x == 0) {
+            mbar_init(smem_u32(&mbar[0]), 1);
+            mbar_init(smem_u32(&mbar[1]), 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
     }
     __syncthreads();
-    if (team >= NG) return;   // fewer groups than teams
+    cluster_sync_all();   // every peer's inbox barriers exist before the first remote store
+    (void)team;
 
     float *ring = P.rings + (size_t)me.ring * NG * R * NU;   // [NG][depth][R x NU]; me.ring counts ring slots
     const int o_cur4 = (2 * R + cin) / 4, R4 = R / 4;
-    // consumer-side mailboxes of this layer (stage l); the producer-side ones (stage l+1) follow at + stage_sz
+    // consumer-side mailboxes of this layer (stage l): x | rs; the producer-side ones (stage l+1) follow at + stage_sz
     unsigned long long *const mbox = P.mail + (long long)l * P.stage_sz;
-#define op_in (mbox)
-#define xr_in (mbox + P.xr_off)
-#define sp_in (mbox + P.sp_off)
+#define x_in (mbox)
 #define rs_in (mbox + P.rs_off)
-#define op_out (mbox + P.stage_sz)
-#define xr_out (mbox + P.stage_sz + P.xr_off)
-#define sp_out (mbox + P.stage_sz + P.sp_off)
+#define x_out (mbox + P.stage_sz)
 #define rs_out (mbox + P.stage_sz + P.rs_off)
 
     // ---- thread roles (everything that only depends on tid is computed once, outside the time loop) -------
@@ -398,8 +409,26 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
     const int NT2 = (R + S) / 2;                            // threads of the blocked chains (2 rows each)
     const bool has_t2 = tid < NT2;
     const int NT2r = (NT2 + 31) & ~31;
-    const int hbase = (NT2r <= PIPE_THREADS - 64) ? NT2r : 0;   // threads [hbase, 256) carry the skip sum meanwhile
+    const int hbase = (NT2r <= PIPE_THREADS - 64) ? NT2r : 0;   // threads [hbase, 256) finish the exchange
     const int hthreads = PIPE_THREADS - hbase;
+    // G: where the two rows of this thread go - the owner CTA of the row (slices lo(n,q) = n*q/P) and the row's place
+    // in the owner's inbox; addresses in the cluster window, inbox of parity 0
+    unsigned g_dst[2] = {0u, 0u}, g_bar[2] = {0u, 0u};
+    const unsigned part_par_bytes = (unsigned)(PP * P.RO * NU * sizeof(float));
+    if (has_t2) {
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int row = tid + i * NT2;
+            int owner, li;
+            if (row < R) { owner = ((row + 1) * PP - 1) / R; li = row - (int)((long long)R * owner / PP); }
+            else { const int c = row - R; owner = ((c + 1) * PP - 1) / S; li = P.rmax + c - (int)((long long)S * owner / PP); }
+            g_dst[i] = mapa_u32(smem_u32(part + ((size_t)me.p * P.RO + li) * NU), (unsigned)owner);
+            g_bar[i] = mapa_u32(smem_u32(&mbar[0]), (unsigned)owner);
+        }
+    }
+    // X: the rows this CTA owns - out rows [r0, r0+rn) (not in the last layer) then skip rows [s0, s0+sn), NP tasks each
+    const int x_rn = last ? 0 : me.rn, x_tasks = (x_rn + me.sn) * NP;
+    const unsigned x_bytes = (unsigned)(PP * (x_rn + me.sn) * NU * sizeof(float));   // what lands in my inbox per item
     // D task of this thread (first loop trip): mailbox row m (e-major: m = (r%4)*R/4 + r/4), utterance pair up
     const int d_m = tid / NP, d_up = tid - d_m * NP, d_e = d_m / R4, d_cr = d_m - d_e * R4;
     // prefetch / commit slots
@@ -464,55 +493,43 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
     const bool do_stats = STATS && P.stats != nullptr && threadIdx.x == 0;
     const long long st_begin = STATS ? clock64() : 0;
 
-    prefetch(team, 0, 0);
+    prefetch(0, 0, 0);
     commit();
-    team_sync(team);
+    team_sync(0);
     phase0();
 
-    const long long n_items = (long long)T * ((NG - team + TEAMS - 1) / TEAMS);   // this team's groups: team, team+TEAMS, ...
-    int t = 0, g = team, rslot = 0;   // rslot = t % depth
+    const long long n_items = (long long)T * NG;
+    int t = 0, g = 0, rslot = 0;   // rslot = t % depth
     for (long long it = 0; it < n_items; ++it) {
         const unsigned tag = (unsigned)t + 1u;
         const int slot_g = (t & 1) * NG + g;
+        const int par = (int)(it & 1);
         const long long c0 = do_stats ? clock64() : 0;
-        // ---- D: wait for the inputs of (t, g) and rebuild x_l(t) ----------------------------------------------
+        // ---- D: wait for x_l(t) of group g (layer 0: the sample fed back by the head) --------------------------
         // mailbox rows are stored e-major (position m = (r%4)*R/4 + r/4), so that consecutive threads read
         // consecutive mailbox words AND write consecutive words of xc and of the ring
         for (int task = tid; task < R * NP; task += PIPE_THREADS) {
             int m = d_m, up = d_up, e = d_e, cr = d_cr;
             if (task != tid) { m = task / NP; up = task - m * NP; e = m / R4; cr = m - e * R4; }
-            const int r = 4 * cr + e;
             float x0, x1;
             if (l == 0) {   // first_conv.incremental_step (wavenet.py:826) on the value the head fed back
+                const int r = 4 * cr + e;
                 float s0, s1;
                 bad |= poll_pair(P.in + slot_g * NU + 2 * up, tag, s0, s1, P.abort_flag);
                 x0 = __fadd_rn(__fmaf_rn(s0, fw[r], 0.0f), fb[r]);
                 x1 = __fadd_rn(__fmaf_rn(s1, fw[r], 0.0f), fb[r]);
-            } else {        // out 1x1 of layer l-1: partial sums in ascending p, bias, residual (modules.py:515-520)
-                unsigned long long wa[MAX_P + 1], wb[MAX_P + 1];
-                bad |= poll_set(op_in + (unsigned)((slot_g * PP * R + m) * NU + 2 * up), (unsigned)(R * NU),
-                                xr_in + (unsigned)((slot_g * R + m) * NU + 2 * up),
-                                ((1u << PP) - 1u) | (1u << MAX_P), tag, wa, wb, P.abort_flag);
-                float y0 = ll_val(wa[0]), y1 = ll_val(wb[0]);
-#pragma unroll
-                for (int pp = 1; pp < MAX_P; ++pp)
-                    if (pp < PP) { y0 = __fadd_rn(y0, ll_val(wa[pp])); y1 = __fadd_rn(y1, ll_val(wb[pp])); }
-                y0 = __fadd_rn(y0, bpo[r]); y1 = __fadd_rn(y1, bpo[r]);
-                y0 = __fadd_rn(y0, ll_val(wa[MAX_P])); y1 = __fadd_rn(y1, ll_val(wb[MAX_P]));
-                x0 = P.residual_legacy ? __fmul_rn(y0, WN_SQRT_HALF) : y0;
-                x1 = P.residual_legacy ? __fmul_rn(y1, WN_SQRT_HALF) : y1;
+            } else {
+                bad |= poll_pair(x_in + (slot_g * R + m) * NU + 2 * up, tag, x0, x1, P.abort_flag);
             }
-            // the residual input x_l(t), slice [r0,r1), travels with the partial sums (the consumer adds it)
-            if (!last && r >= me.r0 && r < me.r0 + me.rn) st_ll2(xr_out + (slot_g * R + m) * NU + 2 * up, x0, x1, tag);
             const int seg = e * (NU / 4) + (up >> 1);
             *reinterpret_cast<float2 *>(xc + (size_t)(seg * KC4 + o_cur4 + cr) * 4 + 2 * (up & 1)) = make_float2(x0, x1);
             __stcg(reinterpret_cast<float2 *>(ring + (size_t)(g * depth + rslot) * R * NU +
                                               (size_t)(seg * R4 + cr) * 4 + 2 * (up & 1)), make_float2(x0, x1));
         }
-        if (team_sync_or(team, bad)) return;                                                         // (1)
+        if (team_sync_or(0, bad)) break;                                                             // (1)
         const long long c1 = do_stats ? clock64() : 0;
-        int g2 = g + TEAMS, t2 = t, rslot2 = rslot;
-        if (g2 >= NG) { g2 = team; t2 = t + 1; rslot2 = rslot + 1 == depth ? 0 : rslot + 1; }
+        int g2 = g + 1, t2 = t, rslot2 = rslot;
+        if (g2 >= NG) { g2 = 0; t2 = t + 1; rslot2 = rslot + 1 == depth ? 0 : rslot + 1; }
         if (t2 < T) prefetch(g2, t2, rslot2);   // ring slots of (t2 - d, g2) were written in an earlier item or just above
         // ---- E: current tap, tree reduction, bias (modules.py:294-297, :497-501) ----------------------------
         if (warp_has_q) {   // warp-uniform: the butterfly shuffles need every lane of the warp
@@ -536,9 +553,10 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
             }
         }
         const long long c2 = do_stats ? clock64() : 0;
-        team_sync(team);                                                                             // (3)
+        team_sync(0);                                                                                // (3)
         const long long c3 = do_stats ? clock64() : 0;
-        // ---- G: my column block of the out / skip 1x1s -> partial sums for layer l+1 / the head ---------------
+        // ---- G: my column block of the out / skip 1x1s -> partial sums, each row sent to the CTA of this layer that
+        //         owns it (reduce-scatter inside the cluster: st.async into the owner's inbox + complete_tx on its barrier)
         if (has_t2) {
             float2 a2[NU];
 #pragma unroll
@@ -546,42 +564,83 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
             chain_tile<NU, 2>(a2, reinterpret_cast<const float4 *>(Wos), R + S, tid, NT2, zs, hk / 4);
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
-                const int row = tid + i * NT2;
-                unsigned long long *dst;
-                if (row < R) {
-                    if (last) continue;
-                    dst = op_out + ((slot_g * PP + me.p) * R + (row & 3) * R4 + (row >> 2)) * NU;
-                } else {
-                    dst = sp_out + ((slot_g * PP + me.p) * S + (row - R)) * NU;
-                }
+                if (last && tid + i * NT2 < R) continue;
+                const unsigned dst = g_dst[i] + (par ? part_par_bytes : 0u), bar = g_bar[i] + (par ? 8u : 0u);
 #pragma unroll
-                for (int up = 0; up < NP; ++up) st_ll2(dst + 2 * up, a2[i * NP + up].x, a2[i * NP + up].y, tag);
+                for (int u4 = 0; u4 < NU / 4; ++u4)
+                    st_async4(dst + 16u * u4, make_float4(a2[i * NP + 2 * u4].x, a2[i * NP + 2 * u4].y,
+                                                          a2[i * NP + 2 * u4 + 1].x, a2[i * NP + 2 * u4 + 1].y), bar);
             }
         }
-        // ---- H: running skip sum through layer l-1, my slice (wavenet.py:833-836), sent to (l+1, p) / the head ---
-        if (l >= 1 && tid >= hbase) {
-            for (int task = tid - hbase; task < me.sn * NP; task += hthreads) {
-                const int cl = task / NP, up = task - cl * NP, c = me.s0 + cl;
-                unsigned long long wa[MAX_P + 1], wb[MAX_P + 1];
-                bad |= poll_set(sp_in + (unsigned)((slot_g * PP * S + c) * NU + 2 * up), (unsigned)(S * NU),
-                                rs_in + (unsigned)((slot_g * S + c) * NU + 2 * up),
-                                ((1u << PP) - 1u) | (l >= 2 ? (1u << MAX_P) : 0u), tag, wa, wb, P.abort_flag);
-                float s0 = ll_val(wa[0]), s1 = ll_val(wb[0]);
+        // ---- X (first half): what the rows I own need besides the partial sums - the residual input x_l(t) (out rows,
+        //      modules.py:515-520) or the running skip sum through layer l-1 (skip rows, wavenet.py:833-836)
+        float xa0[XT], xa1[XT];
+        if (tid >= hbase) {
+            if (tid == hbase) mbar_expect(smem_u32(&mbar[par]), x_bytes);
 #pragma unroll
-                for (int pp = 1; pp < MAX_P; ++pp)
-                    if (pp < PP) { s0 = __fadd_rn(s0, ll_val(wa[pp])); s1 = __fadd_rn(s1, ll_val(wb[pp])); }
-                s0 = __fadd_rn(s0, bps[cl]); s1 = __fadd_rn(s1, bps[cl]);
-                if (l >= 2) {
-                    s0 = __fadd_rn(ll_val(wa[MAX_P]), s0); s1 = __fadd_rn(ll_val(wb[MAX_P]), s1);
-                    if (P.legacy) { s0 = __fmul_rn(s0, WN_SQRT_HALF); s1 = __fmul_rn(s1, WN_SQRT_HALF); }
+            for (int k = 0; k < XT; ++k) {
+                const int task = tid - hbase + k * hthreads;
+                xa0[k] = 0.0f; xa1[k] = 0.0f;
+                if (task < x_tasks) {
+                    const int rl = task / NP, up = task - rl * NP;
+                    if (rl < x_rn) {
+                        const int r = me.r0 + rl, e = r & 3, cr = r >> 2, seg = e * (NU / 4) + (up >> 1);
+                        const float2 xv = *reinterpret_cast<const float2 *>(xc + (size_t)(seg * KC4 + o_cur4 + cr) * 4 + 2 * (up & 1));
+                        xa0[k] = xv.x; xa1[k] = xv.y;
+                    } else if (l >= 1) {
+                        const int c = me.s0 + rl - x_rn;
+                        bad |= poll_pair(rs_in + (slot_g * S + c) * NU + 2 * up, tag, xa0[k], xa1[k], P.abort_flag);
+                    }
                 }
-                st_ll2(rs_out + (slot_g * S + c) * NU + 2 * up, s0, s1, tag);
             }
         }
         const long long c4 = do_stats ? clock64() : 0;
-        // ---- next item: older taps + conditioning into shared memory, then its x(t)-independent part ------------
+        // ---- next item: older taps + conditioning into shared memory ----------------------------------------------
         if (t2 < T) commit();
-        if (team_sync_or(team, bad)) return;                                                         // (4)
+        if (team_sync_or(0, bad)) break;                                                             // (4)
+        // ---- X (second half): partial sums of my rows from all P CTAs of the layer, ascending p, bias, residual /
+        //      running skip sum; x_{l+1}(t) goes to every CTA of layer l+1, the skip sum to (l+1, p) or the head
+        if (tid >= hbase) {
+            unsigned spins = 0;
+            while (!mbar_try(smem_u32(&mbar[par]), (unsigned)(it >> 1) & 1u)) {
+                if ((++spins & 0xffu) == 0) {
+                    if (*(volatile int *)P.abort_flag) { bad = 1; break; }
+                    if (spins > (SPIN_LIMIT >> 4)) { atomicExch(P.abort_flag, 1); bad = 1; break; }
+                }
+            }
+            const float *pin = part + (size_t)par * PP * P.RO * NU;
+#pragma unroll
+            for (int k = 0; k < XT; ++k) {
+                const int task = tid - hbase + k * hthreads;
+                if (task < x_tasks && !bad) {
+                    const int rl = task / NP, up = task - rl * NP;
+                    const bool is_out = rl < x_rn;
+                    const int li = is_out ? rl : P.rmax + rl - x_rn;
+                    float2 y = *reinterpret_cast<const float2 *>(pin + (size_t)li * NU + 2 * up);
+#pragma unroll
+                    for (int pp = 1; pp < MAX_P; ++pp)
+                        if (pp < PP) {
+                            const float2 v = *reinterpret_cast<const float2 *>(pin + ((size_t)pp * P.RO + li) * NU + 2 * up);
+                            y.x = __fadd_rn(y.x, v.x); y.y = __fadd_rn(y.y, v.y);
+                        }
+                    if (is_out) {
+                        const int r = me.r0 + rl;
+                        y.x = __fadd_rn(__fadd_rn(y.x, bpo[r]), xa0[k]); y.y = __fadd_rn(__fadd_rn(y.y, bpo[r]), xa1[k]);
+                        if (P.residual_legacy) { y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF); }
+                        st_ll2(x_out + (slot_g * R + (r & 3) * R4 + (r >> 2)) * NU + 2 * up, y.x, y.y, tag);
+                    } else {
+                        const int cl = rl - x_rn;
+                        y.x = __fadd_rn(y.x, bps[cl]); y.y = __fadd_rn(y.y, bps[cl]);
+                        if (l >= 1) {
+                            y.x = __fadd_rn(xa0[k], y.x); y.y = __fadd_rn(xa1[k], y.y);
+                            if (P.legacy) { y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF); }
+                        }
+                        st_ll2(rs_out + (slot_g * S + me.s0 + cl) * NU + 2 * up, y.x, y.y, tag);
+                    }
+                }
+            }
+        }
+        // ---- the x(t)-independent part of the next item ---------------------------------------------------------------
         if (t2 < T) phase0();
         if (do_stats) {
             const long long c5 = clock64();
@@ -594,15 +653,13 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
         for (int i = 0; i < 5; ++i) o[i] = st_c[i];
         o[5] = clock64() - st_begin; o[6] = n_items; o[7] = 0;
     }
+    __syncthreads();
+    cluster_sync_all();   // no CTA of the cluster leaves while a peer may still store into its inbox
 }
 
-#undef op_in
-#undef xr_in
-#undef sp_in
+#undef x_in
 #undef rs_in
-#undef op_out
-#undef xr_out
-#undef sp_out
+#undef x_out
 #undef rs_out
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -613,13 +670,12 @@ template <int NU, bool STATS>
 __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
     constexpr int NV = 4 * NU, NP = NU / 2;
     const int tid = threadIdx.x % PIPE_THREADS, team = threadIdx.x / PIPE_THREADS;
-    const int S = P.S, O = P.O, NG = P.NG, T = P.T, PP = P.P, L = P.L;
+    const int S = P.S, O = P.O, NG = P.NG, T = P.T, L = P.L;
     const int S4 = S / 4;
     float *W1 = smem;                          // [S][S]   row n = output channel (transposed TF kernel)
     float *W2 = W1 + (size_t)S * S;            // [O][S]
     float *b1 = W2 + (size_t)O * S;            // [S]
     float *b2 = b1 + S;                        // [round4(O)]
-    float *bsl = b2 + round4(O);               // [S]      skip-conv bias of the last layer
     float *hs = smem + P.head_blob_floats + (size_t)team * (2 * S + round4(O)) * NU;   // per team:
                                                // [S x NU] relu(skips), xs_pos order
     float *h1 = hs + (size_t)S * NU;           // [S x NU] xs_pos order
@@ -631,7 +687,7 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
     }
     __syncthreads();
     const int g_first = me.l * TEAMS + team, g_step = P.NH * TEAMS;   // this team's groups
-    const unsigned long long *sp_in = P.mail + (long long)L * P.stage_sz + P.sp_off, *rs_in = sp_in - P.sp_off + P.rs_off;
+    const unsigned long long *rs_in = P.mail + (long long)L * P.stage_sz + P.rs_off;
     const int lane = tid & (LANES - 1), q16 = tid / LANES;
     const int rbase4 = reduce16_base<NV>(lane), rbase1 = reduce16_base<NU>(lane);
 
@@ -663,22 +719,11 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
                 if (O == 2 && P.noise) nz0 = __ldg(P.noise + ((long long)t * P.B + b) * P.NZ);
                 if (P.teacher) tch = P.inputs_mode ? (t + 1 < T ? __ldg(P.teacher + b * T + t + 1) : 0.0f) : __ldg(P.teacher + b * T + t);
             }
-            // ---- skips = (skips_{L-2} + s_{L-1}) * sqrt(.5); relu ----------------------------------------------
+            // ---- relu of the finished skip sum (wavenet.py:833-840; the last layer's CTAs already added their part) ----
             for (int task = tid; task < S * NP; task += PIPE_THREADS) {
                 const int c = task / NP, up = task - c * NP;
-                unsigned long long wa[MAX_P + 1], wb[MAX_P + 1];
-                bad |= poll_set(sp_in + (unsigned)((slot_g * PP * S + c) * NU + 2 * up), (unsigned)(S * NU),
-                                rs_in + (unsigned)((slot_g * S + c) * NU + 2 * up),
-                                ((1u << PP) - 1u) | (L >= 2 ? (1u << MAX_P) : 0u), tag, wa, wb, P.abort_flag);
-                float s0 = ll_val(wa[0]), s1 = ll_val(wb[0]);
-#pragma unroll
-                for (int pp = 1; pp < MAX_P; ++pp)
-                    if (pp < PP) { s0 = __fadd_rn(s0, ll_val(wa[pp])); s1 = __fadd_rn(s1, ll_val(wb[pp])); }
-                s0 = __fadd_rn(s0, bsl[c]); s1 = __fadd_rn(s1, bsl[c]);
-                if (L >= 2) {
-                    s0 = __fadd_rn(ll_val(wa[MAX_P]), s0); s1 = __fadd_rn(ll_val(wb[MAX_P]), s1);
-                    if (P.legacy) { s0 = __fmul_rn(s0, WN_SQRT_HALF); s1 = __fmul_rn(s1, WN_SQRT_HALF); }
-                }
+                float s0, s1;
+                bad |= poll_pair(rs_in + (slot_g * S + c) * NU + 2 * up, tag, s0, s1, P.abort_flag);
                 *reinterpret_cast<float2 *>(hs + xs_pos<NU>(c, 2 * up, S4)) =
                     make_float2(s0 > 0.f ? s0 : 0.f, s1 > 0.f ? s1 : 0.f);
             }
@@ -771,6 +816,7 @@ __global__ void __launch_bounds__(PIPE_THREADS * TEAMS, 1) wn_loop_pipe_kernel(c
 struct WnPipePlan {
     PipeParams prm;                 // model + plan part filled at plan time
     int max_heads = 16;
+    int max_clusters = 0;           // clusters of P CTAs that can be resident at once
     float *d_blobs = nullptr;
     PipeCta *d_ctas = nullptr;
     unsigned long long *d_mail = nullptr;   // op | xr | sp | rs | in
@@ -820,16 +866,37 @@ static const void *pipe_kernel(const PipeParams &p, bool stats) {
     return dflt ? (const void *)wn_loop_pipe_kernel<4, 128, 80, false> : (const void *)wn_loop_pipe_kernel<4, 0, 0, false>;
 }
 
+// How many clusters of P CTAs with `smem` bytes of dynamic shared memory fit the device at once.
+static int pipe_max_clusters(const PipeParams &p, size_t smem) {
+    int best = 0;
+    for (int stats = 0; stats < 2; ++stats) {
+        const void *fn = pipe_kernel(p, stats != 0);
+        if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(p.P * 64); cfg.blockDim = dim3(PIPE_THREADS * TEAMS); cfg.dynamicSmemBytes = smem;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = p.P; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, fn, &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
+        best = stats ? std::min(best, n) : n;
+    }
+    return best;
+}
+
 // Fills the geometry that follows from (model, P, NU); returns the dynamic shared memory the kernel needs, 0 if the
 // split does not fit the thread roles.
 static size_t pipe_geometry(const WnModelDev &m, PipeParams &p) {
     auto lo = [&](int n, int q) { return (int)((long long)n * q / p.P); };
     int hmax = 0;
-    p.smax = 0;
+    p.smax = 0; p.rmax = 0;
     for (int q = 0; q < p.P; ++q) {
         hmax = std::max(hmax, lo(m.H, q + 1) - lo(m.H, q));
         p.smax = std::max(p.smax, lo(m.S, q + 1) - lo(m.S, q));
+        p.rmax = std::max(p.rmax, lo(m.R, q + 1) - lo(m.R, q));
     }
+    p.RO = p.rmax + p.smax;
     p.hq = (hmax + 1) & ~1;
     p.hk = r4(hmax);
     p.NR = 2 * p.hq;
@@ -839,9 +906,14 @@ static size_t pipe_geometry(const WnModelDev &m, PipeParams &p) {
     p.C0 = (2 * m.R + m.cin) / 4;
     if (p.NQ * LANES > PIPE_THREADS || (m.R + m.S) / 2 > PIPE_THREADS) return 0;
     if (p.NU * (m.cin / 4) > PIPE_THREADS || 2 * m.R * p.NU / 4 > MAX_PF * PIPE_THREADS) return 0;
+    {   // the exchange tasks of the rows a CTA owns must fit 4 per thread of the threads that do not run the chains
+        const int nt2r = ((m.R + m.S) / 2 + 31) & ~31, hthreads = nt2r <= PIPE_THREADS - 64 ? PIPE_THREADS - nt2r : PIPE_THREADS;
+        if (p.RO * (p.NU / 2) > 4 * hthreads) return 0;
+    }
     p.layer_blob_floats = p.NR * p.KC + (m.R + m.S) * p.hk + p.NR + m.R + r4(p.smax) + 2 * m.R;
-    p.head_blob_floats = m.S * m.S + m.O * m.S + m.S + r4(m.O) + m.S;
-    const size_t layer_smem = sizeof(float) * ((size_t)p.layer_blob_floats + (size_t)TEAMS * (p.KC + p.NR + p.hk) * p.NU);
+    p.head_blob_floats = m.S * m.S + m.O * m.S + m.S + r4(m.O);
+    const size_t layer_smem = sizeof(float) * ((size_t)p.layer_blob_floats + (size_t)(p.KC + p.NR + p.hk) * p.NU +
+                                               (size_t)2 * p.P * p.RO * p.NU) + 2 * sizeof(unsigned long long);
     const size_t head_smem = sizeof(float) * ((size_t)p.head_blob_floats + (size_t)TEAMS * (2 * m.S + r4(m.O)) * p.NU);
     return std::max(layer_smem, head_smem);
 }
@@ -869,12 +941,16 @@ int wn_pipe_plan(wn_handle *h) {
     cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
     // CTAs per layer: the caller's ksplit (it fixes the summation order), else WN_PIPE_P, else the widest split that
     // leaves SMs for the head CTAs
+    // The P CTAs of a layer form one thread-block cluster; all L layer clusters and at least one cluster of head CTAs
+    // must be resident at once (clusters are placed inside one GPC, so this is tighter than the SM count).
     auto feasible = [&](int P) {
         if (P < 1 || P > MAX_P || P > m.H || P > m.S || P > m.R) return false;
-        if (m.L * P + 1 > h->sm_count) return false;
+        if (m.L * P + P > h->sm_count) return false;
         p.P = P;
         const size_t smem = pipe_geometry(m, p);
-        return smem > 0 && smem <= (size_t)max_optin;
+        if (smem == 0 || smem > (size_t)max_optin) return false;
+        pl->max_clusters = pipe_max_clusters(p, smem);
+        return pl->max_clusters >= m.L + 1;
     };
     int P = c.ksplit > 0 ? c.ksplit : env_int("WN_PIPE_P", 0);
     if (P > 0) {
@@ -891,7 +967,8 @@ int wn_pipe_plan(wn_handle *h) {
     }
     p.P = P;
     pl->smem_bytes = pipe_geometry(m, p);
-    pl->max_heads = std::min(32, h->sm_count - m.L * p.P);
+    pl->max_clusters = pipe_max_clusters(p, pl->smem_bytes);
+    pl->max_heads = std::min((32 / p.P > 0 ? 32 / p.P : 1) * p.P, (pl->max_clusters - m.L) * p.P);   // whole clusters of head CTAs
     m.ksplit = p.P;
 
     // ---- pack weights: one blob per layer CTA in its shared-memory layout, one head blob ---------------------
@@ -909,8 +986,7 @@ int wn_pipe_plan(wn_handle *h) {
         const float *cw = Wt(pre + "causal_conv/kernel"), *cb = Wt(pre + "causal_conv/bias");
         const float *iw = Wt(pre + "cin_conv/kernel"), *ib = Wt(pre + "cin_conv/bias");
         const float *ow = Wt(pre + "out_conv/kernel"), *sw = Wt(pre + "skip_conv/kernel");
-        std::string prv = "ResidualConv1DGLU_" + std::to_string(l - 1) + "/residual_block_";
-        const float *pob = l > 0 ? Wt(prv + "out_conv/bias") : nullptr, *psb = l > 0 ? Wt(prv + "skip_conv/bias") : nullptr;
+        const float *pob = Wt(pre + "out_conv/bias"), *psb = Wt(pre + "skip_conv/bias");
         const float *f = Wt("input_convolution/kernel"), *fbb = Wt("input_convolution/bias");
         for (int q = 0; q < p.P; ++q) {
             PipeCta ct;
@@ -949,14 +1025,12 @@ int wn_pipe_plan(wn_handle *h) {
     {
         const long long hb = (long long)m.L * p.P * p.layer_blob_floats;
         float *b = blobs.data() + hb;
-        float *W1 = b, *W2 = W1 + (size_t)S * S, *b1 = W2 + (size_t)m.O * S, *b2 = b1 + S, *bsl = b2 + r4(m.O);
+        float *W1 = b, *W2 = W1 + (size_t)S * S, *b1 = W2 + (size_t)m.O * S, *b2 = b1 + S;
         const float *w1 = Wt("final_convolution_1/kernel"), *bb1 = Wt("final_convolution_1/bias");
         const float *w2 = Wt("final_convolution_2/kernel"), *bb2 = Wt("final_convolution_2/bias");
-        const float *lsb = Wt("ResidualConv1DGLU_" + std::to_string(m.L - 1) + "/residual_block_skip_conv/bias");
         for (int n = 0; n < S; ++n) {
             for (int k = 0; k < S; ++k) W1[(size_t)n * S + k] = w1[(size_t)k * S + n];
             b1[n] = bb1 ? bb1[n] : 0.0f;
-            bsl[n] = lsb ? lsb[n] : 0.0f;
         }
         for (int n = 0; n < m.O; ++n) {
             for (int k = 0; k < S; ++k) W2[(size_t)n * S + k] = w2[(size_t)k * m.O + n];
@@ -1024,14 +1098,13 @@ int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, con
     if (!pl) { h->err = "pipeline engine not planned"; return WN_ERR_STATE; }
     PipeParams p = pl->prm;
     p.NG = (B + p.NU - 1) / p.NU;
-    p.NH = std::min((p.NG + TEAMS - 1) / TEAMS, pl->max_heads);
+    p.NH = std::min((p.NG + p.P - 1) / p.P * p.P, pl->max_heads);   // whole clusters; surplus head CTAs have no group
     p.B = B; p.T = T;
     p.c_up = c_up; p.noise = noise; p.teacher = teacher; p.audio = audio; p.raw = raw; p.inputs_mode = inputs_mode;
     // mailboxes, 8-byte {value, tag} words, zeroed (tag 0 = empty), double buffered on t&1, one set per consumer stage
-    // (layers 0..L-1, head = L):  op [2][NG][P][R][NU] | xr [2][NG][R][NU] | sp [2][NG][P][S][NU] | rs [2][NG][S][NU]
+    // (layers 0..L-1, head = L):  x [2][NG][R][NU] | rs [2][NG][S][NU]
     const long long slots = 2ll * p.NG * p.NU;
-    const long long op_sz = slots * p.P * p.R, xr_sz = slots * p.R, sp_sz = slots * p.P * p.S, rs_sz = slots * p.S;
-    p.xr_off = op_sz; p.sp_off = op_sz + xr_sz; p.rs_off = op_sz + xr_sz + sp_sz; p.stage_sz = op_sz + xr_sz + sp_sz + rs_sz;
+    p.rs_off = slots * p.R; p.stage_sz = slots * (p.R + p.S);
     const size_t stages = (size_t)p.L + 1;
     const size_t words = stages * (size_t)p.stage_sz + (size_t)slots;
     if (pl->mail_words < words) {
@@ -1061,8 +1134,17 @@ int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, con
         if (!pl->d_stats) cudaMalloc((void **)&pl->d_stats, sizeof(long long) * 16 * 512);
         if (pl->d_stats) { cudaMemsetAsync(pl->d_stats, 0, sizeof(long long) * 16 * 512, st); p.stats = pl->d_stats; pl->stats_ctas = grid; }
     }
+    // every CTA must be resident for the whole launch (they wait for each other): cooperative launch, clusters of P
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(PIPE_THREADS * TEAMS); cfg.dynamicSmemBytes = pl->smem_bytes; cfg.stream = st;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = p.P; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeCooperative;
+    at[1].val.cooperative = 1;
+    cfg.attrs = at; cfg.numAttrs = 2;
     void *args[] = {&p};
-    WN_CUDA_TRY(h, cudaLaunchCooperativeKernel(pipe_kernel(p, p.stats != nullptr), dim3(grid), dim3(PIPE_THREADS * TEAMS), args, pl->smem_bytes, st));
+    WN_CUDA_TRY(h, cudaLaunchKernelExC(&cfg, pipe_kernel(p, p.stats != nullptr), args));
     h->launches++;
     WN_CUDA_TRY(h, cudaMemcpyAsync(pl->h_abort, pl->d_abort, sizeof(int), cudaMemcpyDeviceToHost, st));
     return WN_OK;

@@ -86,7 +86,7 @@ def test_pipeline_default_config_bit_exact():
     _check(net, hp, w, 6, 4)
 
 
-@pytest.mark.parametrize('P', [4, 7])
+@pytest.mark.parametrize('P', [4, 5])
 def test_pipeline_default_config_plans(P):
     hp = common.default_22k()
     w = common.weights_for(hp)
