@@ -40,6 +40,13 @@
 
 #include "wn_common.cuh"
 
+#ifndef WN_CHAIN_ROWS
+#define WN_CHAIN_ROWS 1
+#endif
+#ifndef WN_EARLY_RS
+#define WN_EARLY_RS 1
+#endif
+
 namespace {
 
 constexpr int PIPE_THREADS = 256;     // threads of one TEAM; a CTA runs TEAMS teams that share the resident weights
@@ -47,10 +54,18 @@ constexpr int TEAMS = 1;              // and work on different utterance groups 
 static_assert(TEAMS == 1, "the layer role runs one team per CTA");
 constexpr int LANES = WN_DOT_LANES;            // partial sums per dot16
 constexpr int MAX_P = 8;             // CTAs per layer
+constexpr int CR = WN_CHAIN_ROWS;    // rows of the out / skip 1x1s per thread of the blocked chains
 constexpr int MAX_PF = 2;            // 16-byte prefetch loads per thread for the two older taps
 constexpr unsigned SPIN_LIMIT = 1u << 22;
 #ifndef P_BACKOFF_NS
 #define P_BACKOFF_NS 0
+#endif
+// Development aid (tools/ablate.sh): -DWN_ABLATE=<bits> removes one phase of the layer role so that its share of the
+// step time can be read off the production kernel (results are then wrong, the data flow is intact).  0 in every build
+// that ships.  1 gate -> identity, 2 no current-tap mac, 4 no chains, 8 no phase0, 16 no ring store / prefetch,
+// 32 no reduce16, 64 no intra-layer exchange
+#ifndef WN_ABLATE
+#define WN_ABLATE 0
 #endif
 
 struct PipeCta {
@@ -248,6 +263,25 @@ __device__ __forceinline__ void mac_lane(float2 (&acc)[ROWS * NU / 2], const flo
     }
 }
 
+// Same partial as mac_lane over NC chunks c_first, c_first+16, ... with the weights already in registers (the current-tap
+// columns of the gate matrix never change: a layer CTA keeps its 4 x NC float4 per thread for the whole launch, which
+// takes the weight loads off the critical path between "x_l(t) arrived" and "gate").
+template <int NU, int ROWS, int NC>
+__device__ __forceinline__ void mac_lane_wreg(float2 (&acc)[ROWS * NU / 2], const float4 (&w)[ROWS][NC],
+                                              int KC4, const float *__restrict__ xs, int c_first) {
+    const float4 *x4 = reinterpret_cast<const float4 *>(xs);
+    MacOps<NU, ROWS> o[NC];
+#pragma unroll
+    for (int j = 0; j < NC; ++j) {
+#pragma unroll
+        for (int i = 0; i < ROWS; ++i) o[j].w[i] = w[i][j];
+#pragma unroll
+        for (int u = 0; u < NU; ++u) o[j].x[u] = x4[u * KC4 + c_first + j * LANES];
+    }
+#pragma unroll
+    for (int j = 0; j < NC; ++j) mac_fma<NU, ROWS>(acc, o[j]);
+}
+
 // Butterfly of the 16 lanes' partials: neighbours first (the tree of wn_oracle.c:dot16).  While a lane holds more
 // than one value each step also halves what it keeps (the lane with the mask bit set keeps the upper half), so
 // the whole reduction of NV values costs NV-1 shuffles instead of 4*NV.  On return the lane holds NV/16 (at least
@@ -318,6 +352,31 @@ __device__ __forceinline__ void chain_tile(float2 (&acc)[ROWS * NU / 2], const f
     }
 }
 
+// One instruction stream for both gate activations (modules.py:510): the lanes of a warp hold tanh and sigmoid
+// pre-activations side by side, and calling wn_tanhf / wn_sigmoidf under a branch makes the warp run the tanh polynomial,
+// the tanh exponential path and the sigmoid one after the other.  Operation for operation this is wn_tanhf(x) for
+// sig = false and wn_sigmoidf(x) for sig = true (include/wn_math.h), with selects instead of branches: same bits.
+__device__ __forceinline__ float gate_act(float x, bool sig) {
+    const float ax = fabsf(x);
+    const float e = wn_expf(sig ? -x : __fadd_rn(ax, ax));
+    const float qd = __fdiv_rn(sig ? 1.0f : 2.0f, sig ? __fadd_rn(1.0f, e) : __fadd_rn(e, 1.0f));
+    float r = sig ? qd : __fsub_rn(1.0f, qd);
+    const float z = __fmul_rn(x, x);
+    float p = -5.70498872745e-3f;
+    p = __fmaf_rn(p, z, 2.06390887954e-2f);
+    p = __fmaf_rn(p, z, -5.37397155531e-2f);
+    p = __fmaf_rn(p, z, 1.33314422036e-1f);
+    p = __fmaf_rn(p, z, -3.33332819422e-1f);
+    const float small = __fmaf_rn(__fmul_rn(p, z), x, x);
+    if (!sig) {
+        if (ax > 9.02f) r = 1.0f;
+        if (x < 0.0f) r = -r;
+        if (ax < 0.625f) r = small;
+        if (!(x == x)) r = x;
+    }
+    return r;
+}
+
 __device__ float pipe_sample_gaussian(const PipeParams &P, const float *out, int ostride, float eps) {  // gaussian.py:39-52
     float mean = out[0];
     float ls = out[ostride] > P.log_scale_min_gauss ? out[ostride] : P.log_scale_min_gauss;
@@ -356,10 +415,9 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
     constexpr int XT = 4;                            // exchange tasks per thread at most (checked by the plan)
     const int tid = threadIdx.x % PIPE_THREADS, team = threadIdx.x / PIPE_THREADS;
     const int R = RT ? RT : P.R, S = RT ? RT : P.S, cin = CT ? CT : P.cin;
-    const int NG = P.NG, T = P.T, l = me.l, PP = P.P;
+    const int NG = P.NG, T = P.T, l = me.l, PP = P.P, B = P.B, RO = P.RO, rmax = P.rmax;
     const int KC = 3 * R + cin, KC4 = KC / 4, C0 = (2 * R + cin) / 4;
     const int hk = P.hk, NR = P.NR;
-    const int d = P.dil[l], depth = P.depth[l];
     const bool last = (l == P.L - 1);
     // ---- shared memory carve-up (weights first: identical to the packed blob) ------------------------------
     float *Wcat = smem;                                  // [NR][KC]      gate rows: row 2j = tanh half, 2j+1 = sigmoid half of channel h0+j
@@ -374,7 +432,7 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
     float *zs = pre + (size_t)NR * NU;                   // [hk][NU]
     float *part = zs + (size_t)hk * NU;                  // [2][P][RO][NU] inbox of the intra-layer exchange (written by the
                                                          //               cluster peers with st.async), double buffered on the item parity
-    unsigned long long *mbar = reinterpret_cast<unsigned long long *>(part + (size_t)2 * PP * P.RO * NU);   // [2]
+    unsigned long long *mbar = reinterpret_cast<unsigned long long *>(part + (size_t)2 * P.P * P.RO * NU);   // [2]
     {
         const float4 *src = reinterpret_cast<const float4 *>(P.blobs + me.blob);
         float4 *dst = reinterpret_cast<float4 *>(smem);
@@ -390,14 +448,15 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
     cluster_sync_all();   // every peer's inbox barriers exist before the first remote store
     (void)team;
 
-    float *ring = P.rings + (size_t)me.ring * NG * R * NU;   // [NG][depth][R x NU]; me.ring counts ring slots
     const int o_cur4 = (2 * R + cin) / 4, R4 = R / 4;
+    const int d = P.dil[l], depth = P.depth[l], legacy = P.legacy, residual_legacy = P.residual_legacy;
+    float *const ring = P.rings + (size_t)me.ring * NG * R * NU;   // [NG][depth][R x NU]; me.ring counts ring slots
+    const float *const c_up = P.c_up;
+    int *const abort_flag = P.abort_flag;
     // consumer-side mailboxes of this layer (stage l): x | rs; the producer-side ones (stage l+1) follow at + stage_sz
-    unsigned long long *const mbox = P.mail + (long long)l * P.stage_sz;
-#define x_in (mbox)
-#define rs_in (mbox + P.rs_off)
-#define x_out (mbox + P.stage_sz)
-#define rs_out (mbox + P.stage_sz + P.rs_off)
+    unsigned long long *const x_in = l == 0 ? P.in : P.mail + (long long)l * P.stage_sz;
+    unsigned long long *const rs_in = P.mail + (long long)l * P.stage_sz + P.rs_off;
+    unsigned long long *const x_out = P.mail + (long long)(l + 1) * P.stage_sz, *const rs_out = x_out + P.rs_off;
 
     // ---- thread roles (everything that only depends on tid is computed once, outside the time loop) -------
     const int lane = tid & (LANES - 1), q = tid / LANES;   // dot16: row quad q, partial `lane`
@@ -406,23 +465,25 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
     const float4 *wq = reinterpret_cast<const float4 *>(Wcat) + (size_t)(has_q ? 4 * q : 0) * KC4;
     const int c1_first = C0 + ((lane - C0) % LANES + LANES) % LANES;   // first chunk >= C0 owned by this lane
     const int rbase = reduce16_base<NV>(lane);
-    const int NT2 = (R + S) / 2;                            // threads of the blocked chains (2 rows each)
+    const int NT2 = (R + S) / CR;                           // threads of the blocked chains (CR rows each)
     const bool has_t2 = tid < NT2;
     const int NT2r = (NT2 + 31) & ~31;
     const int hbase = (NT2r <= PIPE_THREADS - 64) ? NT2r : 0;   // threads [hbase, 256) finish the exchange
     const int hthreads = PIPE_THREADS - hbase;
     // G: where the two rows of this thread go - the owner CTA of the row (slices lo(n,q) = n*q/P) and the row's place
     // in the owner's inbox; addresses in the cluster window, inbox of parity 0
-    unsigned g_dst[2] = {0u, 0u}, g_bar[2] = {0u, 0u};
-    const unsigned part_par_bytes = (unsigned)(PP * P.RO * NU * sizeof(float));
+    unsigned g_dst[CR], g_bar[CR];
+    const unsigned part_par_bytes = (unsigned)(PP * RO * NU * sizeof(float));
+#pragma unroll
+    for (int i = 0; i < CR; ++i) { g_dst[i] = 0u; g_bar[i] = 0u; }
     if (has_t2) {
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < CR; ++i) {
             const int row = tid + i * NT2;
             int owner, li;
             if (row < R) { owner = ((row + 1) * PP - 1) / R; li = row - (int)((long long)R * owner / PP); }
-            else { const int c = row - R; owner = ((c + 1) * PP - 1) / S; li = P.rmax + c - (int)((long long)S * owner / PP); }
-            g_dst[i] = mapa_u32(smem_u32(part + ((size_t)me.p * P.RO + li) * NU), (unsigned)owner);
+            else { const int c = row - R; owner = ((c + 1) * PP - 1) / S; li = rmax + c - (int)((long long)S * owner / PP); }
+            g_dst[i] = mapa_u32(smem_u32(part + ((size_t)me.p * RO + li) * NU), (unsigned)owner);
             g_bar[i] = mapa_u32(smem_u32(&mbar[0]), (unsigned)owner);
         }
     }
@@ -460,14 +521,14 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
                 const int tt = t - (2 - pf_tap[k]) * d;
                 int sl = slot + 1 + (pf_tap[k] ? d : 0);
                 if (sl >= depth) sl -= depth;
-                if (tt >= 0)
+                if (tt >= 0 && !(WN_ABLATE & 16))
                     pft[k] = __ldcg(reinterpret_cast<const float4 *>(ring + (size_t)(g * depth + sl) * R * NU) + pf_rem[k]);
             }
         }
         pfc = make_float4(0.f, 0.f, 0.f, 0.f);
         if (tid < n_c16) {
             const int b = g * NU + pc_u;
-            if (b < P.B) pfc = __ldg(reinterpret_cast<const float4 *>(P.c_up + ((long long)b * T + t) * cin) + pc_c4);
+            if (b < B) pfc = __ldg(reinterpret_cast<const float4 *>(c_up + ((long long)b * T + t) * cin) + pc_c4);
         }
     };
     auto commit = [&]() {
@@ -481,17 +542,37 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
         }
     };
 
+    // current-tap weights of this thread's tile, register resident when the chunk count is a compile-time constant
+    constexpr int NC1 = RT ? RT / 4 / LANES : 1;
+    constexpr bool W1_REGS = RT != 0 && RT % (4 * LANES) == 0 && NC1 <= 2;
+    float4 w1[4][NC1];
+    if (W1_REGS) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < NC1; ++j) w1[i][j] = has_q ? wq[i * KC4 + c1_first + j * LANES] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    // X: the first exchange task of this thread, if it is a skip row - its running-sum word is requested early
+    const int x0_task = tid - hbase;
+    const bool x0_skip = tid >= hbase && l >= 1 && x0_task < x_tasks && x0_task / NP >= x_rn;
+    const int x0_off = x0_skip ? (me.s0 + x0_task / NP - x_rn) * NU + 2 * (x0_task % NP) : 0;
+    unsigned long long rs_ea = 0ull, rs_eb = 0ull;
+
     float2 acc[NV / 2];
     auto phase0 = [&]() {   // everything that does not need x_l(t): taps t-2d, t-d and the conditioning column
 #pragma unroll
         for (int i = 0; i < NV / 2; ++i) acc[i] = make_float2(0.0f, 0.0f);
-        if (has_q) mac_lane<NU, 4>(acc, wq, KC4, xc, lane, C0);
+        if (has_q && !(WN_ABLATE & 8)) mac_lane<NU, 4>(acc, wq, KC4, xc, lane, C0);
     };
 
     int bad = 0;
-    long long st_c[5] = {0, 0, 0, 0, 0};
-    const bool do_stats = STATS && P.stats != nullptr && threadIdx.x == 0;
+    // WN_PIPE_STATS: clock64 spent between consecutive stamps, summed over the items, for thread 0 (dot16 / chain
+    // thread) and thread hbase (exchange thread)
+    long long st_c[14] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool do_stats = STATS && P.stats != nullptr && (tid == 0 || tid == hbase);
     const long long st_begin = STATS ? clock64() : 0;
+    long long st_last = st_begin;
+#define STAMP(k) if (do_stats) { const long long now_ = clock64(); st_c[k] += now_ - st_last; st_last = now_; }
 
     prefetch(0, 0, 0);
     commit();
@@ -504,7 +585,7 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
         const unsigned tag = (unsigned)t + 1u;
         const int slot_g = (t & 1) * NG + g;
         const int par = (int)(it & 1);
-        const long long c0 = do_stats ? clock64() : 0;
+        STAMP(13);
         // ---- D: wait for x_l(t) of group g (layer 0: the sample fed back by the head) --------------------------
         // mailbox rows are stored e-major (position m = (r%4)*R/4 + r/4), so that consecutive threads read
         // consecutive mailbox words AND write consecutive words of xc and of the ring
@@ -515,28 +596,36 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
             if (l == 0) {   // first_conv.incremental_step (wavenet.py:826) on the value the head fed back
                 const int r = 4 * cr + e;
                 float s0, s1;
-                bad |= poll_pair(P.in + slot_g * NU + 2 * up, tag, s0, s1, P.abort_flag);
+                bad |= poll_pair(x_in + slot_g * NU + 2 * up, tag, s0, s1, abort_flag);
                 x0 = __fadd_rn(__fmaf_rn(s0, fw[r], 0.0f), fb[r]);
                 x1 = __fadd_rn(__fmaf_rn(s1, fw[r], 0.0f), fb[r]);
             } else {
-                bad |= poll_pair(x_in + (slot_g * R + m) * NU + 2 * up, tag, x0, x1, P.abort_flag);
+                bad |= poll_pair(x_in + (slot_g * R + m) * NU + 2 * up, tag, x0, x1, abort_flag);
             }
             const int seg = e * (NU / 4) + (up >> 1);
             *reinterpret_cast<float2 *>(xc + (size_t)(seg * KC4 + o_cur4 + cr) * 4 + 2 * (up & 1)) = make_float2(x0, x1);
-            __stcg(reinterpret_cast<float2 *>(ring + (size_t)(g * depth + rslot) * R * NU +
-                                              (size_t)(seg * R4 + cr) * 4 + 2 * (up & 1)), make_float2(x0, x1));
+            if (!(WN_ABLATE & 16))
+                __stcg(reinterpret_cast<float2 *>(ring + (size_t)(g * depth + rslot) * R * NU +
+                                                  (size_t)(seg * R4 + cr) * 4 + 2 * (up & 1)), make_float2(x0, x1));
         }
+        STAMP(0);
         if (team_sync_or(0, bad)) break;                                                             // (1)
-        const long long c1 = do_stats ? clock64() : 0;
+        STAMP(1);
         int g2 = g + 1, t2 = t, rslot2 = rslot;
         if (g2 >= NG) { g2 = 0; t2 = t + 1; rslot2 = rslot + 1 == depth ? 0 : rslot + 1; }
         if (t2 < T) prefetch(g2, t2, rslot2);   // ring slots of (t2 - d, g2) were written in an earlier item or just above
+        STAMP(2);
         // ---- E: current tap, tree reduction, bias (modules.py:294-297, :497-501) ----------------------------
         if (warp_has_q) {   // warp-uniform: the butterfly shuffles need every lane of the warp
-            if (has_q) mac_lane<NU, 4>(acc, wq, KC4, xc, c1_first, KC4);
+            if (has_q && !(WN_ABLATE & 2)) {
+                if (W1_REGS) mac_lane_wreg<NU, 4, NC1>(acc, w1, KC4, xc, c1_first);
+                else mac_lane<NU, 4>(acc, wq, KC4, xc, c1_first, KC4);
+            }
+            STAMP(3);
             float a[NV];
             unpack2<NV>(acc, a);
-            reduce16<NV>(a, lane);
+            if (!(WN_ABLATE & 32)) reduce16<NV>(a, lane);
+            STAMP(4);
             // gate (modules.py:510).  Rows of a quad are (tanh j, sigmoid j, tanh j+1, sigmoid j+1), so the two halves of
             // one gated value sit in lanes that differ in the bit the butterfly used for tile-row bit 0 (mask 2): every
             // lane evaluates ONE transcendental, one shuffle brings the partner, the tanh lane stores z.
@@ -546,25 +635,28 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
                 float g_act = 0.0f;
                 if (has_q) {
                     const float pv = __fadd_rn(a[i], bsum[row]);
-                    g_act = (ti & 1) ? wn_sigmoidf(pv) : wn_tanhf(pv);
+                    g_act = (WN_ABLATE & 1) ? pv : gate_act(pv, (ti & 1) != 0);
                 }
                 const float o_act = __shfl_xor_sync(0xffffffffu, g_act, 2);
                 if (has_q && !(ti & 1)) zs[(size_t)(2 * q + (ti >> 1)) * NU + u] = __fmul_rn(g_act, o_act);
             }
         }
-        const long long c2 = do_stats ? clock64() : 0;
+        STAMP(5);
+        // the running skip sum left layer l-1 together with x_l(t): ask for it now, look at it after the chains
+        if (WN_EARLY_RS && x0_skip) ld_ll2(rs_in + slot_g * S * NU + x0_off, rs_ea, rs_eb);
         team_sync(0);                                                                                // (3)
-        const long long c3 = do_stats ? clock64() : 0;
+        STAMP(6);
         // ---- G: my column block of the out / skip 1x1s -> partial sums, each row sent to the CTA of this layer that
         //         owns it (reduce-scatter inside the cluster: st.async into the owner's inbox + complete_tx on its barrier)
         if (has_t2) {
-            float2 a2[NU];
+            float2 a2[CR * NP];
 #pragma unroll
-            for (int i = 0; i < NU; ++i) a2[i] = make_float2(0.0f, 0.0f);
-            chain_tile<NU, 2>(a2, reinterpret_cast<const float4 *>(Wos), R + S, tid, NT2, zs, hk / 4);
+            for (int i = 0; i < CR * NP; ++i) a2[i] = make_float2(0.0f, 0.0f);
+            if (!(WN_ABLATE & 4)) chain_tile<NU, CR>(a2, reinterpret_cast<const float4 *>(Wos), R + S, tid, NT2, zs, hk / 4);
+            STAMP(7);
 #pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                if (last && tid + i * NT2 < R) continue;
+            for (int i = 0; i < CR; ++i) {
+                if ((last && tid + i * NT2 < R) || (WN_ABLATE & 64)) continue;
                 const unsigned dst = g_dst[i] + (par ? part_par_bytes : 0u), bar = g_bar[i] + (par ? 8u : 0u);
 #pragma unroll
                 for (int u4 = 0; u4 < NU / 4; ++u4)
@@ -572,11 +664,12 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
                                                           a2[i * NP + 2 * u4 + 1].x, a2[i * NP + 2 * u4 + 1].y), bar);
             }
         }
+        STAMP(8);
         // ---- X (first half): what the rows I own need besides the partial sums - the residual input x_l(t) (out rows,
         //      modules.py:515-520) or the running skip sum through layer l-1 (skip rows, wavenet.py:833-836)
         float xa0[XT], xa1[XT];
         if (tid >= hbase) {
-            if (tid == hbase) mbar_expect(smem_u32(&mbar[par]), x_bytes);
+            if (tid == hbase && !(WN_ABLATE & 64)) mbar_expect(smem_u32(&mbar[par]), x_bytes);
 #pragma unroll
             for (int k = 0; k < XT; ++k) {
                 const int task = tid - hbase + k * hthreads;
@@ -589,78 +682,78 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
                         xa0[k] = xv.x; xa1[k] = xv.y;
                     } else if (l >= 1) {
                         const int c = me.s0 + rl - x_rn;
-                        bad |= poll_pair(rs_in + (slot_g * S + c) * NU + 2 * up, tag, xa0[k], xa1[k], P.abort_flag);
+                        if (k == 0 && WN_EARLY_RS && ll_tag(rs_ea) == tag && ll_tag(rs_eb) == tag) {
+                            xa0[k] = ll_val(rs_ea); xa1[k] = ll_val(rs_eb);
+                        } else {
+                            bad |= poll_pair(rs_in + (slot_g * S + c) * NU + 2 * up, tag, xa0[k], xa1[k], abort_flag);
+                        }
                     }
                 }
             }
         }
-        const long long c4 = do_stats ? clock64() : 0;
+        STAMP(9);
         // ---- next item: older taps + conditioning into shared memory ----------------------------------------------
         if (t2 < T) commit();
+        STAMP(10);
         if (team_sync_or(0, bad)) break;                                                             // (4)
+        STAMP(11);
         // ---- X (second half): partial sums of my rows from all P CTAs of the layer, ascending p, bias, residual /
         //      running skip sum; x_{l+1}(t) goes to every CTA of layer l+1, the skip sum to (l+1, p) or the head
         if (tid >= hbase) {
             unsigned spins = 0;
-            while (!mbar_try(smem_u32(&mbar[par]), (unsigned)(it >> 1) & 1u)) {
+            while (!(WN_ABLATE & 64) && !mbar_try(smem_u32(&mbar[par]), (unsigned)(it >> 1) & 1u)) {
                 if ((++spins & 0xffu) == 0) {
-                    if (*(volatile int *)P.abort_flag) { bad = 1; break; }
-                    if (spins > (SPIN_LIMIT >> 4)) { atomicExch(P.abort_flag, 1); bad = 1; break; }
+                    if (*(volatile int *)abort_flag) { bad = 1; break; }
+                    if (spins > (SPIN_LIMIT >> 4)) { atomicExch(abort_flag, 1); bad = 1; break; }
                 }
             }
-            const float *pin = part + (size_t)par * PP * P.RO * NU;
+            const float *pin = part + (size_t)par * PP * RO * NU;
 #pragma unroll
             for (int k = 0; k < XT; ++k) {
                 const int task = tid - hbase + k * hthreads;
                 if (task < x_tasks && !bad) {
                     const int rl = task / NP, up = task - rl * NP;
                     const bool is_out = rl < x_rn;
-                    const int li = is_out ? rl : P.rmax + rl - x_rn;
+                    const int li = is_out ? rl : rmax + rl - x_rn;
                     float2 y = *reinterpret_cast<const float2 *>(pin + (size_t)li * NU + 2 * up);
 #pragma unroll
                     for (int pp = 1; pp < MAX_P; ++pp)
                         if (pp < PP) {
-                            const float2 v = *reinterpret_cast<const float2 *>(pin + ((size_t)pp * P.RO + li) * NU + 2 * up);
+                            const float2 v = *reinterpret_cast<const float2 *>(pin + ((size_t)pp * RO + li) * NU + 2 * up);
                             y.x = __fadd_rn(y.x, v.x); y.y = __fadd_rn(y.y, v.y);
                         }
                     if (is_out) {
                         const int r = me.r0 + rl;
                         y.x = __fadd_rn(__fadd_rn(y.x, bpo[r]), xa0[k]); y.y = __fadd_rn(__fadd_rn(y.y, bpo[r]), xa1[k]);
-                        if (P.residual_legacy) { y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF); }
+                        if (residual_legacy) { y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF); }
                         st_ll2(x_out + (slot_g * R + (r & 3) * R4 + (r >> 2)) * NU + 2 * up, y.x, y.y, tag);
                     } else {
                         const int cl = rl - x_rn;
                         y.x = __fadd_rn(y.x, bps[cl]); y.y = __fadd_rn(y.y, bps[cl]);
                         if (l >= 1) {
                             y.x = __fadd_rn(xa0[k], y.x); y.y = __fadd_rn(xa1[k], y.y);
-                            if (P.legacy) { y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF); }
+                            if (legacy) { y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF); }
                         }
                         st_ll2(rs_out + (slot_g * S + me.s0 + cl) * NU + 2 * up, y.x, y.y, tag);
                     }
                 }
             }
         }
+        STAMP(12);
         // ---- the x(t)-independent part of the next item ---------------------------------------------------------------
         if (t2 < T) phase0();
-        if (do_stats) {
-            const long long c5 = clock64();
-            st_c[0] += c1 - c0; st_c[1] += c2 - c1; st_c[2] += c3 - c2; st_c[3] += c4 - c3; st_c[4] += c5 - c4;
-        }
         g = g2; t = t2; rslot = rslot2;
     }
     if (do_stats) {
-        long long *o = P.stats + (long long)blockIdx.x * 16;
-        for (int i = 0; i < 5; ++i) o[i] = st_c[i];
-        o[5] = clock64() - st_begin; o[6] = n_items; o[7] = 0;
+        long long *o = P.stats + (long long)blockIdx.x * 32 + (tid == 0 ? 0 : 16);
+        for (int i = 0; i < 14; ++i) o[i] = st_c[i];
+        o[14] = clock64() - st_begin; o[15] = n_items;
     }
+#undef STAMP
     __syncthreads();
     cluster_sync_all();   // no CTA of the cluster leaves while a peer may still store into its inbox
 }
 
-#undef x_in
-#undef rs_in
-#undef x_out
-#undef rs_out
 
 // ---------------------------------------------------------------------------------------------------------------
 // head CTA: last skip accumulation, relu -> 1x1 -> relu -> 1x1 (wavenet.py:833-844), sampler (:850-859) and the
@@ -794,9 +887,9 @@ __device__ void head_role(const PipeParams &P, const PipeCta &me, float *smem) {
         }
     }
     if (do_stats) {
-        long long *o = P.stats + (long long)blockIdx.x * 16;
-        o[0] = st_c[0]; o[1] = st_c[1]; o[2] = st_c[2]; o[3] = st_c[3]; o[4] = 0;
-        o[5] = clock64() - st_begin; o[6] = T; o[7] = 1;
+        long long *o = P.stats + (long long)blockIdx.x * 32;
+        o[0] = st_c[0]; o[1] = st_c[1]; o[2] = st_c[2]; o[3] = st_c[3];
+        o[14] = clock64() - st_begin; o[15] = T;
     }
 }
 
@@ -904,10 +997,10 @@ static size_t pipe_geometry(const WnModelDev &m, PipeParams &p) {
     p.KC = 3 * m.R + m.cin;
     p.KC4 = p.KC / 4;
     p.C0 = (2 * m.R + m.cin) / 4;
-    if (p.NQ * LANES > PIPE_THREADS || (m.R + m.S) / 2 > PIPE_THREADS) return 0;
+    if (p.NQ * LANES > PIPE_THREADS || (m.R + m.S) / CR > PIPE_THREADS || (m.R + m.S) % CR) return 0;
     if (p.NU * (m.cin / 4) > PIPE_THREADS || 2 * m.R * p.NU / 4 > MAX_PF * PIPE_THREADS) return 0;
     {   // the exchange tasks of the rows a CTA owns must fit 4 per thread of the threads that do not run the chains
-        const int nt2r = ((m.R + m.S) / 2 + 31) & ~31, hthreads = nt2r <= PIPE_THREADS - 64 ? PIPE_THREADS - nt2r : PIPE_THREADS;
+        const int nt2r = ((m.R + m.S) / CR + 31) & ~31, hthreads = nt2r <= PIPE_THREADS - 64 ? PIPE_THREADS - nt2r : PIPE_THREADS;
         if (p.RO * (p.NU / 2) > 4 * hthreads) return 0;
     }
     p.layer_blob_floats = p.NR * p.KC + (m.R + m.S) * p.hk + p.NR + m.R + r4(p.smax) + 2 * m.R;
@@ -1071,17 +1164,21 @@ int wn_pipe_check_abort(wn_handle *h) {   // call after the stream has been sync
     if (!h->pipe || !h->pipe->h_abort) return WN_OK;
     const int code = *h->pipe->h_abort;
     if (h->pipe->d_stats && h->pipe->stats_ctas > 0 && getenv("WN_PIPE_STATS")) {   // development aid
-        std::vector<long long> st((size_t)h->pipe->stats_ctas * 16);
+        std::vector<long long> st((size_t)h->pipe->stats_ctas * 32);
         if (cudaMemcpy(st.data(), h->pipe->d_stats, st.size() * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess) {
             FILE *f = fopen(getenv("WN_PIPE_STATS"), "a");
             if (f) {
                 const PipeParams &q = h->pipe->prm;
-                fprintf(f, "# pipe stats: L=%d P=%d NU=%d ctas=%d  cols: cta role wait+combine ph1 gate ph2+skip commit+ph0 total items\n",
-                        q.L, q.P, q.NU, h->pipe->stats_ctas);
+                fprintf(f, "# pipe stats: L=%d P=%d NU=%d ctas=%d  cols: cta role(0 layer,1 head) thread(0 first,1 exchange) "
+                           "stamp0..stamp13 total items\n", q.L, q.P, q.NU, h->pipe->stats_ctas);
                 for (int i = 0; i < h->pipe->stats_ctas; ++i)
-                    fprintf(f, "%d %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld %lld\n", i, st[i * 16 + 7], st[i * 16 + 0],
-                            st[i * 16 + 1], st[i * 16 + 2], st[i * 16 + 3], st[i * 16 + 4], st[i * 16 + 5], st[i * 16 + 6],
-                            st[i * 16 + 8], st[i * 16 + 9], st[i * 16 + 10], st[i * 16 + 11], st[i * 16 + 12], st[i * 16 + 13]);
+                    for (int th = 0; th < 2; ++th) {
+                        const long long *o = st.data() + (size_t)i * 32 + th * 16;
+                        if (o[15] == 0) continue;
+                        fprintf(f, "%d %d %d", i, i >= q.L * q.P ? 1 : 0, th);
+                        for (int k = 0; k < 16; ++k) fprintf(f, " %lld", o[k]);
+                        fprintf(f, "\n");
+                    }
                 fclose(f);
             }
         }
@@ -1131,8 +1228,8 @@ int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, con
     const int grid = p.L * p.P + p.NH;
     p.stats = nullptr;
     if (getenv("WN_PIPE_STATS")) {
-        if (!pl->d_stats) cudaMalloc((void **)&pl->d_stats, sizeof(long long) * 16 * 512);
-        if (pl->d_stats) { cudaMemsetAsync(pl->d_stats, 0, sizeof(long long) * 16 * 512, st); p.stats = pl->d_stats; pl->stats_ctas = grid; }
+        if (!pl->d_stats) cudaMalloc((void **)&pl->d_stats, sizeof(long long) * 32 * 512);
+        if (pl->d_stats) { cudaMemsetAsync(pl->d_stats, 0, sizeof(long long) * 32 * 512, st); p.stats = pl->d_stats; pl->stats_ctas = grid; }
     }
     // every CTA must be resident for the whole launch (they wait for each other): cooperative launch, clusters of P
     cudaLaunchConfig_t cfg = {};
