@@ -10,26 +10,30 @@
 // so while layer 7 works on group 3 layer 6 works on group 4: the serial chain of one group costs ~(L+1) stage
 // latencies per sample, but all SMs stay busy on different groups.  The only feedback edge is sample(t) -> input(t+1).
 //
-// ONE hand-off per layer.  The P CTAs of a layer never talk to each other: each one gates its own channels and then
-// multiplies them with its column block of the out / skip 1x1s, which yields a PARTIAL sum for every output channel
-// (split-K).  The partial sums travel to all P CTAs of layer l+1, which add them up in a fixed order (p = 0, 1, ...),
-// add the bias and the residual input, and so each rebuild the full x_{l+1}(t) they need.  The running skip sum is
-// carried along the same edges (slice p of it by the CTAs (.,p)) and reaches the head with the last layer's partials.
+// ONE global hand-off per layer.  The P CTAs of a layer form a thread-block cluster.  Each one gates its own channels
+// and multiplies them with its column block of the out / skip 1x1s, which yields a PARTIAL sum for every output channel
+// (split-K).  The partial sums are reduce-scattered inside the cluster over distributed shared memory: every row goes,
+// with one 16-byte st.async, into the inbox of the CTA that owns the row and is counted on that CTA's mbarrier
+// (complete_tx); the owner adds the P partials in a fixed order (p = 0, 1, ...), the bias and the residual input, and
+// publishes its finished slice of x_{l+1}(t) to all P CTAs of layer l+1.  The running skip sum is carried along the same
+// edges (slice p of it by the CTAs (.,p)) and reaches the head finished.
 //
-// Hand-off never uses a barrier or a separate flag: every float travels as an 8-byte {value, tag} word (tag = t+1)
-// written with 128-bit stores and polled with 128-bit loads by the consumer ("LL" protocol), so a value is usable
-// the moment it lands in L2.  Mailboxes are double buffered on t&1 (no CTA can be more than one step ahead of another:
-// step t+1 cannot start before the head sampled step t, which needs every CTA's step-t output).
+// The global hand-off never uses a barrier or a separate flag: every float travels as an 8-byte {value, tag} word
+// (tag = t+1) written with 128-bit stores and polled with 128-bit loads by the consumer ("LL" protocol), so a value is
+// usable the moment it lands in L2.  Mailboxes are double buffered on t&1 (no CTA can be more than one step ahead of
+// another: step t+1 cannot start before the head sampled step t, which needs every CTA's step-t output).  The exchange
+// inboxes are double buffered on the item parity: a peer can only be two items ahead of a CTA after that CTA has sent its
+// partials for the item in between, i.e. after it finished reading the inbox the peer is about to overwrite.
 // The dilation history x_l(t-d), x_l(t-2d) lives in a per-CTA ring in global memory (plain floats, written by the CTA
-// itself right after it rebuilt x_l(t)); it is read one work item ahead into registers, together with the
+// itself right after it received x_l(t)); it is read one work item ahead into registers, together with the
 // conditioning column c(t), and the part of the gate pre-activation that only needs those is computed BEFORE x_l(t)
-// arrives, so the per-layer critical path is: poll -> K=R slice of the dot -> gate -> K=H/P chain -> store.
+// arrives, so the per-layer critical path is: poll -> K=R slice of the dot -> gate -> K=H/P chain -> exchange -> store.
 //
 // Arithmetic is the fixed order of DESIGN.md "Arithmetic" (dot16 / blocked chains with ksplit = P), identical in
 // wn_loop_generic.cu and oracle/c/wn_oracle.c, so results are bit-identical to both.
 //
 // Scope: scalar input (raw / mulaw), Gaussian or mixture-of-logistics head, kernel_size 3, local conditioning on,
-// global conditioning off, fp32 weights that fit shared memory (default config: 163 KB per layer CTA at P = 4).
+// global conditioning off, fp32 weights that fit shared memory (default config: 125 KB per layer CTA at P = 6).
 // Anything else runs on the generic engine.
 #include <cooperative_groups.h>
 
@@ -56,7 +60,7 @@ constexpr int LANES = WN_DOT_LANES;            // partial sums per dot16
 constexpr int MAX_P = 8;             // CTAs per layer
 constexpr int CR = WN_CHAIN_ROWS;    // rows of the out / skip 1x1s per thread of the blocked chains
 constexpr int MAX_PF = 2;            // 16-byte prefetch loads per thread for the two older taps
-constexpr unsigned SPIN_LIMIT = 1u << 22;
+constexpr unsigned long long WATCHDOG_NS = 20ull * 1000 * 1000 * 1000;   // a CTA that waits this long for a peer gives up
 #ifndef P_BACKOFF_NS
 #define P_BACKOFF_NS 0
 #endif
@@ -118,18 +122,27 @@ __device__ __forceinline__ void ld_ll2(const unsigned long long *p, unsigned lon
 __device__ __forceinline__ float ll_val(unsigned long long w) { return __uint_as_float((unsigned)(w & 0xffffffffu)); }
 __device__ __forceinline__ unsigned ll_tag(unsigned long long w) { return (unsigned)(w >> 32); }
 
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 // Poll one pair of {value,tag} words until both carry `tag`.  Returns nonzero if the watchdog fired.
 __device__ __forceinline__ int poll_pair(const unsigned long long *src, unsigned tag, float &v0, float &v1,
                                          int *abort_flag) {
     unsigned spins = 0;
+    unsigned long long t_start = 0;
     for (;;) {
         unsigned long long a, b;
         ld_ll2(src, a, b);
         if (ll_tag(a) == tag && ll_tag(b) == tag) { v0 = ll_val(a); v1 = ll_val(b); return 0; }
         if (P_BACKOFF_NS) __nanosleep(P_BACKOFF_NS);
-        if ((++spins & 0x3ffu) == 0) {
+        if ((++spins & 0x3ffu) == 0) {   // watchdog: wall-clock based, so that a slow run (profiler replay) is not mistaken for a hang
             if (*(volatile int *)abort_flag) return 1;
-            if (spins > SPIN_LIMIT) { atomicExch(abort_flag, 1); return 1; }
+            const unsigned long long now = global_timer_ns();
+            if (t_start == 0) t_start = now;
+            else if (now - t_start > WATCHDOG_NS) { atomicExch(abort_flag, 1); return 1; }
         }
     }
 }
@@ -701,10 +714,13 @@ __device__ void layer_role(const PipeParams &P, const PipeCta &me, float *smem) 
         //      running skip sum; x_{l+1}(t) goes to every CTA of layer l+1, the skip sum to (l+1, p) or the head
         if (tid >= hbase) {
             unsigned spins = 0;
+            unsigned long long t_start = 0;
             while (!(WN_ABLATE & 64) && !mbar_try(smem_u32(&mbar[par]), (unsigned)(it >> 1) & 1u)) {
                 if ((++spins & 0xffu) == 0) {
                     if (*(volatile int *)abort_flag) { bad = 1; break; }
-                    if (spins > (SPIN_LIMIT >> 4)) { atomicExch(abort_flag, 1); bad = 1; break; }
+                    const unsigned long long now = global_timer_ns();
+                    if (t_start == 0) t_start = now;
+                    else if (now - t_start > WATCHDOG_NS) { atomicExch(abort_flag, 1); bad = 1; break; }
                 }
             }
             const float *pin = part + (size_t)par * PP * RO * NU;
@@ -1239,7 +1255,8 @@ int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, con
     at[0].val.clusterDim.x = p.P; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     at[1].id = cudaLaunchAttributeCooperative;
     at[1].val.cooperative = 1;
-    cfg.attrs = at; cfg.numAttrs = 2;
+    // WN_PIPE_NO_COOP=1 (profiling aid): plain cluster launch; residency is then only guaranteed by the plan's occupancy check
+    cfg.attrs = at; cfg.numAttrs = env_int("WN_PIPE_NO_COOP", 0) ? 1 : 2;
     void *args[] = {&p};
     WN_CUDA_TRY(h, cudaLaunchKernelExC(&cfg, pipe_kernel(p, p.stats != nullptr), args));
     h->launches++;

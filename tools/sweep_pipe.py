@@ -47,6 +47,7 @@ def main():
     ap.add_argument('--stats', action='store_true')
     ap.add_argument('--hparams', default='default_22k')
     ap.add_argument('--reps', type=int, default=2)
+    ap.add_argument('--profile-range', action='store_true', help='cudaProfilerStart/Stop around the last repetition (ncu --replay-mode app-range)')
     args = ap.parse_args()
     import torch
     import hparams as hp_mod
@@ -85,7 +86,11 @@ def main():
                 if os.path.exists(stats_path):
                     os.remove(stats_path)
                 os.environ['WN_PIPE_STATS'] = stats_path
+            if args.profile_range and r == args.reps - 1:
+                torch.cuda.synchronize(); torch.cuda.profiler.start()
             a = net.synthesize_host(c, nz)
+            if args.profile_range and r == args.reps - 1:
+                torch.cuda.synchronize(); torch.cuda.profiler.stop()
             best = min(best, net.info()['last_loop_ms'])
         os.environ.pop('WN_PIPE_STATS', None)
         finite = bool(np.isfinite(a).all())   # ablated builds (tools/ablate.sh) may overflow
