@@ -23,6 +23,9 @@ import time
 
 import numpy as np
 
+# stdout carries exactly one JSON line: NCCL's own banner (NCCL_DEBUG=VERSION/INFO) goes to stderr
+os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 for p in (ROOT, os.path.join(ROOT, 'tacotron-2_b200')):
     if p not in sys.path:

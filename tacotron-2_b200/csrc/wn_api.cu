@@ -381,9 +381,18 @@ extern "C" int wn_step_full(wn_handle *h, const float *x, const float *c, const 
     cudaStream_t st = (cudaStream_t)stream;
     const int T = Tc * (h->cfg.cin_channels > 0 ? h->cfg.hop_size : 1);
     const float *c_up, *g_emb;
+    if (!h->ev[0])
+        for (int i = 0; i < 3; ++i) WN_CUDA_TRY(h, cudaEventCreate(&h->ev[i]));
+    h->ev_valid = false;
+    WN_CUDA_TRY(h, cudaEventRecord(h->ev[0], st));
     rc = prep_conditioning(h, c, g_ids, B, Tc, nullptr, &c_up, &g_emb, st);
     if (rc) return rc;
-    return wn_launch_step_full(h, x, c_up, g_emb, B, T, raw, st);
+    WN_CUDA_TRY(h, cudaEventRecord(h->ev[1], st));
+    rc = wn_launch_step_full(h, x, c_up, g_emb, B, T, raw, st);
+    if (rc) return rc;
+    WN_CUDA_TRY(h, cudaEventRecord(h->ev[2], st));
+    h->ev_valid = true;
+    return WN_OK;
 }
 
 template <typename T>
@@ -459,6 +468,7 @@ extern "C" const char *wn_last_error(wn_handle *h) { return h ? h->err.c_str() :
 extern "C" void wn_destroy(wn_handle *h) {
     if (!h) return;
     wn_pipe_free(h);
+    wn_gemm_free(h);
     for (int i = 0; i < 3; ++i)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     float *bufs[] = {h->d_blob, h->d_ring, h->d_cup, h->d_tmp0, h->d_tmp1, h->d_gemb, h->d_in_c, h->d_in_noise,

@@ -48,6 +48,7 @@ struct WnHostTensor {
 };
 
 struct WnPipePlan;  // wn_loop_pipe.cu
+struct WnGemmPlan;  // wn_step_gemm.cu
 
 struct wn_handle {
     wn_config cfg;
@@ -71,6 +72,7 @@ struct wn_handle {
     int32_t *d_in_g = nullptr;
     size_t in_c_n = 0, in_noise_n = 0, in_teacher_n = 0, out_audio_n = 0, out_raw_n = 0, in_g_n = 0;
     WnPipePlan *pipe = nullptr;
+    WnGemmPlan *gemm = nullptr;
     int engine = WN_ENGINE_GENERIC;
     int64_t launches = 0;
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};  // before upsample / before loop / after loop
@@ -101,5 +103,10 @@ void wn_pipe_fill_info(wn_handle *h, wn_info *info);
 int wn_pipe_check_abort(wn_handle *h);  // after a stream sync: WN_ERR_WATCHDOG if the persistent kernel bailed out
 int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int inputs_mode,
                         int B, int T, float *audio, float *raw, cudaStream_t st);
+
+// time-parallel WaveNet.step (wn_step_gemm.cu)
+bool wn_gemm_supported(const wn_handle *h);
+void wn_gemm_free(wn_handle *h);
+int wn_launch_step_gemm(wn_handle *h, const float *x, const float *c_up, int B, int T, float *raw, cudaStream_t st);
 
 int wn_ensure(wn_handle *h, float **p, size_t *cur, size_t need);

@@ -113,8 +113,9 @@ def test_generic_engine_default_config_c1_prefix():
     assert np.all(common.rel_close(raw[:, :550], np.transpose(raw_np, [0, 2, 1])[:, :550]))
 
 
-@pytest.mark.parametrize('engine', ['generic', 'pipeline'])
-def test_step_full_matches_oracle_step(engine):
+@pytest.mark.parametrize('path', ['gemm', 'serial-generic', 'serial-pipeline'])
+def test_step_full_matches_oracle_step(path, monkeypatch):
+    """WaveNet.step (wavenet.py:650-721): the time-parallel GEMM kernels and the loop engines in inputs mode."""
     hp = common.small()
     w = common.weights_for(hp)
     B, Tc = 2, 4
@@ -122,12 +123,34 @@ def test_step_full_matches_oracle_step(engine):
     c = common.cond_for(hp, B, Tc)
     x = common.teacher_for(hp, B, T)
     from wavenet_vocoder.models import create_model
-    model = create_model('WaveNet', hp, engine=engine)
+    if path != 'gemm':
+        monkeypatch.setenv('WN_STEP_SERIAL', '1')
+    model = create_model('WaveNet', hp, engine='auto' if path == 'gemm' else path.split('-')[1])
     model.load_weights(w)
     y = model.step(x[:, None, :], c=np.transpose(c, [0, 2, 1]))
     want = O.WaveNetOracle(hp, w).step(x[:, None, :], c=np.transpose(c, [0, 2, 1]))
     assert y.shape == (B, hp.out_channels, T)
     assert np.all(common.rel_close(y, want)), common.max_rel(y, want)
+
+
+@pytest.mark.parametrize('name', ['default_22k', 'mol_2d_nolegacy'])
+def test_step_gemm_equals_serial_step(name, monkeypatch):
+    """The dense-GEMM step against the position-by-position engines (bit-identical to incremental synthesis) on shapes
+    that do not fill the 128-position tiles; utterance starts exercise the causal zero padding of every dilation."""
+    hp = common.default_22k() if name == 'default_22k' else common.small_variants()[name]
+    w = common.weights_for(hp)
+    B, Tc = 3, 3 if name == 'default_22k' else 9
+    T = Tc * hp.hop_size
+    c = common.cond_for(hp, B, Tc)
+    x = common.teacher_for(hp, B, T)
+    from wavenet_vocoder.models import create_model
+    model = create_model('WaveNet', hp)
+    model.load_weights(w)
+    y = model.step(x[:, None, :], c=np.transpose(c, [0, 2, 1]))
+    monkeypatch.setenv('WN_STEP_SERIAL', '1')
+    y_serial = model.step(x[:, None, :], c=np.transpose(c, [0, 2, 1]))
+    assert np.isfinite(y).all() and not np.array_equal(y, np.zeros_like(y))
+    assert np.all(common.rel_close(y, y_serial)), common.max_rel(y, y_serial)
 
 
 def test_synthesizer_end_to_end_ragged(tmp_path):

@@ -9,7 +9,7 @@ for b in "$@"; do   # <ablate bits>[:extra nvcc flags, comma separated], e.g. 0:
   tag="$b$(echo "$extra" | tr -cd 'A-Za-z0-9=' )"
   nvcc $extra -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 --fmad=false -Xcompiler -fPIC -shared -cudart static \
     -DWN_ABLATE=$b tacotron-2_b200/csrc/wn_api.cu tacotron-2_b200/csrc/wn_upsample.cu tacotron-2_b200/csrc/wn_loop_generic.cu \
-    tacotron-2_b200/csrc/wn_loop_pipe.cu tacotron-2_b200/csrc/wn_step_full.cu -o build/libwn_ab$tag.so &
+    tacotron-2_b200/csrc/wn_loop_pipe.cu tacotron-2_b200/csrc/wn_step_full.cu tacotron-2_b200/csrc/wn_step_gemm.cu -o build/libwn_ab$tag.so &
 done
 wait
 ls -la build/libwn_ab*.so
