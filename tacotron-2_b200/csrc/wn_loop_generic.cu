@@ -28,7 +28,23 @@ __device__ __forceinline__ float dot16_lane(const float *xs, int K, int Kpad, co
         const float4 *w4 = reinterpret_cast<const float4 *>(Wt + (long long)n * Kpad);
         const float4 *x4 = reinterpret_cast<const float4 *>(xs);
         const int nfull = K >> 2;
-        for (int c = lane; c < nfull; c += LANES) {
+        // weights stream from L2: issue a batch of independent loads before the dependent fma chain consumes them
+        constexpr int UB = 8;
+        int c = lane;
+        for (; c + (UB - 1) * LANES < nfull; c += UB * LANES) {
+            float4 wv[UB];
+#pragma unroll
+            for (int u = 0; u < UB; ++u) wv[u] = __ldg(w4 + c + u * LANES);
+#pragma unroll
+            for (int u = 0; u < UB; ++u) {
+                const float4 xv = x4[c + u * LANES];
+                acc = __fmaf_rn(xv.x, wv[u].x, acc);
+                acc = __fmaf_rn(xv.y, wv[u].y, acc);
+                acc = __fmaf_rn(xv.z, wv[u].z, acc);
+                acc = __fmaf_rn(xv.w, wv[u].w, acc);
+            }
+        }
+        for (; c < nfull; c += LANES) {
             const float4 wv = __ldg(w4 + c);
             const float4 xv = x4[c];
             acc = __fmaf_rn(xv.x, wv.x, acc);
@@ -53,7 +69,16 @@ __device__ __forceinline__ float dot_blocked_col(const float *__restrict__ zs, i
     for (int p = 0; p < nsplit; ++p) {
         const int k0 = (int)((long long)K * p / nsplit), k1 = (int)((long long)K * (p + 1) / nsplit);
         float acc = 0.0f;
-        for (int k = k0; k < k1; ++k) acc = __fmaf_rn(zs[k], __ldg(W + (long long)k * N + n), acc);
+        constexpr int UB = 16;   // independent loads in flight per thread; the chain itself stays sequential in k
+        int k = k0;
+        for (; k + UB <= k1; k += UB) {
+            float wv[UB];
+#pragma unroll
+            for (int u = 0; u < UB; ++u) wv[u] = __ldg(W + (long long)(k + u) * N + n);
+#pragma unroll
+            for (int u = 0; u < UB; ++u) acc = __fmaf_rn(zs[k + u], wv[u], acc);
+        }
+        for (; k < k1; ++k) acc = __fmaf_rn(zs[k], __ldg(W + (long long)k * N + n), acc);
         y = p == 0 ? acc : __fadd_rn(y, acc);
     }
     return __fadd_rn(y, bias);
