@@ -61,9 +61,6 @@ constexpr int MAX_P = 8;             // CTAs per layer
 constexpr int CR = WN_CHAIN_ROWS;    // rows of the out / skip 1x1s per thread of the blocked chains
 constexpr int MAX_PF = 2;            // 16-byte prefetch loads per thread for the two older taps
 constexpr unsigned long long WATCHDOG_NS = 20ull * 1000 * 1000 * 1000;   // a CTA that waits this long for a peer gives up
-#ifndef P_BACKOFF_NS
-#define P_BACKOFF_NS 0
-#endif
 // Development aid (tools/ablate.sh): -DWN_ABLATE=<bits> removes one phase of the layer role so that its share of the
 // step time can be read off the production kernel (results are then wrong, the data flow is intact).  0 in every build
 // that ships.  1 gate -> identity, 2 no current-tap mac, 4 no chains, 8 no phase0, 16 no ring store / prefetch,
@@ -133,11 +130,12 @@ __device__ __forceinline__ int poll_pair(const unsigned long long *src, unsigned
                                          int *abort_flag) {
     unsigned spins = 0;
     unsigned long long t_start = 0;
+    // One load in flight.  Measured alternatives, both slower: a __nanosleep back-off between polls, and two loads in
+    // flight staggered by half a round trip (finer sampling of L2, but twice the poll traffic).
     for (;;) {
         unsigned long long a, b;
         ld_ll2(src, a, b);
         if (ll_tag(a) == tag && ll_tag(b) == tag) { v0 = ll_val(a); v1 = ll_val(b); return 0; }
-        if (P_BACKOFF_NS) __nanosleep(P_BACKOFF_NS);
         if ((++spins & 0x3ffu) == 0) {   // watchdog: wall-clock based, so that a slow run (profiler replay) is not mistaken for a hang
             if (*(volatile int *)abort_flag) return 1;
             const unsigned long long now = global_timer_ns();
