@@ -23,8 +23,14 @@ import time
 
 import numpy as np
 
-# stdout carries exactly one JSON line: NCCL's own banner (NCCL_DEBUG=VERSION/INFO) goes to stderr
-os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
+# stdout carries exactly ONE JSON line.  Libraries print there too (NCCL's version banner under NCCL_DEBUG=VERSION, for
+# one), so file descriptor 1 is pointed at stderr for the whole run and the JSON line is written to the saved descriptor.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_REAL_STDOUT, (json.dumps(line) + '\n').encode())
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 for p in (ROOT, os.path.join(ROOT, 'tacotron-2_b200')):
@@ -122,7 +128,7 @@ def run_reference(args):
                                  'restatement of its math (oracle/c/wn_oracle.c)'},
         'e2e': {'value': v, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args, hp, B, Tc, n_gpus):
@@ -344,7 +350,7 @@ def run_ours(args):
                 'value': n / dt, 'unit': UNIT, 'cores': cores, 'kind': 'port',
                 'sample': '{} utterances x 24 frames ({} samples), C oracle port (oracle/c/wn_oracle.c), OpenMP over '
                           'utterances, upsample included'.format(cores, n)}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
