@@ -469,6 +469,7 @@ extern "C" void wn_destroy(wn_handle *h) {
     if (!h) return;
     wn_pipe_free(h);
     wn_gemm_free(h);
+    wn_umma_free(h);
     for (int i = 0; i < 3; ++i)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     float *bufs[] = {h->d_blob, h->d_ring, h->d_cup, h->d_tmp0, h->d_tmp1, h->d_gemb, h->d_in_c, h->d_in_noise,

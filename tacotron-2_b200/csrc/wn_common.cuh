@@ -49,6 +49,7 @@ struct WnHostTensor {
 
 struct WnPipePlan;  // wn_loop_pipe.cu
 struct WnGemmPlan;  // wn_step_gemm.cu
+struct WnUmmaPlan;  // wn_step_umma.cu
 
 struct wn_handle {
     wn_config cfg;
@@ -73,6 +74,7 @@ struct wn_handle {
     size_t in_c_n = 0, in_noise_n = 0, in_teacher_n = 0, out_audio_n = 0, out_raw_n = 0, in_g_n = 0;
     WnPipePlan *pipe = nullptr;
     WnGemmPlan *gemm = nullptr;
+    WnUmmaPlan *umma = nullptr;
     int engine = WN_ENGINE_GENERIC;
     int64_t launches = 0;
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};  // before upsample / before loop / after loop
@@ -108,5 +110,10 @@ int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, con
 bool wn_gemm_supported(const wn_handle *h);
 void wn_gemm_free(wn_handle *h);
 int wn_launch_step_gemm(wn_handle *h, const float *x, const float *c_up, int B, int T, float *raw, cudaStream_t st);
+// the two GEMMs of a residual layer on the tensor cores (wn_step_umma.cu: tcgen05.mma, bf16 hi/lo split, fp32 TMEM accumulators)
+bool wn_umma_supported(const wn_handle *h);
+void wn_umma_free(wn_handle *h);
+int wn_umma_layer(wn_handle *h, int l, const float *x, const float *c_up, float *z, float *x_out, float *skips, long long N, int T,
+                  cudaStream_t st);
 
 int wn_ensure(wn_handle *h, float **p, size_t *cur, size_t need);

@@ -980,6 +980,10 @@ void wn_pipe_fill_info(wn_handle *h, wn_info *info) {
 // clock64 counters are separate instantiations so that the production kernel carries no timing registers.
 static const void *pipe_kernel(const PipeParams &p, bool stats) {
     const bool dflt = p.R == 128 && p.S == 128 && p.cin == 80;
+    if (p.NU == 8) {   // groups of 8 utterances: the default block only (throughput regime, see wn_launch_loop_pipe)
+        if (!dflt) return nullptr;
+        return stats ? (const void *)wn_loop_pipe_kernel<8, 128, 80, true> : (const void *)wn_loop_pipe_kernel<8, 128, 80, false>;
+    }
     if (stats) return dflt ? (const void *)wn_loop_pipe_kernel<4, 128, 80, true> : (const void *)wn_loop_pipe_kernel<4, 0, 0, true>;
     return dflt ? (const void *)wn_loop_pipe_kernel<4, 128, 80, false> : (const void *)wn_loop_pipe_kernel<4, 0, 0, false>;
 }
@@ -1054,7 +1058,8 @@ int wn_pipe_plan(wn_handle *h) {
     for (int l = 0; l < m.L; ++l) { p.dil[l] = m.dil[l]; p.depth[l] = 2 * m.dil[l] + 1; }
     auto bail = [&](const std::string &why) { delete pl; h->err = why; return -1; };
     p.NU = env_int("WN_PIPE_NU", 4);
-    if (p.NU != 4) return bail("WN_PIPE_NU must be 4");
+    if (p.NU != 4 && p.NU != 8) return bail("WN_PIPE_NU must be 4 or 8");
+    if (p.NU == 8 && !(m.R == 128 && m.S == 128 && m.cin == 80)) p.NU = 4;
     int max_optin = 0;
     cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
     // CTAs per layer: the caller's ksplit (it fixes the summation order), else WN_PIPE_P, else the widest split that

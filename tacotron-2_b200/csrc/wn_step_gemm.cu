@@ -383,7 +383,14 @@ int wn_launch_step_gemm(wn_handle *h, const float *x, const float *c_up, int B, 
         h->launches++;
     }
     int cur = 0;
+    const bool tensor = wn_umma_supported(h);
     for (int l = 0; l < m.L; ++l) {
+        if (tensor) {   // tcgen05 path (wn_step_umma.cu)
+            rc = wn_umma_layer(h, l, g->d_x[cur], c_up, g->d_z, g->d_x[cur ^ 1], g->d_skips, N, T, st);
+            if (rc) return rc;
+            cur ^= 1;
+            continue;
+        }
         GemmArgs a;
         memset(&a, 0, sizeof(a));
         a.N = N; a.T = T; a.R = m.R; a.cin = m.cin; a.d = m.dil[l]; a.H = m.H; a.S = m.S;

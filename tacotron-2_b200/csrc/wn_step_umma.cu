@@ -1,0 +1,412 @@
+// wn_step_umma.cu - the two GEMMs of a residual layer of WaveNet.step (wavenet.py:650-721, modules.py:305-325, :471-521
+// with is_incremental = False; BASELINE.json config 5) on the sm_100a tensor cores: tcgen05.mma, accumulators in TMEM.
+//
+//   gate     : D[128 positions x 2*NT]  = Xcat[128 x Kcat] * Wg[2*NT x Kcat]^T,  Xcat(n, :) = [x(t-2d) | x(t-d) | c(t) | x(t)]
+//              epilogue bias, tanh * sigmoid (modules.py:510)                                      -> z [N][H]
+//   out/skip : D[128 positions x (R+S)] = z[128 x H] * [W_out ; W_skip]^T, epilogue bias, residual add / scale
+//              (modules.py:515-520) -> x' [N][R], and the skip recursion of wavenet.py:833-836     -> skips [N][S]
+//
+// Precision.  The criterion of this row is fp32 parity with the sample-by-sample engines (1e-3 relative on the
+// distribution parameters after L layers), which one bf16 or tf32 pass does not meet.  Every fp32 operand is therefore
+// split into two bf16 numbers, v = hi + lo (16 significant bits), and a product is accumulated as three tensor-core
+// passes hi*hi + hi*lo + lo*hi into the same fp32 TMEM accumulator (the dropped lo*lo term is below 2^-16 relative).
+// Weights are split once on the host; activations are split while they are staged into shared memory.
+//
+// One CTA = one tile of 128 positions (MMA M = 128, one TMEM lane per position) x 2*NT or R+S <= 256 columns (MMA N),
+// 256 threads, 2 CTAs per SM (96 KB of shared memory and 256 TMEM columns each) so that one CTA stages while the other
+// one's MMAs run.  K is walked in blocks of 64 (16 for the tail of the 80 conditioning channels); per block
+//   * thread 0 asks for the block's packed weights ([hi | lo] x [bk/8][N][8] bf16, exactly the shared-memory image) with
+//     bulk global->shared copies counted on an mbarrier,
+//   * all threads gather their position's 32 activations (loaded one block ahead into registers), split them and store
+//     them in the K-major core-matrix layout of wn_umma.cuh, fence.proxy.async, barrier,
+//   * thread 0 waits for the weights and issues 3 x bk/16 tcgen05.mma, then tcgen05.commit on the "done" mbarrier that
+//     everybody waits on before overwriting the operands.
+// The epilogue reads the accumulator with tcgen05.ld (32 lanes x 16 columns per instruction): a thread owns one
+// position and half of the columns.
+#include <algorithm>
+#include <array>
+#include <cstdlib>
+#include <cstring>
+
+#include "wn_common.cuh"
+#include "wn_umma.cuh"
+
+namespace {
+
+constexpr int UM = 128, UBK = 64, UTHREADS = 256, UMAXBLK = 16;
+constexpr int A_HALF_BYTES = UM * UBK * 2;                 // one of A_hi / A_lo
+constexpr int U_SMEM = 2 * A_HALF_BYTES + 2 * 256 * UBK * 2;   // + B_hi, B_lo at N = 256
+
+enum { UEPI_GATE = 0, UEPI_OUTSKIP = 1 };
+
+struct UBlock {
+    int seg;        // 0: src row of position n - back (zeros before the utterance starts), 1: cond row of position n
+    int koff, bk, back;
+    unsigned w_off; // byte offset of the block's packed weights inside one column tile's weight set
+};
+
+struct UArgs {
+    const unsigned char *W;      // packed bf16 weights of this GEMM: [column tile][block][hi | lo][bk/8][ncols][8]
+    long long tile_w_bytes;
+    const float *bias;           // [column tile][ncols]
+    const float *src, *cond;
+    int src_ld, cond_ld;
+    long long N;
+    int T, ncols, nblk;
+    UBlock blk[UMAXBLK];
+    float *out, *skips;
+    const float *xin;
+    int H, R, S, NT, first_layer, legacy, residual_legacy;
+};
+
+// same operations as wn_tanhf / wn_sigmoidf (include/wn_math.h), one instruction stream (see wn_loop_pipe.cu: gate_act)
+__device__ __forceinline__ float gate_act_u(float x, bool sig) {
+    const float ax = fabsf(x);
+    const float e = wn_expf(sig ? -x : __fadd_rn(ax, ax));
+    const float qd = __fdiv_rn(sig ? 1.0f : 2.0f, sig ? __fadd_rn(1.0f, e) : __fadd_rn(e, 1.0f));
+    float r = sig ? qd : __fsub_rn(1.0f, qd);
+    const float z = __fmul_rn(x, x);
+    float p = -5.70498872745e-3f;
+    p = __fmaf_rn(p, z, 2.06390887954e-2f);
+    p = __fmaf_rn(p, z, -5.37397155531e-2f);
+    p = __fmaf_rn(p, z, 1.33314422036e-1f);
+    p = __fmaf_rn(p, z, -3.33332819422e-1f);
+    const float small = __fmaf_rn(__fmul_rn(p, z), x, x);
+    if (!sig) {
+        if (ax > 9.02f) r = 1.0f;
+        if (x < 0.0f) r = -r;
+        if (ax < 0.625f) r = small;
+        if (!(x == x)) r = x;
+    }
+    return r;
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(UTHREADS, 2) umma_layer_kernel(const __grid_constant__ UArgs a) {
+    extern __shared__ __align__(128) unsigned char usmem[];
+    unsigned char *As_hi = usmem, *As_lo = usmem + A_HALF_BYTES, *Bs = usmem + 2 * A_HALF_BYTES;
+    __shared__ __align__(8) unsigned long long bars[2];
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t full = umma::smem_addr(&bars[0]), done = umma::smem_addr(&bars[1]);
+    if (tid == 0) { umma::mbar_init(full, 1); umma::mbar_init(done, 1); umma::mbar_fence_init(); }
+    if (warp == 0) umma::tmem_alloc(umma::smem_addr(&tmem_slot), 256);
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+    const uint32_t tmem = tmem_slot;
+
+    const long long n0 = (long long)blockIdx.x * UM;
+    const int ty = blockIdx.y, ncols = a.ncols;
+    const unsigned char *Wt = a.W + (long long)ty * a.tile_w_bytes;
+    // staging role: position pos, k half kh of every block
+    const int pos = tid & (UM - 1), kh = tid >> 7;
+    const long long n = n0 + pos;
+    const bool n_ok = n < a.N;
+    const int t = n_ok ? (int)(n % a.T) : 0;
+
+    float4 pf[8];
+    auto load_block = [&](int b) {
+        const UBlock &k = a.blk[b];
+        const int nch = k.bk >> 4;                           // 8-element chunks per thread
+        const float *p = nullptr;
+        if (n_ok) {
+            if (k.seg == 0) { if (t >= k.back) p = a.src + (n - k.back) * a.src_ld + k.koff + kh * (k.bk >> 1); }
+            else p = a.cond + n * a.cond_ld + k.koff + kh * (k.bk >> 1);
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            if (c < nch) {
+                pf[2 * c] = p ? __ldg(reinterpret_cast<const float4 *>(p + 8 * c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                pf[2 * c + 1] = p ? __ldg(reinterpret_cast<const float4 *>(p + 8 * c + 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+    };
+    auto store_block = [&](int b) {
+        const int nch = a.blk[b].bk >> 4;
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            if (c < nch) {
+                uint4 hi, lo;
+                umma::split8(pf[2 * c], pf[2 * c + 1], hi, lo);
+                const int off = ((kh * nch + c) * UM + pos) * 16;
+                *reinterpret_cast<uint4 *>(As_hi + off) = hi;
+                *reinterpret_cast<uint4 *>(As_lo + off) = lo;
+            }
+    };
+
+    const uint32_t idesc = umma::idesc_bf16(UM, ncols);
+    const uint32_t lboA = UM * 16, lboB = (uint32_t)ncols * 16;
+    const uint32_t As_hi_a = umma::smem_addr(As_hi), As_lo_a = umma::smem_addr(As_lo), Bs_a = umma::smem_addr(Bs);
+
+    load_block(0);
+    for (int b = 0; b < a.nblk; ++b) {
+        const int bk = a.blk[b].bk;
+        if (b > 0) umma::mbar_wait(done, (uint32_t)(b - 1) & 1u);   // the MMAs of block b-1 have read their operands
+        if (tid == 0) {
+            const uint32_t bytes = (uint32_t)bk * (uint32_t)ncols * 4u;
+            umma::mbar_expect_tx(full, bytes);
+            const unsigned char *src = Wt + a.blk[b].w_off;
+            for (uint32_t o = 0; o < bytes; o += 16384u)
+                umma::bulk_g2s(Bs_a + o, src + o, bytes - o < 16384u ? bytes - o : 16384u, full);
+        }
+        store_block(b);
+        umma::fence_proxy_async();
+        __syncthreads();
+        if (tid == 0) {
+            umma::mbar_wait(full, (uint32_t)b & 1u);
+            umma::fence_after_sync();
+            const uint32_t Bl_a = Bs_a + (uint32_t)bk * (uint32_t)ncols * 2u;
+            for (int ks = 0; ks < (bk >> 4); ++ks) {
+                const uint64_t ah = umma::smem_desc(As_hi_a + ks * 2 * lboA, lboA, 128), al = umma::smem_desc(As_lo_a + ks * 2 * lboA, lboA, 128);
+                const uint64_t bh = umma::smem_desc(Bs_a + ks * 2 * lboB, lboB, 128), bl = umma::smem_desc(Bl_a + ks * 2 * lboB, lboB, 128);
+                umma::mma_bf16(tmem, ah, bh, idesc, (b > 0 || ks > 0) ? 1u : 0u);
+                umma::mma_bf16(tmem, ah, bl, idesc, 1u);
+                umma::mma_bf16(tmem, al, bh, idesc, 1u);
+            }
+            umma::mma_commit(done);
+        }
+        if (b + 1 < a.nblk) load_block(b + 1);   // in flight while the tensor core works
+    }
+    umma::mbar_wait(done, (uint32_t)(a.nblk - 1) & 1u);
+    umma::fence_after_sync();
+
+    // ---- epilogue: thread = (position 32q + lane, column half) ---------------------------------------------------------
+    const int q = warp & 3, half = warp >> 2;
+    const long long ne = n0 + 32 * q + lane;
+    const bool ne_ok = ne < a.N;
+    const uint32_t tq = tmem + ((uint32_t)(32 * q) << 16);
+    const float *bias = a.bias + (size_t)ty * ncols;
+    if (EPI == UEPI_GATE) {
+        const int NT = a.NT;
+        for (int c = half * (NT / 2); c < (half + 1) * (NT / 2); c += 16) {
+            float ta[16], sg[16];
+            umma::tmem_ld16(tq + (uint32_t)c, ta);
+            umma::tmem_ld16(tq + (uint32_t)(NT + c), sg);
+            umma::tmem_ld_wait();
+            if (ne_ok) {
+                float *zp = a.out + ne * a.H + ty * NT + c;
+#pragma unroll
+                for (int i4 = 0; i4 < 4; ++i4) {
+                    float zz[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float tv = gate_act_u(__fadd_rn(ta[4 * i4 + i], __ldg(bias + c + 4 * i4 + i)), false);
+                        const float sv = gate_act_u(__fadd_rn(sg[4 * i4 + i], __ldg(bias + NT + c + 4 * i4 + i)), true);
+                        zz[i] = __fmul_rn(tv, sv);
+                    }
+                    *reinterpret_cast<float4 *>(zp + 4 * i4) = make_float4(zz[0], zz[1], zz[2], zz[3]);
+                }
+            }
+        }
+    } else {
+        for (int c = half * (ncols / 2); c < (half + 1) * (ncols / 2); c += 16) {
+            float v[16];
+            umma::tmem_ld16(tq + (uint32_t)c, v);
+            umma::tmem_ld_wait();
+            if (!ne_ok) continue;
+            const int m = ty * ncols + c;
+#pragma unroll
+            for (int i4 = 0; i4 < 4; ++i4) {
+                const float4 bb = __ldg(reinterpret_cast<const float4 *>(bias + c + 4 * i4));
+                float4 y = make_float4(__fadd_rn(v[4 * i4], bb.x), __fadd_rn(v[4 * i4 + 1], bb.y), __fadd_rn(v[4 * i4 + 2], bb.z),
+                                       __fadd_rn(v[4 * i4 + 3], bb.w));
+                if (m < a.R) {           // residual (modules.py:515-520)
+                    const float4 xin = *reinterpret_cast<const float4 *>(a.xin + ne * a.R + m + 4 * i4);
+                    y.x = __fadd_rn(y.x, xin.x); y.y = __fadd_rn(y.y, xin.y); y.z = __fadd_rn(y.z, xin.z); y.w = __fadd_rn(y.w, xin.w);
+                    if (a.residual_legacy) {
+                        y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF);
+                        y.z = __fmul_rn(y.z, WN_SQRT_HALF); y.w = __fmul_rn(y.w, WN_SQRT_HALF);
+                    }
+                    *reinterpret_cast<float4 *>(a.out + ne * a.R + m + 4 * i4) = y;
+                } else {                 // skips (wavenet.py:833-836)
+                    float4 *sp = reinterpret_cast<float4 *>(a.skips + ne * a.S + (m - a.R) + 4 * i4);
+                    if (!a.first_layer) {
+                        const float4 s = *sp;
+                        y.x = __fadd_rn(s.x, y.x); y.y = __fadd_rn(s.y, y.y); y.z = __fadd_rn(s.z, y.z); y.w = __fadd_rn(s.w, y.w);
+                        if (a.legacy) {
+                            y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF);
+                            y.z = __fmul_rn(y.z, WN_SQRT_HALF); y.w = __fmul_rn(y.w, WN_SQRT_HALF);
+                        }
+                    }
+                    *sp = y;
+                }
+            }
+        }
+    }
+    umma::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) umma::tmem_dealloc(tmem, 256);
+}
+
+unsigned short bf16_rn_host(float f) {
+    unsigned u;
+    memcpy(&u, &f, 4);
+    if ((u & 0x7f800000u) == 0x7f800000u) return (unsigned short)(u >> 16);   // inf / nan: truncate
+    return (unsigned short)((u + 0x7fffu + ((u >> 16) & 1u)) >> 16);
+}
+float bf16_to_float_host(unsigned short h) {
+    const unsigned u = (unsigned)h << 16;
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+}
+
+struct KBlockHost { int seg, tap, koff, bk, kcat; unsigned w_off; };
+
+// cuts the segments of K into blocks of at most 64 (multiples of 16); w_off for `ncols` columns per tile
+std::vector<KBlockHost> cut_blocks(const std::vector<std::array<int, 3>> &segs /* seg, tap, len */, int ncols, unsigned *total) {
+    std::vector<KBlockHost> out;
+    unsigned off = 0;
+    int kcat = 0;
+    for (const auto &s : segs) {
+        for (int k = 0; k < s[2];) {
+            const int bk = std::min(UBK, s[2] - k);
+            out.push_back({s[0], s[1], k, bk, kcat + k, off});
+            off += (unsigned)bk * (unsigned)ncols * 4u;
+            k += bk;
+        }
+        kcat += s[2];
+    }
+    *total = off;
+    return out;
+}
+
+}  // namespace
+
+struct WnUmmaPlan {
+    unsigned char *d_w = nullptr;
+    float *d_bias = nullptr;
+    int NT = 0, gate_ncols = 0, gate_tiles = 0, os_ncols = 0, os_tiles = 0;
+    unsigned gate_tile_bytes = 0, os_tile_bytes = 0;
+    std::vector<KBlockHost> gate_blk, os_blk;
+    std::vector<size_t> gate_w, os_w, gate_b, os_b;   // per layer: byte offsets into d_w, float offsets into d_bias
+};
+
+void wn_umma_free(wn_handle *h) {
+    WnUmmaPlan *u = h->umma;
+    if (!u) return;
+    if (u->d_w) cudaFree(u->d_w);
+    if (u->d_bias) cudaFree(u->d_bias);
+    delete u;
+    h->umma = nullptr;
+}
+
+bool wn_umma_supported(const wn_handle *h) {
+    const WnModelDev &m = h->m;
+    if (getenv("WN_STEP_FFMA") && atoi(getenv("WN_STEP_FFMA"))) return false;   // fp32 FFMA2 GEMMs (wn_step_gemm.cu)
+    if (!wn_gemm_supported(h)) return false;
+    if (m.H % 64 || (m.R + m.S) % 128 || m.R % 16 || m.cin % 16) return false;
+    if (3 * ((m.R + UBK - 1) / UBK) + (m.cin + UBK - 1) / UBK > UMAXBLK || (m.H + UBK - 1) / UBK > UMAXBLK) return false;
+    return true;
+}
+
+static int umma_plan(wn_handle *h) {
+    if (h->umma) return WN_OK;
+    const WnModelDev &m = h->m;
+    auto Wt = [&](const std::string &n) -> const float * {
+        auto it = h->host_w.find(n);
+        return it == h->host_w.end() ? nullptr : it->second.data.data();
+    };
+    WnUmmaPlan *u = new WnUmmaPlan();
+    const int R = m.R, S = m.S, H = m.H, G = 2 * H, cin = m.cin;
+    u->NT = H % 128 == 0 ? 128 : 64;
+    u->gate_ncols = 2 * u->NT; u->gate_tiles = H / u->NT;
+    u->os_ncols = (R + S) % 256 == 0 ? 256 : 128; u->os_tiles = (R + S) / u->os_ncols;
+    u->gate_blk = cut_blocks({{0, 0, R}, {0, 1, R}, {1, 0, cin}, {0, 2, R}}, u->gate_ncols, &u->gate_tile_bytes);
+    u->os_blk = cut_blocks({{0, 2, H}}, u->os_ncols, &u->os_tile_bytes);
+    std::vector<unsigned short> w;
+    std::vector<float> bias;
+    auto pack = [&](const std::vector<KBlockHost> &blks, int ncols, int tiles, unsigned tile_bytes, auto &&weight /* (k, row) */) {
+        const size_t base = w.size();
+        w.resize(base + (size_t)tiles * tile_bytes / 2, 0);
+        for (int ty = 0; ty < tiles; ++ty)
+            for (const auto &b : blks) {
+                unsigned short *hi = w.data() + base + ((size_t)ty * tile_bytes + b.w_off) / 2, *lo = hi + (size_t)b.bk * ncols;
+                for (int k = 0; k < b.bk; ++k)
+                    for (int j = 0; j < ncols; ++j) {
+                        const float v = weight(b.kcat + k, ty * ncols + j);
+                        const unsigned short vh = bf16_rn_host(v), vl = bf16_rn_host(v - bf16_to_float_host(vh));
+                        const size_t o = ((size_t)(k / 8) * ncols + j) * 8 + k % 8;
+                        hi[o] = vh; lo[o] = vl;
+                    }
+            }
+        return base * 2;
+    };
+    for (int l = 0; l < m.L; ++l) {
+        const std::string pre = "ResidualConv1DGLU_" + std::to_string(l) + "/residual_block_";
+        const float *cw = Wt(pre + "causal_conv/kernel"), *cb = Wt(pre + "causal_conv/bias");
+        const float *iw = Wt(pre + "cin_conv/kernel"), *ib = Wt(pre + "cin_conv/bias");
+        const float *ow = Wt(pre + "out_conv/kernel"), *ob = Wt(pre + "out_conv/bias");
+        const float *sw = Wt(pre + "skip_conv/kernel"), *sb = Wt(pre + "skip_conv/bias");
+        const int NT = u->NT;
+        // packed gate row `row` of the layer: tile row / (2 NT), inside a tile NT tanh rows then the NT sigmoid rows of the
+        // same channels (modules.py:494: first half of the conv output -> tanh)
+        auto gate_col = [&](int row) { const int ty = row / (2 * NT), j = row % (2 * NT); return (j < NT ? 0 : H) + ty * NT + (j % NT); };
+        u->gate_w.push_back(pack(u->gate_blk, u->gate_ncols, u->gate_tiles, u->gate_tile_bytes, [&](int k, int row) {
+            const int col = gate_col(row);
+            if (k < 2 * R) return cw[(size_t)k * G + col];
+            if (k < 2 * R + cin) return iw[(size_t)(k - 2 * R) * G + col];
+            return cw[(size_t)(k - cin) * G + col];
+        }));
+        u->gate_b.push_back(bias.size());
+        for (int row = 0; row < G; ++row) { const int col = gate_col(row); bias.push_back((cb ? cb[col] : 0.0f) + (ib ? ib[col] : 0.0f)); }
+        u->os_w.push_back(pack(u->os_blk, u->os_ncols, u->os_tiles, u->os_tile_bytes, [&](int k, int row) {
+            return row < R ? ow[(size_t)k * R + row] : sw[(size_t)k * S + (row - R)];
+        }));
+        u->os_b.push_back(bias.size());
+        for (int r = 0; r < R; ++r) bias.push_back(ob ? ob[r] : 0.0f);
+        for (int s = 0; s < S; ++s) bias.push_back(sb ? sb[s] : 0.0f);
+    }
+    if (cudaMalloc((void **)&u->d_w, w.size() * 2) != cudaSuccess ||
+        cudaMemcpy(u->d_w, w.data(), w.size() * 2, cudaMemcpyHostToDevice) != cudaSuccess ||
+        cudaMalloc((void **)&u->d_bias, bias.size() * sizeof(float)) != cudaSuccess ||
+        cudaMemcpy(u->d_bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess ||
+        cudaFuncSetAttribute(umma_layer_kernel<UEPI_GATE>, cudaFuncAttributeMaxDynamicSharedMemorySize, U_SMEM) != cudaSuccess ||
+        cudaFuncSetAttribute(umma_layer_kernel<UEPI_OUTSKIP>, cudaFuncAttributeMaxDynamicSharedMemorySize, U_SMEM) != cudaSuccess) {
+        h->err = std::string("step tensor-core weights: ") + cudaGetErrorString(cudaGetLastError());
+        if (u->d_w) cudaFree(u->d_w);
+        if (u->d_bias) cudaFree(u->d_bias);
+        delete u;
+        return WN_ERR_NOMEM;
+    }
+    h->umma = u;
+    return WN_OK;
+}
+
+// One residual layer: z = gate(x, c), then x' and the skip sum.  x, z, x_out, skips are position-major fp32.
+int wn_umma_layer(wn_handle *h, int l, const float *x, const float *c_up, float *z, float *x_out, float *skips, long long N, int T,
+                  cudaStream_t st) {
+    int rc = umma_plan(h);
+    if (rc) return rc;
+    const WnUmmaPlan *u = h->umma;
+    const WnModelDev &m = h->m;
+    UArgs a;
+    memset(&a, 0, sizeof(a));
+    a.N = N; a.T = T; a.H = m.H; a.R = m.R; a.S = m.S; a.NT = u->NT;
+    a.legacy = m.legacy; a.residual_legacy = m.residual_legacy; a.first_layer = l == 0;
+    const unsigned grid_x = (unsigned)((N + UM - 1) / UM);
+    // gate
+    a.W = u->d_w + u->gate_w[l]; a.tile_w_bytes = u->gate_tile_bytes; a.bias = u->d_bias + u->gate_b[l];
+    a.src = x; a.src_ld = m.R; a.cond = c_up; a.cond_ld = m.cin; a.ncols = u->gate_ncols;
+    a.nblk = (int)u->gate_blk.size();
+    for (int i = 0; i < a.nblk; ++i) {
+        const KBlockHost &b = u->gate_blk[i];
+        a.blk[i] = {b.seg, b.koff, b.bk, b.seg == 0 ? (2 - b.tap) * m.dil[l] : 0, b.w_off};
+    }
+    a.out = z;
+    umma_layer_kernel<UEPI_GATE><<<dim3(grid_x, (unsigned)u->gate_tiles), UTHREADS, U_SMEM, st>>>(a);
+    WN_CUDA_TRY(h, cudaGetLastError());
+    // out / skip
+    a.W = u->d_w + u->os_w[l]; a.tile_w_bytes = u->os_tile_bytes; a.bias = u->d_bias + u->os_b[l];
+    a.src = z; a.src_ld = m.H; a.cond = nullptr; a.cond_ld = 0; a.ncols = u->os_ncols;
+    a.nblk = (int)u->os_blk.size();
+    for (int i = 0; i < a.nblk; ++i) {
+        const KBlockHost &b = u->os_blk[i];
+        a.blk[i] = {0, b.koff, b.bk, 0, b.w_off};
+    }
+    a.out = x_out; a.skips = skips; a.xin = x;
+    umma_layer_kernel<UEPI_OUTSKIP><<<dim3(grid_x, (unsigned)u->os_tiles), UTHREADS, U_SMEM, st>>>(a);
+    WN_CUDA_TRY(h, cudaGetLastError());
+    h->launches += 2;
+    return WN_OK;
+}
