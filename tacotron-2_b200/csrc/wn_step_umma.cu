@@ -33,9 +33,16 @@
 
 namespace {
 
-constexpr int UM = 128, UBK = 64, UTHREADS = 256, UMAXBLK = 16;
-constexpr int A_HALF_BYTES = UM * UBK * 2;                 // one of A_hi / A_lo
-constexpr int U_SMEM = 2 * A_HALF_BYTES + 2 * 256 * UBK * 2;   // + B_hi, B_lo at N = 256
+constexpr int UM = 128, UBK = 32, UMAXBLK = 32, NSTAGE = 2;
+constexpr int USTAGERS = 256, UTHREADS = USTAGERS + 32;   // 8 staging / epilogue warps + the issuing warp
+constexpr int LBO_A = UM * 16 + 16;                        // k-chunk stride of the activation operand (16 B of padding: the
+                                                           // 8 chunks a quarter warp stores land in 8 different bank groups)
+constexpr int A_HALF_BYTES = (UBK / 8) * LBO_A;            // one of A_hi / A_lo
+constexpr int B_OFF = 2 * A_HALF_BYTES;
+constexpr int STAGE_BYTES = B_OFF + 2 * 256 * UBK * 2;     // + B_hi, B_lo at N = 256
+constexpr int U_SMEM = NSTAGE * STAGE_BYTES;
+constexpr int STG_LD = 132;                                // row stride (floats) of the epilogue staging tile [128][128]
+static_assert(UM * STG_LD * 4 <= U_SMEM, "the epilogue staging tile reuses the operand stages");
 
 enum { UEPI_GATE = 0, UEPI_OUTSKIP = 1 };
 
@@ -84,107 +91,131 @@ __device__ __forceinline__ float gate_act_u(float x, bool sig) {
 template <int EPI>
 __global__ void __launch_bounds__(UTHREADS, 2) umma_layer_kernel(const __grid_constant__ UArgs a) {
     extern __shared__ __align__(128) unsigned char usmem[];
-    unsigned char *As_hi = usmem, *As_lo = usmem + A_HALF_BYTES, *Bs = usmem + 2 * A_HALF_BYTES;
-    __shared__ __align__(8) unsigned long long bars[2];
+    __shared__ __align__(8) unsigned long long bars[3 * NSTAGE];   // full (weights landed) | ready (activations staged) | done (MMAs read the stage)
     __shared__ uint32_t tmem_slot;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const uint32_t full = umma::smem_addr(&bars[0]), done = umma::smem_addr(&bars[1]);
-    if (tid == 0) { umma::mbar_init(full, 1); umma::mbar_init(done, 1); umma::mbar_fence_init(); }
-    if (warp == 0) umma::tmem_alloc(umma::smem_addr(&tmem_slot), 256);
+    const uint32_t bar0 = umma::smem_addr(&bars[0]);
+    auto full = [&](int s) { return bar0 + 8u * (uint32_t)s; };
+    auto ready = [&](int s) { return bar0 + 8u * (uint32_t)(NSTAGE + s); };
+    auto done = [&](int s) { return bar0 + 8u * (uint32_t)(2 * NSTAGE + s); };
+    if (tid == 0) {
+        for (int s = 0; s < NSTAGE; ++s) { umma::mbar_init(full(s), 1); umma::mbar_init(ready(s), USTAGERS); umma::mbar_init(done(s), 1); }
+        umma::mbar_fence_init();
+    }
+    if (warp == 8) umma::tmem_alloc(umma::smem_addr(&tmem_slot), 256);
     umma::fence_before_sync();
     __syncthreads();
     umma::fence_after_sync();
     const uint32_t tmem = tmem_slot;
 
     const long long n0 = (long long)blockIdx.x * UM;
-    const int ty = blockIdx.y, ncols = a.ncols;
-    const unsigned char *Wt = a.W + (long long)ty * a.tile_w_bytes;
-    // staging role: position pos, k half kh of every block
-    const int pos = tid & (UM - 1), kh = tid >> 7;
-    const long long n = n0 + pos;
-    const bool n_ok = n < a.N;
-    const int t = n_ok ? (int)(n % a.T) : 0;
+    const int ty = blockIdx.y, ncols = a.ncols, nblk = a.nblk;
+    const uint32_t smem0 = umma::smem_addr(usmem);
 
-    float4 pf[8];
-    auto load_block = [&](int b) {
-        const UBlock &k = a.blk[b];
-        const int nch = k.bk >> 4;                           // 8-element chunks per thread
-        const float *p = nullptr;
-        if (n_ok) {
-            if (k.seg == 0) { if (t >= k.back) p = a.src + (n - k.back) * a.src_ld + k.koff + kh * (k.bk >> 1); }
-            else p = a.cond + n * a.cond_ld + k.koff + kh * (k.bk >> 1);
+    if (warp == 8) {
+        // ---- issuing warp: weights by bulk copy, tcgen05.mma, commit ----------------------------------------------------
+        if (lane == 0) {
+            const unsigned char *Wt = a.W + (long long)ty * a.tile_w_bytes;
+            const uint32_t idesc = umma::idesc_bf16(UM, ncols);
+            const uint32_t lboB = (uint32_t)ncols * 16;
+            for (int b = 0; b < nblk; ++b) {
+                const int s = b % NSTAGE, bk = a.blk[b].bk;
+                const uint32_t use = (uint32_t)(b / NSTAGE);
+                if (b >= NSTAGE) umma::mbar_wait(done(s), (use - 1u) & 1u);   // the MMAs of block b - NSTAGE have read the stage
+                const uint32_t st = smem0 + (uint32_t)s * STAGE_BYTES, Bs_a = st + B_OFF;
+                const uint32_t bytes = (uint32_t)bk * (uint32_t)ncols * 4u;
+                umma::mbar_expect_tx(full(s), bytes);
+                const unsigned char *src = Wt + a.blk[b].w_off;
+                for (uint32_t o = 0; o < bytes; o += 16384u)
+                    umma::bulk_g2s(Bs_a + o, src + o, bytes - o < 16384u ? bytes - o : 16384u, full(s));
+                umma::mbar_wait(ready(s), use & 1u);
+                umma::mbar_wait(full(s), use & 1u);
+                umma::fence_after_sync();
+                const uint32_t Ah_a = st, Al_a = st + A_HALF_BYTES, Bl_a = Bs_a + (uint32_t)bk * (uint32_t)ncols * 2u;
+                for (int ks = 0; ks < (bk >> 4); ++ks) {
+                    const uint64_t ah = umma::smem_desc(Ah_a + ks * 2 * LBO_A, LBO_A, 128), al = umma::smem_desc(Al_a + ks * 2 * LBO_A, LBO_A, 128);
+                    const uint64_t bh = umma::smem_desc(Bs_a + ks * 2 * lboB, lboB, 128), bl = umma::smem_desc(Bl_a + ks * 2 * lboB, lboB, 128);
+                    umma::mma_bf16(tmem, ah, bh, idesc, (b > 0 || ks > 0) ? 1u : 0u);
+                    umma::mma_bf16(tmem, ah, bl, idesc, 1u);
+                    umma::mma_bf16(tmem, al, bh, idesc, 1u);
+                }
+                umma::mma_commit(done(s));
+            }
         }
+        __syncwarp();
+    } else {
+        // ---- staging warps: gather, split into bf16 (hi, lo), store in the K-major core-matrix layout -----------------------
+        // a block of bk columns has cpr = bk / 8 chunks per row; thread = (chunk c, row r0 + j * 256 / cpr): the lanes of a
+        // warp read whole rows (cpr * 32 contiguous bytes each)
+        const int t0 = (int)(n0 % a.T);
+        float4 pf[UBK / 8];
+        auto load_block = [&](int b) {
+            const UBlock &k = a.blk[b];
+            const int cpr = k.bk >> 3, lg = cpr == 4 ? 2 : (cpr == 2 ? 1 : 3), c = tid & (cpr - 1), r0 = tid >> lg, rpp = USTAGERS >> lg;
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
-            if (c < nch) {
-                pf[2 * c] = p ? __ldg(reinterpret_cast<const float4 *>(p + 8 * c)) : make_float4(0.f, 0.f, 0.f, 0.f);
-                pf[2 * c + 1] = p ? __ldg(reinterpret_cast<const float4 *>(p + 8 * c + 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int j = 0; j < UBK / 16; ++j) {
+                const int row = r0 + j * rpp;
+                float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+                if (row < UM) {
+                    const long long n = n0 + row;
+                    if (n < a.N) {
+                        const float *p = nullptr;
+                        if (k.seg == 0) {
+                            const int t = (t0 + row) % a.T;
+                            if (t >= k.back) p = a.src + (n - k.back) * a.src_ld + k.koff + 8 * c;
+                        } else {
+                            p = a.cond + n * a.cond_ld + k.koff + 8 * c;
+                        }
+                        if (p) { v0 = __ldg(reinterpret_cast<const float4 *>(p)); v1 = __ldg(reinterpret_cast<const float4 *>(p + 4)); }
+                    }
+                }
+                pf[2 * j] = v0; pf[2 * j + 1] = v1;
             }
-    };
-    auto store_block = [&](int b) {
-        const int nch = a.blk[b].bk >> 4;
+        };
+        auto store_block = [&](int b, int s) {
+            const int cpr = a.blk[b].bk >> 3, lg = cpr == 4 ? 2 : (cpr == 2 ? 1 : 3), c = tid & (cpr - 1), r0 = tid >> lg, rpp = USTAGERS >> lg;
+            unsigned char *Ah = usmem + (size_t)s * STAGE_BYTES, *Al = Ah + A_HALF_BYTES;
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
-            if (c < nch) {
-                uint4 hi, lo;
-                umma::split8(pf[2 * c], pf[2 * c + 1], hi, lo);
-                const int off = ((kh * nch + c) * UM + pos) * 16;
-                *reinterpret_cast<uint4 *>(As_hi + off) = hi;
-                *reinterpret_cast<uint4 *>(As_lo + off) = lo;
+            for (int j = 0; j < UBK / 16; ++j) {
+                const int row = r0 + j * rpp;
+                if (row < UM) {
+                    uint4 hi, lo;
+                    umma::split8(pf[2 * j], pf[2 * j + 1], hi, lo);
+                    const int off = c * LBO_A + row * 16;
+                    *reinterpret_cast<uint4 *>(Ah + off) = hi;
+                    *reinterpret_cast<uint4 *>(Al + off) = lo;
+                }
             }
-    };
-
-    const uint32_t idesc = umma::idesc_bf16(UM, ncols);
-    const uint32_t lboA = UM * 16, lboB = (uint32_t)ncols * 16;
-    const uint32_t As_hi_a = umma::smem_addr(As_hi), As_lo_a = umma::smem_addr(As_lo), Bs_a = umma::smem_addr(Bs);
-
-    load_block(0);
-    for (int b = 0; b < a.nblk; ++b) {
-        const int bk = a.blk[b].bk;
-        if (b > 0) umma::mbar_wait(done, (uint32_t)(b - 1) & 1u);   // the MMAs of block b-1 have read their operands
-        if (tid == 0) {
-            const uint32_t bytes = (uint32_t)bk * (uint32_t)ncols * 4u;
-            umma::mbar_expect_tx(full, bytes);
-            const unsigned char *src = Wt + a.blk[b].w_off;
-            for (uint32_t o = 0; o < bytes; o += 16384u)
-                umma::bulk_g2s(Bs_a + o, src + o, bytes - o < 16384u ? bytes - o : 16384u, full);
+        };
+        load_block(0);
+        for (int b = 0; b < nblk; ++b) {
+            const int s = b % NSTAGE;
+            if (b >= NSTAGE) umma::mbar_wait(done(s), (uint32_t)(b / NSTAGE - 1) & 1u);
+            store_block(b, s);
+            umma::fence_proxy_async();
+            umma::mbar_arrive(ready(s));
+            if (b + 1 < nblk) load_block(b + 1);   // in flight while the tensor core works
         }
-        store_block(b);
-        umma::fence_proxy_async();
-        __syncthreads();
-        if (tid == 0) {
-            umma::mbar_wait(full, (uint32_t)b & 1u);
-            umma::fence_after_sync();
-            const uint32_t Bl_a = Bs_a + (uint32_t)bk * (uint32_t)ncols * 2u;
-            for (int ks = 0; ks < (bk >> 4); ++ks) {
-                const uint64_t ah = umma::smem_desc(As_hi_a + ks * 2 * lboA, lboA, 128), al = umma::smem_desc(As_lo_a + ks * 2 * lboA, lboA, 128);
-                const uint64_t bh = umma::smem_desc(Bs_a + ks * 2 * lboB, lboB, 128), bl = umma::smem_desc(Bl_a + ks * 2 * lboB, lboB, 128);
-                umma::mma_bf16(tmem, ah, bh, idesc, (b > 0 || ks > 0) ? 1u : 0u);
-                umma::mma_bf16(tmem, ah, bl, idesc, 1u);
-                umma::mma_bf16(tmem, al, bh, idesc, 1u);
-            }
-            umma::mma_commit(done);
-        }
-        if (b + 1 < a.nblk) load_block(b + 1);   // in flight while the tensor core works
+        // the last commit covers every MMA of the tile
+        umma::mbar_wait(done((nblk - 1) % NSTAGE), (uint32_t)((nblk - 1) / NSTAGE) & 1u);
+        umma::fence_after_sync();
     }
-    umma::mbar_wait(done, (uint32_t)(a.nblk - 1) & 1u);
-    umma::fence_after_sync();
 
-    // ---- epilogue: thread = (position 32q + lane, column half) ---------------------------------------------------------
-    const int q = warp & 3, half = warp >> 2;
-    const long long ne = n0 + 32 * q + lane;
-    const bool ne_ok = ne < a.N;
+    // ---- epilogue: TMEM -> registers (thread = position 32q + lane, half of the columns) -> staging tile in shared memory
+    //      -> coalesced rows (one warp per position row) -------------------------------------------------------------------
+    float *stg = reinterpret_cast<float *>(usmem);
+    const int q = warp & 3, half = (warp >> 2) & 1;
     const uint32_t tq = tmem + ((uint32_t)(32 * q) << 16);
     const float *bias = a.bias + (size_t)ty * ncols;
     if (EPI == UEPI_GATE) {
         const int NT = a.NT;
-        for (int c = half * (NT / 2); c < (half + 1) * (NT / 2); c += 16) {
-            float ta[16], sg[16];
-            umma::tmem_ld16(tq + (uint32_t)c, ta);
-            umma::tmem_ld16(tq + (uint32_t)(NT + c), sg);
-            umma::tmem_ld_wait();
-            if (ne_ok) {
-                float *zp = a.out + ne * a.H + ty * NT + c;
+        if (warp < 8) {
+            float *srow = stg + (size_t)(32 * q + lane) * STG_LD;
+            for (int c = half * (NT / 2); c < (half + 1) * (NT / 2); c += 16) {
+                float ta[16], sg[16];
+                umma::tmem_ld16(tq + (uint32_t)c, ta);
+                umma::tmem_ld16(tq + (uint32_t)(NT + c), sg);
+                umma::tmem_ld_wait();
 #pragma unroll
                 for (int i4 = 0; i4 < 4; ++i4) {
                     float zz[4];
@@ -194,48 +225,67 @@ __global__ void __launch_bounds__(UTHREADS, 2) umma_layer_kernel(const __grid_co
                         const float sv = gate_act_u(__fadd_rn(sg[4 * i4 + i], __ldg(bias + NT + c + 4 * i4 + i)), true);
                         zz[i] = __fmul_rn(tv, sv);
                     }
-                    *reinterpret_cast<float4 *>(zp + 4 * i4) = make_float4(zz[0], zz[1], zz[2], zz[3]);
+                    *reinterpret_cast<float4 *>(srow + c + 4 * i4) = make_float4(zz[0], zz[1], zz[2], zz[3]);
                 }
             }
         }
+        __syncthreads();
+        if (warp < 8 && 4 * lane < NT)
+            for (int r = warp; r < UM; r += 8) {
+                const long long n = n0 + r;
+                if (n < a.N)
+                    *reinterpret_cast<float4 *>(a.out + n * a.H + ty * NT + 4 * lane) = *reinterpret_cast<const float4 *>(stg + (size_t)r * STG_LD + 4 * lane);
+            }
     } else {
-        for (int c = half * (ncols / 2); c < (half + 1) * (ncols / 2); c += 16) {
-            float v[16];
-            umma::tmem_ld16(tq + (uint32_t)c, v);
-            umma::tmem_ld_wait();
-            if (!ne_ok) continue;
-            const int m = ty * ncols + c;
+        for (int g = 0; g < ncols / 128; ++g) {
+            if (g > 0) __syncthreads();
+            if (warp < 8) {
+                float *srow = stg + (size_t)(32 * q + lane) * STG_LD;
+                for (int c = half * 64; c < half * 64 + 64; c += 16) {
+                    float v[16];
+                    umma::tmem_ld16(tq + (uint32_t)(g * 128 + c), v);
+                    umma::tmem_ld_wait();
 #pragma unroll
-            for (int i4 = 0; i4 < 4; ++i4) {
-                const float4 bb = __ldg(reinterpret_cast<const float4 *>(bias + c + 4 * i4));
-                float4 y = make_float4(__fadd_rn(v[4 * i4], bb.x), __fadd_rn(v[4 * i4 + 1], bb.y), __fadd_rn(v[4 * i4 + 2], bb.z),
-                                       __fadd_rn(v[4 * i4 + 3], bb.w));
-                if (m < a.R) {           // residual (modules.py:515-520)
-                    const float4 xin = *reinterpret_cast<const float4 *>(a.xin + ne * a.R + m + 4 * i4);
-                    y.x = __fadd_rn(y.x, xin.x); y.y = __fadd_rn(y.y, xin.y); y.z = __fadd_rn(y.z, xin.z); y.w = __fadd_rn(y.w, xin.w);
-                    if (a.residual_legacy) {
-                        y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF);
-                        y.z = __fmul_rn(y.z, WN_SQRT_HALF); y.w = __fmul_rn(y.w, WN_SQRT_HALF);
-                    }
-                    *reinterpret_cast<float4 *>(a.out + ne * a.R + m + 4 * i4) = y;
-                } else {                 // skips (wavenet.py:833-836)
-                    float4 *sp = reinterpret_cast<float4 *>(a.skips + ne * a.S + (m - a.R) + 4 * i4);
-                    if (!a.first_layer) {
-                        const float4 s = *sp;
-                        y.x = __fadd_rn(s.x, y.x); y.y = __fadd_rn(s.y, y.y); y.z = __fadd_rn(s.z, y.z); y.w = __fadd_rn(s.w, y.w);
-                        if (a.legacy) {
+                    for (int i4 = 0; i4 < 4; ++i4)
+                        *reinterpret_cast<float4 *>(srow + c + 4 * i4) = make_float4(v[4 * i4], v[4 * i4 + 1], v[4 * i4 + 2], v[4 * i4 + 3]);
+                }
+            }
+            __syncthreads();
+            if (warp < 8) {
+                const int m = ty * ncols + g * 128 + 4 * lane;            // first of this lane's 4 output rows of the GEMM
+                const float4 bb = __ldg(reinterpret_cast<const float4 *>(bias + g * 128 + 4 * lane));
+                for (int r = warp; r < UM; r += 8) {
+                    const long long n = n0 + r;
+                    if (n >= a.N) continue;
+                    const float4 v = *reinterpret_cast<const float4 *>(stg + (size_t)r * STG_LD + 4 * lane);
+                    float4 y = make_float4(__fadd_rn(v.x, bb.x), __fadd_rn(v.y, bb.y), __fadd_rn(v.z, bb.z), __fadd_rn(v.w, bb.w));
+                    if (m < a.R) {           // residual (modules.py:515-520)
+                        const float4 xin = *reinterpret_cast<const float4 *>(a.xin + n * a.R + m);
+                        y.x = __fadd_rn(y.x, xin.x); y.y = __fadd_rn(y.y, xin.y); y.z = __fadd_rn(y.z, xin.z); y.w = __fadd_rn(y.w, xin.w);
+                        if (a.residual_legacy) {
                             y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF);
                             y.z = __fmul_rn(y.z, WN_SQRT_HALF); y.w = __fmul_rn(y.w, WN_SQRT_HALF);
                         }
+                        *reinterpret_cast<float4 *>(a.out + n * a.R + m) = y;
+                    } else {                 // skips (wavenet.py:833-836)
+                        float4 *sp = reinterpret_cast<float4 *>(a.skips + n * a.S + (m - a.R));
+                        if (!a.first_layer) {
+                            const float4 s = *sp;
+                            y.x = __fadd_rn(s.x, y.x); y.y = __fadd_rn(s.y, y.y); y.z = __fadd_rn(s.z, y.z); y.w = __fadd_rn(s.w, y.w);
+                            if (a.legacy) {
+                                y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF);
+                                y.z = __fmul_rn(y.z, WN_SQRT_HALF); y.w = __fmul_rn(y.w, WN_SQRT_HALF);
+                            }
+                        }
+                        *sp = y;
                     }
-                    *sp = y;
                 }
             }
         }
     }
     umma::fence_before_sync();
     __syncthreads();
-    if (warp == 0) umma::tmem_dealloc(tmem, 256);
+    if (warp == 8) umma::tmem_dealloc(tmem, 256);
 }
 
 unsigned short bf16_rn_host(float f) {
@@ -253,14 +303,15 @@ float bf16_to_float_host(unsigned short h) {
 
 struct KBlockHost { int seg, tap, koff, bk, kcat; unsigned w_off; };
 
-// cuts the segments of K into blocks of at most 64 (multiples of 16); w_off for `ncols` columns per tile
+// cuts the segments of K into blocks of 32 (16 for a tail); w_off for `ncols` columns per tile
 std::vector<KBlockHost> cut_blocks(const std::vector<std::array<int, 3>> &segs /* seg, tap, len */, int ncols, unsigned *total) {
     std::vector<KBlockHost> out;
     unsigned off = 0;
     int kcat = 0;
     for (const auto &s : segs) {
         for (int k = 0; k < s[2];) {
-            const int bk = std::min(UBK, s[2] - k);
+            int bk = UBK;                                    // 32, then 16 for a tail (every length is a multiple of 16)
+            while (bk > s[2] - k) bk >>= 1;
             out.push_back({s[0], s[1], k, bk, kcat + k, off});
             off += (unsigned)bk * (unsigned)ncols * 4u;
             k += bk;
