@@ -66,26 +66,24 @@ struct UArgs {
     int H, R, S, NT, first_layer, legacy, residual_legacy;
 };
 
-// same operations as wn_tanhf / wn_sigmoidf (include/wn_math.h), one instruction stream (see wn_loop_pipe.cu: gate_act)
-__device__ __forceinline__ float gate_act_u(float x, bool sig) {
-    const float ax = fabsf(x);
-    const float e = wn_expf(sig ? -x : __fadd_rn(ax, ax));
-    const float qd = __fdiv_rn(sig ? 1.0f : 2.0f, sig ? __fadd_rn(1.0f, e) : __fadd_rn(e, 1.0f));
-    float r = sig ? qd : __fsub_rn(1.0f, qd);
-    const float z = __fmul_rn(x, x);
+// tanh(t) * sigmoid(s) (modules.py:510) with the hardware exponential and reciprocal (ex2.approx / rcp.approx, relative
+// error ~1e-6).  The sample-by-sample engines use the bit-reproducible functions of include/wn_math.h, ~3x the
+// instructions; with those the gate epilogue, not the tensor pipe, bounded this kernel (ncu: 59 % of the issue slots).
+// This path is compared with them by tolerance (1e-3, observed ~2e-5), so it can afford the fast forms.  The small-|t|
+// polynomial is the one of wn_tanhf, which keeps the relative accuracy of tanh near zero.
+__device__ __forceinline__ float gate_fast(float t, float s) {
+    const float sg = __fdividef(1.0f, 1.0f + __expf(-s));
+    const float at = fabsf(t);
+    float th = 1.0f - __fdividef(2.0f, __expf(at + at) + 1.0f);   // exp overflow -> 2/inf = 0 -> 1
+    const float z = t * t;
     float p = -5.70498872745e-3f;
     p = __fmaf_rn(p, z, 2.06390887954e-2f);
     p = __fmaf_rn(p, z, -5.37397155531e-2f);
     p = __fmaf_rn(p, z, 1.33314422036e-1f);
     p = __fmaf_rn(p, z, -3.33332819422e-1f);
-    const float small = __fmaf_rn(__fmul_rn(p, z), x, x);
-    if (!sig) {
-        if (ax > 9.02f) r = 1.0f;
-        if (x < 0.0f) r = -r;
-        if (ax < 0.625f) r = small;
-        if (!(x == x)) r = x;
-    }
-    return r;
+    th = copysignf(th, t);
+    if (at < 0.625f) th = __fmaf_rn(p * z, t, t);
+    return th * sg;
 }
 
 template <int EPI>
@@ -218,14 +216,11 @@ __global__ void __launch_bounds__(UTHREADS, 2) umma_layer_kernel(const __grid_co
                 umma::tmem_ld_wait();
 #pragma unroll
                 for (int i4 = 0; i4 < 4; ++i4) {
-                    float zz[4];
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const float tv = gate_act_u(__fadd_rn(ta[4 * i4 + i], __ldg(bias + c + 4 * i4 + i)), false);
-                        const float sv = gate_act_u(__fadd_rn(sg[4 * i4 + i], __ldg(bias + NT + c + 4 * i4 + i)), true);
-                        zz[i] = __fmul_rn(tv, sv);
-                    }
-                    *reinterpret_cast<float4 *>(srow + c + 4 * i4) = make_float4(zz[0], zz[1], zz[2], zz[3]);
+                    const float4 bt = __ldg(reinterpret_cast<const float4 *>(bias + c + 4 * i4));
+                    const float4 bs = __ldg(reinterpret_cast<const float4 *>(bias + NT + c + 4 * i4));
+                    *reinterpret_cast<float4 *>(srow + c + 4 * i4) =
+                        make_float4(gate_fast(ta[4 * i4] + bt.x, sg[4 * i4] + bs.x), gate_fast(ta[4 * i4 + 1] + bt.y, sg[4 * i4 + 1] + bs.y),
+                                    gate_fast(ta[4 * i4 + 2] + bt.z, sg[4 * i4 + 2] + bs.z), gate_fast(ta[4 * i4 + 3] + bt.w, sg[4 * i4 + 3] + bs.w));
                 }
             }
         }
@@ -254,30 +249,37 @@ __global__ void __launch_bounds__(UTHREADS, 2) umma_layer_kernel(const __grid_co
             if (warp < 8) {
                 const int m = ty * ncols + g * 128 + 4 * lane;            // first of this lane's 4 output rows of the GEMM
                 const float4 bb = __ldg(reinterpret_cast<const float4 *>(bias + g * 128 + 4 * lane));
-                for (int r = warp; r < UM; r += 8) {
-                    const long long n = n0 + r;
-                    if (n >= a.N) continue;
-                    const float4 v = *reinterpret_cast<const float4 *>(stg + (size_t)r * STG_LD + 4 * lane);
-                    float4 y = make_float4(__fadd_rn(v.x, bb.x), __fadd_rn(v.y, bb.y), __fadd_rn(v.z, bb.z), __fadd_rn(v.w, bb.w));
-                    if (m < a.R) {           // residual (modules.py:515-520)
-                        const float4 xin = *reinterpret_cast<const float4 *>(a.xin + n * a.R + m);
-                        y.x = __fadd_rn(y.x, xin.x); y.y = __fadd_rn(y.y, xin.y); y.z = __fadd_rn(y.z, xin.z); y.w = __fadd_rn(y.w, xin.w);
-                        if (a.residual_legacy) {
+                // what is added to a row: the layer input (residual, modules.py:515-520) or the running skip sum
+                // (wavenet.py:833-836); 8 rows of loads are in flight before the first one is used
+                const bool is_out = m < a.R, has_add = is_out || !a.first_layer;
+                const float *addp = is_out ? a.xin + m : a.skips + (m - a.R);
+                float *dstp = is_out ? a.out + m : a.skips + (m - a.R);
+                const int ld = is_out ? a.R : a.S;
+                const bool scale = is_out ? a.residual_legacy != 0 : (a.legacy != 0 && !a.first_layer);
+                for (int rb = warp; rb < UM; rb += 64) {
+                    float4 add[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const long long n = n0 + rb + 8 * k;
+                        add[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (has_add && n < a.N) add[k] = *reinterpret_cast<const float4 *>(addp + n * ld);
+                    }
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const int r = rb + 8 * k;
+                        const long long n = n0 + r;
+                        if (n >= a.N) continue;
+                        const float4 v = *reinterpret_cast<const float4 *>(stg + (size_t)r * STG_LD + 4 * lane);
+                        float4 y = make_float4(__fadd_rn(v.x, bb.x), __fadd_rn(v.y, bb.y), __fadd_rn(v.z, bb.z), __fadd_rn(v.w, bb.w));
+                        if (has_add) {
+                            if (is_out) { y.x = __fadd_rn(y.x, add[k].x); y.y = __fadd_rn(y.y, add[k].y); y.z = __fadd_rn(y.z, add[k].z); y.w = __fadd_rn(y.w, add[k].w); }
+                            else { y.x = __fadd_rn(add[k].x, y.x); y.y = __fadd_rn(add[k].y, y.y); y.z = __fadd_rn(add[k].z, y.z); y.w = __fadd_rn(add[k].w, y.w); }
+                        }
+                        if (scale) {
                             y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF);
                             y.z = __fmul_rn(y.z, WN_SQRT_HALF); y.w = __fmul_rn(y.w, WN_SQRT_HALF);
                         }
-                        *reinterpret_cast<float4 *>(a.out + n * a.R + m) = y;
-                    } else {                 // skips (wavenet.py:833-836)
-                        float4 *sp = reinterpret_cast<float4 *>(a.skips + n * a.S + (m - a.R));
-                        if (!a.first_layer) {
-                            const float4 s = *sp;
-                            y.x = __fadd_rn(s.x, y.x); y.y = __fadd_rn(s.y, y.y); y.z = __fadd_rn(s.z, y.z); y.w = __fadd_rn(s.w, y.w);
-                            if (a.legacy) {
-                                y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF);
-                                y.z = __fmul_rn(y.z, WN_SQRT_HALF); y.w = __fmul_rn(y.w, WN_SQRT_HALF);
-                            }
-                        }
-                        *sp = y;
+                        *reinterpret_cast<float4 *>(dstp + n * ld) = y;
                     }
                 }
             }
