@@ -42,6 +42,7 @@ constexpr int B_OFF = 2 * A_HALF_BYTES;
 constexpr int STAGE_BYTES = B_OFF + 2 * 256 * UBK * 2;     // + B_hi, B_lo at N = 256
 constexpr int U_SMEM = NSTAGE * STAGE_BYTES;
 constexpr int STG_LD = 132;                                // row stride (floats) of the epilogue staging tile [128][128]
+static_assert(UBK == 32, "the staging threads are mapped for blocks of 32 (tail 16)");
 static_assert(UM * STG_LD * 4 <= U_SMEM, "the epilogue staging tile reuses the operand stages");
 
 enum { UEPI_GATE = 0, UEPI_OUTSKIP = 1 };
@@ -71,10 +72,13 @@ struct UArgs {
 // instructions; with those the gate epilogue, not the tensor pipe, bounded this kernel (ncu: 59 % of the issue slots).
 // This path is compared with them by tolerance (1e-3, observed ~2e-5), so it can afford the fast forms.  The small-|t|
 // polynomial is the one of wn_tanhf, which keeps the relative accuracy of tanh near zero.
+__device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float gate_fast(float t, float s) {
-    const float sg = __fdividef(1.0f, 1.0f + __expf(-s));
+    constexpr float LOG2E = 1.4426950408889634f;
+    const float sg = rcp_approx(1.0f + ex2_approx(-LOG2E * s));
     const float at = fabsf(t);
-    float th = 1.0f - __fdividef(2.0f, __expf(at + at) + 1.0f);   // exp overflow -> 2/inf = 0 -> 1
+    float th = 1.0f - 2.0f * rcp_approx(ex2_approx((2.0f * LOG2E) * at) + 1.0f);   // exp overflow -> rcp(inf) = 0 -> 1
     const float z = t * t;
     float p = -5.70498872745e-3f;
     p = __fmaf_rn(p, z, 2.06390887954e-2f);
@@ -143,46 +147,43 @@ __global__ void __launch_bounds__(UTHREADS, 2) umma_layer_kernel(const __grid_co
         __syncwarp();
     } else {
         // ---- staging warps: gather, split into bf16 (hi, lo), store in the K-major core-matrix layout -----------------------
-        // a block of bk columns has cpr = bk / 8 chunks per row; thread = (chunk c, row r0 + j * 256 / cpr): the lanes of a
-        // warp read whole rows (cpr * 32 contiguous bytes each)
-        const int t0 = (int)(n0 % a.T);
-        float4 pf[UBK / 8];
+        // thread = (8-float chunk c of a 32-wide block, rows r0 and r0 + 64): the lanes of a warp read whole 128-byte row
+        // segments.  Everything that depends only on the thread (row pointers, position inside the utterance) is computed
+        // once; a 16-wide tail block keeps the mapping with the chunks c >= 2 idle.
+        const int c = tid & 3, r0 = tid >> 2;
+        const float *srow[2], *crow[2];
+        int trow[2];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const long long n = n0 + r0 + 64 * j;
+            const bool ok = n < a.N;
+            trow[j] = ok ? (int)(n % a.T) : -1;               // -1: no such position (tail tile) -> zeros
+            srow[j] = a.src + (ok ? n : 0) * a.src_ld + 8 * c;
+            crow[j] = a.cond ? a.cond + (ok ? n : 0) * a.cond_ld + 8 * c : nullptr;
+        }
+        const int soff = (c * LBO_A + r0 * 16);
+        float4 pf[4];
         auto load_block = [&](int b) {
             const UBlock &k = a.blk[b];
-            const int cpr = k.bk >> 3, lg = cpr == 4 ? 2 : (cpr == 2 ? 1 : 3), c = tid & (cpr - 1), r0 = tid >> lg, rpp = USTAGERS >> lg;
+            const bool c_ok = 8 * c < k.bk;
+            const int back_off = k.koff - k.back * a.src_ld;
 #pragma unroll
-            for (int j = 0; j < UBK / 16; ++j) {
-                const int row = r0 + j * rpp;
+            for (int j = 0; j < 2; ++j) {
+                const float *p = k.seg == 0 ? srow[j] + back_off : crow[j] + k.koff;
                 float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
-                if (row < UM) {
-                    const long long n = n0 + row;
-                    if (n < a.N) {
-                        const float *p = nullptr;
-                        if (k.seg == 0) {
-                            const int t = (t0 + row) % a.T;
-                            if (t >= k.back) p = a.src + (n - k.back) * a.src_ld + k.koff + 8 * c;
-                        } else {
-                            p = a.cond + n * a.cond_ld + k.koff + 8 * c;
-                        }
-                        if (p) { v0 = __ldg(reinterpret_cast<const float4 *>(p)); v1 = __ldg(reinterpret_cast<const float4 *>(p + 4)); }
-                    }
-                }
+                if (c_ok && trow[j] >= k.back) { v0 = __ldg(reinterpret_cast<const float4 *>(p)); v1 = __ldg(reinterpret_cast<const float4 *>(p + 4)); }
                 pf[2 * j] = v0; pf[2 * j + 1] = v1;
             }
         };
         auto store_block = [&](int b, int s) {
-            const int cpr = a.blk[b].bk >> 3, lg = cpr == 4 ? 2 : (cpr == 2 ? 1 : 3), c = tid & (cpr - 1), r0 = tid >> lg, rpp = USTAGERS >> lg;
-            unsigned char *Ah = usmem + (size_t)s * STAGE_BYTES, *Al = Ah + A_HALF_BYTES;
+            if (8 * c >= a.blk[b].bk) return;
+            unsigned char *Ah = usmem + (size_t)s * STAGE_BYTES + soff, *Al = Ah + A_HALF_BYTES;
 #pragma unroll
-            for (int j = 0; j < UBK / 16; ++j) {
-                const int row = r0 + j * rpp;
-                if (row < UM) {
-                    uint4 hi, lo;
-                    umma::split8(pf[2 * j], pf[2 * j + 1], hi, lo);
-                    const int off = c * LBO_A + row * 16;
-                    *reinterpret_cast<uint4 *>(Ah + off) = hi;
-                    *reinterpret_cast<uint4 *>(Al + off) = lo;
-                }
+            for (int j = 0; j < 2; ++j) {
+                uint4 hi, lo;
+                umma::split8(pf[2 * j], pf[2 * j + 1], hi, lo);
+                *reinterpret_cast<uint4 *>(Ah + j * 64 * 16) = hi;
+                *reinterpret_cast<uint4 *>(Al + j * 64 * 16) = lo;
             }
         };
         load_block(0);

@@ -99,11 +99,11 @@ __device__ __forceinline__ void split8(const float4 a, const float4 b, uint4 &hi
     uint32_t h[4], l[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const __nv_bfloat16 h0 = __float2bfloat16_rn(v[2 * i]), h1 = __float2bfloat16_rn(v[2 * i + 1]);
-        const __nv_bfloat16 l0 = __float2bfloat16_rn(__fsub_rn(v[2 * i], __bfloat162float(h0)));
-        const __nv_bfloat16 l1 = __float2bfloat16_rn(__fsub_rn(v[2 * i + 1], __bfloat162float(h1)));
-        h[i] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
-        l[i] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+        // cvt.rn.bf16x2.f32 d, hi_half, lo_half: two roundings per instruction; a bf16 widens to fp32 by a shift / mask
+        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(h[i]) : "f"(v[2 * i + 1]), "f"(v[2 * i]));
+        const float r0 = __fsub_rn(v[2 * i], __uint_as_float(h[i] << 16));
+        const float r1 = __fsub_rn(v[2 * i + 1], __uint_as_float(h[i] & 0xffff0000u));
+        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(l[i]) : "f"(r1), "f"(r0));
     }
     hi = make_uint4(h[0], h[1], h[2], h[3]);
     lo = make_uint4(l[0], l[1], l[2], l[3]);
