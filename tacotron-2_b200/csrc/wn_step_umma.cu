@@ -65,6 +65,7 @@ struct UArgs {
     float *out, *skips;
     const float *xin;
     int H, R, S, NT, first_layer, legacy, residual_legacy;
+    int dbg;
 };
 
 // tanh(t) * sigmoid(s) (modules.py:510) with the hardware exponential and reciprocal (ex2.approx / rcp.approx, relative
@@ -125,7 +126,7 @@ __global__ void __launch_bounds__(UTHREADS, 2) umma_layer_kernel(const __grid_co
                 const uint32_t use = (uint32_t)(b / NSTAGE);
                 if (b >= NSTAGE) umma::mbar_wait(done(s), (use - 1u) & 1u);   // the MMAs of block b - NSTAGE have read the stage
                 const uint32_t st = smem0 + (uint32_t)s * STAGE_BYTES, Bs_a = st + B_OFF;
-                const uint32_t bytes = (uint32_t)bk * (uint32_t)ncols * 4u;
+                const uint32_t bytes = ((uint32_t)bk * (uint32_t)ncols * 4u) >> (a.dbg & 7);
                 umma::mbar_expect_tx(full(s), bytes);
                 const unsigned char *src = Wt + a.blk[b].w_off;
                 for (uint32_t o = 0; o < bytes; o += 16384u)
@@ -134,7 +135,7 @@ __global__ void __launch_bounds__(UTHREADS, 2) umma_layer_kernel(const __grid_co
                 umma::mbar_wait(full(s), use & 1u);
                 umma::fence_after_sync();
                 const uint32_t Ah_a = st, Al_a = st + A_HALF_BYTES, Bl_a = Bs_a + (uint32_t)bk * (uint32_t)ncols * 2u;
-                for (int ks = 0; ks < (bk >> 4); ++ks) {
+                for (int ks = 0; ks < ((a.dbg & 512) ? 0 : (bk >> 4)); ++ks) {
                     const uint64_t ah = umma::smem_desc(Ah_a + ks * 2 * LBO_A, LBO_A, 128), al = umma::smem_desc(Al_a + ks * 2 * LBO_A, LBO_A, 128);
                     const uint64_t bh = umma::smem_desc(Bs_a + ks * 2 * lboB, lboB, 128), bl = umma::smem_desc(Bl_a + ks * 2 * lboB, lboB, 128);
                     umma::mma_bf16(tmem, ah, bh, idesc, (b > 0 || ks > 0) ? 1u : 0u);
@@ -171,7 +172,7 @@ __global__ void __launch_bounds__(UTHREADS, 2) umma_layer_kernel(const __grid_co
             for (int j = 0; j < 2; ++j) {
                 const float *p = k.seg == 0 ? srow[j] + back_off : crow[j] + k.koff;
                 float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
-                if (c_ok && trow[j] >= k.back) { v0 = __ldg(reinterpret_cast<const float4 *>(p)); v1 = __ldg(reinterpret_cast<const float4 *>(p + 4)); }
+                if (c_ok && trow[j] >= k.back && !(a.dbg & 256)) { v0 = __ldg(reinterpret_cast<const float4 *>(p)); v1 = __ldg(reinterpret_cast<const float4 *>(p + 4)); }
                 pf[2 * j] = v0; pf[2 * j + 1] = v1;
             }
         };
@@ -206,6 +207,7 @@ __global__ void __launch_bounds__(UTHREADS, 2) umma_layer_kernel(const __grid_co
     const int q = warp & 3, half = (warp >> 2) & 1;
     const uint32_t tq = tmem + ((uint32_t)(32 * q) << 16);
     const float *bias = a.bias + (size_t)ty * ncols;
+    if (a.dbg & 1024) { umma::fence_before_sync(); __syncthreads(); if (warp == 8) umma::tmem_dealloc(tmem, 256); return; }
     if (EPI == UEPI_GATE) {
         const int NT = a.NT;
         if (warp < 8) {
@@ -436,6 +438,7 @@ int wn_umma_layer(wn_handle *h, int l, const float *x, const float *c_up, float 
     const WnModelDev &m = h->m;
     UArgs a;
     memset(&a, 0, sizeof(a));
+    a.dbg = getenv("WN_UMMA_DBG") ? atoi(getenv("WN_UMMA_DBG")) : 0;
     a.N = N; a.T = T; a.H = m.H; a.R = m.R; a.S = m.S; a.NT = u->NT;
     a.legacy = m.legacy; a.residual_legacy = m.residual_legacy; a.first_layer = l == 0;
     const unsigned grid_x = (unsigned)((N + UM - 1) / UM);

@@ -153,6 +153,44 @@ def test_step_gemm_equals_serial_step(name, monkeypatch):
     assert np.all(common.rel_close(y, y_serial)), common.max_rel(y, y_serial)
 
 
+_TENSOR_CASES = {
+    'default_22k': (lambda: common.default_22k(), 3, 3),
+    'r64_g128': (lambda: common.small(residual_channels=64, gate_channels=128, skip_out_channels=64), 2, 40),
+    'paper_block': (lambda: common.small(common.paper(), layers=6, stacks=3, residual_channels=256, gate_channels=512,
+                                         skip_out_channels=256), 2, 20),
+}
+
+
+@pytest.mark.parametrize('name', list(_TENSOR_CASES))
+def test_step_tensor_core_path(name, monkeypatch):
+    """WaveNet.step on the tensor cores (csrc/wn_step_umma.cu: tcgen05.mma, bf16 hi/lo split, three passes) against the fp32
+    FFMA GEMMs (WN_STEP_FFMA=1) and the position-by-position engines: 1e-3 relative (BASELINE.json), observed ~2e-5
+    (default block) / ~2.5e-4 (paper block, mixture head).  One tile (128 positions) column tiles of 256 and 128, K tails
+    of 16, utterance starts inside a tile."""
+    mk, B, Tc = _TENSOR_CASES[name]
+    hp = mk()
+    w = common.weights_for(hp)
+    T = Tc * hp.hop_size
+    c = np.transpose(common.cond_for(hp, B, Tc), [0, 2, 1])
+    x = common.teacher_for(hp, B, T)[:, None, :]
+    from wavenet_vocoder.models import create_model
+    model = create_model('WaveNet', hp)
+    model.load_weights(w)
+    monkeypatch.delenv('WN_STEP_FFMA', raising=False)
+    monkeypatch.delenv('WN_STEP_SERIAL', raising=False)
+    y = model.step(x, c=c)
+    monkeypatch.setenv('WN_STEP_FFMA', '1')
+    y_f = model.step(x, c=c)
+    monkeypatch.delenv('WN_STEP_FFMA')
+    monkeypatch.setenv('WN_STEP_SERIAL', '1')
+    y_s = model.step(x, c=c)
+    assert np.isfinite(y).all()
+    assert not np.array_equal(y, y_f), 'the tensor-core path did not run'
+    assert np.all(common.rel_close(y, y_f)), common.max_rel(y, y_f)
+    assert np.all(common.rel_close(y, y_s)), common.max_rel(y, y_s)
+    assert common.max_rel(y_f, y_s) < 1e-4
+
+
 def test_synthesizer_end_to_end_ragged(tmp_path):
     """Synthesizer.load / .synthesize (the drop-in boundary): ragged mels, padding, crop, wav files."""
     from wavenet_vocoder.synthesizer import Synthesizer

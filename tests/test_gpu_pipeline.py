@@ -95,6 +95,24 @@ def test_pipeline_default_config_plans(P):
     _check(net, hp, w, 5, 3)
 
 
+def test_pipeline_groups_of_8_for_large_batches():
+    """From WN_PIPE_NU8_MIN utterances (default 112) a launch groups the utterances by 8 instead of 4 (fewer hand-offs per
+    step once the engine is throughput bound); the arithmetic per utterance is unchanged, so both stay bit-exact, on one
+    handle, in either order."""
+    hp = common.default_22k()
+    w = common.weights_for(hp)
+    net = _net(hp, w, WN_PIPE_NU8_MIN=9)
+    _check(net, hp, w, 11, 1)
+    assert net.info()['pipeline_group_size'] == 8
+    _check(net, hp, w, 5, 2)
+    assert net.info()['pipeline_group_size'] == 4
+    _check(net, hp, w, 17, 1)
+    assert net.info()['pipeline_group_size'] == 8
+    forced = _net(hp, w, WN_PIPE_NU=8)
+    _check(forced, hp, w, 3, 1)
+    assert forced.info()['pipeline_group_size'] == 8
+
+
 def test_generic_and_pipeline_agree_for_the_same_ksplit():
     """wn_config.ksplit pins the summation order: the two engines then return identical bits."""
     from wavenet_vocoder._native import NativeWaveNet
