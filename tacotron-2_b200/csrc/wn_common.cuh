@@ -113,6 +113,8 @@ int wn_launch_step_gemm(wn_handle *h, const float *x, const float *c_up, int B, 
 // the two GEMMs of a residual layer on the tensor cores (wn_step_umma.cu: tcgen05.mma, bf16 hi/lo split, fp32 TMEM accumulators)
 bool wn_umma_supported(const wn_handle *h);
 void wn_umma_free(wn_handle *h);
+bool wn_umma_head_supported(wn_handle *h);
+int wn_umma_head(wn_handle *h, const float *skips, float *h1, float *raw, long long N, int T, cudaStream_t st);
 int wn_umma_layer(wn_handle *h, int l, const float *x, const float *c_up, float *z, float *x_out, float *skips, long long N, int T,
                   cudaStream_t st);
 

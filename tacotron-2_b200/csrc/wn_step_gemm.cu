@@ -406,7 +406,10 @@ int wn_launch_step_gemm(wn_handle *h, const float *x, const float *c_up, int B, 
         h->launches += 2;
         cur ^= 1;
     }
-    {
+    if (tensor && wn_umma_head_supported(h)) {
+        rc = wn_umma_head(h, g->d_skips, g->d_h1, raw, N, T, st);
+        if (rc) return rc;
+    } else {
         GemmArgs a;
         memset(&a, 0, sizeof(a));
         a.N = N; a.T = T;

@@ -25,6 +25,7 @@
 // position and half of the columns.
 #include <algorithm>
 #include <array>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -33,17 +34,19 @@
 
 namespace {
 
-constexpr int UM = 128, UBK = 32, UMAXBLK = 32, NSTAGE = 2;
-constexpr int USTAGERS = 256, UTHREADS = USTAGERS + 32;   // 8 staging / epilogue warps + the issuing warp
+constexpr int UM = 128, UBK = 32, UMAXBLK = 32, NSTAGE = 3, PD = 1, SROWS = 4;
+constexpr int EPI_WARPS = 8, UEPI = EPI_WARPS * 32, USTAGERS = 256, ISSUE_WARP = (UEPI + USTAGERS) / 32;
+constexpr int COPY_WARP = ISSUE_WARP + 1;
+constexpr int UTHREADS = UEPI + USTAGERS + 64;             // 8 epilogue warps | 8 staging warps | the MMA warp | the copy warp
 constexpr int LBO_A = UM * 16 + 16;                        // k-chunk stride of the activation operand (16 B of padding: the
                                                            // 8 chunks a quarter warp stores land in 8 different bank groups)
 constexpr int A_HALF_BYTES = (UBK / 8) * LBO_A;            // one of A_hi / A_lo
 constexpr int B_OFF = 2 * A_HALF_BYTES;
 constexpr int STAGE_BYTES = B_OFF + 2 * 256 * UBK * 2;     // + B_hi, B_lo at N = 256
-constexpr int U_SMEM = NSTAGE * STAGE_BYTES;
 constexpr int STG_LD = 132;                                // row stride (floats) of the epilogue staging tile [128][128]
+constexpr int U_SMEM = NSTAGE * STAGE_BYTES + UM * STG_LD * 4;
 static_assert(UBK == 32, "the staging threads are mapped for blocks of 32 (tail 16)");
-static_assert(UM * STG_LD * 4 <= U_SMEM, "the epilogue staging tile reuses the operand stages");
+static_assert(U_SMEM <= 227 * 1024, "one CTA per SM");
 
 enum { UEPI_GATE = 0, UEPI_OUTSKIP = 1 };
 
@@ -64,8 +67,9 @@ struct UArgs {
     UBlock blk[UMAXBLK];
     float *out, *skips;
     const float *xin;
-    int H, R, S, NT, first_layer, legacy, residual_legacy;
-    int dbg;
+    int H, R, S, NT, nty, first_layer, legacy, residual_legacy;
+    int relu_in, plain, out_ld;  // head 1x1 (wavenet.py:838-842): relu on the operand, epilogue = bias + relu -> out [N][out_ld]
+    unsigned long long *stats;   // development aid (WN_UMMA_STATS): clock64 sums per role, [EPI][16]
 };
 
 // tanh(t) * sigmoid(s) (modules.py:510) with the hardware exponential and reciprocal (ex2.approx / rcp.approx, relative
@@ -91,206 +95,269 @@ __device__ __forceinline__ float gate_fast(float t, float s) {
     return th * sg;
 }
 
+#define TWAIT(slot, bar, par) do { const long long t0_ = clock64(); umma::mbar_wait(bar, par); st_acc[slot] += clock64() - t0_; } while (0)
+
 template <int EPI>
-__global__ void __launch_bounds__(UTHREADS, 2) umma_layer_kernel(const __grid_constant__ UArgs a) {
+__global__ void __launch_bounds__(UTHREADS, 1) umma_layer_kernel(const __grid_constant__ UArgs a) {
     extern __shared__ __align__(128) unsigned char usmem[];
-    __shared__ __align__(8) unsigned long long bars[3 * NSTAGE];   // full (weights landed) | ready (activations staged) | done (MMAs read the stage)
+    // full (weights landed) | ready (activations staged) | done (MMAs read the stage) per operand stage;
+    // tfull (accumulator finished) | tempty (epilogue has read it) per TMEM accumulator
+    __shared__ __align__(8) unsigned long long bars[3 * NSTAGE + 4];
     __shared__ uint32_t tmem_slot;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t bar0 = umma::smem_addr(&bars[0]);
     auto full = [&](int s) { return bar0 + 8u * (uint32_t)s; };
     auto ready = [&](int s) { return bar0 + 8u * (uint32_t)(NSTAGE + s); };
     auto done = [&](int s) { return bar0 + 8u * (uint32_t)(2 * NSTAGE + s); };
+    auto tfull = [&](int i) { return bar0 + 8u * (uint32_t)(3 * NSTAGE + i); };
+    auto tempty = [&](int i) { return bar0 + 8u * (uint32_t)(3 * NSTAGE + 2 + i); };
     if (tid == 0) {
-        for (int s = 0; s < NSTAGE; ++s) { umma::mbar_init(full(s), 1); umma::mbar_init(ready(s), USTAGERS); umma::mbar_init(done(s), 1); }
+        for (int s = 0; s < NSTAGE; ++s) { umma::mbar_init(full(s), 1); umma::mbar_init(ready(s), USTAGERS / 2); umma::mbar_init(done(s), 1); }
+        for (int i = 0; i < 2; ++i) { umma::mbar_init(tfull(i), 1); umma::mbar_init(tempty(i), UEPI); }
         umma::mbar_fence_init();
     }
-    if (warp == 8) umma::tmem_alloc(umma::smem_addr(&tmem_slot), 256);
+    if (warp == ISSUE_WARP) umma::tmem_alloc(umma::smem_addr(&tmem_slot), 512);
     umma::fence_before_sync();
     __syncthreads();
     umma::fence_after_sync();
     const uint32_t tmem = tmem_slot;
-
-    const long long n0 = (long long)blockIdx.x * UM;
-    const int ty = blockIdx.y, ncols = a.ncols, nblk = a.nblk;
+    const int ncols = a.ncols, nblk = a.nblk, nty = a.nty;
+    const long long total = ((a.N + UM - 1) / UM) * nty;     // work items: (position tile, column tile), column tile minor
     const uint32_t smem0 = umma::smem_addr(usmem);
+    long long st_acc[4] = {0, 0, 0, 0};
+    const long long st_begin = clock64();
 
-    if (warp == 8) {
-        // ---- issuing warp: weights by bulk copy, tcgen05.mma, commit ----------------------------------------------------
+    if (warp == COPY_WARP) {
+        // ---- copy thread: the packed weights of block g go to stage g % NSTAGE as soon as the MMAs that last read that stage
+        //      have completed (up to NSTAGE blocks ahead of the MMA thread) ----------------------------------------------------
         if (lane == 0) {
-            const unsigned char *Wt = a.W + (long long)ty * a.tile_w_bytes;
-            const uint32_t idesc = umma::idesc_bf16(UM, ncols);
-            const uint32_t lboB = (uint32_t)ncols * 16;
-            for (int b = 0; b < nblk; ++b) {
-                const int s = b % NSTAGE, bk = a.blk[b].bk;
-                const uint32_t use = (uint32_t)(b / NSTAGE);
-                if (b >= NSTAGE) umma::mbar_wait(done(s), (use - 1u) & 1u);   // the MMAs of block b - NSTAGE have read the stage
-                const uint32_t st = smem0 + (uint32_t)s * STAGE_BYTES, Bs_a = st + B_OFF;
-                const uint32_t bytes = ((uint32_t)bk * (uint32_t)ncols * 4u) >> (a.dbg & 7);
-                umma::mbar_expect_tx(full(s), bytes);
-                const unsigned char *src = Wt + a.blk[b].w_off;
-                for (uint32_t o = 0; o < bytes; o += 16384u)
-                    umma::bulk_g2s(Bs_a + o, src + o, bytes - o < 16384u ? bytes - o : 16384u, full(s));
-                umma::mbar_wait(ready(s), use & 1u);
-                umma::mbar_wait(full(s), use & 1u);
-                umma::fence_after_sync();
-                const uint32_t Ah_a = st, Al_a = st + A_HALF_BYTES, Bl_a = Bs_a + (uint32_t)bk * (uint32_t)ncols * 2u;
-                for (int ks = 0; ks < ((a.dbg & 512) ? 0 : (bk >> 4)); ++ks) {
-                    const uint64_t ah = umma::smem_desc(Ah_a + ks * 2 * LBO_A, LBO_A, 128), al = umma::smem_desc(Al_a + ks * 2 * LBO_A, LBO_A, 128);
-                    const uint64_t bh = umma::smem_desc(Bs_a + ks * 2 * lboB, lboB, 128), bl = umma::smem_desc(Bl_a + ks * 2 * lboB, lboB, 128);
-                    umma::mma_bf16(tmem, ah, bh, idesc, (b > 0 || ks > 0) ? 1u : 0u);
-                    umma::mma_bf16(tmem, ah, bl, idesc, 1u);
-                    umma::mma_bf16(tmem, al, bh, idesc, 1u);
+            uint32_t s = 0, ph = 0, g = 0;                       // stage, parity of its current use, blocks requested
+            int ty = (int)(blockIdx.x % nty);
+            const int ty_step = (int)(gridDim.x % nty);
+            for (long long w = blockIdx.x; w < total; w += gridDim.x) {
+                const unsigned char *Wt = a.W + (long long)ty * a.tile_w_bytes;
+                for (int b = 0; b < nblk; ++b, ++g) {
+                    if (g >= NSTAGE) TWAIT(3, done(s), ph ^ 1u);   // use - 1 of this stage has been read
+                    const uint32_t bytes = (uint32_t)a.blk[b].bk * (uint32_t)ncols * 4u;
+                    const uint32_t Bs_a = smem0 + s * STAGE_BYTES + B_OFF;
+                    const unsigned char *src = Wt + a.blk[b].w_off;
+                    umma::mbar_expect_tx(full(s), bytes);
+                    for (uint32_t o = 0; o < bytes; o += 16384u)
+                        umma::bulk_g2s(Bs_a + o, src + o, bytes - o < 16384u ? bytes - o : 16384u, full(s));
+                    if (++s == NSTAGE) { s = 0; ph ^= 1u; }
                 }
-                umma::mma_commit(done(s));
+                ty += ty_step;
+                if (ty >= nty) ty -= nty;
             }
+            if (a.stats) atomicAdd(a.stats + EPI * 16 + 3, (unsigned long long)st_acc[3]);
         }
         __syncwarp();
-    } else {
-        // ---- staging warps: gather, split into bf16 (hi, lo), store in the K-major core-matrix layout -----------------------
-        // thread = (8-float chunk c of a 32-wide block, rows r0 and r0 + 64): the lanes of a warp read whole 128-byte row
-        // segments.  Everything that depends only on the thread (row pointers, position inside the utterance) is computed
-        // once; a 16-wide tail block keeps the mapping with the chunks c >= 2 idle.
-        const int c = tid & 3, r0 = tid >> 2;
-        const float *srow[2], *crow[2];
-        int trow[2];
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const long long n = n0 + r0 + 64 * j;
-            const bool ok = n < a.N;
-            trow[j] = ok ? (int)(n % a.T) : -1;               // -1: no such position (tail tile) -> zeros
-            srow[j] = a.src + (ok ? n : 0) * a.src_ld + 8 * c;
-            crow[j] = a.cond ? a.cond + (ok ? n : 0) * a.cond_ld + 8 * c : nullptr;
-        }
-        const int soff = (c * LBO_A + r0 * 16);
-        float4 pf[4];
-        auto load_block = [&](int b) {
-            const UBlock &k = a.blk[b];
-            const bool c_ok = 8 * c < k.bk;
-            const int back_off = k.koff - k.back * a.src_ld;
-#pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                const float *p = k.seg == 0 ? srow[j] + back_off : crow[j] + k.koff;
-                float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
-                if (c_ok && trow[j] >= k.back && !(a.dbg & 256)) { v0 = __ldg(reinterpret_cast<const float4 *>(p)); v1 = __ldg(reinterpret_cast<const float4 *>(p + 4)); }
-                pf[2 * j] = v0; pf[2 * j + 1] = v1;
-            }
-        };
-        auto store_block = [&](int b, int s) {
-            if (8 * c >= a.blk[b].bk) return;
-            unsigned char *Ah = usmem + (size_t)s * STAGE_BYTES + soff, *Al = Ah + A_HALF_BYTES;
-#pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                uint4 hi, lo;
-                umma::split8(pf[2 * j], pf[2 * j + 1], hi, lo);
-                *reinterpret_cast<uint4 *>(Ah + j * 64 * 16) = hi;
-                *reinterpret_cast<uint4 *>(Al + j * 64 * 16) = lo;
-            }
-        };
-        load_block(0);
-        for (int b = 0; b < nblk; ++b) {
-            const int s = b % NSTAGE;
-            if (b >= NSTAGE) umma::mbar_wait(done(s), (uint32_t)(b / NSTAGE - 1) & 1u);
-            store_block(b, s);
-            umma::fence_proxy_async();
-            umma::mbar_arrive(ready(s));
-            if (b + 1 < nblk) load_block(b + 1);   // in flight while the tensor core works
-        }
-        // the last commit covers every MMA of the tile
-        umma::mbar_wait(done((nblk - 1) % NSTAGE), (uint32_t)((nblk - 1) / NSTAGE) & 1u);
-        umma::fence_after_sync();
-    }
-
-    // ---- epilogue: TMEM -> registers (thread = position 32q + lane, half of the columns) -> staging tile in shared memory
-    //      -> coalesced rows (one warp per position row) -------------------------------------------------------------------
-    float *stg = reinterpret_cast<float *>(usmem);
-    const int q = warp & 3, half = (warp >> 2) & 1;
-    const uint32_t tq = tmem + ((uint32_t)(32 * q) << 16);
-    const float *bias = a.bias + (size_t)ty * ncols;
-    if (a.dbg & 1024) { umma::fence_before_sync(); __syncthreads(); if (warp == 8) umma::tmem_dealloc(tmem, 256); return; }
-    if (EPI == UEPI_GATE) {
-        const int NT = a.NT;
-        if (warp < 8) {
-            float *srow = stg + (size_t)(32 * q + lane) * STG_LD;
-            for (int c = half * (NT / 2); c < (half + 1) * (NT / 2); c += 16) {
-                float ta[16], sg[16];
-                umma::tmem_ld16(tq + (uint32_t)c, ta);
-                umma::tmem_ld16(tq + (uint32_t)(NT + c), sg);
-                umma::tmem_ld_wait();
-#pragma unroll
-                for (int i4 = 0; i4 < 4; ++i4) {
-                    const float4 bt = __ldg(reinterpret_cast<const float4 *>(bias + c + 4 * i4));
-                    const float4 bs = __ldg(reinterpret_cast<const float4 *>(bias + NT + c + 4 * i4));
-                    *reinterpret_cast<float4 *>(srow + c + 4 * i4) =
-                        make_float4(gate_fast(ta[4 * i4] + bt.x, sg[4 * i4] + bs.x), gate_fast(ta[4 * i4 + 1] + bt.y, sg[4 * i4 + 1] + bs.y),
-                                    gate_fast(ta[4 * i4 + 2] + bt.z, sg[4 * i4 + 2] + bs.z), gate_fast(ta[4 * i4 + 3] + bt.w, sg[4 * i4 + 3] + bs.w));
+    } else if (warp == ISSUE_WARP) {
+        // ---- MMA thread: tcgen05.mma into accumulator it & 1, commits ------------------------------------------------------
+        if (lane == 0) {
+            const uint32_t idesc = umma::idesc_bf16(UM, ncols);
+            const uint32_t lboB = (uint32_t)ncols * 16;
+            const uint64_t dA = umma::smem_desc(0, LBO_A, 128), dB = umma::smem_desc(0, lboB, 128);   // + (address >> 4)
+            const uint32_t kA = (2 * LBO_A) >> 4, kB = (2 * lboB) >> 4;                             // one K step of 16
+            uint32_t s = 0, ph = 0;
+            int it = 0;
+            for (long long w = blockIdx.x; w < total; w += gridDim.x, ++it) {
+                const int ab = it & 1;
+                if (it >= 2) { TWAIT(0, tempty(ab), (uint32_t)((it >> 1) - 1) & 1u); umma::fence_after_sync(); }
+                const uint32_t d_tmem = tmem + (uint32_t)ab * 256u;
+                for (int b = 0; b < nblk; ++b) {
+                    const int bk = a.blk[b].bk;
+                    TWAIT(1, ready(s), ph);
+                    TWAIT(2, full(s), ph);
+                    umma::fence_after_sync();
+                    const uint32_t st16 = (smem0 + s * STAGE_BYTES) >> 4;
+                    const uint64_t ah = dA + st16, al = ah + (A_HALF_BYTES >> 4), bh = dB + st16 + (B_OFF >> 4),
+                                   bl = bh + (((uint32_t)bk * (uint32_t)ncols * 2u) >> 4);
+                    umma::mma_bf16(d_tmem, ah, bh, idesc, b > 0 ? 1u : 0u);
+                    umma::mma_bf16(d_tmem, ah, bl, idesc, 1u);
+                    umma::mma_bf16(d_tmem, al, bh, idesc, 1u);
+                    if (bk > 16) {
+                        umma::mma_bf16(d_tmem, ah + kA, bh + kB, idesc, 1u);
+                        umma::mma_bf16(d_tmem, ah + kA, bl + kB, idesc, 1u);
+                        umma::mma_bf16(d_tmem, al + kA, bh + kB, idesc, 1u);
+                    }
+                    umma::mma_commit(done(s));
+                    if (++s == NSTAGE) { s = 0; ph ^= 1u; }
                 }
+                umma::mma_commit(tfull(ab));                      // every MMA of the tile has completed
+            }
+            if (a.stats) { for (int i = 0; i < 3; ++i) atomicAdd(a.stats + EPI * 16 + i, (unsigned long long)st_acc[i]); atomicAdd(a.stats + EPI * 16 + 4, (unsigned long long)(clock64() - st_begin)); atomicAdd(a.stats + EPI * 16 + 5, 1ull); }
+        }
+        __syncwarp();
+    } else if (warp >= EPI_WARPS) {
+        // ---- staging warps: gather, split into bf16 (hi, lo), store in the K-major core-matrix layout -----------------------
+        // Two groups of 4 warps take alternate blocks (a block is one dependent chain load -> split -> store -> fence -> arrive
+        // per warp, so two blocks in flight nearly double the staging rate).  thread = (8-float chunk c of a 32-wide block,
+        // rows r0 + 32 j): the lanes of a warp read whole 128-byte row segments.  What depends only on the tile (row pointers,
+        // position inside the utterance) is computed once per tile; a 16-wide tail block keeps the mapping with the chunks
+        // c >= 2 idle.
+        const int st_tid = tid - EPI_WARPS * 32, grp = st_tid >> 7, c = st_tid & 3, r0 = (st_tid & 127) >> 2;
+        const int soff = c * LBO_A + r0 * 16;
+        uint32_t gb0 = 0;                                        // global index of the tile's first block
+        for (long long w = blockIdx.x; w < total; w += gridDim.x, gb0 += (uint32_t)nblk) {
+            const long long n0 = (w / nty) * UM;
+            const float *srow[SROWS], *crow[SROWS];
+            int trow[SROWS];
+#pragma unroll
+            for (int j = 0; j < SROWS; ++j) {
+                const long long n = n0 + r0 + 32 * j;
+                const bool ok = n < a.N;
+                trow[j] = ok ? (int)(n % a.T) : -1;               // -1: no such position (tail tile) -> zeros
+                srow[j] = a.src + (ok ? n : 0) * a.src_ld + 8 * c;
+                crow[j] = a.cond ? a.cond + (ok ? n : 0) * a.cond_ld + 8 * c : nullptr;
+            }
+            // the activations of a block are requested PD of the group's blocks before they are split and stored
+            float4 pf[PD][2 * SROWS];
+            auto load_block = [&](int b, float4 (&pfx)[2 * SROWS]) {
+                const UBlock &k = a.blk[b];
+                const bool c_ok = 8 * c < k.bk;
+                const int back_off = k.koff - k.back * a.src_ld;
+#pragma unroll
+                for (int j = 0; j < SROWS; ++j) {
+                    const float *p = k.seg == 0 ? srow[j] + back_off : crow[j] + k.koff;
+                    float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+                    if (c_ok && trow[j] >= k.back) { v0 = __ldg(reinterpret_cast<const float4 *>(p)); v1 = __ldg(reinterpret_cast<const float4 *>(p + 4)); }
+                    if (a.relu_in) {
+                        v0.x = fmaxf(v0.x, 0.f); v0.y = fmaxf(v0.y, 0.f); v0.z = fmaxf(v0.z, 0.f); v0.w = fmaxf(v0.w, 0.f);
+                        v1.x = fmaxf(v1.x, 0.f); v1.y = fmaxf(v1.y, 0.f); v1.z = fmaxf(v1.z, 0.f); v1.w = fmaxf(v1.w, 0.f);
+                    }
+                    pfx[2 * j] = v0; pfx[2 * j + 1] = v1;
+                }
+            };
+            auto step = [&](int b, float4 (&pfx)[2 * SROWS]) {
+                const uint32_t g = gb0 + (uint32_t)b, s = g % NSTAGE, use = g / NSTAGE;
+                if (g >= NSTAGE) TWAIT(0, done(s), (use - 1u) & 1u);
+                if (8 * c < a.blk[b].bk) {
+                    unsigned char *Ah = usmem + (size_t)s * STAGE_BYTES + soff, *Al = Ah + A_HALF_BYTES;
+#pragma unroll
+                    for (int j = 0; j < SROWS; ++j) {
+                        uint4 hi, lo;
+                        umma::split8(pfx[2 * j], pfx[2 * j + 1], hi, lo);
+                        *reinterpret_cast<uint4 *>(Ah + j * 32 * 16) = hi;
+                        *reinterpret_cast<uint4 *>(Al + j * 32 * 16) = lo;
+                    }
+                }
+                umma::fence_proxy_async();
+                umma::mbar_arrive(ready(s));
+                if (b + 2 * PD < nblk) load_block(b + 2 * PD, pfx);
+            };
+            const int bfirst = (int)((gb0 ^ (uint32_t)grp) & 1u);   // the group's first block of this tile
+#pragma unroll
+            for (int i = 0; i < PD; ++i)
+                if (bfirst + 2 * i < nblk) load_block(bfirst + 2 * i, pf[i]);
+            for (int b = bfirst; b < nblk; b += 2 * PD) {
+#pragma unroll
+                for (int i = 0; i < PD; ++i)
+                    if (b + 2 * i < nblk) step(b + 2 * i, pf[i]);
             }
         }
-        __syncthreads();
-        if (warp < 8 && 4 * lane < NT)
-            for (int r = warp; r < UM; r += 8) {
-                const long long n = n0 + r;
-                if (n < a.N)
-                    *reinterpret_cast<float4 *>(a.out + n * a.H + ty * NT + 4 * lane) = *reinterpret_cast<const float4 *>(stg + (size_t)r * STG_LD + 4 * lane);
-            }
     } else {
-        for (int g = 0; g < ncols / 128; ++g) {
-            if (g > 0) __syncthreads();
-            if (warp < 8) {
-                float *srow = stg + (size_t)(32 * q + lane) * STG_LD;
-                for (int c = half * 64; c < half * 64 + 64; c += 16) {
-                    float v[16];
-                    umma::tmem_ld16(tq + (uint32_t)(g * 128 + c), v);
+        // ---- epilogue warps: TMEM -> registers (thread = position 32q + lane, half of the columns) -> staging tile in shared
+        //      memory -> coalesced rows (one warp per position row), while the other warps work on the next tile ----------------
+        float *stg = reinterpret_cast<float *>(usmem + NSTAGE * STAGE_BYTES);
+        const int q = warp & 3, half = warp >> 2;
+        float *srow = stg + (size_t)(32 * q + lane) * STG_LD;
+        auto epi_sync = [&]() { asm volatile("bar.sync 1, %0;" ::"n"(UEPI) : "memory"); };
+        int it = 0;
+        for (long long w = blockIdx.x; w < total; w += gridDim.x, ++it) {
+            const long long n0 = (w / nty) * UM;
+            const int ty = (int)(w % nty), ab = it & 1;
+            const uint32_t tq = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)ab * 256u;
+            const float *bias = a.bias + (size_t)ty * ncols;
+            TWAIT(0, tfull(ab), (uint32_t)(it >> 1) & 1u);
+            umma::fence_after_sync();
+            if (EPI == UEPI_GATE) {
+                const int NT = a.NT;
+                for (int c = half * (NT / 2); c < (half + 1) * (NT / 2); c += 16) {
+                    float ta[16], sg[16];
+                    umma::tmem_ld16(tq + (uint32_t)c, ta);
+                    umma::tmem_ld16(tq + (uint32_t)(NT + c), sg);
                     umma::tmem_ld_wait();
 #pragma unroll
-                    for (int i4 = 0; i4 < 4; ++i4)
-                        *reinterpret_cast<float4 *>(srow + c + 4 * i4) = make_float4(v[4 * i4], v[4 * i4 + 1], v[4 * i4 + 2], v[4 * i4 + 3]);
+                    for (int i4 = 0; i4 < 4; ++i4) {
+                        const float4 bt = __ldg(reinterpret_cast<const float4 *>(bias + c + 4 * i4));
+                        const float4 bs = __ldg(reinterpret_cast<const float4 *>(bias + NT + c + 4 * i4));
+                        *reinterpret_cast<float4 *>(srow + c + 4 * i4) =
+                            make_float4(gate_fast(ta[4 * i4] + bt.x, sg[4 * i4] + bs.x), gate_fast(ta[4 * i4 + 1] + bt.y, sg[4 * i4 + 1] + bs.y),
+                                        gate_fast(ta[4 * i4 + 2] + bt.z, sg[4 * i4 + 2] + bs.z), gate_fast(ta[4 * i4 + 3] + bt.w, sg[4 * i4 + 3] + bs.w));
+                    }
                 }
-            }
-            __syncthreads();
-            if (warp < 8) {
-                const int m = ty * ncols + g * 128 + 4 * lane;            // first of this lane's 4 output rows of the GEMM
-                const float4 bb = __ldg(reinterpret_cast<const float4 *>(bias + g * 128 + 4 * lane));
-                // what is added to a row: the layer input (residual, modules.py:515-520) or the running skip sum
-                // (wavenet.py:833-836); 8 rows of loads are in flight before the first one is used
-                const bool is_out = m < a.R, has_add = is_out || !a.first_layer;
-                const float *addp = is_out ? a.xin + m : a.skips + (m - a.R);
-                float *dstp = is_out ? a.out + m : a.skips + (m - a.R);
-                const int ld = is_out ? a.R : a.S;
-                const bool scale = is_out ? a.residual_legacy != 0 : (a.legacy != 0 && !a.first_layer);
-                for (int rb = warp; rb < UM; rb += 64) {
-                    float4 add[8];
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) {
-                        const long long n = n0 + rb + 8 * k;
-                        add[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (has_add && n < a.N) add[k] = *reinterpret_cast<const float4 *>(addp + n * ld);
-                    }
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) {
-                        const int r = rb + 8 * k;
+                umma::fence_before_sync();
+                umma::mbar_arrive(tempty(ab));                    // the accumulator may be overwritten
+                epi_sync();
+                if (4 * lane < NT)
+                    for (int r = warp; r < UM; r += EPI_WARPS) {
                         const long long n = n0 + r;
-                        if (n >= a.N) continue;
-                        const float4 v = *reinterpret_cast<const float4 *>(stg + (size_t)r * STG_LD + 4 * lane);
-                        float4 y = make_float4(__fadd_rn(v.x, bb.x), __fadd_rn(v.y, bb.y), __fadd_rn(v.z, bb.z), __fadd_rn(v.w, bb.w));
-                        if (has_add) {
-                            if (is_out) { y.x = __fadd_rn(y.x, add[k].x); y.y = __fadd_rn(y.y, add[k].y); y.z = __fadd_rn(y.z, add[k].z); y.w = __fadd_rn(y.w, add[k].w); }
-                            else { y.x = __fadd_rn(add[k].x, y.x); y.y = __fadd_rn(add[k].y, y.y); y.z = __fadd_rn(add[k].z, y.z); y.w = __fadd_rn(add[k].w, y.w); }
-                        }
-                        if (scale) {
-                            y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF);
-                            y.z = __fmul_rn(y.z, WN_SQRT_HALF); y.w = __fmul_rn(y.w, WN_SQRT_HALF);
-                        }
-                        *reinterpret_cast<float4 *>(dstp + n * ld) = y;
+                        if (n < a.N)
+                            *reinterpret_cast<float4 *>(a.out + n * a.H + ty * NT + 4 * lane) = *reinterpret_cast<const float4 *>(stg + (size_t)r * STG_LD + 4 * lane);
                     }
+                epi_sync();
+            } else {
+                const int ngroups = ncols / 128;
+                for (int g = 0; g < ngroups; ++g) {
+                    for (int c = half * 64; c < half * 64 + 64; c += 16) {
+                        float v[16];
+                        umma::tmem_ld16(tq + (uint32_t)(g * 128 + c), v);
+                        umma::tmem_ld_wait();
+#pragma unroll
+                        for (int i4 = 0; i4 < 4; ++i4)
+                            *reinterpret_cast<float4 *>(srow + c + 4 * i4) = make_float4(v[4 * i4], v[4 * i4 + 1], v[4 * i4 + 2], v[4 * i4 + 3]);
+                    }
+                    if (g == ngroups - 1) { umma::fence_before_sync(); umma::mbar_arrive(tempty(ab)); }
+                    epi_sync();
+                    const int m = ty * ncols + g * 128 + 4 * lane;            // first of this lane's 4 output rows of the GEMM
+                    const float4 bb = __ldg(reinterpret_cast<const float4 *>(bias + g * 128 + 4 * lane));
+                    // what is added to a row: the layer input (residual, modules.py:515-520) or the running skip sum
+                    // (wavenet.py:833-836); 8 rows of loads are in flight before the first one is used
+                    const bool plain = a.plain != 0, is_out = plain || m < a.R, has_add = !plain && (is_out || !a.first_layer);
+                    const float *addp = is_out ? a.xin + m : a.skips + (m - a.R);
+                    float *dstp = is_out ? a.out + m : a.skips + (m - a.R);
+                    const int ld = plain ? a.out_ld : (is_out ? a.R : a.S);
+                    const bool scale = !plain && (is_out ? a.residual_legacy != 0 : (a.legacy != 0 && !a.first_layer));
+                    for (int rb = warp; rb < UM; rb += 8 * EPI_WARPS) {
+                        float4 add[8];
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) {
+                            const long long n = n0 + rb + EPI_WARPS * k;
+                            add[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (has_add && n < a.N) add[k] = *reinterpret_cast<const float4 *>(addp + n * ld);
+                        }
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) {
+                            const int r = rb + EPI_WARPS * k;
+                            const long long n = n0 + r;
+                            if (n >= a.N) continue;
+                            const float4 v = *reinterpret_cast<const float4 *>(stg + (size_t)r * STG_LD + 4 * lane);
+                            float4 y = make_float4(__fadd_rn(v.x, bb.x), __fadd_rn(v.y, bb.y), __fadd_rn(v.z, bb.z), __fadd_rn(v.w, bb.w));
+                            if (has_add) {
+                                if (is_out) { y.x = __fadd_rn(y.x, add[k].x); y.y = __fadd_rn(y.y, add[k].y); y.z = __fadd_rn(y.z, add[k].z); y.w = __fadd_rn(y.w, add[k].w); }
+                                else { y.x = __fadd_rn(add[k].x, y.x); y.y = __fadd_rn(add[k].y, y.y); y.z = __fadd_rn(add[k].z, y.z); y.w = __fadd_rn(add[k].w, y.w); }
+                            }
+                            if (scale) {
+                                y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF);
+                                y.z = __fmul_rn(y.z, WN_SQRT_HALF); y.w = __fmul_rn(y.w, WN_SQRT_HALF);
+                            }
+                            if (plain) { y.x = fmaxf(y.x, 0.f); y.y = fmaxf(y.y, 0.f); y.z = fmaxf(y.z, 0.f); y.w = fmaxf(y.w, 0.f); }
+                            *reinterpret_cast<float4 *>(dstp + n * ld) = y;
+                        }
+                    }
+                    epi_sync();
                 }
             }
         }
+    }
+    if (a.stats && (tid == 0 || tid == UEPI)) {   // (the stagers' wait is that of group 0)
+        const int o = EPI * 16 + (tid == 0 ? 6 : 8);
+        atomicAdd(a.stats + o, (unsigned long long)st_acc[0]); atomicAdd(a.stats + o + 1, (unsigned long long)(clock64() - st_begin));
     }
     umma::fence_before_sync();
     __syncthreads();
-    if (warp == 8) umma::tmem_dealloc(tmem, 256);
+    if (warp == ISSUE_WARP) umma::tmem_dealloc(tmem, 512);
 }
 
 unsigned short bf16_rn_host(float f) {
@@ -335,12 +402,31 @@ struct WnUmmaPlan {
     int NT = 0, gate_ncols = 0, gate_tiles = 0, os_ncols = 0, os_tiles = 0;
     unsigned gate_tile_bytes = 0, os_tile_bytes = 0;
     std::vector<KBlockHost> gate_blk, os_blk;
+    unsigned long long *d_stats = nullptr;
     std::vector<size_t> gate_w, os_w, gate_b, os_b;   // per layer: byte offsets into d_w, float offsets into d_bias
+    // head: final_convolution_1 on the tensor cores when S is a multiple of 128; final_convolution_2 by head2_kernel
+    bool head = false;
+    int h1_ncols = 0, h1_tiles = 0;
+    unsigned h1_tile_bytes = 0;
+    std::vector<KBlockHost> h1_blk;
+    size_t h1_w = 0, h1_b = 0, h2_w = 0, h2_b = 0;    // h2_w: [S][O] floats inside d_bias
 };
 
 void wn_umma_free(wn_handle *h) {
     WnUmmaPlan *u = h->umma;
     if (!u) return;
+    if (u->d_stats) {   // development aid: average clocks per CTA and launch
+        unsigned long long st[32];
+        cudaDeviceSynchronize();
+        if (cudaMemcpy(st, u->d_stats, sizeof(st), cudaMemcpyDeviceToHost) == cudaSuccess)
+            for (int e = 0; e < 2; ++e) {
+                const double n = st[e * 16 + 5] ? (double)st[e * 16 + 5] : 1.0;
+                fprintf(stderr, "umma stats %s: issuer waits tempty %.0f ready %.0f full %.0f done %.0f of %.0f clk | epilogue wait tfull %.0f of %.0f | stager wait done %.0f of %.0f (per CTA launch, %g launches)\n",
+                        e ? "out/skip" : "gate", st[e * 16] / n, st[e * 16 + 1] / n, st[e * 16 + 2] / n, st[e * 16 + 3] / n, st[e * 16 + 4] / n,
+                        st[e * 16 + 6] / n, st[e * 16 + 7] / n, st[e * 16 + 8] / n, st[e * 16 + 9] / n, n);
+            }
+        cudaFree(u->d_stats);
+    }
     if (u->d_w) cudaFree(u->d_w);
     if (u->d_bias) cudaFree(u->d_bias);
     delete u;
@@ -413,6 +499,21 @@ static int umma_plan(wn_handle *h) {
         for (int r = 0; r < R; ++r) bias.push_back(ob ? ob[r] : 0.0f);
         for (int s = 0; s < S; ++s) bias.push_back(sb ? sb[s] : 0.0f);
     }
+    if (S % 128 == 0 && m.O <= 32) {
+        const float *w1 = Wt("final_convolution_1/kernel"), *b1 = Wt("final_convolution_1/bias");
+        const float *w2 = Wt("final_convolution_2/kernel"), *b2 = Wt("final_convolution_2/bias");
+        u->head = true;
+        u->h1_ncols = S % 256 == 0 ? 256 : 128; u->h1_tiles = S / u->h1_ncols;
+        u->h1_blk = cut_blocks({{0, 2, S}}, u->h1_ncols, &u->h1_tile_bytes);
+        u->h1_w = pack(u->h1_blk, u->h1_ncols, u->h1_tiles, u->h1_tile_bytes, [&](int k, int row) { return w1[(size_t)k * S + row]; });
+        u->h1_b = bias.size();
+        for (int n = 0; n < S; ++n) bias.push_back(b1 ? b1[n] : 0.0f);
+        u->h2_w = bias.size();
+        for (int k = 0; k < S; ++k)
+            for (int o = 0; o < m.O; ++o) bias.push_back(w2[(size_t)k * m.O + o]);
+        u->h2_b = bias.size();
+        for (int o = 0; o < m.O; ++o) bias.push_back(b2 ? b2[o] : 0.0f);
+    }
     if (cudaMalloc((void **)&u->d_w, w.size() * 2) != cudaSuccess ||
         cudaMemcpy(u->d_w, w.data(), w.size() * 2, cudaMemcpyHostToDevice) != cudaSuccess ||
         cudaMalloc((void **)&u->d_bias, bias.size() * sizeof(float)) != cudaSuccess ||
@@ -425,6 +526,8 @@ static int umma_plan(wn_handle *h) {
         delete u;
         return WN_ERR_NOMEM;
     }
+    if (getenv("WN_UMMA_STATS") && cudaMalloc((void **)&u->d_stats, 32 * sizeof(unsigned long long)) == cudaSuccess)
+        cudaMemset(u->d_stats, 0, 32 * sizeof(unsigned long long));
     h->umma = u;
     return WN_OK;
 }
@@ -438,10 +541,11 @@ int wn_umma_layer(wn_handle *h, int l, const float *x, const float *c_up, float 
     const WnModelDev &m = h->m;
     UArgs a;
     memset(&a, 0, sizeof(a));
-    a.dbg = getenv("WN_UMMA_DBG") ? atoi(getenv("WN_UMMA_DBG")) : 0;
+    a.stats = u->d_stats;
     a.N = N; a.T = T; a.H = m.H; a.R = m.R; a.S = m.S; a.NT = u->NT;
     a.legacy = m.legacy; a.residual_legacy = m.residual_legacy; a.first_layer = l == 0;
-    const unsigned grid_x = (unsigned)((N + UM - 1) / UM);
+    const long long ptiles = (N + UM - 1) / UM;
+    auto grid_for = [&](int nty) { return (unsigned)std::min<long long>(ptiles * nty, h->sm_count); };   // persistent: one CTA per SM
     // gate
     a.W = u->d_w + u->gate_w[l]; a.tile_w_bytes = u->gate_tile_bytes; a.bias = u->d_bias + u->gate_b[l];
     a.src = x; a.src_ld = m.R; a.cond = c_up; a.cond_ld = m.cin; a.ncols = u->gate_ncols;
@@ -451,7 +555,8 @@ int wn_umma_layer(wn_handle *h, int l, const float *x, const float *c_up, float 
         a.blk[i] = {b.seg, b.koff, b.bk, b.seg == 0 ? (2 - b.tap) * m.dil[l] : 0, b.w_off};
     }
     a.out = z;
-    umma_layer_kernel<UEPI_GATE><<<dim3(grid_x, (unsigned)u->gate_tiles), UTHREADS, U_SMEM, st>>>(a);
+    a.nty = u->gate_tiles;
+    umma_layer_kernel<UEPI_GATE><<<grid_for(a.nty), UTHREADS, U_SMEM, st>>>(a);
     WN_CUDA_TRY(h, cudaGetLastError());
     // out / skip
     a.W = u->d_w + u->os_w[l]; a.tile_w_bytes = u->os_tile_bytes; a.bias = u->d_bias + u->os_b[l];
@@ -462,7 +567,66 @@ int wn_umma_layer(wn_handle *h, int l, const float *x, const float *c_up, float 
         a.blk[i] = {0, b.koff, b.bk, 0, b.w_off};
     }
     a.out = x_out; a.skips = skips; a.xin = x;
-    umma_layer_kernel<UEPI_OUTSKIP><<<dim3(grid_x, (unsigned)u->os_tiles), UTHREADS, U_SMEM, st>>>(a);
+    a.nty = u->os_tiles;
+    umma_layer_kernel<UEPI_OUTSKIP><<<grid_for(a.nty), UTHREADS, U_SMEM, st>>>(a);
+    WN_CUDA_TRY(h, cudaGetLastError());
+    h->launches += 2;
+    return WN_OK;
+}
+
+namespace {
+// final_convolution_2 (wavenet.py:842-844): raw[n][o] = b2[o] + sum_k h1[n][k] * W2[k][o], one warp per position (the row is
+// read once, coalesced); K ascending inside a lane, lanes combined by a butterfly
+__global__ void __launch_bounds__(256) head2_kernel(const float *__restrict__ h1, const float *__restrict__ w2, const float *__restrict__ b2,
+                                                    long long N, int S, int O, float *__restrict__ raw) {
+    const int lane = threadIdx.x & 31;
+    const long long n = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (n >= N) return;
+    for (int o0 = 0; o0 < O; o0 += 2) {
+        float acc0 = 0.f, acc1 = 0.f;
+        for (int k = 4 * lane; k < S; k += 128) {
+            const float4 v = *reinterpret_cast<const float4 *>(h1 + n * S + k);
+            const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                acc0 = __fmaf_rn(vv[e], __ldg(w2 + (size_t)(k + e) * O + o0), acc0);
+                if (o0 + 1 < O) acc1 = __fmaf_rn(vv[e], __ldg(w2 + (size_t)(k + e) * O + o0 + 1), acc1);
+            }
+        }
+#pragma unroll
+        for (int msk = 16; msk >= 1; msk >>= 1) {
+            acc0 = __fadd_rn(acc0, __shfl_xor_sync(0xffffffffu, acc0, msk));
+            acc1 = __fadd_rn(acc1, __shfl_xor_sync(0xffffffffu, acc1, msk));
+        }
+        if (lane == 0) {
+            raw[n * O + o0] = __fadd_rn(acc0, b2[o0]);
+            if (o0 + 1 < O) raw[n * O + o0 + 1] = __fadd_rn(acc1, b2[o0 + 1]);
+        }
+    }
+}
+}  // namespace
+
+bool wn_umma_head_supported(wn_handle *h) { return umma_plan(h) == WN_OK && h->umma->head; }
+
+// relu -> final_convolution_1 -> relu (tensor cores) -> final_convolution_2: skips [N][S] -> raw [N][O]; h1 is scratch [N][S]
+int wn_umma_head(wn_handle *h, const float *skips, float *h1, float *raw, long long N, int T, cudaStream_t st) {
+    int rc = umma_plan(h);
+    if (rc) return rc;
+    const WnUmmaPlan *u = h->umma;
+    const WnModelDev &m = h->m;
+    UArgs a;
+    memset(&a, 0, sizeof(a));
+    a.stats = nullptr;
+    a.N = N; a.T = T; a.H = m.H; a.R = m.R; a.S = m.S; a.NT = u->NT;
+    a.W = u->d_w + u->h1_w; a.tile_w_bytes = u->h1_tile_bytes; a.bias = u->d_bias + u->h1_b;
+    a.src = skips; a.src_ld = m.S; a.ncols = u->h1_ncols; a.nty = u->h1_tiles;
+    a.nblk = (int)u->h1_blk.size();
+    for (int i = 0; i < a.nblk; ++i) a.blk[i] = {0, u->h1_blk[i].koff, u->h1_blk[i].bk, 0, u->h1_blk[i].w_off};
+    a.relu_in = 1; a.plain = 1; a.out = h1; a.out_ld = m.S;
+    const long long ptiles = (N + UM - 1) / UM;
+    umma_layer_kernel<UEPI_OUTSKIP><<<(unsigned)std::min<long long>(ptiles * a.nty, h->sm_count), UTHREADS, U_SMEM, st>>>(a);
+    WN_CUDA_TRY(h, cudaGetLastError());
+    head2_kernel<<<(unsigned)((N + 7) / 8), 256, 0, st>>>(h1, u->d_bias + u->h2_w, u->d_bias + u->h2_b, N, m.S, m.O, raw);
     WN_CUDA_TRY(h, cudaGetLastError());
     h->launches += 2;
     return WN_OK;

@@ -25,3 +25,4 @@ for _ in range(2):
     net.step_full(dx, dc, B, frames, raw, stream=torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
 print('step ms', net.info()['last_loop_ms'], 'TFLOP/s', B * T * 6095616 / (net.info()['last_loop_ms'] / 1e3) / 1e12)
+net.close()
