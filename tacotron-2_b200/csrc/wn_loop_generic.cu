@@ -10,6 +10,10 @@
 // Arithmetic: the fixed fp32 orders of DESIGN.md "Arithmetic" (dot16 for the gate pre-activation and the head,
 // blocked sequential chains for the out / skip 1x1s), every transcendental from include/wn_math.h - the exact
 // operations oracle/c/wn_oracle.c performs, so free-running audio can be compared bit for bit.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+
 #include "wn_common.cuh"
 
 namespace {
@@ -28,29 +32,23 @@ __device__ __forceinline__ float dot16_lane(const float *xs, int K, int Kpad, co
         const float4 *w4 = reinterpret_cast<const float4 *>(Wt + (long long)n * Kpad);
         const float4 *x4 = reinterpret_cast<const float4 *>(xs);
         const int nfull = K >> 2;
-        // weights stream from L2: issue a batch of independent loads before the dependent fma chain consumes them
+        // weights stream from L2: a round issues up to UB independent loads (predicated at the end of the row) before the
+        // dependent fma chain consumes them, so a row costs ceil(K / (64 UB)) L2 round trips
         constexpr int UB = 8;
-        int c = lane;
-        for (; c + (UB - 1) * LANES < nfull; c += UB * LANES) {
+        for (int c = lane; c < nfull; c += UB * LANES) {
             float4 wv[UB];
 #pragma unroll
-            for (int u = 0; u < UB; ++u) wv[u] = __ldg(w4 + c + u * LANES);
+            for (int u = 0; u < UB; ++u)
+                if (c + u * LANES < nfull) wv[u] = __ldg(w4 + c + u * LANES);
 #pragma unroll
-            for (int u = 0; u < UB; ++u) {
-                const float4 xv = x4[c + u * LANES];
-                acc = __fmaf_rn(xv.x, wv[u].x, acc);
-                acc = __fmaf_rn(xv.y, wv[u].y, acc);
-                acc = __fmaf_rn(xv.z, wv[u].z, acc);
-                acc = __fmaf_rn(xv.w, wv[u].w, acc);
-            }
-        }
-        for (; c < nfull; c += LANES) {
-            const float4 wv = __ldg(w4 + c);
-            const float4 xv = x4[c];
-            acc = __fmaf_rn(xv.x, wv.x, acc);
-            acc = __fmaf_rn(xv.y, wv.y, acc);
-            acc = __fmaf_rn(xv.z, wv.z, acc);
-            acc = __fmaf_rn(xv.w, wv.w, acc);
+            for (int u = 0; u < UB; ++u)
+                if (c + u * LANES < nfull) {
+                    const float4 xv = x4[c + u * LANES];
+                    acc = __fmaf_rn(xv.x, wv[u].x, acc);
+                    acc = __fmaf_rn(xv.y, wv[u].y, acc);
+                    acc = __fmaf_rn(xv.z, wv[u].z, acc);
+                    acc = __fmaf_rn(xv.w, wv[u].w, acc);
+                }
         }
         if ((K & 3) && (nfull % LANES) == lane) {   // ragged tail chunk: only the elements below K
             const float *wr = Wt + (long long)n * Kpad;
@@ -82,6 +80,34 @@ __device__ __forceinline__ float dot_blocked_col(const float *__restrict__ zs, i
         y = p == 0 ? acc : __fadd_rn(y, acc);
     }
     return __fadd_rn(y, bias);
+}
+
+// the same chains with the weights of this CTA's rows staged in shared memory: Ws[k * nq + j], j = row - first row
+__device__ __forceinline__ float dot_blocked_smem(const float *__restrict__ zs, int K, const float *__restrict__ Ws, int nq,
+                                                  int j, int nsplit, float bias) {
+    float y = 0.0f;
+    for (int p = 0; p < nsplit; ++p) {
+        const int k0 = (int)((long long)K * p / nsplit), k1 = (int)((long long)K * (p + 1) / nsplit);
+        float acc = 0.0f;
+        const float *wp = Ws + (size_t)k0 * nq + j;
+        int k = k0;
+        for (; k + 8 <= k1; k += 8, wp += 8 * nq) {   // 16 shared-memory loads in flight, then the sequential chain
+            float wv[8], zv[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { wv[u] = wp[u * nq]; zv[u] = zs[k + u]; }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) acc = __fmaf_rn(zv[u], wv[u], acc);
+        }
+        for (; k < k1; ++k, wp += nq) acc = __fmaf_rn(zs[k], *wp, acc);
+        y = p == 0 ? acc : __fadd_rn(y, acc);
+    }
+    return __fadd_rn(y, bias);
+}
+__device__ __forceinline__ void cp_async4(float *dst_smem, const float *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async16(float *dst_smem, const float *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
 }
 
 __device__ float sample_gaussian(const WnModelDev &m, const float *out, float eps) {  // gaussian.py:39-52
@@ -124,13 +150,40 @@ __device__ int sample_categorical(const float *logits, int C, float u, float *e)
 
 __device__ __forceinline__ int round4(int v) { return (v + 3) & ~3; }
 
-// grid = B utterances, block = GEN_THREADS.  Dynamic shared memory carved below.
-__global__ void __launch_bounds__(GEN_THREADS) wn_loop_generic_kernel(
+// ---- thread-block cluster: the C CTAs of one utterance split the rows of every inner product and exchange the results
+//      through distributed shared memory ------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned cluster_rank() { unsigned r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ unsigned cluster_size() { unsigned r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
+// v -> the same shared-memory variable of every CTA of the cluster (this one included)
+__device__ __forceinline__ void bcast_f32(float *p, float v, int C) {
+    if (C == 1) { *p = v; return; }
+    const unsigned a = (unsigned)__cvta_generic_to_shared(p);
+    for (int q = 0; q < C; ++q) {
+        unsigned ra;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(a), "r"(q));
+        asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(ra), "f"(v) : "memory");
+    }
+}
+// every thread of every CTA of the cluster; orders the remote stores above before the reads below
+__device__ __forceinline__ void cluster_barrier(int C) {
+    if (C == 1) { __syncthreads(); return; }
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ int slice_lo(int n, int q, int C) { return (int)((long long)n * q / C); }
+
+// grid = B utterances x C CTAs (one cluster per utterance), block = GEN_THREADS.  Every CTA holds the utterance's small
+// state (x, the concatenated operand, z, skips, ...) in its own shared memory; CTA `cr` of the cluster computes the gate
+// channels [H cr / C, H (cr+1) / C) (tanh and sigmoid rows), the rows [(S+R) cr / C, ...) of the skip / out 1x1s and the
+// rows [S cr / C, ...) of the first head 1x1, and writes its results into all C copies.  The arithmetic of a row does not
+// depend on who computes it, so every C gives the same bits.  Two cluster barriers per layer and one in the head.
+// Dynamic shared memory carved below.
+__global__ void __launch_bounds__(GEN_THREADS, 1) wn_loop_generic_kernel(
     const WnModelDev m, const float *__restrict__ c_up, const float *__restrict__ g_emb,
     const float *__restrict__ noise, const float *__restrict__ teacher, int inputs_mode, int B, int T,
-    float *__restrict__ rings, float *__restrict__ audio, float *__restrict__ raw) {
+    float *__restrict__ rings, float *__restrict__ audio, float *__restrict__ raw, int wos_floats) {
     extern __shared__ __align__(16) float sm[];
-    const int tid = threadIdx.x, NT = blockDim.x, b = blockIdx.x;
+    const int C = (int)cluster_size(), cr = (int)cluster_rank();
+    const int tid = threadIdx.x, NT = blockDim.x, b = blockIdx.x / C;
     const int lane = tid & (LANES - 1), group = tid / LANES, ngroups = NT / LANES;
     const int R = m.R, G = m.G, S = m.S, O = m.O, H = m.H, ks = m.ksize;
     float *x = sm;                            // [round4(R)]  current residual-stream vector
@@ -142,6 +195,7 @@ __global__ void __launch_bounds__(GEN_THREADS) wn_loop_generic_kernel(
     float *outv = h1 + m.Spad;                // [round4(O)]
     float *ev = outv + round4(O);             // [round4(O)]  categorical scratch
     float *fb = ev + round4(O);               // [4]: fb[0] next scalar input, fb[1] next class
+    float *wos = fb + 4;                      // [H][rows of this CTA] skip / out weights of the current layer (if they fit)
     const bool quant = m.input_type == WN_INPUT_MULAW_QUANTIZE;
     float *ring = rings + (long long)b * m.ring_per_utt;
     const int o_cond = (ks - 1) * R, o_g = o_cond + m.cin, o_cur = o_g + m.gin;
@@ -173,7 +227,41 @@ __global__ void __launch_bounds__(GEN_THREADS) wn_loop_generic_kernel(
             const float *lw = m.layers + (long long)l * m.layer_stride;
             const int d = m.dil[l], ql = m.qlen[l];
             float *rq = ring + m.qoff[l];
+            // this CTA's rows of [skip ; out], requested now (cp.async) and used after the gate: the blocked chains are
+            // sequential in k, so reading their weights from L2 on demand costs one round trip per 16 k
+            const int q0 = slice_lo(S + R, cr, C), q1 = slice_lo(S + R, cr + 1, C), nq = q1 - q0;
+            const bool staged = nq * H <= wos_floats;
+            if (staged) {
+                if (!(q0 & 3) && !(nq & 3) && !(S & 3) && !(R & 3)) {   // 16-byte pieces never straddle the skip / out boundary
+                    const int nq4 = nq >> 2;
+                    for (int i = tid; i < H * nq4; i += NT) {
+                        const int k = i / nq4, n = q0 + 4 * (i - k * nq4);
+                        cp_async16(wos + (size_t)k * nq + (n - q0), n < S ? lw + m.off_skip_w + (size_t)k * S + n : lw + m.off_out_w + (size_t)k * R + (n - S));
+                    }
+                } else {
+                    for (int i = tid; i < H * nq; i += NT) {
+                        const int k = i / nq, n = q0 + (i - k * nq);
+                        cp_async4(wos + i, n < S ? lw + m.off_skip_w + (size_t)k * S + n : lw + m.off_out_w + (size_t)k * R + (n - S));
+                    }
+                }
+                asm volatile("cp.async.commit_group;" ::: "memory");
+            }
             // ---- CausalConv1D incremental: push x_t, gather the k taps (modules.py:273-292) ----------------
+            if (!(R & 3) && !(o_cur & 3)) {   // 16-byte pieces: one round of loads for the usual sizes
+                const int R4 = R >> 2;
+                float4 *xc4 = reinterpret_cast<float4 *>(xcat), *rq4 = reinterpret_cast<float4 *>(rq);
+                for (int i = tid; i < ks * R4; i += NT) {
+                    const int j = i / R4, n4 = i - j * R4;
+                    const int tt = t - (ks - 1 - j) * d;
+                    if (j == ks - 1) {
+                        const float4 v = reinterpret_cast<const float4 *>(x)[n4];
+                        rq4[(long long)(t % ql) * R4 + n4] = v;
+                        xc4[(o_cur >> 2) + n4] = v;
+                    } else {
+                        xc4[i] = tt >= 0 ? rq4[(long long)(tt % ql) * R4 + n4] : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                }
+            } else
             for (int i = tid; i < ks * R; i += NT) {
                 const int j = i / R, n = i - j * R;
                 const int tt = t - (ks - 1 - j) * d;
@@ -181,49 +269,61 @@ __global__ void __launch_bounds__(GEN_THREADS) wn_loop_generic_kernel(
                 else xcat[i] = tt >= 0 ? rq[(long long)(tt % ql) * R + n] : 0.0f;
             }
             __syncthreads();
-            // ---- gate pre-activation: one dot16 over [taps | c | g | x(t)] (modules.py:294-297, :497-508) ----
-            for (int nb = 0; nb < G; nb += ngroups) {
-                const int n = nb + group;
-                const float a = dot16_lane(xcat, m.Kcat, m.KcatPad, lw + m.off_cat_w, n, n < G, lane);
-                if (lane == 0 && n < G) pre[n] = __fadd_rn(a, __ldg(lw + m.off_bsum + n));
+            // ---- gate pre-activation: one dot16 over [taps | c | g | x(t)] (modules.py:294-297, :497-508); this CTA's
+            //      channels: rows h0.. (tanh half) and H + h0.. (sigmoid half)
+            const int h0 = slice_lo(H, cr, C), hn = slice_lo(H, cr + 1, C) - h0;
+            for (int ib = 0; ib < 2 * hn; ib += ngroups) {
+                const int i = ib + group;
+                const bool valid = i < 2 * hn;
+                const int n = i < hn ? h0 + i : H + h0 + (i - hn);
+                const float a = dot16_lane(xcat, m.Kcat, m.KcatPad, lw + m.off_cat_w, n, valid, lane);
+                if (lane == 0 && valid) pre[n] = __fadd_rn(a, __ldg(lw + m.off_bsum + n));
             }
             __syncthreads();
-            for (int n = tid; n < H; n += NT) z[n] = __fmul_rn(wn_tanhf(pre[n]), wn_sigmoidf(pre[H + n]));  // :510
-            __syncthreads();
-            // ---- skip and residual 1x1s (modules.py:512-520, wavenet.py:833-836) ---------------------------
-            for (int n = tid; n < S + R; n += NT) {
+            for (int i = tid; i < hn; i += NT) {   // :510
+                const int n = h0 + i;
+                bcast_f32(z + n, __fmul_rn(wn_tanhf(pre[n]), wn_sigmoidf(pre[H + n])), C);
+            }
+            if (staged) asm volatile("cp.async.wait_group 0;" ::: "memory");
+            cluster_barrier(C);
+            // ---- skip and residual 1x1s (modules.py:512-520, wavenet.py:833-836): this CTA's rows of [skip ; out] ------
+            for (int n = q0 + tid; n < q1; n += NT) {
                 if (n < S) {
-                    float s = dot_blocked_col(z, H, lw + m.off_skip_w, S, n, m.ksplit, __ldg(lw + m.off_skip_b + n));
-                    if (l == 0) skips[n] = s;
-                    else {
-                        float v = __fadd_rn(skips[n], s);
-                        skips[n] = m.legacy ? __fmul_rn(v, WN_SQRT_HALF) : v;
+                    float s = staged ? dot_blocked_smem(z, H, wos, nq, n - q0, m.ksplit, __ldg(lw + m.off_skip_b + n))
+                                     : dot_blocked_col(z, H, lw + m.off_skip_w, S, n, m.ksplit, __ldg(lw + m.off_skip_b + n));
+                    if (l > 0) {
+                        const float v = __fadd_rn(skips[n], s);
+                        s = m.legacy ? __fmul_rn(v, WN_SQRT_HALF) : v;
                     }
+                    if (l == m.L - 1) bcast_f32(skips + n, s, C);   // the head needs the whole sum
+                    else skips[n] = s;                              // the running sum stays with its owner
                 } else {
                     const int r = n - S;
-                    float o = dot_blocked_col(z, H, lw + m.off_out_w, R, r, m.ksplit, __ldg(lw + m.off_out_b + r));
+                    float o = staged ? dot_blocked_smem(z, H, wos, nq, n - q0, m.ksplit, __ldg(lw + m.off_out_b + r))
+                                     : dot_blocked_col(z, H, lw + m.off_out_w, R, r, m.ksplit, __ldg(lw + m.off_out_b + r));
                     float v = __fadd_rn(o, x[r]);
-                    x[r] = m.residual_legacy ? __fmul_rn(v, WN_SQRT_HALF) : v;
+                    bcast_f32(x + r, m.residual_legacy ? __fmul_rn(v, WN_SQRT_HALF) : v, C);
                 }
             }
-            __syncthreads();
+            cluster_barrier(C);
         }
         // ---- head (wavenet.py:840-844) ---------------------------------------------------------------------
         for (int n = tid; n < S; n += NT) skips[n] = skips[n] > 0.0f ? skips[n] : 0.0f;
         __syncthreads();
-        for (int nb = 0; nb < S; nb += ngroups) {
+        const int s0 = slice_lo(S, cr, C), s1 = slice_lo(S, cr + 1, C);
+        for (int nb = s0; nb < s1; nb += ngroups) {
             const int n = nb + group;
-            const float a = dot16_lane(skips, S, m.Spad, m.h1_w, n, n < S, lane);
-            if (lane == 0 && n < S) { const float v = __fadd_rn(a, __ldg(m.h1_b + n)); h1[n] = v > 0.0f ? v : 0.0f; }
+            const float a = dot16_lane(skips, S, m.Spad, m.h1_w, n, n < s1, lane);
+            if (lane == 0 && n < s1) { const float v = __fadd_rn(a, __ldg(m.h1_b + n)); bcast_f32(h1 + n, v > 0.0f ? v : 0.0f, C); }
         }
-        __syncthreads();
+        cluster_barrier(C);   // (every CTA evaluates the small output 1x1 and the sampler itself: no feedback broadcast)
         for (int nb = 0; nb < O; nb += ngroups) {
             const int n = nb + group;
             const float a = dot16_lane(h1, S, m.Spad, m.h2_w, n, n < O, lane);
             if (lane == 0 && n < O) {
                 const float v = __fadd_rn(a, __ldg(m.h2_b + n));
                 outv[n] = v;
-                if (raw) raw[((long long)b * T + t) * O + n] = v;  // wavenet.py:847
+                if (raw && cr == 0) raw[((long long)b * T + t) * O + n] = v;  // wavenet.py:847
             }
         }
         __syncthreads();
@@ -235,13 +335,13 @@ __global__ void __launch_bounds__(GEN_THREADS) wn_loop_generic_kernel(
             } else if (!quant) {
                 const float *nz = noise + ((long long)t * B + b) * m.NZ;
                 float smp = (O == 2) ? sample_gaussian(m, outv, nz[0]) : sample_mol(m, outv, nz);
-                if (audio) audio[(long long)b * T + t] = m.input_type == WN_INPUT_MULAW ? wn_inv_mulawf(smp) : smp;
+                if (audio && cr == 0) audio[(long long)b * T + t] = m.input_type == WN_INPUT_MULAW ? wn_inv_mulawf(smp) : smp;
                 fb[0] = teacher ? (ti < T ? teacher[(long long)b * T + ti] : 0.0f) : smp;
             } else {
                 const float *nz = noise + ((long long)t * B + b) * m.NZ;
                 int cls = sample_categorical(outv, O, nz[0], ev);
                 float yq = __fsub_rn(__fdiv_rn(__fmul_rn(2.0f, (float)cls), 255.0f), 1.0f);
-                if (audio) audio[(long long)b * T + t] = wn_inv_mulawf(yq);
+                if (audio && cr == 0) audio[(long long)b * T + t] = wn_inv_mulawf(yq);
                 fb[1] = teacher ? (ti < T ? teacher[(long long)b * T + ti] : 0.0f) : (float)cls;
             }
         }
@@ -259,10 +359,41 @@ int wn_launch_loop_generic(wn_handle *h, const float *c_up, const float *g_emb, 
     WN_CUDA_TRY(h, cudaMemsetAsync(h->d_ring, 0, sizeof(float) * (size_t)B * (size_t)m.ring_per_utt, st));
     auto r4 = [](int v) { return (v + 3) & ~3; };
     size_t smem = sizeof(float) * (size_t)(r4(m.R) + m.KcatPad + r4(m.G) + r4(m.H) + 2 * m.Spad + 2 * r4(m.O) + 4);
-    if (smem > 48 * 1024)
-        WN_CUDA_TRY(h, cudaFuncSetAttribute(wn_loop_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    wn_loop_generic_kernel<<<B, GEN_THREADS, smem, st>>>(m, c_up, g_emb, noise, teacher, inputs_mode, B, T, h->d_ring,
-                                                         audio, raw);
+    // CTAs per utterance: the largest power of two (at most 8, the portable cluster size) for which all B clusters are
+    // resident at once (cudaOccupancyMaxActiveClusters: clusters live inside one GPC); WN_GEN_CLUSTER overrides.  One
+    // CTA per utterance streams every weight from L2 itself (the paper model: 54.7 MB per step and CTA); C CTAs stream
+    // 1 / C each.  The CTA's rows of the skip / out 1x1s of one layer are staged in shared memory if that fits next to
+    // the state (else they stream from L2 as well).
+    const size_t smem_state = smem;
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute at[1];
+    int wos_floats = 0;
+    auto configure = [&](int C) {
+        wos_floats = (int)(((size_t)(m.S + m.R + C - 1) / C + 1) * (size_t)m.H);
+        if (smem_state + sizeof(float) * (size_t)wos_floats > 160 * 1024) wos_floats = 0;
+        smem = smem_state + sizeof(float) * (size_t)wos_floats;
+        cfg.gridDim = dim3((unsigned)(B * C)); cfg.blockDim = dim3(GEN_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = (unsigned)C; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        if (cudaFuncSetAttribute(wn_loop_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem, 48 * 1024)) != cudaSuccess) { cudaGetLastError(); return 0; }
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, wn_loop_generic_kernel, &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
+        return n;
+    };
+    int C = 1;
+    if (const char *e = getenv("WN_GEN_CLUSTER")) {
+        C = atoi(e);
+        if (C != 1 && C != 2 && C != 4 && C != 8) C = 1;
+    } else {
+        for (C = 8; C > 1; C >>= 1)
+            if (configure(C) >= B) break;
+    }
+    const int resident = configure(C);
+    if (getenv("WN_GEN_DEBUG")) fprintf(stderr, "generic engine: B=%d cluster=%d resident clusters=%d smem=%zu staged=%d\n", B, C, resident, smem, wos_floats != 0);
+    if (resident < 1) { h->err = "generic engine: the cluster does not fit the device"; return WN_ERR_CUDA; }
+    WN_CUDA_TRY(h, cudaLaunchKernelEx(&cfg, wn_loop_generic_kernel, m, c_up, g_emb, noise, teacher, inputs_mode, B, T, h->d_ring,
+                                      audio, raw, wos_floats));
     h->launches++;
     WN_CUDA_TRY(h, cudaGetLastError());
     return WN_OK;
