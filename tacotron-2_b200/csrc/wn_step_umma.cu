@@ -12,17 +12,23 @@
 // passes hi*hi + hi*lo + lo*hi into the same fp32 TMEM accumulator (the dropped lo*lo term is below 2^-16 relative).
 // Weights are split once on the host; activations are split while they are staged into shared memory.
 //
-// One CTA = one tile of 128 positions (MMA M = 128, one TMEM lane per position) x 2*NT or R+S <= 256 columns (MMA N),
-// 256 threads, 2 CTAs per SM (96 KB of shared memory and 256 TMEM columns each) so that one CTA stages while the other
-// one's MMAs run.  K is walked in blocks of 64 (16 for the tail of the 80 conditioning channels); per block
-//   * thread 0 asks for the block's packed weights ([hi | lo] x [bk/8][N][8] bf16, exactly the shared-memory image) with
-//     bulk global->shared copies counted on an mbarrier,
-//   * all threads gather their position's 32 activations (loaded one block ahead into registers), split them and store
-//     them in the K-major core-matrix layout of wn_umma.cuh, fence.proxy.async, barrier,
-//   * thread 0 waits for the weights and issues 3 x bk/16 tcgen05.mma, then tcgen05.commit on the "done" mbarrier that
-//     everybody waits on before overwriting the operands.
-// The epilogue reads the accumulator with tcgen05.ld (32 lanes x 16 columns per instruction): a thread owns one
-// position and half of the columns.
+// Persistent kernel, one CTA per SM (215 KB of shared memory, all 512 TMEM columns), 18 warps with fixed roles; a work
+// item is a tile of 128 positions (MMA M = 128, one TMEM lane per position) x 2*NT or R+S <= 256 columns (MMA N):
+//   * copy thread: the packed weights of a K block ([hi | lo] x [bk/8][N][8] bf16, exactly the shared-memory image, L2
+//     resident) go into one of 3 operand stages by bulk global->shared copies counted on the stage's "full" mbarrier, as
+//     soon as the MMAs that last read the stage have completed ("done");
+//   * 8 staging warps in two groups that take alternate K blocks (32 wide, 16 for the tail of the 80 conditioning
+//     channels): gather the positions' activations (requested one block ahead into registers), split, store in the
+//     K-major core-matrix layout of wn_umma.cuh, fence.proxy.async, arrive on "ready";
+//   * MMA thread: waits for "ready" and "full", issues 3 x bk/16 tcgen05.mma into accumulator (tile & 1), tcgen05.commit
+//     on "done"; after the last block of a tile a second commit on "tfull";
+//   * 8 epilogue warps: wait for "tfull", tcgen05.ld (32 lanes x 16 columns per instruction; a thread owns one position and
+//     half of the columns), gate / bias in registers, release the accumulator ("tempty"), pass the tile through a
+//     shared-memory staging tile so that one warp writes (and, for the residual and the skip sum, reads) whole 512-byte
+//     rows - while the other warps already work on the next tile in the other accumulator.
+// Measured (profiles/README_r1.md): C5 253 ms (fp32 FFMA2 GEMMs) -> 46 ms.  What bounds it now: the out/skip kernel
+// moves 5 x N x 512 bytes for one K = 128 GEMM and runs at ~72 % of the HBM roof; fusing it with the gate (z stays on
+// chip) is the next step.
 #include <algorithm>
 #include <array>
 #include <cstdio>

@@ -4,8 +4,9 @@
 // Operand layout used throughout (K-major, no swizzle; "canonical INTERLEAVE layout" of the tcgen05 shared-memory
 // descriptor): a [rows x K] bf16 operand tile is stored as [K/8][rows][8 bf16], i.e. one 16-byte word holds 8
 // consecutive k of one row, the 8 rows of a core matrix are contiguous (128 B), 8-row groups follow each other at
-// SBO = 128 B, and the next 8 k start LBO = rows * 16 B later.  One tcgen05.mma (kind::f16, K = 16) reads two such
-// k-chunks; the next K step starts 2 * LBO further.
+// SBO = 128 B, and the next 8 k start LBO >= rows * 16 B later (any multiple of 16: a little padding keeps the staging
+// stores free of bank conflicts).  One tcgen05.mma (kind::f16, K = 16) reads two such k-chunks; the next K step starts
+// 2 * LBO further.  The convention was checked on a B200 with tools/umma_probe.cu before anything was built on it.
 #pragma once
 
 #include <cuda_bf16.h>
