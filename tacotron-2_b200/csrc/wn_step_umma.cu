@@ -366,6 +366,271 @@ __global__ void __launch_bounds__(UTHREADS, 1) umma_layer_kernel(const __grid_co
     if (warp == ISSUE_WARP) umma::tmem_dealloc(tmem, 512);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Fused residual layer: gate GEMM -> tanh * sigmoid -> out/skip GEMM in ONE persistent kernel; z never leaves the SM.
+// For H = 128 and R + S = 256 (one column tile each: the default block).  TMEM: gate accumulator in columns [0, 256),
+// out/skip accumulator in [256, 512).  Per tile of 128 positions:
+//   G   the 15 K blocks of the gate as in umma_layer_kernel (copy thread, staging warps, MMA thread)       -> accG
+//   E1  epilogue warps: accG -> gate -> z split into bf16 (hi, lo) and stored as the A operand of the second GEMM
+//       (K-major core-matrix layout, 16 chunks of 8 channels); every 32 channels finished are announced on their own
+//       mbarrier, so the MMA thread starts the out/skip K block b while E1 still works on later channels
+//   O   4 K blocks: A = z from shared memory, B = [W_out ; W_skip] through the same operand stages           -> accO
+//   E2  epilogue warps: accO -> staging tile (the z buffer, dead by then) -> residual / skip rows, coalesced
+// G of the next tile starts as soon as E1 has drained accG and runs under E2.  HBM traffic per layer: x (+ its two
+// older taps, mostly L2 hits), c, the skip sum in and out, x' out - the [N][H] round trip of z is gone (-36 %).
+struct FArgs {
+    const unsigned char *Wg, *Wo;     // packed weights of the layer: gate blocks, out/skip blocks
+    const float *bias_g, *bias_o;
+    const float *x, *cond;            // layer input [N][R], conditioning [N][cin]
+    float *x_out, *skips;
+    long long N;
+    int T, R, S, cin, nblk_g, nblk_o, first_layer, legacy, residual_legacy;
+    UBlock blk[UMAXBLK];              // gate blocks, then out/skip blocks
+    unsigned long long *stats;
+};
+
+constexpr int F_NBAR = 3 * NSTAGE + 2 + 4 + 1;   // full | ready | done per stage, tgfull, tgempty, zready[4], tofull
+constexpr int Z_HALF_BYTES = 16 * LBO_A;         // z_hi or z_lo: 16 chunks of 8 channels x 128 positions
+static_assert(2 * Z_HALF_BYTES <= UM * STG_LD * 4, "the z operand and the epilogue staging tile share one region");
+
+__global__ void __launch_bounds__(UTHREADS, 1) umma_fused_layer_kernel(const __grid_constant__ FArgs a) {
+    extern __shared__ __align__(128) unsigned char usmem[];
+    __shared__ __align__(8) unsigned long long bars[F_NBAR];
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t bar0 = umma::smem_addr(&bars[0]);
+    auto full = [&](int s) { return bar0 + 8u * (uint32_t)s; };
+    auto ready = [&](int s) { return bar0 + 8u * (uint32_t)(NSTAGE + s); };
+    auto done = [&](int s) { return bar0 + 8u * (uint32_t)(2 * NSTAGE + s); };
+    const uint32_t tgfull = bar0 + 8u * (3 * NSTAGE), tgempty = tgfull + 8u, zready0 = tgfull + 16u, tofull = tgfull + 48u;
+    if (tid == 0) {
+        for (int s = 0; s < NSTAGE; ++s) { umma::mbar_init(full(s), 1); umma::mbar_init(ready(s), USTAGERS / 2); umma::mbar_init(done(s), 1); }
+        umma::mbar_init(tgfull, 1); umma::mbar_init(tgempty, UEPI); umma::mbar_init(tofull, 1);
+        for (int i = 0; i < 4; ++i) umma::mbar_init(zready0 + 8u * i, UEPI / 2);
+        umma::mbar_fence_init();
+    }
+    if (warp == ISSUE_WARP) umma::tmem_alloc(umma::smem_addr(&tmem_slot), 512);
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+    const uint32_t tmem = tmem_slot;
+    const int nbg = a.nblk_g, nbo = a.nblk_o, nb = nbg + nbo;
+    const long long total = (a.N + UM - 1) / UM;
+    const uint32_t smem0 = umma::smem_addr(usmem);
+    unsigned char *zbuf = usmem + NSTAGE * STAGE_BYTES;          // z_hi | z_lo, later the staging tile of E2
+    const uint32_t z_a = smem0 + NSTAGE * STAGE_BYTES;
+
+    if (warp == COPY_WARP) {
+        if (lane == 0) {
+            uint32_t s = 0, ph = 0, g = 0;
+            for (long long w = blockIdx.x; w < total; w += gridDim.x) {
+                for (int b = 0; b < nb; ++b, ++g) {
+                    if (g >= NSTAGE) umma::mbar_wait(done(s), ph ^ 1u);
+                    const uint32_t bytes = (uint32_t)a.blk[b].bk * 256u * 4u;
+                    const uint32_t Bs_a = smem0 + s * STAGE_BYTES + B_OFF;
+                    const unsigned char *src = (b < nbg ? a.Wg : a.Wo) + a.blk[b].w_off;
+                    umma::mbar_expect_tx(full(s), bytes);
+                    for (uint32_t o = 0; o < bytes; o += 16384u)
+                        umma::bulk_g2s(Bs_a + o, src + o, bytes - o < 16384u ? bytes - o : 16384u, full(s));
+                    if (++s == NSTAGE) { s = 0; ph ^= 1u; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == ISSUE_WARP) {
+        if (lane == 0) {
+            const uint32_t idesc = umma::idesc_bf16(UM, 256);
+            const uint32_t lboB = 256u * 16u;
+            const uint64_t dA = umma::smem_desc(0, LBO_A, 128), dB = umma::smem_desc(0, lboB, 128);
+            const uint32_t kA = (2 * LBO_A) >> 4, kB = (2 * lboB) >> 4;
+            const uint64_t zh = dA + (z_a >> 4), zl = zh + (Z_HALF_BYTES >> 4);
+            uint32_t s = 0, ph = 0;
+            int it = 0;
+            for (long long w = blockIdx.x; w < total; w += gridDim.x, ++it) {
+                if (it >= 1) { umma::mbar_wait(tgempty, (uint32_t)(it - 1) & 1u); umma::fence_after_sync(); }
+                for (int b = 0; b < nb; ++b) {
+                    const int bk = a.blk[b].bk;
+                    const bool gate = b < nbg;
+                    if (!gate) { umma::mbar_wait(zready0 + 8u * (uint32_t)(b - nbg), (uint32_t)it & 1u); }
+                    umma::mbar_wait(ready(s), ph);
+                    umma::mbar_wait(full(s), ph);
+                    umma::fence_after_sync();
+                    const uint32_t st16 = (smem0 + s * STAGE_BYTES) >> 4;
+                    const uint64_t bh = dB + st16 + (B_OFF >> 4), bl = bh + (((uint32_t)bk * 256u * 2u) >> 4);
+                    uint64_t ah, al;
+                    if (gate) { ah = dA + st16; al = ah + (A_HALF_BYTES >> 4); }
+                    else { const uint32_t o = (uint32_t)(b - nbg) * 4u * (LBO_A >> 4); ah = zh + o; al = zl + o; }
+                    const uint32_t d_tmem = tmem + (gate ? 0u : 256u);
+                    const uint32_t acc0 = (gate ? b > 0 : b > nbg) ? 1u : 0u;
+                    umma::mma_bf16(d_tmem, ah, bh, idesc, acc0);
+                    umma::mma_bf16(d_tmem, ah, bl, idesc, 1u);
+                    umma::mma_bf16(d_tmem, al, bh, idesc, 1u);
+                    if (bk > 16) {
+                        umma::mma_bf16(d_tmem, ah + kA, bh + kB, idesc, 1u);
+                        umma::mma_bf16(d_tmem, ah + kA, bl + kB, idesc, 1u);
+                        umma::mma_bf16(d_tmem, al + kA, bh + kB, idesc, 1u);
+                    }
+                    umma::mma_commit(done(s));
+                    if (b == nbg - 1) umma::mma_commit(tgfull);
+                    if (++s == NSTAGE) { s = 0; ph ^= 1u; }
+                }
+                umma::mma_commit(tofull);
+            }
+        }
+        __syncwarp();
+    } else if (warp >= EPI_WARPS) {
+        // ---- staging warps (two groups on alternate blocks); the out/skip blocks have nothing to stage, their turn only
+        //      keeps the stage bookkeeping uniform -------------------------------------------------------------------------
+        const int st_tid = tid - EPI_WARPS * 32, grp = st_tid >> 7, c = st_tid & 3, r0 = (st_tid & 127) >> 2;
+        const int soff = c * LBO_A + r0 * 16;
+        uint32_t gb0 = 0;
+        for (long long w = blockIdx.x; w < total; w += gridDim.x, gb0 += (uint32_t)nb) {
+            const long long n0 = w * UM;
+            const float *srow[SROWS], *crow[SROWS];
+            int trow[SROWS];
+#pragma unroll
+            for (int j = 0; j < SROWS; ++j) {
+                const long long n = n0 + r0 + 32 * j;
+                const bool ok = n < a.N;
+                trow[j] = ok ? (int)(n % a.T) : -1;
+                srow[j] = a.x + (ok ? n : 0) * a.R + 8 * c;
+                crow[j] = a.cond + (ok ? n : 0) * a.cin + 8 * c;
+            }
+            float4 pf[2 * SROWS];
+            auto load_block = [&](int b) {
+                if (b >= nbg) return;
+                const UBlock &k = a.blk[b];
+                const bool c_ok = 8 * c < k.bk;
+                const int back_off = k.koff - k.back * a.R;
+#pragma unroll
+                for (int j = 0; j < SROWS; ++j) {
+                    const float *p = k.seg == 0 ? srow[j] + back_off : crow[j] + k.koff;
+                    float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+                    if (c_ok && trow[j] >= k.back) { v0 = __ldg(reinterpret_cast<const float4 *>(p)); v1 = __ldg(reinterpret_cast<const float4 *>(p + 4)); }
+                    pf[2 * j] = v0; pf[2 * j + 1] = v1;
+                }
+            };
+            const int bfirst = (int)((gb0 ^ (uint32_t)grp) & 1u);
+            load_block(bfirst);
+            for (int b = bfirst; b < nb; b += 2) {
+                const uint32_t g = gb0 + (uint32_t)b, s = g % NSTAGE, use = g / NSTAGE;
+                if (g >= NSTAGE) umma::mbar_wait(done(s), (use - 1u) & 1u);
+                if (b < nbg && 8 * c < a.blk[b].bk) {
+                    unsigned char *Ah = usmem + (size_t)s * STAGE_BYTES + soff, *Al = Ah + A_HALF_BYTES;
+#pragma unroll
+                    for (int j = 0; j < SROWS; ++j) {
+                        uint4 hi, lo;
+                        umma::split8(pf[2 * j], pf[2 * j + 1], hi, lo);
+                        *reinterpret_cast<uint4 *>(Ah + j * 32 * 16) = hi;
+                        *reinterpret_cast<uint4 *>(Al + j * 32 * 16) = lo;
+                    }
+                }
+                umma::fence_proxy_async();
+                umma::mbar_arrive(ready(s));
+                if (b + 2 < nb) load_block(b + 2);
+            }
+        }
+    } else {
+        // ---- epilogue warps -----------------------------------------------------------------------------------------------
+        float *stg = reinterpret_cast<float *>(zbuf);
+        const int q = warp & 3, half = warp >> 2, row = 32 * q + lane;
+        float *srow = stg + (size_t)row * STG_LD;
+        const uint32_t tq = tmem + ((uint32_t)(32 * q) << 16);
+        auto epi_sync = [&]() { asm volatile("bar.sync 1, %0;" ::"n"(UEPI) : "memory"); };
+        int it = 0;
+        for (long long w = blockIdx.x; w < total; w += gridDim.x, ++it) {
+            const long long n0 = w * UM;
+            // E1: gate -> z (bf16 hi / lo) as the A operand of the second GEMM
+            umma::mbar_wait(tgfull, (uint32_t)it & 1u);
+            umma::fence_after_sync();
+            for (int c = half * 64; c < half * 64 + 64; c += 16) {
+                float ta[16], sg[16];
+                umma::tmem_ld16(tq + (uint32_t)c, ta);
+                umma::tmem_ld16(tq + (uint32_t)(128 + c), sg);
+                umma::tmem_ld_wait();
+                float zz[16];
+#pragma unroll
+                for (int i4 = 0; i4 < 4; ++i4) {
+                    const float4 bt = __ldg(reinterpret_cast<const float4 *>(a.bias_g + c + 4 * i4));
+                    const float4 bs = __ldg(reinterpret_cast<const float4 *>(a.bias_g + 128 + c + 4 * i4));
+                    zz[4 * i4] = gate_fast(ta[4 * i4] + bt.x, sg[4 * i4] + bs.x);
+                    zz[4 * i4 + 1] = gate_fast(ta[4 * i4 + 1] + bt.y, sg[4 * i4 + 1] + bs.y);
+                    zz[4 * i4 + 2] = gate_fast(ta[4 * i4 + 2] + bt.z, sg[4 * i4 + 2] + bs.z);
+                    zz[4 * i4 + 3] = gate_fast(ta[4 * i4 + 3] + bt.w, sg[4 * i4 + 3] + bs.w);
+                }
+#pragma unroll
+                for (int h8 = 0; h8 < 2; ++h8) {
+                    uint4 hi, lo;
+                    umma::split8(make_float4(zz[8 * h8], zz[8 * h8 + 1], zz[8 * h8 + 2], zz[8 * h8 + 3]),
+                                 make_float4(zz[8 * h8 + 4], zz[8 * h8 + 5], zz[8 * h8 + 6], zz[8 * h8 + 7]), hi, lo);
+                    const int off = ((c >> 3) + h8) * LBO_A + row * 16;
+                    *reinterpret_cast<uint4 *>(zbuf + off) = hi;
+                    *reinterpret_cast<uint4 *>(zbuf + Z_HALF_BYTES + off) = lo;
+                }
+                if (c & 16) {   // 32 channels of all this half's positions are in place: out/skip K block c / 32 may start
+                    umma::fence_proxy_async();
+                    umma::mbar_arrive(zready0 + 8u * (uint32_t)(c >> 5));
+                }
+            }
+            umma::fence_before_sync();
+            umma::mbar_arrive(tgempty);                       // accG may be overwritten by the next tile's gate
+            // E2: out / skip
+            umma::mbar_wait(tofull, (uint32_t)it & 1u);
+            umma::fence_after_sync();
+            for (int g = 0; g < 2; ++g) {
+                for (int c = half * 64; c < half * 64 + 64; c += 16) {
+                    float v[16];
+                    umma::tmem_ld16(tq + (uint32_t)(256 + g * 128 + c), v);
+                    umma::tmem_ld_wait();
+#pragma unroll
+                    for (int i4 = 0; i4 < 4; ++i4)
+                        *reinterpret_cast<float4 *>(srow + c + 4 * i4) = make_float4(v[4 * i4], v[4 * i4 + 1], v[4 * i4 + 2], v[4 * i4 + 3]);
+                }
+                epi_sync();
+                const int m = g * 128 + 4 * lane;                         // first of this lane's 4 rows of [out ; skip]
+                const float4 bb = __ldg(reinterpret_cast<const float4 *>(a.bias_o + m));
+                // what is added to a row: the layer input (residual, modules.py:515-520) or the running skip sum
+                // (wavenet.py:833-836); 8 rows of loads are in flight before the first one is used
+                const bool is_out = m < a.R, has_add = is_out || !a.first_layer;
+                const float *addp = is_out ? a.x + m : a.skips + (m - a.R);
+                float *dstp = is_out ? a.x_out + m : a.skips + (m - a.R);
+                const int ld = is_out ? a.R : a.S;
+                const bool scale = is_out ? a.residual_legacy != 0 : (a.legacy != 0 && !a.first_layer);
+                for (int rb = warp; rb < UM; rb += 8 * EPI_WARPS) {
+                    float4 add[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const long long n = n0 + rb + EPI_WARPS * k;
+                        add[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (has_add && n < a.N) add[k] = *reinterpret_cast<const float4 *>(addp + n * ld);
+                    }
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const int r = rb + EPI_WARPS * k;
+                        const long long n = n0 + r;
+                        if (n >= a.N) continue;
+                        const float4 v = *reinterpret_cast<const float4 *>(stg + (size_t)r * STG_LD + 4 * lane);
+                        float4 y = make_float4(__fadd_rn(v.x, bb.x), __fadd_rn(v.y, bb.y), __fadd_rn(v.z, bb.z), __fadd_rn(v.w, bb.w));
+                        if (has_add) {
+                            if (is_out) { y.x = __fadd_rn(y.x, add[k].x); y.y = __fadd_rn(y.y, add[k].y); y.z = __fadd_rn(y.z, add[k].z); y.w = __fadd_rn(y.w, add[k].w); }
+                            else { y.x = __fadd_rn(add[k].x, y.x); y.y = __fadd_rn(add[k].y, y.y); y.z = __fadd_rn(add[k].z, y.z); y.w = __fadd_rn(add[k].w, y.w); }
+                        }
+                        if (scale) {
+                            y.x = __fmul_rn(y.x, WN_SQRT_HALF); y.y = __fmul_rn(y.y, WN_SQRT_HALF);
+                            y.z = __fmul_rn(y.z, WN_SQRT_HALF); y.w = __fmul_rn(y.w, WN_SQRT_HALF);
+                        }
+                        *reinterpret_cast<float4 *>(dstp + n * ld) = y;
+                    }
+                }
+                epi_sync();
+            }
+        }
+    }
+    umma::fence_before_sync();
+    __syncthreads();
+    if (warp == ISSUE_WARP) umma::tmem_dealloc(tmem, 512);
+}
+
 unsigned short bf16_rn_host(float f) {
     unsigned u;
     memcpy(&u, &f, 4);
@@ -525,7 +790,8 @@ static int umma_plan(wn_handle *h) {
         cudaMalloc((void **)&u->d_bias, bias.size() * sizeof(float)) != cudaSuccess ||
         cudaMemcpy(u->d_bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess ||
         cudaFuncSetAttribute(umma_layer_kernel<UEPI_GATE>, cudaFuncAttributeMaxDynamicSharedMemorySize, U_SMEM) != cudaSuccess ||
-        cudaFuncSetAttribute(umma_layer_kernel<UEPI_OUTSKIP>, cudaFuncAttributeMaxDynamicSharedMemorySize, U_SMEM) != cudaSuccess) {
+        cudaFuncSetAttribute(umma_layer_kernel<UEPI_OUTSKIP>, cudaFuncAttributeMaxDynamicSharedMemorySize, U_SMEM) != cudaSuccess ||
+        cudaFuncSetAttribute(umma_fused_layer_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, U_SMEM) != cudaSuccess) {
         h->err = std::string("step tensor-core weights: ") + cudaGetErrorString(cudaGetLastError());
         if (u->d_w) cudaFree(u->d_w);
         if (u->d_bias) cudaFree(u->d_bias);
@@ -551,6 +817,31 @@ int wn_umma_layer(wn_handle *h, int l, const float *x, const float *c_up, float 
     a.N = N; a.T = T; a.H = m.H; a.R = m.R; a.S = m.S; a.NT = u->NT;
     a.legacy = m.legacy; a.residual_legacy = m.residual_legacy; a.first_layer = l == 0;
     const long long ptiles = (N + UM - 1) / UM;
+    // one fused kernel when each GEMM is a single column tile of 256 (the default block); WN_STEP_UNFUSED=1: two kernels
+    const bool unfused = getenv("WN_STEP_UNFUSED") && atoi(getenv("WN_STEP_UNFUSED"));
+    if (!unfused && m.H == 128 && m.R + m.S == 256 && u->gate_tiles == 1 && u->os_tiles == 1 &&
+        (int)(u->gate_blk.size() + u->os_blk.size()) <= UMAXBLK) {
+        FArgs f;
+        memset(&f, 0, sizeof(f));
+        f.Wg = u->d_w + u->gate_w[l]; f.Wo = u->d_w + u->os_w[l];
+        f.bias_g = u->d_bias + u->gate_b[l]; f.bias_o = u->d_bias + u->os_b[l];
+        f.x = x; f.cond = c_up; f.x_out = x_out; f.skips = skips;
+        f.N = N; f.T = T; f.R = m.R; f.S = m.S; f.cin = m.cin;
+        f.nblk_g = (int)u->gate_blk.size(); f.nblk_o = (int)u->os_blk.size();
+        f.first_layer = l == 0; f.legacy = m.legacy; f.residual_legacy = m.residual_legacy;
+        for (int i = 0; i < f.nblk_g; ++i) {
+            const KBlockHost &b = u->gate_blk[i];
+            f.blk[i] = {b.seg, b.koff, b.bk, b.seg == 0 ? (2 - b.tap) * m.dil[l] : 0, b.w_off};
+        }
+        for (int i = 0; i < f.nblk_o; ++i) {
+            const KBlockHost &b = u->os_blk[i];
+            f.blk[f.nblk_g + i] = {0, b.koff, b.bk, 0, b.w_off};
+        }
+        umma_fused_layer_kernel<<<(unsigned)std::min<long long>(ptiles, h->sm_count), UTHREADS, U_SMEM, st>>>(f);
+        WN_CUDA_TRY(h, cudaGetLastError());
+        h->launches += 1;
+        return WN_OK;
+    }
     auto grid_for = [&](int nty) { return (unsigned)std::min<long long>(ptiles * nty, h->sm_count); };   // persistent: one CTA per SM
     // gate
     a.W = u->d_w + u->gate_w[l]; a.tile_w_bytes = u->gate_tile_bytes; a.bias = u->d_bias + u->gate_b[l];
