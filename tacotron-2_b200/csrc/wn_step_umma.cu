@@ -26,9 +26,9 @@
 //     half of the columns), gate / bias in registers, release the accumulator ("tempty"), pass the tile through a
 //     shared-memory staging tile so that one warp writes (and, for the residual and the skip sum, reads) whole 512-byte
 //     rows - while the other warps already work on the next tile in the other accumulator.
-// Measured (profiles/README_r1.md): C5 253 ms (fp32 FFMA2 GEMMs) -> 46 ms.  What bounds it now: the out/skip kernel
-// moves 5 x N x 512 bytes for one K = 128 GEMM and runs at ~72 % of the HBM roof; fusing it with the gate (z stays on
-// chip) is the next step.
+// Measured (profiles/README_r1.md): C5 253 ms (fp32 FFMA2 GEMMs) -> 46 ms with this kernel (the out/skip launch moves
+// 5 x N x 512 bytes for one K = 128 GEMM and runs at ~72 % of the HBM roof) -> 38 ms with umma_fused_layer_kernel below,
+// which keeps z on the SM (default block).
 #include <algorithm>
 #include <array>
 #include <cstdio>
@@ -101,7 +101,16 @@ __device__ __forceinline__ float gate_fast(float t, float s) {
     return th * sg;
 }
 
+// Development aid: -DWN_UMMA_STATS_BUILD adds clock64 sums of the time every role of umma_layer_kernel waits on its
+// mbarriers (printed by wn_umma_free when WN_UMMA_STATS is set); production builds carry neither the counters nor their
+// registers.
+#ifdef WN_UMMA_STATS_BUILD
 #define TWAIT(slot, bar, par) do { const long long t0_ = clock64(); umma::mbar_wait(bar, par); st_acc[slot] += clock64() - t0_; } while (0)
+#define STATS_ONLY(...) __VA_ARGS__
+#else
+#define TWAIT(slot, bar, par) umma::mbar_wait(bar, par)
+#define STATS_ONLY(...)
+#endif
 
 template <int EPI>
 __global__ void __launch_bounds__(UTHREADS, 1) umma_layer_kernel(const __grid_constant__ UArgs a) {
@@ -130,8 +139,7 @@ __global__ void __launch_bounds__(UTHREADS, 1) umma_layer_kernel(const __grid_co
     const int ncols = a.ncols, nblk = a.nblk, nty = a.nty;
     const long long total = ((a.N + UM - 1) / UM) * nty;     // work items: (position tile, column tile), column tile minor
     const uint32_t smem0 = umma::smem_addr(usmem);
-    long long st_acc[4] = {0, 0, 0, 0};
-    const long long st_begin = clock64();
+    STATS_ONLY(long long st_acc[4] = {0, 0, 0, 0}; const long long st_begin = clock64();)
 
     if (warp == COPY_WARP) {
         // ---- copy thread: the packed weights of block g go to stage g % NSTAGE as soon as the MMAs that last read that stage
@@ -155,7 +163,7 @@ __global__ void __launch_bounds__(UTHREADS, 1) umma_layer_kernel(const __grid_co
                 ty += ty_step;
                 if (ty >= nty) ty -= nty;
             }
-            if (a.stats) atomicAdd(a.stats + EPI * 16 + 3, (unsigned long long)st_acc[3]);
+            STATS_ONLY(if (a.stats) atomicAdd(a.stats + EPI * 16 + 3, (unsigned long long)st_acc[3]);)
         }
         __syncwarp();
     } else if (warp == ISSUE_WARP) {
@@ -192,7 +200,7 @@ __global__ void __launch_bounds__(UTHREADS, 1) umma_layer_kernel(const __grid_co
                 }
                 umma::mma_commit(tfull(ab));                      // every MMA of the tile has completed
             }
-            if (a.stats) { for (int i = 0; i < 3; ++i) atomicAdd(a.stats + EPI * 16 + i, (unsigned long long)st_acc[i]); atomicAdd(a.stats + EPI * 16 + 4, (unsigned long long)(clock64() - st_begin)); atomicAdd(a.stats + EPI * 16 + 5, 1ull); }
+            STATS_ONLY(if (a.stats) { for (int i = 0; i < 3; ++i) atomicAdd(a.stats + EPI * 16 + i, (unsigned long long)st_acc[i]); atomicAdd(a.stats + EPI * 16 + 4, (unsigned long long)(clock64() - st_begin)); atomicAdd(a.stats + EPI * 16 + 5, 1ull); })
         }
         __syncwarp();
     } else if (warp >= EPI_WARPS) {
@@ -357,10 +365,12 @@ __global__ void __launch_bounds__(UTHREADS, 1) umma_layer_kernel(const __grid_co
             }
         }
     }
+#ifdef WN_UMMA_STATS_BUILD
     if (a.stats && (tid == 0 || tid == UEPI)) {   // (the stagers' wait is that of group 0)
         const int o = EPI * 16 + (tid == 0 ? 6 : 8);
         atomicAdd(a.stats + o, (unsigned long long)st_acc[0]); atomicAdd(a.stats + o + 1, (unsigned long long)(clock64() - st_begin));
     }
+#endif
     umma::fence_before_sync();
     __syncthreads();
     if (warp == ISSUE_WARP) umma::tmem_dealloc(tmem, 512);
@@ -390,6 +400,7 @@ struct FArgs {
 };
 
 constexpr int F_NBAR = 3 * NSTAGE + 2 + 4 + 1;   // full | ready | done per stage, tgfull, tgempty, zready[4], tofull
+constexpr int ERB = 8;                           // rows per warp whose residual / skip loads are in flight together
 constexpr int Z_HALF_BYTES = 16 * LBO_A;         // z_hi or z_lo: 16 chunks of 8 channels x 128 positions
 static_assert(2 * Z_HALF_BYTES <= UM * STG_LD * 4, "the z operand and the epilogue staging tile share one region");
 
@@ -590,22 +601,22 @@ __global__ void __launch_bounds__(UTHREADS, 1) umma_fused_layer_kernel(const __g
                 const int m = g * 128 + 4 * lane;                         // first of this lane's 4 rows of [out ; skip]
                 const float4 bb = __ldg(reinterpret_cast<const float4 *>(a.bias_o + m));
                 // what is added to a row: the layer input (residual, modules.py:515-520) or the running skip sum
-                // (wavenet.py:833-836); 8 rows of loads are in flight before the first one is used
+                // (wavenet.py:833-836); 8 rows of loads are in flight before the first one is used (16 in flight, with or without setmaxnreg moving registers from the staging to the epilogue warps, measured 25-30 % slower)
                 const bool is_out = m < a.R, has_add = is_out || !a.first_layer;
                 const float *addp = is_out ? a.x + m : a.skips + (m - a.R);
                 float *dstp = is_out ? a.x_out + m : a.skips + (m - a.R);
                 const int ld = is_out ? a.R : a.S;
                 const bool scale = is_out ? a.residual_legacy != 0 : (a.legacy != 0 && !a.first_layer);
-                for (int rb = warp; rb < UM; rb += 8 * EPI_WARPS) {
-                    float4 add[8];
+                for (int rb = warp; rb < UM; rb += ERB * EPI_WARPS) {
+                    float4 add[ERB];
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) {
+                    for (int k = 0; k < ERB; ++k) {
                         const long long n = n0 + rb + EPI_WARPS * k;
                         add[k] = make_float4(0.f, 0.f, 0.f, 0.f);
                         if (has_add && n < a.N) add[k] = *reinterpret_cast<const float4 *>(addp + n * ld);
                     }
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) {
+                    for (int k = 0; k < ERB; ++k) {
                         const int r = rb + EPI_WARPS * k;
                         const long long n = n0 + r;
                         if (n >= a.N) continue;

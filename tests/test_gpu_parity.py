@@ -165,8 +165,8 @@ _TENSOR_CASES = {
 def test_step_tensor_core_path(name, monkeypatch):
     """WaveNet.step on the tensor cores (csrc/wn_step_umma.cu: tcgen05.mma, bf16 hi/lo split, three passes) against the fp32
     FFMA GEMMs (WN_STEP_FFMA=1) and the position-by-position engines: 1e-3 relative (BASELINE.json), observed ~2e-5
-    (default block) / ~2.5e-4 (paper block, mixture head).  One tile (128 positions) column tiles of 256 and 128, K tails
-    of 16, utterance starts inside a tile."""
+    (default block) / ~3e-4 (paper block, mixture head).  Column tiles of 256 and 128, K tails of 16, utterance starts inside
+    a tile; the default block takes the fused layer kernel, the others the two-kernel form."""
     mk, B, Tc = _TENSOR_CASES[name]
     hp = mk()
     w = common.weights_for(hp)
@@ -184,6 +184,10 @@ def test_step_tensor_core_path(name, monkeypatch):
     monkeypatch.delenv('WN_STEP_FFMA')
     monkeypatch.setenv('WN_STEP_SERIAL', '1')
     y_s = model.step(x, c=c)
+    monkeypatch.delenv('WN_STEP_SERIAL')
+    monkeypatch.setenv('WN_STEP_UNFUSED', '1')   # two kernels per layer (z through HBM) instead of the fused layer kernel
+    y_u = model.step(x, c=c)
+    assert common.max_rel(y, y_u) < 1e-5, common.max_rel(y, y_u)
     assert np.isfinite(y).all()
     assert not np.array_equal(y, y_f), 'the tensor-core path did not run'
     assert np.all(common.rel_close(y, y_f)), common.max_rel(y, y_f)
