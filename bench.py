@@ -58,6 +58,7 @@ def parse_args():
     ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS))
     ap.add_argument('--engine', default='auto', choices=['auto', 'generic', 'pipeline'])
     ap.add_argument('--hparams', default='default_22k', choices=['default_22k', 'paper'])
+    ap.add_argument('--no-step-full', action='store_true', help='skip the secondary WaveNet.step (configs[4]) figure')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
     return ap.parse_args()
@@ -198,6 +199,37 @@ class ClockSampler(object):
 # ---------------------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------------
+def step_full_point(torch, net, hp, peaks):
+    """BASELINE.json configs[4]: WaveNet.step (teacher forced, full sequence) on 8 x 10 s - the dense-GEMM formulation on the
+    tensor cores (csrc/wn_step_umma.cu: tcgen05.mma, every fp32 operand split into two bf16 numbers, three passes).  A
+    secondary figure: outside the timed region of the headline metric, device-resident buffers, CUDA events."""
+    B, frames = 8, 802
+    T = frames * hp.hop_size
+    rng = np.random.default_rng(0)
+    dc = torch.from_numpy(rng.uniform(0, 1, (B, frames, hp.num_mels)).astype(np.float32)).cuda()
+    dx = torch.from_numpy(rng.uniform(-1, 1, (B, T)).astype(np.float32)).cuda()
+    raw = torch.empty((B, T, hp.out_channels), dtype=torch.float32, device='cuda')
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sp = torch.cuda.current_stream().cuda_stream
+    best = None
+    for i in range(4):   # the first call allocates the scratch
+        ev0.record()
+        net.step_full(dx, dc, B, frames, raw, stream=sp)
+        ev1.record()
+        torch.cuda.synchronize()
+        if i:
+            best = ev0.elapsed_time(ev1) if best is None else min(best, ev0.elapsed_time(ev1))
+    assert bool(torch.isfinite(raw).all())
+    flops = float(net.info()['flops_per_sample']) * B * T
+    peak = peaks.get('bf16_tflops', 1590.0)
+    tensor_tflops = 3 * flops / (best / 1e3) / 1e12
+    return {'workload': 'configs[4]: WaveNet.step, default_22k, 8 utterances x 10 s (1 764 400 positions)', 'ms': best,
+            'fp32_equivalent_tflops': flops / (best / 1e3) / 1e12, 'bf16_tensor_tflops': tensor_tflops,
+            'roofline': {'bound': 'tensor', 'achieved': tensor_tflops, 'peak': peak, 'unit': 'TFLOP/s', 'frac': tensor_tflops / peak,
+                         'peak_source': 'measured burst (MEASURED_PEAKS.json)' if 'bf16_tflops' in peaks else 'fallback (B200_PROFILING.md)',
+                         'note': 'three bf16 passes (hi*hi, hi*lo, lo*hi) per fp32 product; see DESIGN.md 4.5'}}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -343,6 +375,8 @@ def run_ours(args):
         }
         if e2e is not None:
             line['e2e'] = e2e
+        if world == 1 and not args.no_step_full and args.hparams == 'default_22k':
+            line['step_full'] = step_full_point(torch, net, hp, peaks)
         if not args.no_cpu_baseline and world == 1:
             cores = os.cpu_count() or 1
             n, dt = cpu_sample(hp, weights, cores)

@@ -174,3 +174,32 @@ class WaveNet(object):
 			e = np.exp(out - out.max(axis=1, keepdims=True))
 			out = e / e.sum(axis=1, keepdims=True)
 		return out
+
+	def eval_loss(self, y, c=None, g=None, reduce=True):
+		"""Likelihood of a waveform under the model, the reference's eval-mode loss (wavenet.py:497-506 with
+		modules.py:800-836): one teacher-forced pass over y [B, T] (in [-1, 1]; mulaw input types: already companded)
+		on the GPU (step()), then the negative log-likelihood of y[t+1] under the parameters predicted at t, averaged
+		over all predicted samples (reduce=True) or returned per sample [B, T-1].  Gaussian head:
+		gaussian_maximum_likelihood_estimation_loss (CDF form, as hparams.cdf_loss), mixture head:
+		discretized_mix_logistic_loss, categorical head: cross entropy."""
+		from wavenet_vocoder.models.gaussian import gaussian_maximum_likelihood_estimation_loss
+		from wavenet_vocoder.models.mixture import discretized_mix_logistic_loss, log_prob_from_logits
+		hp = self._hparams
+		y = np.asarray(y, np.float32)
+		B, T = y.shape
+		if self.scalar_input:
+			x = y[:, None, :]
+		else:
+			x = np.eye(hp.quantize_channels, dtype=np.float32)[y.astype(np.int64)].transpose(0, 2, 1)
+		y_hat = self.step(x, c=c, g=g)[:, :, :-1]          # parameters for samples 1 .. T-1
+		tgt = y[:, 1:, None]
+		if not self.scalar_input:
+			logp = log_prob_from_logits(np.transpose(y_hat, [0, 2, 1]))
+			nll = -np.take_along_axis(logp, tgt.astype(np.int64), axis=-1)
+		elif hp.out_channels == 2:
+			nll = gaussian_maximum_likelihood_estimation_loss(y_hat, tgt, hp.log_scale_min_gauss, hp.quantize_channels,
+				use_cdf=getattr(hp, 'cdf_loss', False), reduce=False)
+		else:
+			nll = discretized_mix_logistic_loss(y_hat, tgt, num_classes=hp.quantize_channels,
+				log_scale_min=hp.log_scale_min, reduce=False)
+		return float(np.mean(nll)) if reduce else nll[..., 0]
