@@ -1,5 +1,6 @@
 // wn_step_full.cu - WaveNet.step (wavenet.py:650-721): the teacher-forced full-sequence pass used for logit
-// equivalence checks (BASELINE.json config 5).  Default: the time-parallel dense-GEMM formulation of wn_step_gemm.cu.
+// equivalence checks (BASELINE.json config 5).  Default: the time-parallel dense-GEMM formulation - on the tensor cores (wn_step_umma.cu, tcgen05.mma) where the channel
+// counts allow, else the fp32 FFMA2 kernels of wn_step_gemm.cu.
 // Configurations outside its scope, or WN_STEP_SERIAL=1, use the loop engines in "inputs mode" (x[t] is the network input
 // of step t, nothing is sampled), which evaluate the same causal dilated convolutions position by position and are
 // bit-identical to incremental synthesis under teacher forcing.
