@@ -234,9 +234,16 @@ __global__ void __launch_bounds__(GEN_THREADS, 1) wn_loop_generic_kernel(
             if (staged) {
                 if (!(q0 & 3) && !(nq & 3) && !(S & 3) && !(R & 3)) {   // 16-byte pieces never straddle the skip / out boundary
                     const int nq4 = nq >> 2;
-                    for (int i = tid; i < H * nq4; i += NT) {
-                        const int k = i / nq4, n = q0 + 4 * (i - k * nq4);
-                        cp_async16(wos + (size_t)k * nq + (n - q0), n < S ? lw + m.off_skip_w + (size_t)k * S + n : lw + m.off_out_w + (size_t)k * R + (n - S));
+                    if (NT % nq4 == 0) {   // a thread keeps its column and walks k with a constant stride: no division per copy
+                        const int n = q0 + 4 * (tid % nq4), kstep = NT / nq4;
+                        const float *src = (n < S ? lw + m.off_skip_w + n : lw + m.off_out_w + (n - S));
+                        const int ld = n < S ? S : R;
+                        for (int k = tid / nq4; k < H; k += kstep) cp_async16(wos + (size_t)k * nq + (n - q0), src + (size_t)k * ld);
+                    } else {
+                        for (int i = tid; i < H * nq4; i += NT) {
+                            const int k = i / nq4, n = q0 + 4 * (i - k * nq4);
+                            cp_async16(wos + (size_t)k * nq + (n - q0), n < S ? lw + m.off_skip_w + (size_t)k * S + n : lw + m.off_out_w + (size_t)k * R + (n - S));
+                        }
                     }
                 } else {
                     for (int i = tid; i < H * nq; i += NT) {
