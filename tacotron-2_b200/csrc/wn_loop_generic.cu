@@ -60,6 +60,46 @@ __device__ __forceinline__ float dot16_lane(const float *xs, int K, int Kpad, co
     return acc;
 }
 
+// Two rows (nA, nB) per call: the loads of both rows are issued in the same round, which halves the L2 round trips of a
+// CTA that owns more rows than it has lane groups.  Each row's arithmetic is exactly dot16_lane's.
+__device__ __forceinline__ void dot16_lane2(const float *xs, int K, int Kpad, const float *__restrict__ Wt, int nA, bool vA,
+                                            int nB, bool vB, int lane, float &outA, float &outB) {
+    float accA = 0.0f, accB = 0.0f;
+    const float4 *wA = reinterpret_cast<const float4 *>(Wt + (long long)(vA ? nA : 0) * Kpad);
+    const float4 *wB = reinterpret_cast<const float4 *>(Wt + (long long)(vB ? nB : 0) * Kpad);
+    const float4 *x4 = reinterpret_cast<const float4 *>(xs);
+    const int nfull = K >> 2;
+    constexpr int UB = 8;
+    for (int c = lane; c < nfull; c += UB * LANES) {
+        float4 a[UB], b[UB];
+#pragma unroll
+        for (int u = 0; u < UB; ++u)
+            if (c + u * LANES < nfull) {
+                if (vA) a[u] = __ldg(wA + c + u * LANES);
+                if (vB) b[u] = __ldg(wB + c + u * LANES);
+            }
+#pragma unroll
+        for (int u = 0; u < UB; ++u)
+            if (c + u * LANES < nfull) {
+                const float4 xv = x4[c + u * LANES];
+                if (vA) { accA = __fmaf_rn(xv.x, a[u].x, accA); accA = __fmaf_rn(xv.y, a[u].y, accA); accA = __fmaf_rn(xv.z, a[u].z, accA); accA = __fmaf_rn(xv.w, a[u].w, accA); }
+                if (vB) { accB = __fmaf_rn(xv.x, b[u].x, accB); accB = __fmaf_rn(xv.y, b[u].y, accB); accB = __fmaf_rn(xv.z, b[u].z, accB); accB = __fmaf_rn(xv.w, b[u].w, accB); }
+            }
+    }
+    if ((K & 3) && (nfull % LANES) == lane) {   // ragged tail chunk: only the elements below K
+        for (int k = nfull * 4; k < K; ++k) {
+            if (vA) accA = __fmaf_rn(xs[k], __ldg(Wt + (long long)nA * Kpad + k), accA);
+            if (vB) accB = __fmaf_rn(xs[k], __ldg(Wt + (long long)nB * Kpad + k), accB);
+        }
+    }
+#pragma unroll
+    for (int s = 1; s < LANES; s <<= 1) {
+        accA = __fadd_rn(accA, __shfl_xor_sync(0xffffffffu, accA, s));
+        accB = __fadd_rn(accB, __shfl_xor_sync(0xffffffffu, accB, s));
+    }
+    outA = accA; outB = accB;
+}
+
 // blocked sequential chains (wn_oracle.c:dot_blocked): y = ((o_0 + o_1) + ...) + b, o_p over k in [K*p/P, K*(p+1)/P).
 __device__ __forceinline__ float dot_blocked_col(const float *__restrict__ zs, int K, const float *__restrict__ W,
                                                  int N, int n, int nsplit, float bias) {
@@ -279,12 +319,14 @@ __global__ void __launch_bounds__(GEN_THREADS, 1) wn_loop_generic_kernel(
             // ---- gate pre-activation: one dot16 over [taps | c | g | x(t)] (modules.py:294-297, :497-508); this CTA's
             //      channels: rows h0.. (tanh half) and H + h0.. (sigmoid half)
             const int h0 = slice_lo(H, cr, C), hn = slice_lo(H, cr + 1, C) - h0;
-            for (int ib = 0; ib < 2 * hn; ib += ngroups) {
-                const int i = ib + group;
-                const bool valid = i < 2 * hn;
-                const int n = i < hn ? h0 + i : H + h0 + (i - hn);
-                const float a = dot16_lane(xcat, m.Kcat, m.KcatPad, lw + m.off_cat_w, n, valid, lane);
-                if (lane == 0 && valid) pre[n] = __fadd_rn(a, __ldg(lw + m.off_bsum + n));
+            for (int ib = 0; ib < 2 * hn; ib += 2 * ngroups) {
+                const int iA = ib + group, iB = iA + ngroups;
+                const bool vA = iA < 2 * hn, vB = iB < 2 * hn;
+                const int nA = iA < hn ? h0 + iA : H + h0 + (iA - hn), nB = iB < hn ? h0 + iB : H + h0 + (iB - hn);
+                float a, b2;
+                dot16_lane2(xcat, m.Kcat, m.KcatPad, lw + m.off_cat_w, nA, vA, nB, vB, lane, a, b2);
+                if (lane == 0 && vA) pre[nA] = __fadd_rn(a, __ldg(lw + m.off_bsum + nA));
+                if (lane == 0 && vB) pre[nB] = __fadd_rn(b2, __ldg(lw + m.off_bsum + nB));
             }
             __syncthreads();
             for (int i = tid; i < hn; i += NT) {   // :510
