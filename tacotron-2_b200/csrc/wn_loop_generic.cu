@@ -122,32 +122,33 @@ __device__ __forceinline__ float dot_blocked_col(const float *__restrict__ zs, i
     return __fadd_rn(y, bias);
 }
 
-// the same chains with the weights of this CTA's rows staged in shared memory: Ws[k * nq + j], j = row - first row
-__device__ __forceinline__ float dot_blocked_smem(const float *__restrict__ zs, int K, const float *__restrict__ Ws, int nq,
-                                                  int j, int nsplit, float bias) {
+// the same chains with the weights of this CTA's rows staged in shared memory, one row per output: Wrow[k], k contiguous
+// (rows are WOS_PAD floats longer than K, so that the 16-byte loads of consecutive threads fall into different banks).
+// Four k per load instruction: ptxas, short of registers in this kernel, issues every load right before its fma, so the
+// chain pays one shared-memory latency per LOAD - with scalar loads that was 33 cycles per k.
+constexpr int WOS_PAD = 4;
+__device__ __forceinline__ float dot_blocked_smem(const float *__restrict__ zs, int K, const float *__restrict__ Wrow, int nsplit,
+                                                  float bias) {
     float y = 0.0f;
     for (int p = 0; p < nsplit; ++p) {
         const int k0 = (int)((long long)K * p / nsplit), k1 = (int)((long long)K * (p + 1) / nsplit);
         float acc = 0.0f;
-        const float *wp = Ws + (size_t)k0 * nq + j;
         int k = k0;
-        for (; k + 8 <= k1; k += 8, wp += 8 * nq) {   // 16 shared-memory loads in flight, then the sequential chain
-            float wv[8], zv[8];
-#pragma unroll
-            for (int u = 0; u < 8; ++u) { wv[u] = wp[u * nq]; zv[u] = zs[k + u]; }
-#pragma unroll
-            for (int u = 0; u < 8; ++u) acc = __fmaf_rn(zv[u], wv[u], acc);
+        for (; k < k1 && (k & 3); ++k) acc = __fmaf_rn(zs[k], Wrow[k], acc);
+        for (; k + 4 <= k1; k += 4) {
+            const float4 w = *reinterpret_cast<const float4 *>(Wrow + k), z = *reinterpret_cast<const float4 *>(zs + k);
+            acc = __fmaf_rn(z.x, w.x, acc);
+            acc = __fmaf_rn(z.y, w.y, acc);
+            acc = __fmaf_rn(z.z, w.z, acc);
+            acc = __fmaf_rn(z.w, w.w, acc);
         }
-        for (; k < k1; ++k, wp += nq) acc = __fmaf_rn(zs[k], *wp, acc);
+        for (; k < k1; ++k) acc = __fmaf_rn(zs[k], Wrow[k], acc);
         y = p == 0 ? acc : __fadd_rn(y, acc);
     }
     return __fadd_rn(y, bias);
 }
 __device__ __forceinline__ void cp_async4(float *dst_smem, const float *src) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async16(float *dst_smem, const float *src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
 }
 
 __device__ float sample_gaussian(const WnModelDev &m, const float *out, float eps) {  // gaussian.py:39-52
@@ -235,7 +236,7 @@ __global__ void __launch_bounds__(GEN_THREADS, 1) wn_loop_generic_kernel(
     float *outv = h1 + m.Spad;                // [round4(O)]
     float *ev = outv + round4(O);             // [round4(O)]  categorical scratch
     float *fb = ev + round4(O);               // [4]: fb[0] next scalar input, fb[1] next class
-    float *wos = fb + 4;                      // [H][rows of this CTA] skip / out weights of the current layer (if they fit)
+    float *wos = fb + 4;                      // [rows of this CTA][H + WOS_PAD] skip / out weights of the current layer (if they fit)
     const bool quant = m.input_type == WN_INPUT_MULAW_QUANTIZE;
     float *ring = rings + (long long)b * m.ring_per_utt;
     const int o_cond = (ks - 1) * R, o_g = o_cond + m.cin, o_cur = o_g + m.gin;
@@ -270,25 +271,19 @@ __global__ void __launch_bounds__(GEN_THREADS, 1) wn_loop_generic_kernel(
             // this CTA's rows of [skip ; out], requested now (cp.async) and used after the gate: the blocked chains are
             // sequential in k, so reading their weights from L2 on demand costs one round trip per 16 k
             const int q0 = slice_lo(S + R, cr, C), q1 = slice_lo(S + R, cr + 1, C), nq = q1 - q0;
-            const bool staged = nq * H <= wos_floats;
-            if (staged) {
-                if (!(q0 & 3) && !(nq & 3) && !(S & 3) && !(R & 3)) {   // 16-byte pieces never straddle the skip / out boundary
-                    const int nq4 = nq >> 2;
-                    if (NT % nq4 == 0) {   // a thread keeps its column and walks k with a constant stride: no division per copy
-                        const int n = q0 + 4 * (tid % nq4), kstep = NT / nq4;
-                        const float *src = (n < S ? lw + m.off_skip_w + n : lw + m.off_out_w + (n - S));
-                        const int ld = n < S ? S : R;
-                        for (int k = tid / nq4; k < H; k += kstep) cp_async16(wos + (size_t)k * nq + (n - q0), src + (size_t)k * ld);
-                    } else {
-                        for (int i = tid; i < H * nq4; i += NT) {
-                            const int k = i / nq4, n = q0 + 4 * (i - k * nq4);
-                            cp_async16(wos + (size_t)k * nq + (n - q0), n < S ? lw + m.off_skip_w + (size_t)k * S + n : lw + m.off_out_w + (size_t)k * R + (n - S));
-                        }
-                    }
+            const int wld = H + WOS_PAD;                           // row stride of the staged copy
+            const bool staged = nq * wld <= wos_floats && !(H & 3);
+            if (staged) {   // W[k][n] (n contiguous in global memory) -> wos[n - q0][k]
+                if (NT % nq == 0) {   // a thread keeps its row and walks k with a constant stride: no division per copy
+                    const int n = q0 + tid % nq, kstep = NT / nq;
+                    const float *src = n < S ? lw + m.off_skip_w + n : lw + m.off_out_w + (n - S);
+                    const int ld = n < S ? S : R;
+                    float *dst = wos + (size_t)(n - q0) * wld;
+                    for (int k = tid / nq; k < H; k += kstep) cp_async4(dst + k, src + (size_t)k * ld);
                 } else {
                     for (int i = tid; i < H * nq; i += NT) {
                         const int k = i / nq, n = q0 + (i - k * nq);
-                        cp_async4(wos + i, n < S ? lw + m.off_skip_w + (size_t)k * S + n : lw + m.off_out_w + (size_t)k * R + (n - S));
+                        cp_async4(wos + (size_t)(n - q0) * wld + k, n < S ? lw + m.off_skip_w + (size_t)k * S + n : lw + m.off_out_w + (size_t)k * R + (n - S));
                     }
                 }
                 asm volatile("cp.async.commit_group;" ::: "memory");
@@ -338,7 +333,7 @@ __global__ void __launch_bounds__(GEN_THREADS, 1) wn_loop_generic_kernel(
             // ---- skip and residual 1x1s (modules.py:512-520, wavenet.py:833-836): this CTA's rows of [skip ; out] ------
             for (int n = q0 + tid; n < q1; n += NT) {
                 if (n < S) {
-                    float s = staged ? dot_blocked_smem(z, H, wos, nq, n - q0, m.ksplit, __ldg(lw + m.off_skip_b + n))
+                    float s = staged ? dot_blocked_smem(z, H, wos + (size_t)(n - q0) * wld, m.ksplit, __ldg(lw + m.off_skip_b + n))
                                      : dot_blocked_col(z, H, lw + m.off_skip_w, S, n, m.ksplit, __ldg(lw + m.off_skip_b + n));
                     if (l > 0) {
                         const float v = __fadd_rn(skips[n], s);
@@ -348,7 +343,7 @@ __global__ void __launch_bounds__(GEN_THREADS, 1) wn_loop_generic_kernel(
                     else skips[n] = s;                              // the running sum stays with its owner
                 } else {
                     const int r = n - S;
-                    float o = staged ? dot_blocked_smem(z, H, wos, nq, n - q0, m.ksplit, __ldg(lw + m.off_out_b + r))
+                    float o = staged ? dot_blocked_smem(z, H, wos + (size_t)(n - q0) * wld, m.ksplit, __ldg(lw + m.off_out_b + r))
                                      : dot_blocked_col(z, H, lw + m.off_out_w, R, r, m.ksplit, __ldg(lw + m.off_out_b + r));
                     float v = __fadd_rn(o, x[r]);
                     bcast_f32(x + r, m.residual_legacy ? __fmul_rn(v, WN_SQRT_HALF) : v, C);
@@ -418,7 +413,7 @@ int wn_launch_loop_generic(wn_handle *h, const float *c_up, const float *g_emb, 
     cudaLaunchAttribute at[1];
     int wos_floats = 0;
     auto configure = [&](int C) {
-        wos_floats = (int)(((size_t)(m.S + m.R + C - 1) / C + 1) * (size_t)m.H);
+        wos_floats = (int)(((size_t)(m.S + m.R + C - 1) / C + 1) * (size_t)(m.H + WOS_PAD));
         if (smem_state + sizeof(float) * (size_t)wos_floats > 160 * 1024) wos_floats = 0;
         smem = smem_state + sizeof(float) * (size_t)wos_floats;
         cfg.gridDim = dim3((unsigned)(B * C)); cfg.blockDim = dim3(GEN_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
