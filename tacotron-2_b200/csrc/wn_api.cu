@@ -246,6 +246,16 @@ extern "C" int wn_finalize(wn_handle *h) {
         m.off_out_b = (int)(bb.add(W(p + "out_conv/bias"), m.R) - base);
         m.off_skip_w = (int)(bb.add(W(p + "skip_conv/kernel"), (size_t)m.H * m.S) - base);
         m.off_skip_b = (int)(bb.add(W(p + "skip_conv/bias"), m.S) - base);
+        {   // rows of [skip ; out] with k contiguous (16-byte staging copies of wn_loop_generic.cu)
+            m.Hpad = r4(m.H);
+            const float *sw = W(p + "skip_conv/kernel"), *ow = W(p + "out_conv/kernel");
+            std::vector<float> ost((size_t)(m.S + m.R) * m.Hpad, 0.0f);
+            for (int k = 0; k < m.H; ++k) {
+                for (int n = 0; n < m.S; ++n) ost[(size_t)n * m.Hpad + k] = sw[(size_t)k * m.S + n];
+                for (int n = 0; n < m.R; ++n) ost[(size_t)(m.S + n) * m.Hpad + k] = ow[(size_t)k * m.R + n];
+            }
+            m.off_os_t = (int)(bb.add(ost.data(), ost.size()) - base);
+        }
         bb.add(nullptr, 0);
         if (l == 0) stride = bb.v.size() - base;
     }

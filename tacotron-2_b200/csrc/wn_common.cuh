@@ -33,6 +33,7 @@ struct WnModelDev {
     const float *layers;           // base of layer 0
     long long layer_stride;        // floats
     int off_cat_w, off_bsum, off_out_w, off_out_b, off_skip_w, off_skip_b;
+    int off_os_t, Hpad;            // [skip ; out] transposed, [(S + R)][Hpad]: the copy the cluster engine stages in shared memory
     const float *h1_w, *h1_b, *h2_w, *h2_b;   // h1_w [S][Spad], h2_w [O][Spad] (transposed)
     const float *emb;              // [n_speakers][gin] or nullptr
 };

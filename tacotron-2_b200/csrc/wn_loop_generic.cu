@@ -147,8 +147,8 @@ __device__ __forceinline__ float dot_blocked_smem(const float *__restrict__ zs, 
     }
     return __fadd_rn(y, bias);
 }
-__device__ __forceinline__ void cp_async4(float *dst_smem, const float *src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+__device__ __forceinline__ void cp_async16(float *dst_smem, const float *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
 }
 
 __device__ float sample_gaussian(const WnModelDev &m, const float *out, float eps) {  // gaussian.py:39-52
@@ -273,17 +273,16 @@ __global__ void __launch_bounds__(GEN_THREADS, 1) wn_loop_generic_kernel(
             const int q0 = slice_lo(S + R, cr, C), q1 = slice_lo(S + R, cr + 1, C), nq = q1 - q0;
             const int wld = H + WOS_PAD;                           // row stride of the staged copy
             const bool staged = nq * wld <= wos_floats && !(H & 3);
-            if (staged) {   // W[k][n] (n contiguous in global memory) -> wos[n - q0][k]
-                if (NT % nq == 0) {   // a thread keeps its row and walks k with a constant stride: no division per copy
-                    const int n = q0 + tid % nq, kstep = NT / nq;
-                    const float *src = n < S ? lw + m.off_skip_w + n : lw + m.off_out_w + (n - S);
-                    const int ld = n < S ? S : R;
-                    float *dst = wos + (size_t)(n - q0) * wld;
-                    for (int k = tid / nq; k < H; k += kstep) cp_async4(dst + k, src + (size_t)k * ld);
+            if (staged) {   // rows [q0, q1) of the transposed [skip ; out] copy of the blob -> wos[row - q0][k], 16 bytes per copy
+                const int H4 = H >> 2;
+                const float *src = lw + m.off_os_t + (size_t)q0 * m.Hpad;
+                if (NT % H4 == 0) {   // a thread keeps its k and walks the rows with a constant stride: no division per copy
+                    const int k4 = tid % H4, jstep = NT / H4;
+                    for (int j = tid / H4; j < nq; j += jstep) cp_async16(wos + (size_t)j * wld + 4 * k4, src + (size_t)j * m.Hpad + 4 * k4);
                 } else {
-                    for (int i = tid; i < H * nq; i += NT) {
-                        const int k = i / nq, n = q0 + (i - k * nq);
-                        cp_async4(wos + (size_t)(n - q0) * wld + k, n < S ? lw + m.off_skip_w + (size_t)k * S + n : lw + m.off_out_w + (size_t)k * R + (n - S));
+                    for (int i = tid; i < nq * H4; i += NT) {
+                        const int j = i / H4, k4 = i - j * H4;
+                        cp_async16(wos + (size_t)j * wld + 4 * k4, src + (size_t)j * m.Hpad + 4 * k4);
                     }
                 }
                 asm volatile("cp.async.commit_group;" ::: "memory");
