@@ -153,6 +153,25 @@ def test_step_gemm_equals_serial_step(name, monkeypatch):
     assert np.all(common.rel_close(y, y_serial)), common.max_rel(y, y_serial)
 
 
+@pytest.mark.parametrize('name', ['gauss_subpixel', 'mulaw_gin_1d', 'subpixel_no_nninit_odd', 'mulaw_quantize'])
+def test_generic_engine_cluster_sizes_bit_identical(name, monkeypatch):
+    """The generic engine splits the rows of every inner product over a thread-block cluster of 1, 2, 4 or 8 CTAs per
+    utterance (csrc/wn_loop_generic.cu); a row's arithmetic does not depend on who computes it, so every size returns
+    the bits of the C oracle - also with channel counts that do not divide by the cluster size (24 / 40 / 20)."""
+    hp = common.small_variants()[name]
+    w = common.weights_for(hp)
+    B, Tc = 3, 3
+    T = Tc * hp.hop_size
+    c, nz, g = common.cond_for(hp, B, Tc), common.noise_for(hp, T, B), common.speaker_ids(hp, B)
+    a_c, _, raw_c, _ = COracle(hp, w).synthesize(c, noise=nz, g=g)
+    for C in (1, 2, 4, 8):
+        monkeypatch.setenv('WN_GEN_CLUSTER', str(C))
+        net = _native(hp, w, 'generic')
+        audio, raw = net.synthesize_host(c, nz, g_ids=g, want_raw=True)
+        assert np.array_equal(audio, a_c) and np.array_equal(raw, raw_c), 'cluster of {}'.format(C)
+        net.close()
+
+
 _TENSOR_CASES = {
     'default_22k': (lambda: common.default_22k(), 3, 3),
     'r64_g128': (lambda: common.small(residual_channels=64, gate_channels=128, skip_out_channels=64), 2, 40),
