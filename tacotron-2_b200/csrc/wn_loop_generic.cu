@@ -218,7 +218,10 @@ __device__ __forceinline__ int slice_lo(int n, int q, int C) { return (int)((lon
 // rows [S cr / C, ...) of the first head 1x1, and writes its results into all C copies.  The arithmetic of a row does not
 // depend on who computes it, so every C gives the same bits.  Two cluster barriers per layer and one in the head.
 // Dynamic shared memory carved below.
-__global__ void __launch_bounds__(GEN_THREADS, 1) wn_loop_generic_kernel(
+// MINB = CTAs per SM the register budget allows: 1 -> 128 registers (two gate rows per lane group and round), 2 -> 64
+// registers (one row per round), which lets clusters share SMs when one CTA per SM does not keep every utterance resident.
+template <int MINB>
+__global__ void __launch_bounds__(GEN_THREADS, MINB) wn_loop_generic_kernel(
     const WnModelDev m, const float *__restrict__ c_up, const float *__restrict__ g_emb,
     const float *__restrict__ noise, const float *__restrict__ teacher, int inputs_mode, int B, int T,
     float *__restrict__ rings, float *__restrict__ audio, float *__restrict__ raw, int wos_floats) {
@@ -313,14 +316,24 @@ __global__ void __launch_bounds__(GEN_THREADS, 1) wn_loop_generic_kernel(
             // ---- gate pre-activation: one dot16 over [taps | c | g | x(t)] (modules.py:294-297, :497-508); this CTA's
             //      channels: rows h0.. (tanh half) and H + h0.. (sigmoid half)
             const int h0 = slice_lo(H, cr, C), hn = slice_lo(H, cr + 1, C) - h0;
-            for (int ib = 0; ib < 2 * hn; ib += 2 * ngroups) {
-                const int iA = ib + group, iB = iA + ngroups;
-                const bool vA = iA < 2 * hn, vB = iB < 2 * hn;
-                const int nA = iA < hn ? h0 + iA : H + h0 + (iA - hn), nB = iB < hn ? h0 + iB : H + h0 + (iB - hn);
-                float a, b2;
-                dot16_lane2(xcat, m.Kcat, m.KcatPad, lw + m.off_cat_w, nA, vA, nB, vB, lane, a, b2);
-                if (lane == 0 && vA) pre[nA] = __fadd_rn(a, __ldg(lw + m.off_bsum + nA));
-                if (lane == 0 && vB) pre[nB] = __fadd_rn(b2, __ldg(lw + m.off_bsum + nB));
+            if (MINB == 1) {
+                for (int ib = 0; ib < 2 * hn; ib += 2 * ngroups) {
+                    const int iA = ib + group, iB = iA + ngroups;
+                    const bool vA = iA < 2 * hn, vB = iB < 2 * hn;
+                    const int nA = iA < hn ? h0 + iA : H + h0 + (iA - hn), nB = iB < hn ? h0 + iB : H + h0 + (iB - hn);
+                    float a, b2;
+                    dot16_lane2(xcat, m.Kcat, m.KcatPad, lw + m.off_cat_w, nA, vA, nB, vB, lane, a, b2);
+                    if (lane == 0 && vA) pre[nA] = __fadd_rn(a, __ldg(lw + m.off_bsum + nA));
+                    if (lane == 0 && vB) pre[nB] = __fadd_rn(b2, __ldg(lw + m.off_bsum + nB));
+                }
+            } else {
+                for (int ib = 0; ib < 2 * hn; ib += ngroups) {
+                    const int i = ib + group;
+                    const bool valid = i < 2 * hn;
+                    const int n = i < hn ? h0 + i : H + h0 + (i - hn);
+                    const float a = dot16_lane(xcat, m.Kcat, m.KcatPad, lw + m.off_cat_w, n, valid, lane);
+                    if (lane == 0 && valid) pre[n] = __fadd_rn(a, __ldg(lw + m.off_bsum + n));
+                }
             }
             __syncthreads();
             for (int i = tid; i < hn; i += NT) {   // :510
@@ -411,32 +424,49 @@ int wn_launch_loop_generic(wn_handle *h, const float *c_up, const float *g_emb, 
     cudaLaunchConfig_t cfg = {};
     cudaLaunchAttribute at[1];
     int wos_floats = 0;
-    auto configure = [&](int C) {
+    const void *kern = nullptr;
+    auto configure = [&](int C, int minb) {
+        kern = minb == 1 ? (const void *)wn_loop_generic_kernel<1> : (const void *)wn_loop_generic_kernel<2>;
         wos_floats = (int)(((size_t)(m.S + m.R + C - 1) / C + 1) * (size_t)(m.H + WOS_PAD));
-        if (smem_state + sizeof(float) * (size_t)wos_floats > 160 * 1024) wos_floats = 0;
+        if (smem_state + sizeof(float) * (size_t)wos_floats > (size_t)(minb == 1 ? 160 : 100) * 1024) wos_floats = 0;
         smem = smem_state + sizeof(float) * (size_t)wos_floats;
         cfg.gridDim = dim3((unsigned)(B * C)); cfg.blockDim = dim3(GEN_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = (unsigned)C; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         cfg.attrs = at; cfg.numAttrs = 1;
-        if (cudaFuncSetAttribute(wn_loop_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem, 48 * 1024)) != cudaSuccess) { cudaGetLastError(); return 0; }
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem, 48 * 1024)) != cudaSuccess) { cudaGetLastError(); return 0; }
         int n = 0;
-        if (cudaOccupancyMaxActiveClusters(&n, wn_loop_generic_kernel, &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
+        if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
         return n;
     };
-    int C = 1;
-    if (const char *e = getenv("WN_GEN_CLUSTER")) {
-        C = atoi(e);
+    // Largest cluster first; per size the 128-register variant (one CTA per SM), then the 64-register one that lets
+    // clusters share SMs (paper block, 16 utterances: 15 clusters of 8 fit with one CTA per SM, 33 with two; 333 us/step
+    // against 348 with clusters of 4).  WN_GEN_CLUSTER / WN_GEN_MINB force the choice.
+    int C = 1, minb = 1;
+    const char *eC = getenv("WN_GEN_CLUSTER"), *eM = getenv("WN_GEN_MINB");
+    if (eC || eM) {
+        if (eC) C = atoi(eC);
         if (C != 1 && C != 2 && C != 4 && C != 8) C = 1;
+        minb = eM && atoi(eM) == 2 ? 2 : 1;
+        if (!eC)
+            for (C = 8; C > 1; C >>= 1)
+                if (configure(C, minb) >= B) break;
     } else {
-        for (C = 8; C > 1; C >>= 1)
-            if (configure(C) >= B) break;
+        bool found = false;
+        for (int c = 8; c > 1 && !found; c >>= 1)
+            for (int mb = 1; mb <= 2 && !found; ++mb)
+                if (configure(c, mb) >= B) { C = c; minb = mb; found = true; }
     }
-    const int resident = configure(C);
-    if (getenv("WN_GEN_DEBUG")) fprintf(stderr, "generic engine: B=%d cluster=%d resident clusters=%d smem=%zu staged=%d\n", B, C, resident, smem, wos_floats != 0);
+    const int resident = configure(C, minb);
+    if (getenv("WN_GEN_DEBUG")) fprintf(stderr, "generic engine: B=%d cluster=%d CTAs/SM=%d resident clusters=%d smem=%zu staged=%d\n", B, C, minb, resident, smem, wos_floats != 0);
     if (resident < 1) { h->err = "generic engine: the cluster does not fit the device"; return WN_ERR_CUDA; }
-    WN_CUDA_TRY(h, cudaLaunchKernelEx(&cfg, wn_loop_generic_kernel, m, c_up, g_emb, noise, teacher, inputs_mode, B, T, h->d_ring,
-                                      audio, raw, wos_floats));
+    {
+        const WnModelDev mm = m;
+        float *ring_p = h->d_ring;
+        void *args[] = {(void *)&mm, (void *)&c_up, (void *)&g_emb, (void *)&noise, (void *)&teacher, (void *)&inputs_mode, (void *)&B, (void *)&T,
+                        (void *)&ring_p, (void *)&audio, (void *)&raw, (void *)&wos_floats};
+        WN_CUDA_TRY(h, cudaLaunchKernelExC(&cfg, kern, args));
+    }
     h->launches++;
     WN_CUDA_TRY(h, cudaGetLastError());
     return WN_OK;

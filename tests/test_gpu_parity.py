@@ -164,8 +164,9 @@ def test_generic_engine_cluster_sizes_bit_identical(name, monkeypatch):
     T = Tc * hp.hop_size
     c, nz, g = common.cond_for(hp, B, Tc), common.noise_for(hp, T, B), common.speaker_ids(hp, B)
     a_c, _, raw_c, _ = COracle(hp, w).synthesize(c, noise=nz, g=g)
-    for C in (1, 2, 4, 8):
+    for C, minb in ((1, 1), (2, 1), (4, 2), (8, 1), (8, 2)):   # minb: the 128- / 64-register variant of the kernel
         monkeypatch.setenv('WN_GEN_CLUSTER', str(C))
+        monkeypatch.setenv('WN_GEN_MINB', str(minb))
         net = _native(hp, w, 'generic')
         audio, raw = net.synthesize_host(c, nz, g_ids=g, want_raw=True)
         assert np.array_equal(audio, a_c) and np.array_equal(raw, raw_c), 'cluster of {}'.format(C)
