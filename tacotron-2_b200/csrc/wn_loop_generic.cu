@@ -19,12 +19,16 @@
 namespace {
 
 constexpr int GEN_THREADS = 512;
+#ifndef GEN_UB_LOWREG
+#define GEN_UB_LOWREG 4   // independent 16-byte weight loads per round in the 64-register variant (8 spills there)
+#endif
 constexpr int LANES = WN_DOT_LANES;   // partial sums per dot reduction
 
 // dot16 of xs[0..K) (shared memory, zero padded to a multiple of 4) with row n of Wt ([N][Kpad], global), for the
 // outputs n = nb + group.  Every thread of the CTA calls it with the same trip count (shuffles are warp-wide).
 // Lane j owns the float4 chunks c = j, j+16, ... ; the xor butterfly adds neighbours first, which is the tree of
 // wn_oracle.c:dot16.  Returns the full sum on every lane of the group.
+template <int UB = 8>
 __device__ __forceinline__ float dot16_lane(const float *xs, int K, int Kpad, const float *__restrict__ Wt, int n,
                                             bool valid, int lane) {
     float acc = 0.0f;
@@ -34,7 +38,6 @@ __device__ __forceinline__ float dot16_lane(const float *xs, int K, int Kpad, co
         const int nfull = K >> 2;
         // weights stream from L2: a round issues up to UB independent loads (predicated at the end of the row) before the
         // dependent fma chain consumes them, so a row costs ceil(K / (64 UB)) L2 round trips
-        constexpr int UB = 8;
         for (int c = lane; c < nfull; c += UB * LANES) {
             float4 wv[UB];
 #pragma unroll
@@ -331,7 +334,7 @@ __global__ void __launch_bounds__(GEN_THREADS, MINB) wn_loop_generic_kernel(
                     const int i = ib + group;
                     const bool valid = i < 2 * hn;
                     const int n = i < hn ? h0 + i : H + h0 + (i - hn);
-                    const float a = dot16_lane(xcat, m.Kcat, m.KcatPad, lw + m.off_cat_w, n, valid, lane);
+                    const float a = dot16_lane<GEN_UB_LOWREG>(xcat, m.Kcat, m.KcatPad, lw + m.off_cat_w, n, valid, lane);
                     if (lane == 0 && valid) pre[n] = __fadd_rn(a, __ldg(lw + m.off_bsum + n));
                 }
             }
