@@ -4,7 +4,7 @@ Same ``load(checkpoint_path, hparams, model_name)`` / ``synthesize(mel_spectrogr
 out_dir, log_dir)`` contract: a list of un-normalised ``[frames, num_mels]`` mels in, peak-normalised int16 wav files
 out.  Where the reference does one ``session.run`` on a TF graph (:97) this does one ``wn_synthesize_host`` call into
 libwavenet_b200.so.  Differences, all stated in DESIGN.md: weights come from an ``.npz`` weight table or
-``random:<seed>`` (TF-checkpoint import is a "next" row); PNG plots are skipped (no matplotlib here,
+``random:<seed>`` or a TensorFlow V2 checkpoint prefix (wavenet_vocoder/tf_checkpoint.py; see its STATUS note); PNG plots are skipped (no matplotlib here,
 out of scope); an optional ``seed`` makes the draws reproducible (the reference's are unseeded).
 """
 import os
@@ -29,7 +29,7 @@ def _pad_inputs(x, maxlen, _pad=0):
 
 def resolve_weights(checkpoint_path, hparams):
 	"""'random:<seed>[:kind]' -> deterministic random init; '*.npz' -> weight table; anything else is a TF checkpoint,
-	which this build cannot read yet."""
+	read without TensorFlow by wavenet_vocoder/tf_checkpoint.py."""
 	if isinstance(checkpoint_path, dict):
 		return checkpoint_path
 	if checkpoint_path is None or str(checkpoint_path).startswith('random'):
@@ -39,8 +39,11 @@ def resolve_weights(checkpoint_path, hparams):
 		return wn_weights.init_weights(hparams, seed=seed, kind=kind)
 	if str(checkpoint_path).endswith('.npz') and os.path.exists(checkpoint_path):
 		return wn_weights.load_weights(checkpoint_path)
-	raise RuntimeError('Failed to load checkpoint at {} (expected an .npz weight table or random:<seed>; '
-		'TensorFlow checkpoints are not readable by this build)'.format(checkpoint_path))
+	if os.path.exists(str(checkpoint_path) + '.index'):      # a TensorFlow V2 checkpoint prefix (train.py:67-86)
+		from wavenet_vocoder.tf_checkpoint import load_tf_checkpoint
+		return load_tf_checkpoint(str(checkpoint_path), hparams)
+	raise RuntimeError('Failed to load checkpoint at {} (expected a TensorFlow checkpoint prefix, an .npz weight table or '
+		'random:<seed>)'.format(checkpoint_path))
 
 
 class Synthesizer:
