@@ -40,10 +40,13 @@
 
 namespace {
 
-constexpr int UM = 128, UBK = 32, UMAXBLK = 32, NSTAGE = 3, PD = 1, SROWS = 4;
-constexpr int EPI_WARPS = 8, UEPI = EPI_WARPS * 32, USTAGERS = 256, ISSUE_WARP = (UEPI + USTAGERS) / 32;
+constexpr int UM = 128, UBK = 32, UMAXBLK = 32, NSTAGE = 3, PD = 1;
+constexpr int EPI_WARPS = 8, UEPI = EPI_WARPS * 32, USTAGERS = 192, ISSUE_WARP = (UEPI + USTAGERS) / 32;
+constexpr int SG_THREADS = USTAGERS / 2, SG_ROWS = SG_THREADS / 4, SROWS = (UM + SG_ROWS - 1) / SG_ROWS;   // per staging group: threads,
+                                                           // rows per pass (4 threads = the 4 chunks of a row), passes
 constexpr int COPY_WARP = ISSUE_WARP + 1;
-constexpr int UTHREADS = UEPI + USTAGERS + 64;             // 8 epilogue warps | 8 staging warps | the MMA warp | the copy warp
+constexpr int UTHREADS = UEPI + USTAGERS + 64;             // 8 epilogue warps | 6 staging warps | the MMA warp | the copy warp:
+                                                           // 16 warps, so that a thread may use 128 registers (18 warps: 96)
 constexpr int LBO_A = UM * 16 + 16;                        // k-chunk stride of the activation operand (16 B of padding: the
                                                            // 8 chunks a quarter warp stores land in 8 different bank groups)
 constexpr int A_HALF_BYTES = (UBK / 8) * LBO_A;            // one of A_hi / A_lo
@@ -210,7 +213,7 @@ __global__ void __launch_bounds__(UTHREADS, 1) umma_layer_kernel(const __grid_co
         // rows r0 + 32 j): the lanes of a warp read whole 128-byte row segments.  What depends only on the tile (row pointers,
         // position inside the utterance) is computed once per tile; a 16-wide tail block keeps the mapping with the chunks
         // c >= 2 idle.
-        const int st_tid = tid - EPI_WARPS * 32, grp = st_tid >> 7, c = st_tid & 3, r0 = (st_tid & 127) >> 2;
+        const int st_tid = tid - EPI_WARPS * 32, grp = st_tid / SG_THREADS, c = st_tid & 3, r0 = (st_tid % SG_THREADS) >> 2;
         const int soff = c * LBO_A + r0 * 16;
         uint32_t gb0 = 0;                                        // global index of the tile's first block
         for (long long w = blockIdx.x; w < total; w += gridDim.x, gb0 += (uint32_t)nblk) {
@@ -219,8 +222,8 @@ __global__ void __launch_bounds__(UTHREADS, 1) umma_layer_kernel(const __grid_co
             int trow[SROWS];
 #pragma unroll
             for (int j = 0; j < SROWS; ++j) {
-                const long long n = n0 + r0 + 32 * j;
-                const bool ok = n < a.N;
+                const long long n = n0 + r0 + SG_ROWS * j;
+                const bool ok = n < a.N && r0 + SG_ROWS * j < UM;
                 trow[j] = ok ? (int)(n % a.T) : -1;               // -1: no such position (tail tile) -> zeros
                 srow[j] = a.src + (ok ? n : 0) * a.src_ld + 8 * c;
                 crow[j] = a.cond ? a.cond + (ok ? n : 0) * a.cond_ld + 8 * c : nullptr;
@@ -250,10 +253,11 @@ __global__ void __launch_bounds__(UTHREADS, 1) umma_layer_kernel(const __grid_co
                     unsigned char *Ah = usmem + (size_t)s * STAGE_BYTES + soff, *Al = Ah + A_HALF_BYTES;
 #pragma unroll
                     for (int j = 0; j < SROWS; ++j) {
+                        if (r0 + SG_ROWS * j >= UM) continue;
                         uint4 hi, lo;
                         umma::split8(pfx[2 * j], pfx[2 * j + 1], hi, lo);
-                        *reinterpret_cast<uint4 *>(Ah + j * 32 * 16) = hi;
-                        *reinterpret_cast<uint4 *>(Al + j * 32 * 16) = lo;
+                        *reinterpret_cast<uint4 *>(Ah + j * SG_ROWS * 16) = hi;
+                        *reinterpret_cast<uint4 *>(Al + j * SG_ROWS * 16) = lo;
                     }
                 }
                 umma::fence_proxy_async();
@@ -492,7 +496,7 @@ __global__ void __launch_bounds__(UTHREADS, 1) umma_fused_layer_kernel(const __g
     } else if (warp >= EPI_WARPS) {
         // ---- staging warps (two groups on alternate blocks); the out/skip blocks have nothing to stage, their turn only
         //      keeps the stage bookkeeping uniform -------------------------------------------------------------------------
-        const int st_tid = tid - EPI_WARPS * 32, grp = st_tid >> 7, c = st_tid & 3, r0 = (st_tid & 127) >> 2;
+        const int st_tid = tid - EPI_WARPS * 32, grp = st_tid / SG_THREADS, c = st_tid & 3, r0 = (st_tid % SG_THREADS) >> 2;
         const int soff = c * LBO_A + r0 * 16;
         uint32_t gb0 = 0;
         for (long long w = blockIdx.x; w < total; w += gridDim.x, gb0 += (uint32_t)nb) {
@@ -501,8 +505,8 @@ __global__ void __launch_bounds__(UTHREADS, 1) umma_fused_layer_kernel(const __g
             int trow[SROWS];
 #pragma unroll
             for (int j = 0; j < SROWS; ++j) {
-                const long long n = n0 + r0 + 32 * j;
-                const bool ok = n < a.N;
+                const long long n = n0 + r0 + SG_ROWS * j;
+                const bool ok = n < a.N && r0 + SG_ROWS * j < UM;
                 trow[j] = ok ? (int)(n % a.T) : -1;
                 srow[j] = a.x + (ok ? n : 0) * a.R + 8 * c;
                 crow[j] = a.cond + (ok ? n : 0) * a.cin + 8 * c;
@@ -530,10 +534,11 @@ __global__ void __launch_bounds__(UTHREADS, 1) umma_fused_layer_kernel(const __g
                     unsigned char *Ah = usmem + (size_t)s * STAGE_BYTES + soff, *Al = Ah + A_HALF_BYTES;
 #pragma unroll
                     for (int j = 0; j < SROWS; ++j) {
+                        if (r0 + SG_ROWS * j >= UM) continue;
                         uint4 hi, lo;
                         umma::split8(pf[2 * j], pf[2 * j + 1], hi, lo);
-                        *reinterpret_cast<uint4 *>(Ah + j * 32 * 16) = hi;
-                        *reinterpret_cast<uint4 *>(Al + j * 32 * 16) = lo;
+                        *reinterpret_cast<uint4 *>(Ah + j * SG_ROWS * 16) = hi;
+                        *reinterpret_cast<uint4 *>(Al + j * SG_ROWS * 16) = lo;
                     }
                 }
                 umma::fence_proxy_async();
