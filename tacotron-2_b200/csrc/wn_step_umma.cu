@@ -12,12 +12,12 @@
 // passes hi*hi + hi*lo + lo*hi into the same fp32 TMEM accumulator (the dropped lo*lo term is below 2^-16 relative).
 // Weights are split once on the host; activations are split while they are staged into shared memory.
 //
-// Persistent kernel, one CTA per SM (215 KB of shared memory, all 512 TMEM columns), 18 warps with fixed roles; a work
+// Persistent kernel, one CTA per SM (215 KB of shared memory, all 512 TMEM columns), 16 warps with fixed roles; a work
 // item is a tile of 128 positions (MMA M = 128, one TMEM lane per position) x 2*NT or R+S <= 256 columns (MMA N):
 //   * copy thread: the packed weights of a K block ([hi | lo] x [bk/8][N][8] bf16, exactly the shared-memory image, L2
 //     resident) go into one of 3 operand stages by bulk global->shared copies counted on the stage's "full" mbarrier, as
 //     soon as the MMAs that last read the stage have completed ("done");
-//   * 8 staging warps in two groups that take alternate K blocks (32 wide, 16 for the tail of the 80 conditioning
+//   * 6 staging warps in two groups that take alternate K blocks (32 wide, 16 for the tail of the 80 conditioning
 //     channels): gather the positions' activations (requested one block ahead into registers), split, store in the
 //     K-major core-matrix layout of wn_umma.cuh, fence.proxy.async, arrive on "ready";
 //   * MMA thread: waits for "ready" and "full", issues 3 x bk/16 tcgen05.mma into accumulator (tile & 1), tcgen05.commit
