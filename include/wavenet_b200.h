@@ -124,6 +124,18 @@ int wn_synthesize_host(wn_handle *h, const float *c, const int32_t *g_ids, int B
 int wn_step_full(wn_handle *h, const float *x, const float *c, const int32_t *g_ids, int B, int Tc, float *raw,
                  void *stream);
 
+/* The upsampling network without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments, kernels and bits as wn_upsample, but the intermediate layers live in a file-scope
+ * __device__ array of WN_STATIC_SCRATCH_FLOATS floats (16 MiB, held by every GPU that loads the library until exit)
+ * instead of scratch grown with cudaMalloc.  Limit: the input of the last layer, B * Tc * prod(upsample_scales[:-1]) *
+ * cin floats, must fit the array (half of it for networks of three or more layers); larger calls return
+ * WN_ERR_INVALID with a message.  All calls share the array and it keeps the last call's contents (nothing in it has
+ * to start at zero); calls that overlap on the GPU race on it.  The first call on a device looks the array's device
+ * address up (cudaGetSymbolAddress): make one call before starting a graph capture. */
+#define WN_STATIC_SCRATCH_FLOATS (4u * 1024u * 1024u)
+int wn_upsample_static(wn_handle *h, const float *c, int B, int Tc, float *c_up, void *stream);
+
 int wn_query(wn_handle *h, wn_info *info);
 const char *wn_last_error(wn_handle *h);   /* h may be NULL: error of the last failed wn_create on this thread */
 void wn_destroy(wn_handle *h);

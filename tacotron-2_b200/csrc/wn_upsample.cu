@@ -275,3 +275,105 @@ int wn_launch_upsample(wn_handle *h, const float *c, int B, int Tc, float *c_up,
     }
     return WN_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// wn_upsample_static: the upsampling network for callers that may not allocate (CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Same kernels, same arithmetic, same bits as wn_upsample; the only difference is where the intermediate
+// layers live: in a file-scope device array of fixed size instead of the handle's grown-on-demand scratch.
+//
+// * The array is WN_STATIC_SCRATCH_FLOATS floats (16 MiB); every GPU that loads the library holds it until exit.
+// * In host code the array's name is only a host-side stand-in, so the device address is looked up once per device
+//   with cudaGetSymbolAddress (with that device current) and cached; kernels only ever get that address.
+// * Every call shares the array and it keeps the previous call's contents.  Nothing has to start at zero: each layer
+//   overwrites every element the next layer reads.  Two calls that overlap on the GPU (different streams, or two
+//   handles on one device) race on it: serialise them.
+// * This function calls no cudaMalloc / cudaFree and no allocating library routine.
+static __device__ __align__(256) float g_up_static_scratch[WN_STATIC_SCRATCH_FLOATS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float *g_static_scratch_addr[kMaxDevices] = {};   // device address of g_up_static_scratch, per device, 0 = not looked up
+
+// One layer of the network, identical dispatch to the loop in wn_launch_upsample.
+cudaError_t launch_up_layer(const wn_handle *h, int i, const float *src, float *dst, int B, int W, cudaStream_t st) {
+    const wn_config &cfg = h->cfg;
+    const int C = cfg.cin_channels, kh = cfg.freq_axis_kernel_size, akind = cfg.upsample_activation;
+    const float alpha = cfg.leaky_alpha;
+    const int s = h->up[i].scale;
+    const bool vec = (C % 4 == 0) && (kh == 3);
+    if (cfg.upsample_type == WN_UP_SUBPIXEL && vec) {
+        const long long items = (long long)B * W * (C / 4);
+        const size_t smem = sizeof(float) * (size_t)(s * 9 + s);
+        up_subpixel_kernel<3><<<grid_for(items, 256, h->sm_count), 256, smem, st>>>(src, dst, h->up[i].w, h->up[i].b, B, W,
+                                                                                   C, s, akind, alpha);
+    } else if (cfg.upsample_type == WN_UP_2D && vec) {
+        const long long items = (long long)B * W * (C / 4);
+        const size_t smem = sizeof(float) * (size_t)(s * 3);
+        up_convt2d_kernel<3><<<grid_for(items, 256, h->sm_count), 256, smem, st>>>(src, dst, h->up[i].w, h->up[i].b, B, W,
+                                                                                  C, s, akind, alpha);
+    } else {
+        const long long total = (long long)B * W * s * C;
+        up_generic_kernel<<<grid_for(total, 256, h->sm_count), 256, 0, st>>>(src, dst, h->up[i].w, h->up[i].b, B, W, C, s,
+                                                                            kh, cfg.upsample_type, akind, alpha);
+    }
+    return cudaGetLastError();
+}
+}  // namespace
+
+extern "C" int wn_upsample_static(wn_handle *h, const float *c, int B, int Tc, float *c_up, void *stream) {
+    if (!h) return WN_ERR_INVALID;
+    if (!h->finalized) { h->err = "wn_upsample_static: model not finalized"; return WN_ERR_STATE; }
+    if (!c || !c_up || B <= 0 || Tc <= 0) { h->err = "wn_upsample_static: null buffer or non-positive size"; return WN_ERR_INVALID; }
+    const wn_config &cfg = h->cfg;
+    const int C = cfg.cin_channels;
+    if (C <= 0) { h->err = "wn_upsample_static: local conditioning is disabled (cin_channels <= 0)"; return WN_ERR_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    int dev = -1;
+    WN_CUDA_TRY(h, cudaGetDevice(&dev));
+    if (dev != h->device) {
+        h->err = "wn_upsample_static: the handle was created on device " + std::to_string(h->device) +
+                 " but device " + std::to_string(dev) + " is current";
+        return WN_ERR_INVALID;
+    }
+    if (dev < 0 || dev >= kMaxDevices) { h->err = "wn_upsample_static: device ordinal out of range"; return WN_ERR_INVALID; }
+    if (cfg.upsample_type == WN_UP_NEAREST) {   // one gather, no intermediate
+        const long long total = (long long)B * Tc * cfg.hop_size * C;
+        up_generic_kernel<<<grid_for(total, 256, h->sm_count), 256, 0, st>>>(c, c_up, nullptr, nullptr, B, Tc, C,
+                                                                            cfg.hop_size, 1, WN_UP_NEAREST, 0, 0.f);
+        h->launches++;
+        WN_CUDA_TRY(h, cudaGetLastError());
+        return WN_OK;
+    }
+    // size check: the largest intermediate (the input of the last layer); networks of three or more layers ping-pong
+    // between the two halves of the array
+    size_t max_mid = 0;
+    {
+        long long W = Tc;
+        for (int i = 0; i + 1 < h->n_up; ++i) { W *= h->up[i].scale; max_mid = (size_t)B * W * C; }
+    }
+    const size_t part = h->n_up > 2 ? WN_STATIC_SCRATCH_FLOATS / 2 : WN_STATIC_SCRATCH_FLOATS;
+    if (max_mid > part) {
+        h->err = "wn_upsample_static: the intermediate layer needs " + std::to_string(max_mid) +
+                 " floats but the static scratch holds " + std::to_string(part) + " per buffer (" +
+                 std::to_string(WN_STATIC_SCRATCH_FLOATS) + " floats = 16 MiB in total); use wn_upsample, or a smaller batch";
+        return WN_ERR_INVALID;
+    }
+    if (max_mid > 0 && !g_static_scratch_addr[dev]) {   // set-up, once per device, with that device current
+        float *p = nullptr;
+        WN_CUDA_TRY(h, cudaGetSymbolAddress((void **)&p, g_up_static_scratch));
+        if (!p) { h->err = "wn_upsample_static: cudaGetSymbolAddress returned a null address"; return WN_ERR_CUDA; }
+        g_static_scratch_addr[dev] = p;
+    }
+    float *scratch = g_static_scratch_addr[dev];
+    const float *src = c;
+    int W = Tc;
+    for (int i = 0; i < h->n_up; ++i) {
+        float *dst = (i == h->n_up - 1) ? c_up : scratch + ((i & 1) ? part : 0);
+        WN_CUDA_TRY(h, launch_up_layer(h, i, src, dst, B, W, st));
+        h->launches++;
+        src = dst;
+        W *= h->up[i].scale;
+    }
+    return WN_OK;
+}

@@ -22,7 +22,8 @@ ENGINES = {'auto': 0, 'generic': 1, 'pipeline': 2}
 ENGINE_NAMES = {v: k for k, v in ENGINES.items()}
 
 EXPORTS = ('wn_create', 'wn_load_weights', 'wn_finalize', 'wn_upsample', 'wn_synthesize', 'wn_synthesize_host',
-	'wn_step_full', 'wn_query', 'wn_last_error', 'wn_destroy')
+	'wn_step_full', 'wn_query', 'wn_last_error', 'wn_destroy', 'wn_upsample_static')
+STATIC_SCRATCH_FLOATS = 4 * 1024 * 1024   # WN_STATIC_SCRATCH_FLOATS of include/wavenet_b200.h
 
 
 class NativeLibraryError(RuntimeError):
@@ -78,6 +79,8 @@ def load_library(path=None):
 	lib.wn_finalize.argtypes = [vp]
 	lib.wn_upsample.restype = ip
 	lib.wn_upsample.argtypes = [vp, fp, ip, ip, fp, vp]
+	lib.wn_upsample_static.restype = ip
+	lib.wn_upsample_static.argtypes = [vp, fp, ip, ip, fp, vp]
 	lib.wn_synthesize.restype = ip
 	lib.wn_synthesize.argtypes = [vp, fp, fp, ip, ip, fp, fp, fp, fp, fp, vp]
 	lib.wn_synthesize_host.restype = ip
@@ -188,6 +191,10 @@ class NativeWaveNet(object):
 	# -- device-pointer calls (torch CUDA tensors or raw ints); asynchronous on `stream` ----------------
 	def upsample(self, c, B, Tc, c_up, stream=0):
 		self._check(self.lib.wn_upsample(self._h, _ptr(c), B, Tc, _ptr(c_up), C.c_void_p(stream)))
+
+	def upsample_static(self, c, B, Tc, c_up, stream=0):
+		"""wn_upsample without allocation (intermediates in the library's static device array; see the header)."""
+		self._check(self.lib.wn_upsample_static(self._h, _ptr(c), B, Tc, _ptr(c_up), C.c_void_p(stream)))
 
 	def synthesize(self, c, B, Tc, noise, audio, g_ids=None, teacher=None, raw=None, c_up=None, stream=0):
 		self._check(self.lib.wn_synthesize(self._h, _ptr(c), _ptr(g_ids), B, Tc, _ptr(noise), _ptr(teacher),
