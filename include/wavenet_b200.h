@@ -37,7 +37,7 @@ typedef enum { WN_INPUT_RAW = 0, WN_INPUT_MULAW = 1, WN_INPUT_MULAW_QUANTIZE = 2
 typedef enum { WN_UP_SUBPIXEL = 0, WN_UP_2D = 1, WN_UP_1D = 2, WN_UP_RESIZE = 3, WN_UP_NEAREST = 4 } wn_upsample_type;
 typedef enum { WN_ACT_NONE = 0, WN_ACT_RELU = 1, WN_ACT_LEAKY = 2 } wn_activation;
 typedef enum { WN_MEM_DEVICE = 0, WN_MEM_HOST = 1 } wn_mem_kind;
-typedef enum { WN_ENGINE_AUTO = 0, WN_ENGINE_GENERIC = 1, WN_ENGINE_PIPELINE = 2 } wn_engine;
+typedef enum { WN_ENGINE_AUTO = 0, WN_ENGINE_GENERIC = 1, WN_ENGINE_PIPELINE = 2, WN_ENGINE_TC = 3 } wn_engine;
 
 /* Mirrors the hparams keys the path reads (code/hparams.py:207-253). */
 typedef struct wn_config {

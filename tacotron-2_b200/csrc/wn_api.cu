@@ -312,6 +312,11 @@ extern "C" int wn_finalize(wn_handle *h) {
         else if (c.engine == WN_ENGINE_PIPELINE) return fail(h, WN_ERR_INVALID, "pipeline engine unavailable: " + h->err);
         else h->err.clear();
     }
+    if (c.engine == WN_ENGINE_TC) {   // the tensor-core loop engine; the fp32 engines stay planned as its fall-back (large batches, WaveNet.step)
+        int trc = wn_tc_plan(h);
+        if (trc) return fail(h, WN_ERR_INVALID, "tensor-core engine unavailable: " + h->err);
+        h->engine = WN_ENGINE_TC;
+    }
     h->finalized = true;
     return WN_OK;
 }
@@ -375,7 +380,8 @@ extern "C" int wn_synthesize(wn_handle *h, const float *c, const int32_t *g_ids,
     rc = prep_conditioning(h, c, g_ids, B, Tc, c_up_out, &c_up, &g_emb, st);
     if (rc) return rc;
     WN_CUDA_TRY(h, cudaEventRecord(h->ev[1], st));
-    if (h->engine == WN_ENGINE_PIPELINE) rc = wn_launch_loop_pipe(h, c_up, noise, teacher, 0, B, T, audio, raw, st);
+    if (h->engine == WN_ENGINE_TC && B <= wn_tc_max_batch(h)) rc = wn_launch_loop_tc(h, c_up, noise, teacher, 0, B, T, audio, raw, st);
+    else if (h->pipe) rc = wn_launch_loop_pipe(h, c_up, noise, teacher, 0, B, T, audio, raw, st);
     else rc = wn_launch_loop_generic(h, c_up, g_emb, noise, teacher, 0, B, T, audio, raw, st);
     if (rc) return rc;
     WN_CUDA_TRY(h, cudaEventRecord(h->ev[2], st));
@@ -437,7 +443,8 @@ extern "C" int wn_synthesize_host(wn_handle *h, const float *c, const int32_t *g
     WN_CUDA_TRY(h, cudaMemcpyAsync(audio, h->d_out_audio, sizeof(float) * n_a, cudaMemcpyDeviceToHost, st));
     if (raw) WN_CUDA_TRY(h, cudaMemcpyAsync(raw, h->d_out_raw, sizeof(float) * n_a * cfg.out_channels, cudaMemcpyDeviceToHost, st));
     WN_CUDA_TRY(h, cudaStreamSynchronize(st));
-    return wn_pipe_check_abort(h);
+    rc = wn_tc_check_abort(h);
+    return rc ? rc : wn_pipe_check_abort(h);
 }
 
 extern "C" int wn_query(wn_handle *h, wn_info *info) {
@@ -470,6 +477,7 @@ extern "C" int wn_query(wn_handle *h, wn_info *info) {
         cudaEventElapsedTime(&info->last_loop_ms, h->ev[1], h->ev[2]);
     }
     wn_pipe_fill_info(h, info);
+    wn_tc_fill_info(h, info);
     return WN_OK;
 }
 
@@ -478,6 +486,7 @@ extern "C" const char *wn_last_error(wn_handle *h) { return h ? h->err.c_str() :
 extern "C" void wn_destroy(wn_handle *h) {
     if (!h) return;
     wn_pipe_free(h);
+    wn_tc_free(h);
     wn_gemm_free(h);
     wn_umma_free(h);
     for (int i = 0; i < 3; ++i)

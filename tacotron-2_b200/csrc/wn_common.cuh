@@ -51,6 +51,7 @@ struct WnHostTensor {
 struct WnPipePlan;  // wn_loop_pipe.cu
 struct WnGemmPlan;  // wn_step_gemm.cu
 struct WnUmmaPlan;  // wn_step_umma.cu
+struct WnTcPlan;    // wn_loop_tc.cu
 
 struct wn_handle {
     wn_config cfg;
@@ -76,6 +77,7 @@ struct wn_handle {
     WnPipePlan *pipe = nullptr;
     WnGemmPlan *gemm = nullptr;
     WnUmmaPlan *umma = nullptr;
+    WnTcPlan *tc = nullptr;
     int engine = WN_ENGINE_GENERIC;
     int64_t launches = 0;
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};  // before upsample / before loop / after loop
@@ -106,6 +108,16 @@ void wn_pipe_fill_info(wn_handle *h, wn_info *info);
 int wn_pipe_check_abort(wn_handle *h);  // after a stream sync: WN_ERR_WATCHDOG if the persistent kernel bailed out
 int wn_launch_loop_pipe(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int inputs_mode,
                         int B, int T, float *audio, float *raw, cudaStream_t st);
+
+// tensor-core loop engine (wn_loop_tc.cu): tcgen05.mma with the step-critical weights resident in tensor memory
+bool wn_tc_supported(const wn_handle *h);
+int wn_tc_plan(wn_handle *h);
+void wn_tc_free(wn_handle *h);
+int wn_tc_max_batch(const wn_handle *h);
+void wn_tc_fill_info(wn_handle *h, wn_info *info);
+int wn_tc_check_abort(wn_handle *h);
+int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int inputs_mode, int B, int T,
+                      float *audio, float *raw, cudaStream_t st);
 
 // time-parallel WaveNet.step (wn_step_gemm.cu)
 bool wn_gemm_supported(const wn_handle *h);

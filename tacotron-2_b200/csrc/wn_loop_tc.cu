@@ -1,0 +1,1012 @@
+// wn_loop_tc.cu - the autoregressive loop of WaveNet.incremental (wavenet.py:805-911) on the sm_100a tensor cores.
+//
+// ONE cooperative launch runs all T steps.  The batch is cut into NR "replicas" of NB utterances (NB = 16 or 32 = the N of
+// every MMA); a replica is a chain of L + 1 CTAs, one per residual layer plus one head CTA, each alone on its SM:
+//
+//   layer CTA l  (ResidualConv1DGLU.incremental_step, modules.py:468-521)
+//     * the weights every step needs at once stay ON CHIP for the whole launch, as bf16 (hi, lo) pairs:
+//         current-tap rows of the dilated conv (256 x 128) and the residual 1x1 (128 x 128) in TENSOR MEMORY as the A operand
+//         of tcgen05.mma (lane = output channel, one 32-bit column = two consecutive k), the skip 1x1 in shared memory;
+//     * per step: x_l(t) arrives -> bf16 (hi, lo) image in shared memory (the B operand, K-major) -> 48 MMAs
+//       (M = 128, N = NB, K = 16; two gate halves x 8 k steps x three passes hi*hi + hi*lo + lo*hi) on top of the part of the
+//       pre-activation that does not depend on x_l(t) -> tcgen05.ld -> tanh * sigmoid -> z image -> 24 MMAs (residual
+//       1x1) -> x_{l+1}(t) = (out + b + x_l(t)) * sqrt(0.5) leaves for the next CTA; 24 more MMAs (skip 1x1) -> the skip
+//       contribution leaves for the head CTA;
+//     * between two steps (the CTA idles ~95 % of a step): the x-independent part of the NEXT step, W[tap0 | tap1 | cin]
+//       * [x_l(t+1-2d) ; x_l(t+1-d) ; c(t+1)], is accumulated straight into the gate accumulator in tensor memory; its
+//       weights (344 KB per layer) are streamed from L2 through two 16 KB shared-memory stages with cp.async.bulk.
+//   head CTA  (wavenet.py:828-878): running skip sum in the reference's order, relu, 1x1, relu, 1x1 (both on the tensor
+//     cores), the sampler (gaussian.py:39-52 / mixture.py:76-107) from the caller's noise buffer, audio / raw outputs,
+//     and the sample fed back to layer 0.
+//
+// Hand-offs between CTAs are {value, tag} words in L2 (tag = step + 1, double buffered on t & 1): no fence, no flag
+// separate from the data.  The dilation rings live in global memory (L2); every ring element is written and later read
+// by the same thread.
+//
+// Arithmetic: fp32 accumulation everywhere; products are bf16-split (16 mantissa bits per operand), so results agree
+// with the fp32 engines to ~1e-5 relative, not bit for bit (tests: tests/test_gpu_tc.py, criterion 1e-3 of BASELINE.json).
+#include <cuda_bf16.h>
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+#include "wn_common.cuh"
+#include "wn_umma.cuh"
+
+namespace {
+
+constexpr int CH = 128;                  // residual = gate / 2 = skip channels of the block this engine is built for
+constexpr int EPI_THREADS = 256;         // 8 epilogue warps: TMEM lane quarter = warp % 4, utterance half = warp / 4
+constexpr int MMA_WARP = 8, LOAD_WARP = 9;
+constexpr int TC_THREADS = 320;
+constexpr int KB_TOTAL = 11;             // 32-wide k blocks of the streamed weights: tap0 4, tap1 4, cin 3 (80 + 16 zero)
+constexpr int NCHUNK = 2 * KB_TOTAL;     // (k block, gate half), 16 KB each: A image [4][128][8] bf16 hi, then lo
+constexpr int CHUNK_BYTES = 16384;
+constexpr int CI_K = 96;                 // K of the conditioning image (cin <= 96, zero padded)
+constexpr unsigned long long WATCHDOG_NS = 20ull * 1000 * 1000 * 1000;
+
+// layer blob (bytes)
+constexpr int OFF_TMEM = 0;                       // 6 x [128 rows][64 words]: Wcur a hi, a lo, b hi, b lo, Wout hi, lo
+constexpr int OFF_WS = 6 * 32768;                 // skip 1x1, A image [16][128][8] hi, lo
+constexpr int OFF_STREAM = OFF_WS + 65536;        // NCHUNK chunks
+constexpr int OFF_BIAS = OFF_STREAM + NCHUNK * CHUNK_BYTES;   // gate a, gate b, out, skip: 4 x 128 floats
+constexpr int LAYER_BLOB_BYTES = OFF_BIAS + 4 * CH * 4;
+// head blob: 4 x [128][64] words (W1 hi, lo, W2 hi, lo; W2 rows >= O zero), then b1[128], b2[128]
+constexpr int HEAD_BLOB_BYTES = 4 * 32768 + 2 * CH * 4;
+
+// tensor memory columns of a layer CTA
+constexpr int COL_WCUR = 0, COL_WOUT = 256, COL_ACC = 384;   // accumulators: gate a | gate b | out | skip, NB columns each
+// head CTA
+constexpr int COL_W1 = 0, COL_W2 = 128, COL_HACC = 256;      // h1 | out
+
+struct TcParams {
+    int L, O, cin, NZ, input_type, legacy, residual_legacy;
+    float log_scale_min, log_scale_min_gauss;
+    int dil[WN_MAX_LAYERS];
+    long long ring_off[WN_MAX_LAYERS];   // first ring slot of layer l inside a replica's ring block
+    long long ring_slots;                // slots per replica
+    const unsigned char *layer_blobs, *head_blob;
+    const float *first_wb;               // input 1x1: w[128], b[128]
+    unsigned long long *mail_x, *mail_skip, *mail_in;
+    float *ring;
+    int *abort_flag;
+    long long *stats;
+    const float *c_up, *noise, *teacher;
+    int inputs_mode;
+    float *audio, *raw;
+    int B, T, NR;
+};
+
+template <int NB>
+struct Geo {
+    static constexpr int NH = NB / 2;            // utterances per epilogue thread
+    static constexpr int NU = NH / 2;            // 16-byte units of two {value, tag} words
+    static constexpr int NQ = NH / 4;            // 16-byte units of four floats (ring)
+    static constexpr int LBO = NB * 16 + 16;     // k-chunk stride of the activation images (16 B of padding: conflict-free stores)
+    static constexpr int PLANE = 16 * LBO;       // 128 channels
+    static constexpr int IMG = 2 * PLANE;        // hi, lo
+    static constexpr int CI_PLANE = (CI_K / 8) * LBO;
+    // shared memory of a layer CTA
+    static constexpr int S_WS = 0, S_WST = 65536, S_XI = S_WST + 2 * CHUNK_BYTES, S_ZI = S_XI + 2 * IMG, S_TAP = S_ZI + IMG,
+                         S_CI = S_TAP + 2 * IMG, S_END = S_CI + 2 * CI_PLANE;
+    // head CTA
+    static constexpr int S_HI = 0, S_H2 = IMG, S_PRM = 2 * IMG, S_HEND = S_PRM + NB * CH * 4;
+    static constexpr int SMEM = S_END > S_HEND ? S_END : S_HEND;
+    static constexpr int MAILW = CH * NB;        // words of one mailbox buffer (and floats of one ring slot)
+};
+
+// ---- {value, tag} words -----------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long pack_ll(float v, unsigned tag) {
+    return ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v);
+}
+__device__ __forceinline__ void st_ll2(unsigned long long *p, float v0, float v1, unsigned tag) {
+    const unsigned long long a = pack_ll(v0, tag), b = pack_ll(v1, tag);
+    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
+}
+__device__ __forceinline__ void st_ll1(unsigned long long *p, float v, unsigned tag) {
+    const unsigned long long a = pack_ll(v, tag);
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(a) : "memory");
+}
+__device__ __forceinline__ void ld_ll2(const unsigned long long *p, unsigned long long &a, unsigned long long &b) {
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// shared watchdog of every wait in this kernel: a waiter that sees the abort flag, or that has waited WATCHDOG_NS of wall
+// clock, gives up (and tells everybody else); the launch then ends with wrong output and WN_ERR_WATCHDOG instead of a hang
+struct Watch {
+    int *flag;
+    unsigned spins = 0;
+    unsigned long long t0 = 0;
+    __device__ __forceinline__ bool expired() {
+        if ((++spins & 0x3ffu) != 0) return false;
+        if (*(volatile int *)flag) return true;
+        const unsigned long long now = global_timer_ns();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > WATCHDOG_NS) { atomicExch(flag, 1); return true; }
+        return false;
+    }
+};
+// NU units of two words, `stride` words apart; returns true if the watchdog fired
+template <int NU>
+__device__ __forceinline__ bool poll_units(const unsigned long long *p, long long stride, unsigned tag, float *v, int *abort_flag) {
+    Watch wd{abort_flag};
+    for (;;) {
+        unsigned long long w[2 * NU];
+#pragma unroll
+        for (int u = 0; u < NU; ++u) ld_ll2(p + u * stride, w[2 * u], w[2 * u + 1]);
+        bool ok = true;
+#pragma unroll
+        for (int i = 0; i < 2 * NU; ++i) ok = ok && ((unsigned)(w[i] >> 32) == tag);
+        if (ok) {
+#pragma unroll
+            for (int i = 0; i < 2 * NU; ++i) v[i] = __uint_as_float((unsigned)(w[i] & 0xffffffffu));
+            return false;
+        }
+        if (wd.expired()) return true;
+    }
+}
+__device__ __forceinline__ bool mbar_wait_wd(uint32_t bar, uint32_t parity, int *abort_flag) {
+    Watch wd{abort_flag};
+    while (!umma::mbar_try(bar, parity))
+        if (wd.expired()) return true;
+    return false;
+}
+
+// ---- activation images: [K/8][NB][8] bf16, hi plane then lo plane; one thread per channel writes 2-byte elements ---------
+__device__ __forceinline__ void img_put(unsigned char *img, int plane, int lbo, int j, int n, float v) {
+    const uint32_t h = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(v));
+    const float r = __fsub_rn(v, __uint_as_float(h << 16));
+    const uint32_t l = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(r));
+    const int off = (j >> 3) * lbo + n * 16 + (j & 7) * 2;
+    *reinterpret_cast<unsigned short *>(img + off) = (unsigned short)h;
+    *reinterpret_cast<unsigned short *>(img + plane + off) = (unsigned short)l;
+}
+
+// tanh(t) * sigmoid(s) (modules.py:510) with ex2.approx / rcp.approx; same form as wn_step_umma.cu
+__device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float gate_fast(float t, float s) {
+    constexpr float LOG2E = 1.4426950408889634f;
+    const float sg = rcp_approx(__fadd_rn(1.0f, ex2_approx(__fmul_rn(-LOG2E, s))));
+    const float at = fabsf(t);
+    float th = __fmaf_rn(-2.0f, rcp_approx(__fadd_rn(ex2_approx(__fmul_rn(2.0f * LOG2E, at)), 1.0f)), 1.0f);
+    const float z = __fmul_rn(t, t);
+    float p = -5.70498872745e-3f;
+    p = __fmaf_rn(p, z, 2.06390887954e-2f);
+    p = __fmaf_rn(p, z, -5.37397155531e-2f);
+    p = __fmaf_rn(p, z, 1.33314422036e-1f);
+    p = __fmaf_rn(p, z, -3.33332819422e-1f);
+    th = copysignf(th, t);
+    if (at < 0.625f) th = __fmaf_rn(__fmul_rn(p, z), t, t);
+    return __fmul_rn(th, sg);
+}
+
+__device__ __forceinline__ float tc_sample_gaussian(const TcParams &P, const float *out, float eps) {   // gaussian.py:39-52
+    const float mean = out[0];
+    const float ls = out[1] > P.log_scale_min_gauss ? out[1] : P.log_scale_min_gauss;
+    float x = __fadd_rn(mean, __fmul_rn(wn_expf(ls), eps));
+    x = x > -1.0f ? x : -1.0f;
+    return x < 1.0f ? x : 1.0f;
+}
+__device__ float tc_sample_mol(const TcParams &P, const float *out, const float *u) {   // mixture.py:76-107
+    const int K = P.O / 3;
+    int best = 0;
+    float bestv = 0.0f;
+    for (int k = 0; k < K; ++k) {
+        const float v = __fsub_rn(out[k], wn_logf(-wn_logf(u[k])));
+        if (k == 0 || v > bestv) { bestv = v; best = k; }
+    }
+    const float mean = out[K + best], lsr = out[2 * K + best];
+    const float ls = lsr > P.log_scale_min ? lsr : P.log_scale_min;
+    const float u2 = u[K];
+    const float lg = __fsub_rn(wn_logf(u2), wn_logf(__fsub_rn(1.0f, u2)));
+    float x = __fadd_rn(mean, __fmul_rn(wn_expf(ls), lg));
+    x = x > -1.0f ? x : -1.0f;
+    return x < 1.0f ? x : 1.0f;
+}
+
+// mbarriers of a CTA
+struct Bars {
+    unsigned long long x[4], z[4], gate, out, skip, p, wfull[2], wempty[2];
+};
+
+// =========================================================================================================================
+// layer CTA
+// =========================================================================================================================
+template <int NB, bool STATS>
+__device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsigned char *smem, const uint32_t tmem, Bars &bars) {
+    using G = Geo<NB>;
+    constexpr int NH = G::NH, NU = G::NU, NQ = G::NQ, LBO = G::LBO, PLANE = G::PLANE;
+    const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, q = w & 3, hh = w >> 2;
+    const int j = 32 * q + lane, n0 = hh * NH;
+    const uint32_t lane_addr = tmem + ((uint32_t)(32 * q) << 16);
+    const int L = P.L, T = P.T, cin = P.cin;
+    const unsigned char *blob = P.layer_blobs + (long long)l * LAYER_BLOB_BYTES;
+    const float *bias = reinterpret_cast<const float *>(blob + OFF_BIAS);
+    const float ba = __ldg(bias + j), bb = __ldg(bias + CH + j), bo = __ldg(bias + 2 * CH + j), bs = __ldg(bias + 3 * CH + j);
+    const float wf = l == 0 ? __ldg(P.first_wb + j) : 0.0f, bf = l == 0 ? __ldg(P.first_wb + CH + j) : 0.0f;
+    const float cres = P.residual_legacy ? 0.70710677f : 1.0f;   // np.sqrt(0.5) as float32 (modules.py:517-520)
+    const int d = P.dil[l], qmask = 2 * d - 1;
+    const long long unit0 = ((long long)(hh * NU) * CH + j) * 2;      // word offset of this thread's first unit inside a mailbox buffer
+    const unsigned long long *mx_in = P.mail_x + (long long)(r * L + l) * 2 * G::MAILW + unit0;
+    unsigned long long *mx_out = P.mail_x + (long long)(r * L + l + 1) * 2 * G::MAILW + unit0;
+    unsigned long long *ms_out = P.mail_skip + (long long)(r * L + l) * 2 * G::MAILW + unit0;
+    const unsigned long long *min_in = P.mail_in + (long long)r * 2 * NB + n0;
+    float *ring = P.ring + ((long long)r * P.ring_slots + P.ring_off[l]) * G::MAILW + ((long long)(hh * NQ) * CH + j) * 4;
+    unsigned char *XI = smem + G::S_XI, *ZI = smem + G::S_ZI, *TAP = smem + G::S_TAP, *CI = smem + G::S_CI;
+    const uint32_t bx = umma::smem_addr(&bars.x[q]), bz = umma::smem_addr(&bars.z[q]), bp = umma::smem_addr(&bars.p),
+                   bgate = umma::smem_addr(&bars.gate), bout = umma::smem_addr(&bars.out), bskip = umma::smem_addr(&bars.skip);
+    constexpr int CN = (CI_K * NB + EPI_THREADS - 1) / EPI_THREADS;   // conditioning elements per thread (upper bound)
+    long long st_c[6] = {0, 0, 0, 0, 0, 0};
+    const bool do_stats = STATS && P.stats != nullptr && tid == 0;
+
+    // operands of the x-independent part of step t: the two older taps from the ring and the conditioning column c(t)
+    float tp0[NH], tp1[NH], cnd[CN];
+    auto prep_load = [&](int t) {
+        const int t0 = t - 2 * d, t1 = t - d;
+#pragma unroll
+        for (int u = 0; u < NQ; ++u) {
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+            if (t0 >= 0) a = *reinterpret_cast<const float4 *>(ring + (long long)(t0 & qmask) * G::MAILW + (long long)u * CH * 4);
+            if (t1 >= 0) b = *reinterpret_cast<const float4 *>(ring + (long long)(t1 & qmask) * G::MAILW + (long long)u * CH * 4);
+            tp0[4 * u] = a.x; tp0[4 * u + 1] = a.y; tp0[4 * u + 2] = a.z; tp0[4 * u + 3] = a.w;
+            tp1[4 * u] = b.x; tp1[4 * u + 1] = b.y; tp1[4 * u + 2] = b.z; tp1[4 * u + 3] = b.w;
+        }
+#pragma unroll
+        for (int i = 0; i < CN; ++i) {
+            const int e = tid + i * EPI_THREADS;
+            const int n = e / cin, k = e - n * cin;
+            const long long b = (long long)r * NB + n;
+            cnd[i] = (n < NB && b < P.B) ? __ldg(P.c_up + (b * T + t) * cin + k) : 0.0f;
+        }
+    };
+    auto prep_store = [&]() {
+#pragma unroll
+        for (int i = 0; i < NH; ++i) {
+            img_put(TAP, PLANE, LBO, j, n0 + i, tp0[i]);
+            img_put(TAP + G::IMG, PLANE, LBO, j, n0 + i, tp1[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < CN; ++i) {
+            const int e = tid + i * EPI_THREADS;
+            const int n = e / cin, k = e - n * cin;
+            if (n < NB) img_put(CI, G::CI_PLANE, LBO, k, n, cnd[i]);
+        }
+        umma::fence_proxy_async();
+        umma::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) umma::mbar_arrive(bp);
+    };
+    prep_load(0);
+    prep_store();
+
+    const long long st_begin = clock64();
+    for (int t = 0; t < T; ++t) {
+        const int par = t & 1;
+        const unsigned tag = (unsigned)t + 1u;
+        const long long c0 = do_stats ? clock64() : 0;
+        // ---- x_l(t) arrives (layer 0: the fed-back sample through the input 1x1, wavenet.py:826) ---------------------------
+        float xin[NH];
+        if (l == 0) {
+            float s[NH];
+            if (poll_units<NU>(min_in + par * NB, 2, tag, s, P.abort_flag)) return;
+#pragma unroll
+            for (int i = 0; i < NH; ++i) xin[i] = __fmaf_rn(s[i], wf, bf);
+        } else {
+            if (poll_units<NU>(mx_in + (long long)par * G::MAILW, (long long)CH * 2, tag, xin, P.abort_flag)) return;
+        }
+        const long long c1 = do_stats ? clock64() : 0;
+        unsigned char *xi = XI + par * G::IMG;
+#pragma unroll
+        for (int i = 0; i < NH; ++i) img_put(xi, PLANE, LBO, j, n0 + i, xin[i]);
+        umma::fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) umma::mbar_arrive(bx);
+#pragma unroll
+        for (int u = 0; u < NQ; ++u)
+            *reinterpret_cast<float4 *>(ring + (long long)(t & qmask) * G::MAILW + (long long)u * CH * 4) =
+                make_float4(xin[4 * u], xin[4 * u + 1], xin[4 * u + 2], xin[4 * u + 3]);
+        if (t + 1 < T) prep_load(t + 1);   // in flight while the gate MMAs run
+        // ---- gate (modules.py:494-510) ----------------------------------------------------------------------------------------
+        if (mbar_wait_wd(bgate, par, P.abort_flag)) return;
+        umma::fence_after_sync();
+        const long long c2 = do_stats ? clock64() : 0;
+        {
+            float a[NH], b[NH];
+            if constexpr (NH == 8) {
+                umma::tmem_ld8(lane_addr + COL_ACC + n0, reinterpret_cast<float(&)[8]>(a));
+                umma::tmem_ld8(lane_addr + COL_ACC + NB + n0, reinterpret_cast<float(&)[8]>(b));
+            } else {
+                umma::tmem_ld16(lane_addr + COL_ACC + n0, reinterpret_cast<float(&)[16]>(a));
+                umma::tmem_ld16(lane_addr + COL_ACC + NB + n0, reinterpret_cast<float(&)[16]>(b));
+            }
+            umma::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < NH; ++i) img_put(ZI, PLANE, LBO, j, n0 + i, gate_fast(__fadd_rn(a[i], ba), __fadd_rn(b[i], bb)));
+        }
+        umma::fence_proxy_async();
+        umma::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) umma::mbar_arrive(bz);
+        const long long c3 = do_stats ? clock64() : 0;
+        if (t + 1 < T) prep_store();
+        // ---- residual 1x1 -> x_{l+1}(t) (modules.py:515-520) ----------------------------------------------------------------
+        if (mbar_wait_wd(bout, par, P.abort_flag)) return;
+        umma::fence_after_sync();
+        const long long c4 = do_stats ? clock64() : 0;
+        {
+            float o[NH];
+            if constexpr (NH == 8) umma::tmem_ld8(lane_addr + COL_ACC + 2 * NB + n0, reinterpret_cast<float(&)[8]>(o));
+            else umma::tmem_ld16(lane_addr + COL_ACC + 2 * NB + n0, reinterpret_cast<float(&)[16]>(o));
+            umma::tmem_ld_wait();
+            if (l + 1 < L) {
+#pragma unroll
+                for (int u = 0; u < NU; ++u) {
+                    const float v0 = __fmul_rn(__fadd_rn(__fadd_rn(o[2 * u], bo), xin[2 * u]), cres);
+                    const float v1 = __fmul_rn(__fadd_rn(__fadd_rn(o[2 * u + 1], bo), xin[2 * u + 1]), cres);
+                    st_ll2(mx_out + (long long)par * G::MAILW + (long long)u * CH * 2, v0, v1, tag);
+                }
+            }
+        }
+        // ---- skip 1x1 -> head (modules.py:512) ------------------------------------------------------------------------------
+        if (mbar_wait_wd(bskip, par, P.abort_flag)) return;
+        umma::fence_after_sync();
+        {
+            float s[NH];
+            if constexpr (NH == 8) umma::tmem_ld8(lane_addr + COL_ACC + 3 * NB + n0, reinterpret_cast<float(&)[8]>(s));
+            else umma::tmem_ld16(lane_addr + COL_ACC + 3 * NB + n0, reinterpret_cast<float(&)[16]>(s));
+            umma::tmem_ld_wait();
+#pragma unroll
+            for (int u = 0; u < NU; ++u)
+                st_ll2(ms_out + (long long)par * G::MAILW + (long long)u * CH * 2, __fadd_rn(s[2 * u], bs), __fadd_rn(s[2 * u + 1], bs), tag);
+        }
+        umma::fence_before_sync();
+        if (do_stats) {
+            const long long c5 = clock64();
+            st_c[0] += c1 - c0; st_c[1] += c2 - c1; st_c[2] += c3 - c2; st_c[3] += c4 - c3; st_c[4] += c5 - c4;
+        }
+    }
+    if (do_stats) {
+        long long *o = P.stats + (long long)blockIdx.x * 16;
+        for (int i = 0; i < 5; ++i) o[i] = st_c[i];
+        o[14] = clock64() - st_begin; o[15] = T;
+    }
+}
+
+template <int NB>
+__device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t tmem, Bars &bars) {
+    using G = Geo<NB>;
+    constexpr int LBO = G::LBO, PLANE = G::PLANE;
+    constexpr uint32_t idesc = umma::idesc_bf16(CH, NB);
+    const int T = P.T;
+    const uint32_t s0 = umma::smem_addr(smem);
+    const uint32_t D_A = tmem + COL_ACC, D_B = tmem + COL_ACC + NB, D_O = tmem + COL_ACC + 2 * NB, D_S = tmem + COL_ACC + 3 * NB;
+    const uint64_t zi_hi = umma::smem_desc(s0 + G::S_ZI, LBO, 128), zi_lo = umma::smem_desc(s0 + G::S_ZI + PLANE, LBO, 128);
+    const uint64_t ws_hi = umma::smem_desc(s0 + G::S_WS, CH * 16, 128), ws_lo = umma::smem_desc(s0 + G::S_WS + 32768, CH * 16, 128);
+    const uint64_t st_hi[2] = {umma::smem_desc(s0 + G::S_WST, CH * 16, 128), umma::smem_desc(s0 + G::S_WST + CHUNK_BYTES, CH * 16, 128)};
+    const uint64_t st_lo[2] = {umma::smem_desc(s0 + G::S_WST + 8192, CH * 16, 128), umma::smem_desc(s0 + G::S_WST + CHUNK_BYTES + 8192, CH * 16, 128)};
+    const uint64_t tap_hi[3] = {umma::smem_desc(s0 + G::S_TAP, LBO, 128), umma::smem_desc(s0 + G::S_TAP + G::IMG, LBO, 128),
+                                umma::smem_desc(s0 + G::S_CI, LBO, 128)};
+    const uint64_t tap_lo[3] = {umma::smem_desc(s0 + G::S_TAP + PLANE, LBO, 128), umma::smem_desc(s0 + G::S_TAP + G::IMG + PLANE, LBO, 128),
+                                umma::smem_desc(s0 + G::S_CI + G::CI_PLANE, LBO, 128)};
+    constexpr uint64_t KS_B = (uint64_t)((2 * LBO) >> 4);        // descriptor step per k step (16 k) of an activation image
+    constexpr uint64_t KS_A = (uint64_t)((2 * CH * 16) >> 4);    // ... of a 128-row weight image
+    const uint32_t bgate = umma::smem_addr(&bars.gate), bout = umma::smem_addr(&bars.out), bskip = umma::smem_addr(&bars.skip),
+                   bp = umma::smem_addr(&bars.p);
+
+    // the x-independent part of step tp, accumulated from scratch into the gate accumulators
+    auto p_phase = [&](int tp) -> bool {
+        if (mbar_wait_wd(bp, tp & 1, P.abort_flag)) return true;
+        umma::fence_after_sync();
+#pragma unroll
+        for (int kb = 0; kb < KB_TOTAL; ++kb) {
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const uint32_t use = (uint32_t)(KB_TOTAL * tp + kb);
+                if (mbar_wait_wd(umma::smem_addr(&bars.wfull[half]), use & 1, P.abort_flag)) return true;
+                umma::fence_after_sync();
+                if (umma::elect_one()) {
+                    const int src = kb / 4, kin = (kb % 4) * 2;   // image (tap0, tap1, cin) and first k step inside it
+#pragma unroll
+                    for (int kk = 0; kk < 2; ++kk) {
+                        const uint64_t ah = st_hi[half] + kk * KS_A, al = st_lo[half] + kk * KS_A;
+                        const uint64_t bh = tap_hi[src] + (kin + kk) * KS_B, bl = tap_lo[src] + (kin + kk) * KS_B;
+                        const uint32_t dd = half ? D_B : D_A;
+                        umma::mma_bf16(dd, ah, bh, idesc, (kb | kk) != 0);
+                        umma::mma_bf16(dd, ah, bl, idesc, 1);
+                        umma::mma_bf16(dd, al, bh, idesc, 1);
+                    }
+                    umma::mma_commit(umma::smem_addr(&bars.wempty[half]));
+                }
+                __syncwarp();
+            }
+        }
+        return false;
+    };
+    if (p_phase(0)) return;
+    for (int t = 0; t < T; ++t) {
+        const int par = t & 1;
+        const uint64_t xi_hi = umma::smem_desc(s0 + G::S_XI + par * G::IMG, LBO, 128),
+                       xi_lo = umma::smem_desc(s0 + G::S_XI + par * G::IMG + PLANE, LBO, 128);
+        // current tap of the dilated conv (modules.py:294-297), K slice by K slice as the epilogue warps deliver the image
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            if (mbar_wait_wd(umma::smem_addr(&bars.x[s]), par, P.abort_flag)) return;
+            umma::fence_after_sync();
+            if (umma::elect_one()) {
+#pragma unroll
+                for (int kk = 0; kk < 2; ++kk) {
+                    const int ks = 2 * s + kk;
+                    const uint64_t bh = xi_hi + ks * KS_B, bl = xi_lo + ks * KS_B;
+                    umma::mma_bf16_ts(D_A, tmem + COL_WCUR + ks * 8, bh, idesc, 1);
+                    umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 128 + ks * 8, bh, idesc, 1);
+                    umma::mma_bf16_ts(D_A, tmem + COL_WCUR + ks * 8, bl, idesc, 1);
+                    umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 128 + ks * 8, bl, idesc, 1);
+                    umma::mma_bf16_ts(D_A, tmem + COL_WCUR + 64 + ks * 8, bh, idesc, 1);
+                    umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 192 + ks * 8, bh, idesc, 1);
+                }
+                if (s == 3) umma::mma_commit(bgate);
+            }
+            __syncwarp();
+        }
+        // residual 1x1 on z (modules.py:515)
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            if (mbar_wait_wd(umma::smem_addr(&bars.z[s]), par, P.abort_flag)) return;
+            umma::fence_after_sync();
+            if (umma::elect_one()) {
+#pragma unroll
+                for (int kk = 0; kk < 2; ++kk) {
+                    const int ks = 2 * s + kk;
+                    umma::mma_bf16_ts(D_O, tmem + COL_WOUT + ks * 8, zi_hi + ks * KS_B, idesc, ks != 0);
+                    umma::mma_bf16_ts(D_O, tmem + COL_WOUT + ks * 8, zi_lo + ks * KS_B, idesc, 1);
+                    umma::mma_bf16_ts(D_O, tmem + COL_WOUT + 64 + ks * 8, zi_hi + ks * KS_B, idesc, 1);
+                }
+                if (s == 3) umma::mma_commit(bout);
+            }
+            __syncwarp();
+        }
+        // skip 1x1 on z (modules.py:512), weights in shared memory
+        if (umma::elect_one()) {
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks) {
+                umma::mma_bf16(D_S, ws_hi + ks * KS_A, zi_hi + ks * KS_B, idesc, ks != 0);
+                umma::mma_bf16(D_S, ws_hi + ks * KS_A, zi_lo + ks * KS_B, idesc, 1);
+                umma::mma_bf16(D_S, ws_lo + ks * KS_A, zi_hi + ks * KS_B, idesc, 1);
+            }
+            umma::mma_commit(bskip);
+        }
+        __syncwarp();
+        if (t + 1 < T && p_phase(t + 1)) return;
+    }
+}
+
+// streams the [tap0 | tap1 | cin] weights of the layer, NCHUNK chunks per step, through the two stages
+__device__ void layer_loader(const TcParams &P, const int l, unsigned char *smem, Bars &bars, int wst_off) {
+    if ((threadIdx.x & 31) != 0) return;
+    const unsigned char *stream = P.layer_blobs + (long long)l * LAYER_BLOB_BYTES + OFF_STREAM;
+    const uint32_t dst0 = umma::smem_addr(smem + wst_off);
+    for (int tp = 0; tp < P.T; ++tp)
+        for (int kb = 0; kb < KB_TOTAL; ++kb)
+            for (int half = 0; half < 2; ++half) {
+                const uint32_t use = (uint32_t)(KB_TOTAL * tp + kb);
+                if (mbar_wait_wd(umma::smem_addr(&bars.wempty[half]), (use & 1) ^ 1, P.abort_flag)) return;
+                const uint32_t full = umma::smem_addr(&bars.wfull[half]);
+                umma::mbar_expect_tx(full, CHUNK_BYTES);
+                umma::bulk_g2s(dst0 + half * CHUNK_BYTES, stream + (size_t)(kb * 2 + half) * CHUNK_BYTES, CHUNK_BYTES, full);
+            }
+}
+
+// =========================================================================================================================
+// head CTA
+// =========================================================================================================================
+template <int NB, bool STATS>
+__device__ void head_epilogue(const TcParams &P, const int r, unsigned char *smem, const uint32_t tmem, Bars &bars) {
+    using G = Geo<NB>;
+    constexpr int NH = G::NH, NU = G::NU, LBO = G::LBO, PLANE = G::PLANE;
+    const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, q = w & 3, hh = w >> 2;
+    const int j = 32 * q + lane, n0 = hh * NH;
+    const uint32_t lane_addr = tmem + ((uint32_t)(32 * q) << 16);
+    const int L = P.L, T = P.T, O = P.O;
+    const float *hb = reinterpret_cast<const float *>(P.head_blob + 4 * 32768);
+    const float b1 = __ldg(hb + j), b2 = __ldg(hb + CH + j);
+    const float cskip = 0.70710677f;
+    const long long unit0 = ((long long)(hh * NU) * CH + j) * 2;
+    const unsigned long long *ms_in = P.mail_skip + (long long)r * L * 2 * G::MAILW + unit0;
+    unsigned long long *min_out = P.mail_in + (long long)r * 2 * NB;
+    unsigned char *HI = smem + G::S_HI, *H2 = smem + G::S_H2;
+    float *prm = reinterpret_cast<float *>(smem + G::S_PRM);   // [NB][CH]
+    const uint32_t bh = umma::smem_addr(&bars.x[q]), bh2 = umma::smem_addr(&bars.z[q]), bh1 = umma::smem_addr(&bars.gate),
+                   bo = umma::smem_addr(&bars.out), bprm = umma::smem_addr(&bars.skip);
+    const long long bu = (long long)r * NB + tid;          // utterance of the sampler thread
+    const bool sampler = tid < NB && bu < P.B;
+    // initial input (wavenet.py:433-445): raw 0.0, mulaw mulaw(0) = 0.0; WaveNet.step semantics: the first input is x[0]
+    if (tid < NB) st_ll1(min_out + tid, (sampler && P.inputs_mode) ? P.teacher[bu * T] : 0.0f, 1u);
+    long long st_c[4] = {0, 0, 0, 0};
+    const bool do_stats = STATS && P.stats != nullptr && tid == 0;
+    const long long st_begin = clock64();
+    for (int t = 0; t < T; ++t) {
+        const int par = t & 1;
+        const unsigned tag = (unsigned)t + 1u;
+        const long long c0 = do_stats ? clock64() : 0;
+        float nz0 = 0.0f, tch = 0.0f;
+        if (sampler) {
+            if (O == 2 && P.noise) nz0 = __ldg(P.noise + ((long long)t * P.B + bu) * P.NZ);
+            if (P.teacher) tch = P.inputs_mode ? (t + 1 < T ? __ldg(P.teacher + bu * T + t + 1) : 0.0f) : __ldg(P.teacher + bu * T + t);
+        }
+        // running skip sum in the reference's order (wavenet.py:833-836)
+        float S[NH];
+        for (int l = 0; l < L; ++l) {
+            float s[NH];
+            if (poll_units<NU>(ms_in + ((long long)l * 2 + par) * G::MAILW, (long long)CH * 2, tag, s, P.abort_flag)) return;
+#pragma unroll
+            for (int i = 0; i < NH; ++i) {
+                if (l == 0) S[i] = s[i];
+                else S[i] = P.legacy ? __fmul_rn(__fadd_rn(S[i], s[i]), cskip) : __fadd_rn(S[i], s[i]);
+            }
+        }
+        const long long c1 = do_stats ? clock64() : 0;
+#pragma unroll
+        for (int i = 0; i < NH; ++i) img_put(HI, PLANE, LBO, j, n0 + i, S[i] > 0.0f ? S[i] : 0.0f);   // relu (wavenet.py:840)
+        umma::fence_proxy_async();
+        umma::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) umma::mbar_arrive(bh);
+        if (mbar_wait_wd(bh1, par, P.abort_flag)) return;
+        umma::fence_after_sync();
+        {
+            float h[NH];
+            if constexpr (NH == 8) umma::tmem_ld8(lane_addr + COL_HACC + n0, reinterpret_cast<float(&)[8]>(h));
+            else umma::tmem_ld16(lane_addr + COL_HACC + n0, reinterpret_cast<float(&)[16]>(h));
+            umma::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < NH; ++i) {
+                const float y = __fadd_rn(h[i], b1);
+                img_put(H2, PLANE, LBO, j, n0 + i, y > 0.0f ? y : 0.0f);
+            }
+        }
+        umma::fence_proxy_async();
+        umma::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) umma::mbar_arrive(bh2);
+        if (mbar_wait_wd(bo, par, P.abort_flag)) return;
+        umma::fence_after_sync();
+        const long long c2 = do_stats ? clock64() : 0;
+        {
+            float o[NH];
+            if constexpr (NH == 8) umma::tmem_ld8(lane_addr + COL_HACC + NB + n0, reinterpret_cast<float(&)[8]>(o));
+            else umma::tmem_ld16(lane_addr + COL_HACC + NB + n0, reinterpret_cast<float(&)[16]>(o));
+            umma::tmem_ld_wait();
+            if (j < O) {
+#pragma unroll
+                for (int i = 0; i < NH; ++i) {
+                    const float y = __fadd_rn(o[i], b2);
+                    prm[(n0 + i) * CH + j] = y;
+                    const long long b = (long long)r * NB + n0 + i;
+                    if (P.raw && b < P.B) P.raw[(b * T + t) * O + j] = y;   // wavenet.py:847
+                }
+            }
+        }
+        umma::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) umma::mbar_arrive(bprm);
+        if (mbar_wait_wd(bprm, par, P.abort_flag)) return;   // all parameters of the step are in shared memory
+        // sampling + feedback (wavenet.py:850-878)
+        if (tid < NB) {
+            float nxt = 0.0f;
+            if (sampler && P.inputs_mode) {
+                nxt = tch;
+            } else if (sampler) {
+                const float smp = (O == 2) ? tc_sample_gaussian(P, prm + tid * CH, nz0)
+                                           : tc_sample_mol(P, prm + tid * CH, P.noise + ((long long)t * P.B + bu) * P.NZ);
+                P.audio[bu * T + t] = P.input_type == WN_INPUT_MULAW ? wn_inv_mulawf(smp) : smp;
+                nxt = P.teacher ? tch : smp;
+            }
+            if (t + 1 < T) st_ll1(min_out + ((t + 1) & 1) * NB + tid, nxt, tag + 1u);
+        }
+        if (do_stats) {
+            const long long c3 = clock64();
+            st_c[0] += c1 - c0; st_c[1] += c2 - c1; st_c[2] += c3 - c2;
+        }
+    }
+    if (do_stats) {
+        long long *o = P.stats + (long long)blockIdx.x * 16;
+        for (int i = 0; i < 3; ++i) o[i] = st_c[i];
+        o[14] = clock64() - st_begin; o[15] = T;
+    }
+}
+
+template <int NB>
+__device__ void head_mma(const TcParams &P, unsigned char *smem, const uint32_t tmem, Bars &bars) {
+    using G = Geo<NB>;
+    constexpr int LBO = G::LBO, PLANE = G::PLANE;
+    constexpr uint32_t idesc = umma::idesc_bf16(CH, NB);
+    const uint32_t s0 = umma::smem_addr(smem);
+    const uint64_t hi_hi = umma::smem_desc(s0 + G::S_HI, LBO, 128), hi_lo = umma::smem_desc(s0 + G::S_HI + PLANE, LBO, 128);
+    const uint64_t h2_hi = umma::smem_desc(s0 + G::S_H2, LBO, 128), h2_lo = umma::smem_desc(s0 + G::S_H2 + PLANE, LBO, 128);
+    constexpr uint64_t KS_B = (uint64_t)((2 * LBO) >> 4);
+    const uint32_t D_H = tmem + COL_HACC, D_O = tmem + COL_HACC + NB;
+    const uint32_t bh1 = umma::smem_addr(&bars.gate), bo = umma::smem_addr(&bars.out);
+    for (int t = 0; t < P.T; ++t) {
+        const int par = t & 1;
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {   // final_convolution_1 (wavenet.py:841)
+            if (mbar_wait_wd(umma::smem_addr(&bars.x[s]), par, P.abort_flag)) return;
+            umma::fence_after_sync();
+            if (umma::elect_one()) {
+#pragma unroll
+                for (int kk = 0; kk < 2; ++kk) {
+                    const int ks = 2 * s + kk;
+                    umma::mma_bf16_ts(D_H, tmem + COL_W1 + ks * 8, hi_hi + ks * KS_B, idesc, ks != 0);
+                    umma::mma_bf16_ts(D_H, tmem + COL_W1 + ks * 8, hi_lo + ks * KS_B, idesc, 1);
+                    umma::mma_bf16_ts(D_H, tmem + COL_W1 + 64 + ks * 8, hi_hi + ks * KS_B, idesc, 1);
+                }
+                if (s == 3) umma::mma_commit(bh1);
+            }
+            __syncwarp();
+        }
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {   // final_convolution_2 (wavenet.py:843), rows >= O of the tile are zero
+            if (mbar_wait_wd(umma::smem_addr(&bars.z[s]), par, P.abort_flag)) return;
+            umma::fence_after_sync();
+            if (umma::elect_one()) {
+#pragma unroll
+                for (int kk = 0; kk < 2; ++kk) {
+                    const int ks = 2 * s + kk;
+                    umma::mma_bf16_ts(D_O, tmem + COL_W2 + ks * 8, h2_hi + ks * KS_B, idesc, ks != 0);
+                    umma::mma_bf16_ts(D_O, tmem + COL_W2 + ks * 8, h2_lo + ks * KS_B, idesc, 1);
+                    umma::mma_bf16_ts(D_O, tmem + COL_W2 + 64 + ks * 8, h2_hi + ks * KS_B, idesc, 1);
+                }
+                if (s == 3) umma::mma_commit(bo);
+            }
+            __syncwarp();
+        }
+    }
+}
+
+// rows [128][64] words of `nmat` matrices -> tensor memory columns [col0, col0 + 64 * nmat): warps 0..3, thread = row
+__device__ void load_tmem_weights(const unsigned char *src, int nmat, uint32_t tmem, int col0) {
+    const int tid = threadIdx.x;
+    if (tid >= 128) return;
+    const uint32_t lane_addr = tmem + ((uint32_t)(tid & ~31) << 16);
+    for (int m = 0; m < nmat; ++m) {
+        const uint4 *row = reinterpret_cast<const uint4 *>(src + ((size_t)m * CH + tid) * 256);
+        for (int c0 = 0; c0 < 64; c0 += 16) {
+            uint32_t r[16];
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+                const uint4 x = __ldg(row + c0 / 4 + v);
+                r[4 * v] = x.x; r[4 * v + 1] = x.y; r[4 * v + 2] = x.z; r[4 * v + 3] = x.w;
+            }
+            umma::tmem_st16(lane_addr + col0 + m * 64 + c0, r);
+        }
+    }
+    umma::tmem_st_wait();
+}
+
+template <int NB, bool STATS>
+__global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParams P) {
+    using G = Geo<NB>;
+    extern __shared__ __align__(128) unsigned char tc_smem[];
+    __shared__ Bars bars;
+    __shared__ uint32_t tmem_base_s;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int stages = P.L + 1;
+    const int r = blockIdx.x / stages, l = blockIdx.x - r * stages;
+    const bool head = l == P.L;
+    if (tid == 0) {
+        for (int i = 0; i < 4; ++i) { umma::mbar_init(umma::smem_addr(&bars.x[i]), 2); umma::mbar_init(umma::smem_addr(&bars.z[i]), 2); }
+        umma::mbar_init(umma::smem_addr(&bars.gate), 1);
+        umma::mbar_init(umma::smem_addr(&bars.out), 1);
+        umma::mbar_init(umma::smem_addr(&bars.skip), head ? EPI_THREADS / 32 : 1);   // head: "parameters written" barrier
+        umma::mbar_init(umma::smem_addr(&bars.p), EPI_THREADS / 32);
+        for (int i = 0; i < 2; ++i) { umma::mbar_init(umma::smem_addr(&bars.wfull[i]), 1); umma::mbar_init(umma::smem_addr(&bars.wempty[i]), 1); }
+        umma::mbar_fence_init();
+    }
+    if (warp == 0) umma::tmem_alloc(umma::smem_addr(&tmem_base_s), 512);
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+    const uint32_t tmem = tmem_base_s;
+    // resident weights; zero the activation images (the padding rows / columns of the images are never written again)
+    if (head) {
+        load_tmem_weights(P.head_blob, 4, tmem, COL_W1);
+        for (int i = tid; i < G::S_HEND / 16; i += TC_THREADS) reinterpret_cast<uint4 *>(tc_smem)[i] = make_uint4(0, 0, 0, 0);
+    } else {
+        const unsigned char *blob = P.layer_blobs + (long long)l * LAYER_BLOB_BYTES;
+        load_tmem_weights(blob + OFF_TMEM, 6, tmem, COL_WCUR);
+        const uint4 *ws = reinterpret_cast<const uint4 *>(blob + OFF_WS);
+        for (int i = tid; i < 65536 / 16; i += TC_THREADS) reinterpret_cast<uint4 *>(tc_smem + G::S_WS)[i] = __ldg(ws + i);
+        for (int i = tid; i < (G::S_END - G::S_XI) / 16; i += TC_THREADS) reinterpret_cast<uint4 *>(tc_smem + G::S_XI)[i] = make_uint4(0, 0, 0, 0);
+    }
+    umma::fence_proxy_async();
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+    if (head) {
+        if (warp < 8) head_epilogue<NB, STATS>(P, r, tc_smem, tmem, bars);
+        else if (warp == MMA_WARP) head_mma<NB>(P, tc_smem, tmem, bars);
+    } else {
+        if (warp < 8) layer_epilogue<NB, STATS>(P, r, l, tc_smem, tmem, bars);
+        else if (warp == MMA_WARP) layer_mma<NB>(P, tc_smem, tmem, bars);
+        else layer_loader(P, l, tc_smem, bars, G::S_WST);
+    }
+    // every role returns when the sequence is done (or the watchdog fired): release tensor memory
+    umma::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) umma::tmem_dealloc(tmem, 512);
+}
+
+}  // namespace
+
+// =========================================================================================================================
+// host side
+// =========================================================================================================================
+struct WnTcPlan {
+    TcParams prm;
+    unsigned char *d_layer_blobs = nullptr, *d_head_blob = nullptr;
+    float *d_first = nullptr;
+    unsigned long long *d_mail = nullptr;
+    size_t mail_words = 0;
+    float *d_ring = nullptr;
+    size_t ring_floats = 0;
+    int *d_abort = nullptr, *h_abort = nullptr;
+    long long *d_stats = nullptr;
+    int stats_ctas = 0;
+    int max_replicas = 0;
+    int last_nb = 0, last_nr = 0;
+};
+
+static uint16_t bf16_rn_host(float f) {
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    if ((u & 0x7f800000u) == 0x7f800000u) return (uint16_t)(u >> 16);   // inf / nan: truncate
+    const uint32_t r = u + 0x7fffu + ((u >> 16) & 1u);
+    return (uint16_t)(r >> 16);
+}
+static float bf16_f_host(uint16_t h) {
+    const uint32_t u = (uint32_t)h << 16;
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+}
+static void split_host(float v, uint16_t &hi, uint16_t &lo) {
+    hi = bf16_rn_host(v);
+    lo = bf16_rn_host(v - bf16_f_host(hi));
+}
+
+bool wn_tc_supported(const wn_handle *h) {
+    const wn_config &c = h->cfg;
+    return c.residual_channels == CH && c.gate_channels == 2 * CH && c.skip_out_channels == CH && c.kernel_size == 3 &&
+           c.input_type != WN_INPUT_MULAW_QUANTIZE && c.gin_channels <= 0 && c.cin_channels > 0 && c.cin_channels <= CI_K &&
+           c.out_channels <= CH && c.layers >= 1 && c.layers / c.stacks <= 16;
+}
+
+void wn_tc_free(wn_handle *h) {
+    WnTcPlan *pl = h->tc;
+    if (!pl) return;
+    if (pl->d_layer_blobs) cudaFree(pl->d_layer_blobs);
+    if (pl->d_head_blob) cudaFree(pl->d_head_blob);
+    if (pl->d_first) cudaFree(pl->d_first);
+    if (pl->d_mail) cudaFree(pl->d_mail);
+    if (pl->d_ring) cudaFree(pl->d_ring);
+    if (pl->d_abort) cudaFree(pl->d_abort);
+    if (pl->h_abort) cudaFreeHost(pl->h_abort);
+    if (pl->d_stats) cudaFree(pl->d_stats);
+    delete pl;
+    h->tc = nullptr;
+}
+
+template <int NB>
+static const void *tc_kernel(bool stats) {
+    return stats ? (const void *)wn_loop_tc_kernel<NB, true> : (const void *)wn_loop_tc_kernel<NB, false>;
+}
+
+// Packs the weights (TF layouts) into the per-CTA blobs described at the top of this file.
+int wn_tc_plan(wn_handle *h) {
+    if (!wn_tc_supported(h)) { h->err = "tensor-core loop engine: needs R = G/2 = S = 128, kernel_size 3, scalar input, local conditioning (<= 96 channels), no global conditioning"; return WN_ERR_INVALID; }
+    const wn_config &c = h->cfg;
+    const int L = c.layers, cin = c.cin_channels, O = c.out_channels, G2 = 2 * CH;
+    auto W = [&](const std::string &n) -> const float * {
+        auto it = h->host_w.find(n);
+        return it == h->host_w.end() ? nullptr : it->second.data.data();
+    };
+    std::vector<unsigned char> blobs((size_t)L * LAYER_BLOB_BYTES, 0);
+    // rows [128][64 words] of a tensor-memory matrix: word c = bf16(k = 2c) | bf16(k = 2c + 1) << 16
+    auto put_tmem = [](unsigned char *dst_hi, unsigned char *dst_lo, int row, int k, float v) {
+        uint16_t hi, lo;
+        split_host(v, hi, lo);
+        reinterpret_cast<uint16_t *>(dst_hi)[(size_t)row * 128 + k] = hi;
+        reinterpret_cast<uint16_t *>(dst_lo)[(size_t)row * 128 + k] = lo;
+    };
+    // A image [K/8][128 rows][8] of a shared-memory operand
+    auto put_img = [](unsigned char *dst_hi, unsigned char *dst_lo, int row, int k, float v) {
+        uint16_t hi, lo;
+        split_host(v, hi, lo);
+        const size_t e = ((size_t)(k / 8) * CH + row) * 8 + k % 8;
+        reinterpret_cast<uint16_t *>(dst_hi)[e] = hi;
+        reinterpret_cast<uint16_t *>(dst_lo)[e] = lo;
+    };
+    for (int l = 0; l < L; ++l) {
+        const std::string p = "ResidualConv1DGLU_" + std::to_string(l) + "/residual_block_";
+        const float *cw = W(p + "causal_conv/kernel"), *iw = W(p + "cin_conv/kernel"), *ow = W(p + "out_conv/kernel"),
+                    *sw = W(p + "skip_conv/kernel");
+        const float *cb = W(p + "causal_conv/bias"), *ib = W(p + "cin_conv/bias"), *ob = W(p + "out_conv/bias"),
+                    *sb = W(p + "skip_conv/bias");
+        unsigned char *b = blobs.data() + (size_t)l * LAYER_BLOB_BYTES;
+        for (int j = 0; j < CH; ++j)
+            for (int k = 0; k < CH; ++k) {
+                // current tap = tap 2 of the [3][R][G] kernel (modules.py:238-251: row = tap * R + ci, tap 0 oldest)
+                put_tmem(b + OFF_TMEM, b + OFF_TMEM + 32768, j, k, cw[((size_t)2 * CH + k) * G2 + j]);
+                put_tmem(b + OFF_TMEM + 2 * 32768, b + OFF_TMEM + 3 * 32768, j, k, cw[((size_t)2 * CH + k) * G2 + CH + j]);
+                put_tmem(b + OFF_TMEM + 4 * 32768, b + OFF_TMEM + 5 * 32768, j, k, ow[(size_t)k * CH + j]);
+                put_img(b + OFF_WS, b + OFF_WS + 32768, j, k, sw[(size_t)k * CH + j]);
+            }
+        for (int kb = 0; kb < KB_TOTAL; ++kb)
+            for (int half = 0; half < 2; ++half) {
+                unsigned char *ch = b + OFF_STREAM + (size_t)(kb * 2 + half) * CHUNK_BYTES;
+                for (int j = 0; j < CH; ++j)
+                    for (int kk = 0; kk < 32; ++kk) {
+                        const int k = kb * 32 + kk, g = half * CH + j;
+                        float v = 0.0f;
+                        if (k < 2 * CH) v = cw[(size_t)k * G2 + g];                       // taps 0 and 1: rows 0 .. 2R-1
+                        else if (k - 2 * CH < cin) v = iw[(size_t)(k - 2 * CH) * G2 + g];
+                        put_img(ch, ch + 8192, j, kk, v);
+                    }
+            }
+        float *bias = reinterpret_cast<float *>(b + OFF_BIAS);
+        for (int j = 0; j < CH; ++j) {
+            bias[j] = (cb ? cb[j] : 0.0f) + (ib ? ib[j] : 0.0f);
+            bias[CH + j] = (cb ? cb[CH + j] : 0.0f) + (ib ? ib[CH + j] : 0.0f);
+            bias[2 * CH + j] = ob ? ob[j] : 0.0f;
+            bias[3 * CH + j] = sb ? sb[j] : 0.0f;
+        }
+    }
+    std::vector<unsigned char> hb(HEAD_BLOB_BYTES, 0);
+    {
+        const float *w1 = W("final_convolution_1/kernel"), *w2 = W("final_convolution_2/kernel");
+        const float *b1 = W("final_convolution_1/bias"), *b2 = W("final_convolution_2/bias");
+        for (int j = 0; j < CH; ++j)
+            for (int k = 0; k < CH; ++k) {
+                put_tmem(hb.data(), hb.data() + 32768, j, k, w1[(size_t)k * CH + j]);
+                put_tmem(hb.data() + 2 * 32768, hb.data() + 3 * 32768, j, k, j < O ? w2[(size_t)k * O + j] : 0.0f);
+            }
+        float *bias = reinterpret_cast<float *>(hb.data() + 4 * 32768);
+        for (int j = 0; j < CH; ++j) { bias[j] = b1 ? b1[j] : 0.0f; bias[CH + j] = (b2 && j < O) ? b2[j] : 0.0f; }
+    }
+    std::vector<float> first(2 * CH, 0.0f);
+    {
+        const float *fw = W("input_convolution/kernel"), *fb = W("input_convolution/bias");
+        for (int j = 0; j < CH; ++j) { first[j] = fw[j]; first[CH + j] = fb ? fb[j] : 0.0f; }
+    }
+    WnTcPlan *pl = new WnTcPlan();
+    h->tc = pl;
+    auto bail = [&](const std::string &msg) { h->err = msg; wn_tc_free(h); return WN_ERR_CUDA; };
+    if (cudaMalloc((void **)&pl->d_layer_blobs, blobs.size()) != cudaSuccess) return bail("tensor-core loop engine: cudaMalloc(layer blobs)");
+    if (cudaMalloc((void **)&pl->d_head_blob, hb.size()) != cudaSuccess) return bail("tensor-core loop engine: cudaMalloc(head blob)");
+    if (cudaMalloc((void **)&pl->d_first, first.size() * 4) != cudaSuccess) return bail("tensor-core loop engine: cudaMalloc(first conv)");
+    if (cudaMalloc((void **)&pl->d_abort, sizeof(int)) != cudaSuccess) return bail("tensor-core loop engine: cudaMalloc(abort flag)");
+    if (cudaMallocHost((void **)&pl->h_abort, sizeof(int)) != cudaSuccess) return bail("tensor-core loop engine: cudaMallocHost(abort flag)");
+    *pl->h_abort = 0;
+    cudaMemcpy(pl->d_layer_blobs, blobs.data(), blobs.size(), cudaMemcpyHostToDevice);
+    cudaMemcpy(pl->d_head_blob, hb.data(), hb.size(), cudaMemcpyHostToDevice);
+    cudaMemcpy(pl->d_first, first.data(), first.size() * 4, cudaMemcpyHostToDevice);
+    TcParams &p = pl->prm;
+    memset(&p, 0, sizeof(p));
+    p.L = L; p.O = O; p.cin = cin; p.NZ = h->m.NZ; p.input_type = c.input_type; p.legacy = c.legacy; p.residual_legacy = c.residual_legacy;
+    p.log_scale_min = c.log_scale_min; p.log_scale_min_gauss = c.log_scale_min_gauss;
+    long long slots = 0;
+    for (int l = 0; l < L; ++l) { p.dil[l] = h->m.dil[l]; p.ring_off[l] = slots; slots += 2 * p.dil[l]; }
+    p.ring_slots = slots;
+    p.layer_blobs = pl->d_layer_blobs; p.head_blob = pl->d_head_blob; p.first_wb = pl->d_first; p.abort_flag = pl->d_abort;
+    pl->max_replicas = h->sm_count / (L + 1);
+    for (int nb : {16, 32}) {
+        const void *k0 = nb == 16 ? tc_kernel<16>(false) : tc_kernel<32>(false), *k1 = nb == 16 ? tc_kernel<16>(true) : tc_kernel<32>(true);
+        const int smem = nb == 16 ? Geo<16>::SMEM : Geo<32>::SMEM;
+        if (cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
+            cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
+            return bail("tensor-core loop engine: shared memory attribute");
+    }
+    if (pl->max_replicas < 1) return bail("tensor-core loop engine: fewer SMs than layers + 1");
+    return WN_OK;
+}
+
+// largest batch one launch takes (wn_synthesize falls back to the fp32 pipelined engine above it)
+int wn_tc_max_batch(const wn_handle *h) { return h->tc ? h->tc->max_replicas * 32 : 0; }
+
+void wn_tc_fill_info(wn_handle *h, wn_info *info) {
+    if (!h->tc || h->engine != WN_ENGINE_TC) return;
+    info->pipeline_ctas = h->tc->last_nr * (h->cfg.layers + 1);
+    info->pipeline_ctas_per_layer = h->tc->last_nr;
+    info->pipeline_group_size = h->tc->last_nb;
+}
+
+int wn_tc_check_abort(wn_handle *h) {   // after the stream has been synchronised
+    WnTcPlan *pl = h->tc;
+    if (!pl || !pl->h_abort) return WN_OK;
+    if (pl->d_stats && pl->stats_ctas > 0 && getenv("WN_TC_STATS")) {   // development aid
+        std::vector<long long> st((size_t)pl->stats_ctas * 16);
+        if (cudaMemcpy(st.data(), pl->d_stats, st.size() * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess) {
+            FILE *f = fopen(getenv("WN_TC_STATS"), "a");
+            if (f) {
+                fprintf(f, "# tc stats: L=%d NB=%d NR=%d; cols: cta stage  layer: poll image+arrive->gate gate-epilogue->z z->out out+skip | head: skip-polls 1x1s sampler ; total steps\n",
+                        pl->prm.L, pl->last_nb, pl->last_nr);
+                for (int i = 0; i < pl->stats_ctas; ++i) {
+                    const long long *o = st.data() + (size_t)i * 16;
+                    if (o[15] == 0) continue;
+                    fprintf(f, "%d %d", i, i % (pl->prm.L + 1));
+                    for (int k = 0; k < 5; ++k) fprintf(f, " %.0f", (double)o[k] / (double)o[15]);
+                    fprintf(f, " | %.0f %lld\n", (double)o[14] / (double)o[15], o[15]);
+                }
+                fclose(f);
+            }
+        }
+        pl->stats_ctas = 0;
+    }
+    if (*pl->h_abort == 0) return WN_OK;
+    h->err = "tensor-core loop engine: watchdog - a CTA waited too long for a peer";
+    return WN_ERR_WATCHDOG;
+}
+
+int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int inputs_mode, int B, int T,
+                      float *audio, float *raw, cudaStream_t st) {
+    WnTcPlan *pl = h->tc;
+    if (!pl) { h->err = "tensor-core loop engine not planned"; return WN_ERR_STATE; }
+    TcParams p = pl->prm;
+    int nb = (B <= pl->max_replicas * 16) ? 16 : 32;
+    if (const char *e = getenv("WN_TC_NB")) { const int v = atoi(e); if (v == 16 || v == 32) nb = v; }
+    const int nr = (B + nb - 1) / nb;
+    if (nr > pl->max_replicas) { h->err = "tensor-core loop engine: batch too large for one launch"; return WN_ERR_INVALID; }
+    pl->last_nb = nb; pl->last_nr = nr;
+    p.B = B; p.T = T; p.NR = nr;
+    p.c_up = c_up; p.noise = noise; p.teacher = teacher; p.inputs_mode = inputs_mode; p.audio = audio; p.raw = raw;
+    const int L = p.L;
+    // mailboxes: x [NR][L][2][128*NB] | skip [NR][L][2][128*NB] | in [NR][2][NB], 8-byte {value, tag} words, zeroed (tag 0 = empty)
+    const size_t mailw = (size_t)CH * nb;
+    const size_t words = 2 * (size_t)nr * L * 2 * mailw + (size_t)nr * 2 * nb;
+    if (pl->mail_words < words) {
+        if (pl->d_mail) cudaFree(pl->d_mail);
+        pl->d_mail = nullptr; pl->mail_words = 0;
+        if (cudaMalloc((void **)&pl->d_mail, words * 8) != cudaSuccess) { h->err = "tensor-core loop engine: cudaMalloc(mailboxes)"; return WN_ERR_NOMEM; }
+        pl->mail_words = words;
+    }
+    p.mail_x = pl->d_mail;
+    p.mail_skip = p.mail_x + (size_t)nr * L * 2 * mailw;
+    p.mail_in = p.mail_skip + (size_t)nr * L * 2 * mailw;
+    // dilation rings [NR][sum 2d][128*NB] floats: every slot is written before it is read (steps before 0 read zeros instead)
+    const size_t ring_floats = (size_t)nr * p.ring_slots * mailw;
+    if (pl->ring_floats < ring_floats) {
+        if (pl->d_ring) cudaFree(pl->d_ring);
+        pl->d_ring = nullptr; pl->ring_floats = 0;
+        if (cudaMalloc((void **)&pl->d_ring, ring_floats * sizeof(float)) != cudaSuccess) { h->err = "tensor-core loop engine: cudaMalloc(rings)"; return WN_ERR_NOMEM; }
+        pl->ring_floats = ring_floats;
+    }
+    p.ring = pl->d_ring;
+    WN_CUDA_TRY(h, cudaMemsetAsync(pl->d_mail, 0, words * 8, st));
+    WN_CUDA_TRY(h, cudaMemsetAsync(pl->d_abort, 0, sizeof(int), st));
+    const int grid = nr * (L + 1);
+    p.stats = nullptr;
+    if (getenv("WN_TC_STATS")) {
+        if (!pl->d_stats) cudaMalloc((void **)&pl->d_stats, sizeof(long long) * 16 * 256);
+        if (pl->d_stats) { cudaMemsetAsync(pl->d_stats, 0, sizeof(long long) * 16 * 256, st); p.stats = pl->d_stats; pl->stats_ctas = grid; }
+    }
+    // all CTAs wait for each other: they must be co-resident -> cooperative launch (one CTA per SM, grid <= SM count)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(TC_THREADS); cfg.stream = st;
+    cfg.dynamicSmemBytes = nb == 16 ? Geo<16>::SMEM : Geo<32>::SMEM;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeCooperative;
+    at[0].val.cooperative = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    void *args[] = {&p};
+    const void *kern = nb == 16 ? tc_kernel<16>(p.stats != nullptr) : tc_kernel<32>(p.stats != nullptr);
+    WN_CUDA_TRY(h, cudaLaunchKernelExC(&cfg, kern, args));
+    h->launches++;
+    WN_CUDA_TRY(h, cudaMemcpyAsync(pl->h_abort, pl->d_abort, sizeof(int), cudaMemcpyDeviceToHost, st));
+    return WN_OK;
+}

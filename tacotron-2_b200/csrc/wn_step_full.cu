@@ -9,7 +9,7 @@
 int wn_launch_step_full(wn_handle *h, const float *x, const float *c_up, const float *g_emb, int B, int T,
                         float *raw, cudaStream_t st) {
     if (wn_gemm_supported(h)) return wn_launch_step_gemm(h, x, c_up, B, T, raw, st);
-    if (h->engine == WN_ENGINE_PIPELINE) {
+    if (h->pipe && h->engine != WN_ENGINE_GENERIC) {
         return wn_launch_loop_pipe(h, c_up, nullptr, x, 1, B, T, nullptr, raw, st);
     }
     return wn_launch_loop_generic(h, c_up, g_emb, nullptr, x, 1, B, T, nullptr, raw, st);

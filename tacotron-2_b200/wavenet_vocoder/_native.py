@@ -18,7 +18,7 @@ MAX_UP = 8
 INPUT_TYPES = {'raw': 0, 'mulaw': 1, 'mulaw-quantize': 2}
 UP_TYPES = {'SubPixel': 0, '2D': 1, '1D': 2, 'Resize': 3, 'NearestNeighbor': 4}
 ACTS = {None: 0, 'Relu': 1, 'LeakyRelu': 2}
-ENGINES = {'auto': 0, 'generic': 1, 'pipeline': 2}
+ENGINES = {'auto': 0, 'generic': 1, 'pipeline': 2, 'tc': 3}
 ENGINE_NAMES = {v: k for k, v in ENGINES.items()}
 
 EXPORTS = ('wn_create', 'wn_load_weights', 'wn_finalize', 'wn_upsample', 'wn_synthesize', 'wn_synthesize_host',
