@@ -89,7 +89,7 @@ struct Geo {
     static constexpr int CI_PLANE = (CI_K / 8) * LBO;
     // shared memory of a layer CTA
     static constexpr int S_WS = 0, S_WST = 65536, S_XI = S_WST + 2 * CHUNK_BYTES, S_ZI = S_XI + 2 * IMG, S_TAP = S_ZI + IMG,
-                         S_CI = S_TAP + 2 * IMG, S_END = S_CI + 2 * CI_PLANE;
+                         S_CI = S_TAP + 2 * IMG, S_XF = S_CI + 2 * CI_PLANE, S_END = S_XF + CH * NB * 4;   // S_XF: fp32 inbox of x
     // head CTA
     static constexpr int S_HI = 0, S_H2 = IMG, S_PRM = 2 * IMG, S_HEND = S_PRM + NB * CH * 4;
     static constexpr int SMEM = S_END > S_HEND ? S_END : S_HEND;
@@ -157,6 +157,36 @@ __device__ __forceinline__ bool mbar_wait_wd(uint32_t bar, uint32_t parity, int 
     return false;
 }
 
+// ---- thread-block cluster / distributed shared memory: consecutive stages of a replica that share a cluster hand x over
+// with st.async straight into the next CTA's shared memory (counted in bytes on that CTA's mbarrier) ----------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t cluster_nctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_async4(uint32_t raddr, float4 v, uint32_t rmbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%1, %2, %3, %4}, [%5];"
+                 ::"r"(raddr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(rmbar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_cluster(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ bool mbar_wait_cluster_wd(uint32_t bar, uint32_t parity, int *abort_flag) {
+    Watch wd{abort_flag};
+    while (!mbar_try_cluster(bar, parity))
+        if (wd.expired()) return true;
+    return false;
+}
+
 // ---- activation images: [K/8][NB][8] bf16, hi plane then lo plane; one thread per channel writes 2-byte elements ---------
 __device__ __forceinline__ void img_put(unsigned char *img, int plane, int lbo, int j, int n, float v) {
     const uint32_t h = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(v));
@@ -166,24 +196,40 @@ __device__ __forceinline__ void img_put(unsigned char *img, int plane, int lbo, 
     *reinterpret_cast<unsigned short *>(img + off) = (unsigned short)h;
     *reinterpret_cast<unsigned short *>(img + plane + off) = (unsigned short)l;
 }
+// two neighbouring utterances n, n + 1 of one channel: one packed conversion per plane (float -> bf16 conversions run on the
+// 16-lane special-function pipe, which bounds the epilogues of this kernel)
+__device__ __forceinline__ void img_put2(unsigned char *p /* element (j, n) of the hi plane */, int plane, float v0, float v1) {
+    uint32_t h, l;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(v1), "f"(v0));
+    const float r0 = __fsub_rn(v0, __uint_as_float(h << 16)), r1 = __fsub_rn(v1, __uint_as_float(h & 0xffff0000u));
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(l) : "f"(r1), "f"(r0));
+    *reinterpret_cast<unsigned short *>(p) = (unsigned short)h;
+    *reinterpret_cast<unsigned short *>(p + 16) = (unsigned short)(h >> 16);
+    *reinterpret_cast<unsigned short *>(p + plane) = (unsigned short)l;
+    *reinterpret_cast<unsigned short *>(p + plane + 16) = (unsigned short)(l >> 16);
+}
 
 // tanh(t) * sigmoid(s) (modules.py:510) with ex2.approx / rcp.approx; same form as wn_step_umma.cu
 __device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float gate_fast(float t, float s) {
+    // tanh(t) * sigmoid(s) = sign(t) (1 - E) / ((1 + E)(1 + F)), E = exp(-2|t|) in (0, 1], F = exp(-s): two ex2 and ONE rcp per
+    // element (the MUFU pipe, 16 lanes per clock and SM, bounds this epilogue); F = inf gives rcp(inf) = 0, the right limit
     constexpr float LOG2E = 1.4426950408889634f;
-    const float sg = rcp_approx(__fadd_rn(1.0f, ex2_approx(__fmul_rn(-LOG2E, s))));
     const float at = fabsf(t);
-    float th = __fmaf_rn(-2.0f, rcp_approx(__fadd_rn(ex2_approx(__fmul_rn(2.0f * LOG2E, at)), 1.0f)), 1.0f);
-    const float z = __fmul_rn(t, t);
+    const float E = ex2_approx(__fmul_rn(-2.0f * LOG2E, at)), F = ex2_approx(__fmul_rn(-LOG2E, s));
+    const float den = __fmul_rn(__fadd_rn(1.0f, E), __fadd_rn(1.0f, F));
+    const float r = rcp_approx(den);
+    // 1 - E cancels for small |t|: tanh(|t|) (1 + E) from the polynomial of wn_tanhf instead (select, no branch)
+    const float z = __fmul_rn(at, at);
     float p = -5.70498872745e-3f;
     p = __fmaf_rn(p, z, 2.06390887954e-2f);
     p = __fmaf_rn(p, z, -5.37397155531e-2f);
     p = __fmaf_rn(p, z, 1.33314422036e-1f);
     p = __fmaf_rn(p, z, -3.33332819422e-1f);
-    th = copysignf(th, t);
-    if (at < 0.625f) th = __fmaf_rn(__fmul_rn(p, z), t, t);
-    return __fmul_rn(th, sg);
+    const float small = __fmul_rn(__fmaf_rn(__fmul_rn(p, z), at, at), __fadd_rn(1.0f, E));
+    const float num = at < 0.625f ? small : __fsub_rn(1.0f, E);
+    return copysignf(__fmul_rn(num, r), t);
 }
 
 __device__ __forceinline__ float tc_sample_gaussian(const TcParams &P, const float *out, float eps) {   // gaussian.py:39-52
@@ -212,7 +258,7 @@ __device__ float tc_sample_mol(const TcParams &P, const float *out, const float 
 
 // mbarriers of a CTA
 struct Bars {
-    unsigned long long x[4], z[4], gate, out, skip, p, wfull[2], wempty[2];
+    unsigned long long x, z, gate, out, skip, p, wfull[2], wempty[2], xf;
 };
 
 // =========================================================================================================================
@@ -232,6 +278,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     const float wf = l == 0 ? __ldg(P.first_wb + j) : 0.0f, bf = l == 0 ? __ldg(P.first_wb + CH + j) : 0.0f;
     const float cres = P.residual_legacy ? 0.70710677f : 1.0f;   // np.sqrt(0.5) as float32 (modules.py:517-520)
     const int d = P.dil[l], qmask = 2 * d - 1;
+    const int joff = (j >> 3) * LBO + n0 * 16 + (j & 7) * 2;            // element (j, n0) inside an image plane
     const long long unit0 = ((long long)(hh * NU) * CH + j) * 2;      // word offset of this thread's first unit inside a mailbox buffer
     const unsigned long long *mx_in = P.mail_x + (long long)(r * L + l) * 2 * G::MAILW + unit0;
     unsigned long long *mx_out = P.mail_x + (long long)(r * L + l + 1) * 2 * G::MAILW + unit0;
@@ -239,8 +286,15 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     const unsigned long long *min_in = P.mail_in + (long long)r * 2 * NB + n0;
     float *ring = P.ring + ((long long)r * P.ring_slots + P.ring_off[l]) * G::MAILW + ((long long)(hh * NQ) * CH + j) * 4;
     unsigned char *XI = smem + G::S_XI, *ZI = smem + G::S_ZI, *TAP = smem + G::S_TAP, *CI = smem + G::S_CI;
-    const uint32_t bx = umma::smem_addr(&bars.x[q]), bz = umma::smem_addr(&bars.z[q]), bp = umma::smem_addr(&bars.p),
+    const uint32_t bx = umma::smem_addr(&bars.x), bz = umma::smem_addr(&bars.z), bp = umma::smem_addr(&bars.p),
                    bgate = umma::smem_addr(&bars.gate), bout = umma::smem_addr(&bars.out), bskip = umma::smem_addr(&bars.skip);
+    // x arrives / leaves through distributed shared memory when the neighbouring stage shares this CTA's cluster, else
+    // through the L2 mailboxes
+    const uint32_t crank = cluster_ctarank(), csize = cluster_nctarank();
+    const bool in_dsmem = l > 0 && crank > 0, out_dsmem = l + 1 < L && crank + 1 < csize;
+    float *XF = reinterpret_cast<float *>(smem + G::S_XF) + ((hh * NQ) * CH + j) * 4;     // [half][unit][channel][4 utterances]
+    const uint32_t bxf = umma::smem_addr(&bars.xf);
+    const uint32_t r_xf = mapa_u32(umma::smem_addr(XF), out_dsmem ? crank + 1 : crank), r_bxf = mapa_u32(bxf, out_dsmem ? crank + 1 : crank);
     constexpr int CN = (CI_K * NB + EPI_THREADS - 1) / EPI_THREADS;   // conditioning elements per thread (upper bound)
     long long st_c[6] = {0, 0, 0, 0, 0, 0};
     const bool do_stats = STATS && P.stats != nullptr && tid == 0;
@@ -267,9 +321,9 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     };
     auto prep_store = [&]() {
 #pragma unroll
-        for (int i = 0; i < NH; ++i) {
-            img_put(TAP, PLANE, LBO, j, n0 + i, tp0[i]);
-            img_put(TAP + G::IMG, PLANE, LBO, j, n0 + i, tp1[i]);
+        for (int i = 0; i < NH; i += 2) {
+            img_put2(TAP + joff + i * 16, PLANE, tp0[i], tp0[i + 1]);
+            img_put2(TAP + G::IMG + joff + i * 16, PLANE, tp1[i], tp1[i + 1]);
         }
 #pragma unroll
         for (int i = 0; i < CN; ++i) {
@@ -297,13 +351,24 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
             if (poll_units<NU>(min_in + par * NB, 2, tag, s, P.abort_flag)) return;
 #pragma unroll
             for (int i = 0; i < NH; ++i) xin[i] = __fmaf_rn(s[i], wf, bf);
+        } else if (in_dsmem) {
+            if (tid == 0) umma::mbar_expect_tx(bxf, CH * NB * 4);
+            if (mbar_wait_cluster_wd(bxf, par, P.abort_flag)) return;
+#pragma unroll
+            for (int u = 0; u < NQ; ++u) {
+                const float4 v = *reinterpret_cast<const float4 *>(XF + u * CH * 4);
+                xin[4 * u] = v.x; xin[4 * u + 1] = v.y; xin[4 * u + 2] = v.z; xin[4 * u + 3] = v.w;
+            }
         } else {
             if (poll_units<NU>(mx_in + (long long)par * G::MAILW, (long long)CH * 2, tag, xin, P.abort_flag)) return;
         }
         const long long c1 = do_stats ? clock64() : 0;
         unsigned char *xi = XI + par * G::IMG;
+        {
+            unsigned char *px = xi + joff;
 #pragma unroll
-        for (int i = 0; i < NH; ++i) img_put(xi, PLANE, LBO, j, n0 + i, xin[i]);
+            for (int i = 0; i < NH; i += 2) img_put2(px + i * 16, PLANE, xin[i], xin[i + 1]);
+        }
         umma::fence_proxy_async();
         __syncwarp();
         if (lane == 0) umma::mbar_arrive(bx);
@@ -311,7 +376,6 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         for (int u = 0; u < NQ; ++u)
             *reinterpret_cast<float4 *>(ring + (long long)(t & qmask) * G::MAILW + (long long)u * CH * 4) =
                 make_float4(xin[4 * u], xin[4 * u + 1], xin[4 * u + 2], xin[4 * u + 3]);
-        if (t + 1 < T) prep_load(t + 1);   // in flight while the gate MMAs run
         // ---- gate (modules.py:494-510) ----------------------------------------------------------------------------------------
         if (mbar_wait_wd(bgate, par, P.abort_flag)) return;
         umma::fence_after_sync();
@@ -327,14 +391,15 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
             }
             umma::tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < NH; ++i) img_put(ZI, PLANE, LBO, j, n0 + i, gate_fast(__fadd_rn(a[i], ba), __fadd_rn(b[i], bb)));
+            for (int i = 0; i < NH; i += 2)
+                img_put2(ZI + joff + i * 16, PLANE, gate_fast(__fadd_rn(a[i], ba), __fadd_rn(b[i], bb)),
+                         gate_fast(__fadd_rn(a[i + 1], ba), __fadd_rn(b[i + 1], bb)));
         }
         umma::fence_proxy_async();
         umma::fence_before_sync();
         __syncwarp();
         if (lane == 0) umma::mbar_arrive(bz);
         const long long c3 = do_stats ? clock64() : 0;
-        if (t + 1 < T) prep_store();
         // ---- residual 1x1 -> x_{l+1}(t) (modules.py:515-520) ----------------------------------------------------------------
         if (mbar_wait_wd(bout, par, P.abort_flag)) return;
         umma::fence_after_sync();
@@ -344,7 +409,17 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
             if constexpr (NH == 8) umma::tmem_ld8(lane_addr + COL_ACC + 2 * NB + n0, reinterpret_cast<float(&)[8]>(o));
             else umma::tmem_ld16(lane_addr + COL_ACC + 2 * NB + n0, reinterpret_cast<float(&)[16]>(o));
             umma::tmem_ld_wait();
-            if (l + 1 < L) {
+            if (out_dsmem) {
+#pragma unroll
+                for (int u = 0; u < NQ; ++u) {
+                    float4 v;
+                    v.x = __fmul_rn(__fadd_rn(__fadd_rn(o[4 * u], bo), xin[4 * u]), cres);
+                    v.y = __fmul_rn(__fadd_rn(__fadd_rn(o[4 * u + 1], bo), xin[4 * u + 1]), cres);
+                    v.z = __fmul_rn(__fadd_rn(__fadd_rn(o[4 * u + 2], bo), xin[4 * u + 2]), cres);
+                    v.w = __fmul_rn(__fadd_rn(__fadd_rn(o[4 * u + 3], bo), xin[4 * u + 3]), cres);
+                    st_async4(r_xf + u * CH * 16, v, r_bxf);
+                }
+            } else if (l + 1 < L) {
 #pragma unroll
                 for (int u = 0; u < NU; ++u) {
                     const float v0 = __fmul_rn(__fadd_rn(__fadd_rn(o[2 * u], bo), xin[2 * u]), cres);
@@ -365,7 +440,11 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
             for (int u = 0; u < NU; ++u)
                 st_ll2(ms_out + (long long)par * G::MAILW + (long long)u * CH * 2, __fadd_rn(s[2 * u], bs), __fadd_rn(s[2 * u + 1], bs), tag);
         }
-        umma::fence_before_sync();
+        // ---- off the critical path: operands of the x-independent part of the next step ---------------------------------------
+        if (t + 1 < T) {
+            prep_load(t + 1);
+            prep_store();
+        }
         if (do_stats) {
             const long long c5 = clock64();
             st_c[0] += c1 - c0; st_c[1] += c2 - c1; st_c[2] += c3 - c2; st_c[3] += c4 - c3; st_c[4] += c5 - c4;
@@ -433,44 +512,36 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
         const int par = t & 1;
         const uint64_t xi_hi = umma::smem_desc(s0 + G::S_XI + par * G::IMG, LBO, 128),
                        xi_lo = umma::smem_desc(s0 + G::S_XI + par * G::IMG + PLANE, LBO, 128);
-        // current tap of the dilated conv (modules.py:294-297), K slice by K slice as the epilogue warps deliver the image
+        // current tap of the dilated conv (modules.py:294-297) on top of the x-independent part
+        if (mbar_wait_wd(umma::smem_addr(&bars.x), par, P.abort_flag)) return;
+        umma::fence_after_sync();
+        if (umma::elect_one()) {
 #pragma unroll
-        for (int s = 0; s < 4; ++s) {
-            if (mbar_wait_wd(umma::smem_addr(&bars.x[s]), par, P.abort_flag)) return;
-            umma::fence_after_sync();
-            if (umma::elect_one()) {
-#pragma unroll
-                for (int kk = 0; kk < 2; ++kk) {
-                    const int ks = 2 * s + kk;
-                    const uint64_t bh = xi_hi + ks * KS_B, bl = xi_lo + ks * KS_B;
-                    umma::mma_bf16_ts(D_A, tmem + COL_WCUR + ks * 8, bh, idesc, 1);
-                    umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 128 + ks * 8, bh, idesc, 1);
-                    umma::mma_bf16_ts(D_A, tmem + COL_WCUR + ks * 8, bl, idesc, 1);
-                    umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 128 + ks * 8, bl, idesc, 1);
-                    umma::mma_bf16_ts(D_A, tmem + COL_WCUR + 64 + ks * 8, bh, idesc, 1);
-                    umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 192 + ks * 8, bh, idesc, 1);
-                }
-                if (s == 3) umma::mma_commit(bgate);
+            for (int ks = 0; ks < 8; ++ks) {
+                const uint64_t bh = xi_hi + ks * KS_B, bl = xi_lo + ks * KS_B;
+                umma::mma_bf16_ts(D_A, tmem + COL_WCUR + ks * 8, bh, idesc, 1);
+                umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 128 + ks * 8, bh, idesc, 1);
+                umma::mma_bf16_ts(D_A, tmem + COL_WCUR + ks * 8, bl, idesc, 1);
+                umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 128 + ks * 8, bl, idesc, 1);
+                umma::mma_bf16_ts(D_A, tmem + COL_WCUR + 64 + ks * 8, bh, idesc, 1);
+                umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 192 + ks * 8, bh, idesc, 1);
             }
-            __syncwarp();
+            umma::mma_commit(bgate);
         }
+        __syncwarp();
         // residual 1x1 on z (modules.py:515)
+        if (mbar_wait_wd(umma::smem_addr(&bars.z), par, P.abort_flag)) return;
+        umma::fence_after_sync();
+        if (umma::elect_one()) {
 #pragma unroll
-        for (int s = 0; s < 4; ++s) {
-            if (mbar_wait_wd(umma::smem_addr(&bars.z[s]), par, P.abort_flag)) return;
-            umma::fence_after_sync();
-            if (umma::elect_one()) {
-#pragma unroll
-                for (int kk = 0; kk < 2; ++kk) {
-                    const int ks = 2 * s + kk;
-                    umma::mma_bf16_ts(D_O, tmem + COL_WOUT + ks * 8, zi_hi + ks * KS_B, idesc, ks != 0);
-                    umma::mma_bf16_ts(D_O, tmem + COL_WOUT + ks * 8, zi_lo + ks * KS_B, idesc, 1);
-                    umma::mma_bf16_ts(D_O, tmem + COL_WOUT + 64 + ks * 8, zi_hi + ks * KS_B, idesc, 1);
-                }
-                if (s == 3) umma::mma_commit(bout);
+            for (int ks = 0; ks < 8; ++ks) {
+                umma::mma_bf16_ts(D_O, tmem + COL_WOUT + ks * 8, zi_hi + ks * KS_B, idesc, ks != 0);
+                umma::mma_bf16_ts(D_O, tmem + COL_WOUT + ks * 8, zi_lo + ks * KS_B, idesc, 1);
+                umma::mma_bf16_ts(D_O, tmem + COL_WOUT + 64 + ks * 8, zi_hi + ks * KS_B, idesc, 1);
             }
-            __syncwarp();
+            umma::mma_commit(bout);
         }
+        __syncwarp();
         // skip 1x1 on z (modules.py:512), weights in shared memory
         if (umma::elect_one()) {
 #pragma unroll
@@ -516,12 +587,13 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
     const float *hb = reinterpret_cast<const float *>(P.head_blob + 4 * 32768);
     const float b1 = __ldg(hb + j), b2 = __ldg(hb + CH + j);
     const float cskip = 0.70710677f;
+    const int joff = (j >> 3) * LBO + n0 * 16 + (j & 7) * 2;
     const long long unit0 = ((long long)(hh * NU) * CH + j) * 2;
     const unsigned long long *ms_in = P.mail_skip + (long long)r * L * 2 * G::MAILW + unit0;
     unsigned long long *min_out = P.mail_in + (long long)r * 2 * NB;
     unsigned char *HI = smem + G::S_HI, *H2 = smem + G::S_H2;
     float *prm = reinterpret_cast<float *>(smem + G::S_PRM);   // [NB][CH]
-    const uint32_t bh = umma::smem_addr(&bars.x[q]), bh2 = umma::smem_addr(&bars.z[q]), bh1 = umma::smem_addr(&bars.gate),
+    const uint32_t bh = umma::smem_addr(&bars.x), bh2 = umma::smem_addr(&bars.z), bh1 = umma::smem_addr(&bars.gate),
                    bo = umma::smem_addr(&bars.out), bprm = umma::smem_addr(&bars.skip);
     const long long bu = (long long)r * NB + tid;          // utterance of the sampler thread
     const bool sampler = tid < NB && bu < P.B;
@@ -552,7 +624,8 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
         }
         const long long c1 = do_stats ? clock64() : 0;
 #pragma unroll
-        for (int i = 0; i < NH; ++i) img_put(HI, PLANE, LBO, j, n0 + i, S[i] > 0.0f ? S[i] : 0.0f);   // relu (wavenet.py:840)
+        for (int i = 0; i < NH; i += 2)   // relu (wavenet.py:840)
+            img_put2(HI + joff + i * 16, PLANE, S[i] > 0.0f ? S[i] : 0.0f, S[i + 1] > 0.0f ? S[i + 1] : 0.0f);
         umma::fence_proxy_async();
         umma::fence_before_sync();
         __syncwarp();
@@ -565,9 +638,9 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
             else umma::tmem_ld16(lane_addr + COL_HACC + n0, reinterpret_cast<float(&)[16]>(h));
             umma::tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < NH; ++i) {
-                const float y = __fadd_rn(h[i], b1);
-                img_put(H2, PLANE, LBO, j, n0 + i, y > 0.0f ? y : 0.0f);
+            for (int i = 0; i < NH; i += 2) {
+                const float y0 = __fadd_rn(h[i], b1), y1 = __fadd_rn(h[i + 1], b1);
+                img_put2(H2 + joff + i * 16, PLANE, y0 > 0.0f ? y0 : 0.0f, y1 > 0.0f ? y1 : 0.0f);
             }
         }
         umma::fence_proxy_async();
@@ -634,38 +707,30 @@ __device__ void head_mma(const TcParams &P, unsigned char *smem, const uint32_t 
     const uint32_t bh1 = umma::smem_addr(&bars.gate), bo = umma::smem_addr(&bars.out);
     for (int t = 0; t < P.T; ++t) {
         const int par = t & 1;
+        if (mbar_wait_wd(umma::smem_addr(&bars.x), par, P.abort_flag)) return;   // final_convolution_1 (wavenet.py:841)
+        umma::fence_after_sync();
+        if (umma::elect_one()) {
 #pragma unroll
-        for (int s = 0; s < 4; ++s) {   // final_convolution_1 (wavenet.py:841)
-            if (mbar_wait_wd(umma::smem_addr(&bars.x[s]), par, P.abort_flag)) return;
-            umma::fence_after_sync();
-            if (umma::elect_one()) {
-#pragma unroll
-                for (int kk = 0; kk < 2; ++kk) {
-                    const int ks = 2 * s + kk;
-                    umma::mma_bf16_ts(D_H, tmem + COL_W1 + ks * 8, hi_hi + ks * KS_B, idesc, ks != 0);
-                    umma::mma_bf16_ts(D_H, tmem + COL_W1 + ks * 8, hi_lo + ks * KS_B, idesc, 1);
-                    umma::mma_bf16_ts(D_H, tmem + COL_W1 + 64 + ks * 8, hi_hi + ks * KS_B, idesc, 1);
-                }
-                if (s == 3) umma::mma_commit(bh1);
+            for (int ks = 0; ks < 8; ++ks) {
+                umma::mma_bf16_ts(D_H, tmem + COL_W1 + ks * 8, hi_hi + ks * KS_B, idesc, ks != 0);
+                umma::mma_bf16_ts(D_H, tmem + COL_W1 + ks * 8, hi_lo + ks * KS_B, idesc, 1);
+                umma::mma_bf16_ts(D_H, tmem + COL_W1 + 64 + ks * 8, hi_hi + ks * KS_B, idesc, 1);
             }
-            __syncwarp();
+            umma::mma_commit(bh1);
         }
+        __syncwarp();
+        if (mbar_wait_wd(umma::smem_addr(&bars.z), par, P.abort_flag)) return;   // final_convolution_2 (wavenet.py:843), rows >= O zero
+        umma::fence_after_sync();
+        if (umma::elect_one()) {
 #pragma unroll
-        for (int s = 0; s < 4; ++s) {   // final_convolution_2 (wavenet.py:843), rows >= O of the tile are zero
-            if (mbar_wait_wd(umma::smem_addr(&bars.z[s]), par, P.abort_flag)) return;
-            umma::fence_after_sync();
-            if (umma::elect_one()) {
-#pragma unroll
-                for (int kk = 0; kk < 2; ++kk) {
-                    const int ks = 2 * s + kk;
-                    umma::mma_bf16_ts(D_O, tmem + COL_W2 + ks * 8, h2_hi + ks * KS_B, idesc, ks != 0);
-                    umma::mma_bf16_ts(D_O, tmem + COL_W2 + ks * 8, h2_lo + ks * KS_B, idesc, 1);
-                    umma::mma_bf16_ts(D_O, tmem + COL_W2 + 64 + ks * 8, h2_hi + ks * KS_B, idesc, 1);
-                }
-                if (s == 3) umma::mma_commit(bo);
+            for (int ks = 0; ks < 8; ++ks) {
+                umma::mma_bf16_ts(D_O, tmem + COL_W2 + ks * 8, h2_hi + ks * KS_B, idesc, ks != 0);
+                umma::mma_bf16_ts(D_O, tmem + COL_W2 + ks * 8, h2_lo + ks * KS_B, idesc, 1);
+                umma::mma_bf16_ts(D_O, tmem + COL_W2 + 64 + ks * 8, h2_hi + ks * KS_B, idesc, 1);
             }
-            __syncwarp();
+            umma::mma_commit(bo);
         }
+        __syncwarp();
     }
 }
 
@@ -700,12 +765,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
     const int r = blockIdx.x / stages, l = blockIdx.x - r * stages;
     const bool head = l == P.L;
     if (tid == 0) {
-        for (int i = 0; i < 4; ++i) { umma::mbar_init(umma::smem_addr(&bars.x[i]), 2); umma::mbar_init(umma::smem_addr(&bars.z[i]), 2); }
+        umma::mbar_init(umma::smem_addr(&bars.x), EPI_THREADS / 32);
+        umma::mbar_init(umma::smem_addr(&bars.z), EPI_THREADS / 32);
         umma::mbar_init(umma::smem_addr(&bars.gate), 1);
         umma::mbar_init(umma::smem_addr(&bars.out), 1);
         umma::mbar_init(umma::smem_addr(&bars.skip), head ? EPI_THREADS / 32 : 1);   // head: "parameters written" barrier
         umma::mbar_init(umma::smem_addr(&bars.p), EPI_THREADS / 32);
         for (int i = 0; i < 2; ++i) { umma::mbar_init(umma::smem_addr(&bars.wfull[i]), 1); umma::mbar_init(umma::smem_addr(&bars.wempty[i]), 1); }
+        umma::mbar_init(umma::smem_addr(&bars.xf), 1);
         umma::mbar_fence_init();
     }
     if (warp == 0) umma::tmem_alloc(umma::smem_addr(&tmem_base_s), 512);
@@ -728,6 +795,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
     umma::fence_before_sync();
     __syncthreads();
     umma::fence_after_sync();
+    cluster_sync_all();   // the peers' mbarriers exist before anything is sent to them
     if (head) {
         if (warp < 8) head_epilogue<NB, STATS>(P, r, tc_smem, tmem, bars);
         else if (warp == MMA_WARP) head_mma<NB>(P, tc_smem, tmem, bars);
@@ -739,6 +807,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
     // every role returns when the sequence is done (or the watchdog fired): release tensor memory
     umma::fence_before_sync();
     __syncthreads();
+    cluster_sync_all();   // nobody leaves while a peer may still write into its shared memory
     if (warp == 0) umma::tmem_dealloc(tmem, 512);
 }
 
@@ -999,12 +1068,28 @@ int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(TC_THREADS); cfg.stream = st;
     cfg.dynamicSmemBytes = nb == 16 ? Geo<16>::SMEM : Geo<32>::SMEM;
-    cudaLaunchAttribute at[1];
+    const void *kern = nb == 16 ? tc_kernel<16>(p.stats != nullptr) : tc_kernel<32>(p.stats != nullptr);
+    cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeCooperative;
     at[0].val.cooperative = 1;
-    cfg.attrs = at; cfg.numAttrs = 1;
+    // consecutive stages of a replica share a thread-block cluster (a divisor of L + 1, at most 8): inside a cluster x is
+    // handed over through distributed shared memory.  The largest size whose clusters are all co-resident is used.
+    int csize = 1;
+    for (int c = 8; c >= 2; --c) {
+        if ((L + 1) % c) continue;
+        cfg.gridDim = dim3(grid);
+        at[1].id = cudaLaunchAttributeClusterDimension;
+        at[1].val.clusterDim.x = c; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+        cfg.attrs = at + 1; cfg.numAttrs = 1;
+        int ncl = 0;
+        if (cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg) == cudaSuccess && ncl * c >= grid) { csize = c; break; }
+        cudaGetLastError();
+    }
+    if (const char *e = getenv("WN_TC_CLUSTER")) { const int v = atoi(e); if (v >= 1 && v <= 8 && (L + 1) % v == 0) csize = v; }
+    at[1].id = cudaLaunchAttributeClusterDimension;
+    at[1].val.clusterDim.x = csize; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = csize > 1 ? 2 : 1;
     void *args[] = {&p};
-    const void *kern = nb == 16 ? tc_kernel<16>(p.stats != nullptr) : tc_kernel<32>(p.stats != nullptr);
     WN_CUDA_TRY(h, cudaLaunchKernelExC(&cfg, kern, args));
     h->launches++;
     WN_CUDA_TRY(h, cudaMemcpyAsync(pl->h_abort, pl->d_abort, sizeof(int), cudaMemcpyDeviceToHost, st));
