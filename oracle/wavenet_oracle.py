@@ -5,17 +5,23 @@ This file restates, op for op, what the reference's TF-1.x graph computes on the
 It is the checker the CUDA path is compared with.  Only ``tests/``, ``__graft_entry__.smoke()`` and the
 ``cpu_baseline`` / ``--impl reference`` legs of ``bench.py`` may import it; the product never does.
 
-PARITY STATUS: **parity unpinned** for the TF numerics.  The reference ships no golden vectors, no unit tests
-and no fixtures for this path, and TensorFlow 1.x cannot be installed here (F3), so the TF
-ops themselves (matmul, conv2d SAME padding, conv2d_transpose, batch_to_space_nd, resize_images) are
-restated from their published semantics.  What *is* pinned: (a) the reference's own numpy-level helpers
-(mu-law, _interp, _pad_inputs, NN-init kernels, receptive_field_size, save_wavenet_wav, the hparams WaveNet
-blocks) are executed from /root/reference by tests/golden/make_golden.py and committed as fixtures;
-(b) the reference's graph-building Python (modules.py / wavenet.py / gaussian.py / mixture.py) is executed
-over a numpy stand-in for the `tf` namespace by the same script, and this oracle is checked against those
-outputs (tests/test_oracle_vs_reference_shim.py); (c) self-consistency: incremental(teacher forced) ==
-step() with the one-sample conditioning shift, ring buffer == literal shift queue, every upsampler ==
-brute-force loops, NN-init == scaled nearest-neighbour repeat.
+PARITY STATUS: pinned to the reference's own Python, executed here; the TensorFlow kernels themselves stay unpinned.
+The reference ships no golden vectors, unit tests or fixtures for this path and TensorFlow 1.x cannot be
+installed here (F3).  What is pinned, and how:
+(a) tests/golden/make_ref_golden.py imports /root/reference/code and EXECUTES the reference's functions over a numpy
+    stand-in for the `tf` namespace (tests/golden/tf_shim.py): util.py mu-law helpers, feeder._interp,
+    datasets/audio.save_wavenet_wav, receptive_field_size, hparams.py / paper_hparams.py (WaveNet keys),
+    sample_from_gaussian, sample_from_discretized_mix_logistic, and - on six seeded small models covering every input
+    type, head and upsampler - create_model -> WaveNet.initialize (synthesis branch) -> WaveNet.incremental (its
+    while_loop body, CausalConv1D.call(incremental=True), ResidualConv1DGLU.step; free running and teacher forced) and
+    WaveNet.step.  The outputs are committed as tests/golden/ref_*.npz / ref_hparams.json and
+    tests/test_oracle_vs_reference_shim.py holds this oracle and oracle/c to them (1e-5; discrete results exactly).
+(b) NOT pinned: the kernels behind the TF ops (matmul, Conv1D / Conv2D SAME / Conv2DTranspose, batch_to_space_nd,
+    resize_images) - the stand-in restates those from their published semantics, independently of this file; and global
+    conditioning, which the reference's own synthesis branch rejects (wavenet.py:430 compares a TensorShape with a tuple
+    holding a Tensor) and is therefore restated only.
+(c) self-consistency on top: incremental(teacher forced) == step() with the one-sample conditioning shift, ring buffer ==
+    literal shift queue, every upsampler == brute-force loops, NN-init == scaled nearest-neighbour repeat.
 
 Citations are file:line into /root/reference/code/wavenet_vocoder/.
 """

@@ -100,11 +100,13 @@ static std::map<std::string, std::vector<int64_t>> expected_shapes(const wn_conf
     std::map<std::string, std::vector<int64_t>> s;
     const int64_t R = c.residual_channels, G = c.gate_channels, S = c.skip_out_channels, O = c.out_channels,
                   k = c.kernel_size, in_ch = scalar_input(c) ? 1 : c.quantize_channels;
-    auto conv = [&](const std::string &n, int64_t kw, int64_t ci, int64_t co) {
+    auto conv = [&](const std::string &n, int64_t kw, int64_t ci, int64_t co, bool always_bias = false) {
         s[n + "/kernel"] = {kw, ci, co};
-        if (c.use_bias) s[n + "/bias"] = {co};
+        if (c.use_bias || always_bias) s[n + "/bias"] = {co};
     };
-    conv("input_convolution", 1, in_ch, R);
+    // hparams.use_bias reaches the residual blocks only (wavenet.py:118-133); the input and final 1x1s always have a bias
+    // (wavenet.py:103-115, :136-149 build them without the argument)
+    conv("input_convolution", 1, in_ch, R, true);
     for (int l = 0; l < c.layers; ++l) {
         std::string p = "ResidualConv1DGLU_" + std::to_string(l) + "/residual_block_";
         conv(p + "causal_conv", k, R, G);
@@ -113,8 +115,8 @@ static std::map<std::string, std::vector<int64_t>> expected_shapes(const wn_conf
         conv(p + "out_conv", 1, G / 2, R);
         conv(p + "skip_conv", 1, G / 2, S);
     }
-    conv("final_convolution_1", 1, S, S);
-    conv("final_convolution_2", 1, S, O);
+    conv("final_convolution_1", 1, S, S, true);
+    conv("final_convolution_2", 1, S, O, true);
     if (c.gin_channels > 0 && c.use_speaker_embedding) s["gc_embedding"] = {c.n_speakers, c.gin_channels};
     if (c.cin_channels > 0 && c.upsample_type != WN_UP_NEAREST) {
         for (int i = 0; i < c.n_upsample_scales; ++i) {

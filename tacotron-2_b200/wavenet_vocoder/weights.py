@@ -56,12 +56,14 @@ def weight_specs(hp):
 	in_ch = 1 if is_scalar_input(hp.input_type) else hp.quantize_channels
 	specs = OrderedDict()
 
-	def conv(name, kw, cin, cout):
+	def conv(name, kw, cin, cout, bias=None):
 		specs[name + '/kernel'] = (kw, cin, cout)
-		if hp.use_bias:
+		if hp.use_bias if bias is None else bias:
 			specs[name + '/bias'] = (cout,)
 
-	conv('input_convolution', 1, in_ch, R)
+	# hparams.use_bias reaches the residual blocks only (wavenet.py:118-133); the input and the two final 1x1s are built
+	# without the argument and always carry a bias (wavenet.py:103-115, :136-149; Conv1D1x1 default use_bias=True)
+	conv('input_convolution', 1, in_ch, R, bias=True)
 	for l in range(hp.layers):
 		p = 'ResidualConv1DGLU_{}/'.format(l)
 		conv(p + 'residual_block_causal_conv', k, R, G)
@@ -71,8 +73,8 @@ def weight_specs(hp):
 			conv(p + 'residual_block_gin_conv', 1, hp.gin_channels, G)
 		conv(p + 'residual_block_out_conv', 1, G // 2, R)
 		conv(p + 'residual_block_skip_conv', 1, G // 2, S)
-	conv('final_convolution_1', 1, S, S)
-	conv('final_convolution_2', 1, S, O)
+	conv('final_convolution_1', 1, S, S, bias=True)
+	conv('final_convolution_2', 1, S, O, bias=True)
 	if hp.gin_channels > 0 and hp.use_speaker_embedding:
 		specs['gc_embedding'] = (hp.n_speakers, hp.gin_channels)
 	for i, (kshape, bshape, _) in enumerate(upsample_layer_specs(hp)):
@@ -153,7 +155,7 @@ def init_weights(hp, seed=5339, kind='stress'):
 		else:
 			w[name] = (rng.normal(0., 0.05, size=shape).astype(np.float32) if kind == 'stress'
 				else np.zeros(shape, np.float32))
-	if kind == 'stress' and hp.use_bias and is_scalar_input(hp.input_type):
+	if kind == 'stress' and is_scalar_input(hp.input_type):
 		b = w['final_convolution_2/bias']
 		if hp.out_channels == 2:
 			b[1] = -4.
