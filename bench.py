@@ -56,11 +56,12 @@ def parse_args():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS))
-    ap.add_argument('--engine', default='auto', choices=['auto', 'generic', 'pipeline'])
+    ap.add_argument('--engine', default='auto', choices=['auto', 'generic', 'pipeline', 'tc'])
     ap.add_argument('--hparams', default='default_22k', choices=['default_22k', 'paper'])
     ap.add_argument('--no-step-full', action='store_true', help='skip the secondary WaveNet.step (configs[4]) figure')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-strong-c3', action='store_true', help='skip the configs[2] strong-scaling pass (256 x 10 s over the ranks)')
     return ap.parse_args()
 
 
@@ -101,6 +102,17 @@ def cpu_sample(hp, weights, cores, frames=None):
     return cores * frames * hp.hop_size, dt
 
 
+def cpu_shiftqueue_sample(hp, weights, frames=2):
+    """The reference-faithful CPU row of BASELINE.md: one utterance with the LITERAL convolution queues of modules.py:285-292
+    (the whole [2d+1, R] queue of every layer is shifted and re-concatenated every sample), scalar C, one core."""
+    from oracle.c_oracle import COracle
+    co = COracle(hp, weights)
+    c, noise = synth_inputs(hp, [0], frames)
+    t0 = time.perf_counter()
+    co.synthesize(c, noise=noise, nthreads=1, shiftqueue=True)
+    return frames * hp.hop_size, time.perf_counter() - t0
+
+
 def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
@@ -110,25 +122,38 @@ def run_reference(args):
     weights = W.init_weights(hp, seed=5339, kind='tf-init')
     cores = os.cpu_count() or 1
     B, Tc, weak = WORKLOADS[args.workload]
+    frames = 24   # 6 600 samples per utterance, ~5 s per core
     for _ in range(args.warmup):
         cpu_sample(hp, weights, cores, frames=2)
     n_tot, t_tot = 0, 0.0
     for _ in range(args.steps):
-        n, dt = cpu_sample(hp, weights, cores)
+        n, dt = cpu_sample(hp, weights, cores, frames=frames)
         n_tot += n
         t_tot += dt
     v = n_tot / t_tot
-    sample = '{} utterances x 24 frames ({} samples) per step, C oracle port with OpenMP over utterances'.format(cores, cores * 24 * hp.hop_size)
+    sample = ('{} utterances x {} frames ({} samples) per step: a bounded sample of the workload (the CPU cost per sample does not '
+              'depend on batch or length), C restatement of the reference math (oracle/c/wn_oracle.c, ring-buffer queues), OpenMP '
+              'over utterances, upsample included').format(cores, frames, cores * frames * hp.hop_size)
+    cfg = workload_config(args, hp, B, Tc, args.gpus)
+    cfg['measured_sample'] = sample
+    cfg['note'] = ('this arm times the bounded sample above on ONE host (rank 0) whatever --gpus is: the ratio against an N-GPU '
+                   'line compares N GPUs with one host')
     line = {
         'impl': 'reference', 'metric': METRIC, 'value': v, 'unit': UNIT, 'rtf': v / SAMPLE_RATE, 'n_gpus': args.gpus,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * t_tot / args.steps, 'higher_is_better': True,
-        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': workload_config(args, hp, B, Tc, args.gpus),
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': cfg,
         'cpu_baseline': {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample,
                          'note': 'the reference is TensorFlow-1.x Python and cannot run on this box; this is the CPU '
-                                 'restatement of its math (oracle/c/wn_oracle.c)'},
+                                 'restatement of its math (oracle/c/wn_oracle.c), pinned to the reference\'s own Python by '
+                                 'tests/test_oracle_vs_reference_shim.py'},
         'e2e': {'value': v, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
     }
+    try:
+        n, dt = cpu_shiftqueue_sample(hp, weights)
+        line['cpu_baseline_shiftqueue'] = {'value': n / dt, 'unit': UNIT, 'cores': 1, 'kind': 'port',
+                                           'sample': '1 utterance x 2 frames ({} samples), literal shift-and-concat queues (modules.py:285-292)'.format(n)}
+    except Exception as e:
+        line['cpu_baseline_shiftqueue'] = {'error': '{}: {}'.format(type(e).__name__, e)}
     emit(line)
 
 
@@ -225,9 +250,52 @@ def step_full_point(torch, net, hp, peaks):
     tensor_tflops = 3 * flops / (best / 1e3) / 1e12
     return {'workload': 'configs[4]: WaveNet.step, default_22k, 8 utterances x 10 s (1 764 400 positions)', 'ms': best,
             'fp32_equivalent_tflops': flops / (best / 1e3) / 1e12, 'bf16_tensor_tflops': tensor_tflops,
-            'roofline': {'bound': 'tensor', 'achieved': tensor_tflops, 'peak': peak, 'unit': 'TFLOP/s', 'frac': tensor_tflops / peak,
+            'roofline': {'bound': 'tensor', 'achieved': flops / (best / 1e3) / 1e12, 'peak': peak, 'unit': 'TFLOP/s',
+                         'frac': flops / (best / 1e3) / 1e12 / peak, 'executed_bf16_tflops': tensor_tflops, 'executed_frac': tensor_tflops / peak,
                          'peak_source': 'measured burst (MEASURED_PEAKS.json)' if 'bf16_tflops' in peaks else 'fallback (B200_PROFILING.md)',
                          'note': 'three bf16 passes (hi*hi, hi*lo, lo*hi) per fp32 product; see DESIGN.md 4.5'}}
+
+
+def strong_c3_point(torch, dist, net, hp, world, rank):
+    """BASELINE.json configs[2]: 256 utterances x 10 s (802 frames) sharded over the ranks with wavenet_vocoder.sharding (the
+    product's own functions), one pass, end to end: host buffers through wn_synthesize_host on every rank, then the final
+    gather of the audio onto rank 0.  Wall clock between barriers, max over ranks.  Strong scaling: total work is fixed."""
+    from wavenet_vocoder import sharding
+    n_utt, frames = WORKLOADS['c3'][0], WORKLOADS['c3'][1]
+    T = frames * hp.hop_size
+    mine = sharding.shard_utterances([T] * n_utt, world)[rank]
+    c_np, noise_np = synth_inputs(hp, mine, frames)
+    h_audio = np.empty((len(mine), T), np.float32)
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    sync()
+    t0 = time.perf_counter()
+    net.synthesize_host(c_np, noise_np, audio_out=h_audio)
+    info = net.info()
+    if world > 1:
+        out = sharding.gather_wavs(list(h_audio), mine, n_utt)
+    else:
+        out = list(h_audio)
+    sync()
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device='cuda')
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    dt = float(dt.item())
+    if rank != 0:
+        return None
+    assert len(out) == n_utt and all(len(w) == T and np.isfinite(w).all() for w in out) and not info['aborted']
+    v = n_utt * T / dt
+    return {'workload': 'configs[2]: default_22k, 256 utterances x 10 s (802 frames -> 220 550 samples each) sharded over {} GPU(s) '
+                        'with sharding.shard_utterances, final gather with sharding.gather_wavs included'.format(world),
+            'scaling': 'strong', 'value': v, 'unit': UNIT, 'rtf': v / SAMPLE_RATE, 'rtf_target': 1000.0, 'seconds': dt, 'n_gpus': world,
+            'utterances_per_gpu': len(mine), 'engine': info['engine'], 'loop_ms_rank0': info['last_loop_ms'],
+            'us_per_step_rank0': 1e3 * info['last_loop_ms'] / T * (1 if len(mine) <= 224 else 0.5),
+            'replicas': info['pipeline_ctas_per_layer'], 'utterances_per_replica': info['pipeline_group_size'],
+            'limiter': 'serial stage latency of the layer chain (us_per_step x 220 550 steps); no collective on the data path',
+            'api': 'wn_synthesize_host per rank (host buffers) + one gather'}
 
 
 def run_ours(args):
@@ -296,9 +364,10 @@ def run_ours(args):
         loop_ms.append(inf['last_loop_ms'])
         up_ms.append(inf['last_upsample_ms'])
     barrier()
+    assert not net.info()['aborted'], 'the persistent loop kernel hit its watchdog (WN_ERR_WATCHDOG): the numbers would be meaningless'
+    assert bool(torch.isfinite(d_audio).all()), 'non-finite audio after the timed steps'
     total_ms = sum(s.elapsed_time(e) for s, e in ev)
-    launches = net.info()['kernel_launches'] - launches0 + args.steps   # + the flush fill kernels are torch's, not ours
-    launches -= args.steps
+    launches = net.info()['kernel_launches'] - launches0   # this library's kernels only (the L2 flush fills are torch's)
     clocks = sampler.stop() if rank == 0 else None
     t = torch.tensor([total_ms], dtype=torch.float64, device='cuda')
     if world > 1:
@@ -319,6 +388,9 @@ def run_ours(args):
         t0 = time.perf_counter()
         for _ in range(n_e2e):
             net.synthesize_host(h_c.numpy(), h_noise.numpy(), audio_out=h_audio.numpy(), stream=sp)
+            if world > 1:   # the final gather belongs to the path: rank 0 ends up holding every rank's audio
+                d_audio.copy_(h_audio, non_blocking=True)
+                dist.gather(d_audio, gathered, dst=0)
         torch.cuda.synchronize()
         dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device='cuda')
         if world > 1:
@@ -328,6 +400,12 @@ def run_ours(args):
                'steps': n_e2e, 'api': 'wn_synthesize_host (libwavenet_b200.so C ABI), pinned host buffers'}
         assert bool(np.isfinite(h_audio.numpy()).all())
 
+    strong = None
+    if not args.no_strong_c3 and args.workload == 'c2' and args.hparams == 'default_22k':
+        try:
+            strong = strong_c3_point(torch, dist, net, hp, world, rank)
+        except Exception as e:   # a secondary figure must never cost the headline line
+            strong = {'error': '{}: {}'.format(type(e).__name__, e)}
     if rank == 0:
         info = net.info()
         peaks = {}
@@ -355,17 +433,28 @@ def run_ours(args):
         except Exception:
             pass
         fp32_peak = 148 * 128 * 2 * 1.965e9 / 1e12   # CUDA-core fp32 peak (FFMA2), nominal: MEASURED_PEAKS.json has no fp32 figure
-        roofline = {
-            'kernel': 'autoregressive loop kernel ({} engine)'.format(info['engine']), 'bound': 'hbm',
-            'achieved': achieved, 'peak': hbm_peak, 'unit': 'GB/s', 'frac': achieved / hbm_peak, 'traffic': traffic,
-            'traffic_source': traffic_src, 'fp32_peak_tflops_nominal': fp32_peak,
-            'fp32_frac_nominal': info['flops_per_sample'] * B * T / (lm / 1e3) / 1e12 / fp32_peak,
-            'peak_source': peak_src, 'algorithmic_bytes_per_launch': alg_bytes,
-            'bytes_per_sample': int(info['bytes_per_sample']), 'kernel_ms': lm, 'upsample_ms': float(np.mean(up_ms)),
-            'us_per_step': 1e3 * lm / T, 'fp32_tflops': info['flops_per_sample'] * B * T / (lm / 1e3) / 1e12,
+        alg_tflops = info['flops_per_sample'] * B * T / (lm / 1e3) / 1e12
+        common_fields = {
+            'kernel': 'autoregressive loop kernel ({} engine)'.format(info['engine']),
+            'kernel_ms': lm, 'upsample_ms': float(np.mean(up_ms)), 'us_per_step': 1e3 * lm / T,
+            'us_per_step_budget': 11.6, 'algorithmic_flops_per_launch': float(info['flops_per_sample']) * B * T,
+            'algorithmic_bytes_per_launch': alg_bytes, 'bytes_per_sample': int(info['bytes_per_sample']),
+            'hbm_gbs_algorithmic': achieved, 'hbm_frac': achieved / hbm_peak, 'hbm_peak_gbs': hbm_peak, 'peak_source': peak_src,
             'upsample_gbs': B * T * hp.num_mels * 4 * (1 + 1.0 / hp.hop_size) / (float(np.mean(up_ms)) / 1e3) / 1e9,
-            'note': 'the loop is bound by serial step latency (us_per_step), not by bytes or flops; see DESIGN.md',
+            'note': 'the loop is a serial chain of layers + 1 stages per sample: us_per_step (budget 11.6 for the 1000x target) is '
+                    'the figure of merit; bytes and flops are far from their roofs; see DESIGN.md 4.2 / 4.7',
         }
+        if info['engine'] == 'tc':
+            # tcgen05 engine: a batched step is tensor work (north_star); the fraction is on ALGORITHMIC flops against the
+            # measured sustained bf16 GEMM rate; the kernel executes 3 bf16 MMA passes per fp32 product
+            t_peak = peaks.get('bf16_tflops_sustained', peaks.get('bf16_tflops', 1590.0))
+            roofline = dict(common_fields, bound='tensor', achieved=alg_tflops, peak=t_peak, unit='TFLOP/s', frac=alg_tflops / t_peak,
+                            traffic=None, traffic_source='not captured on the timed shape (see profiles/ for the range capture)',
+                            executed_bf16_tflops=3 * alg_tflops, replicas=info['pipeline_ctas_per_layer'], utterances_per_replica=info['pipeline_group_size'])
+        else:
+            roofline = dict(common_fields, bound='hbm', achieved=achieved, peak=hbm_peak, unit='GB/s', frac=achieved / hbm_peak,
+                            traffic=traffic, traffic_source=None if traffic is None else 'EXTRAPOLATED, not measured on this launch: ' + traffic_src,
+                            fp32_peak_tflops_nominal=fp32_peak, fp32_frac_nominal=alg_tflops / fp32_peak, fp32_tflops=alg_tflops)
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'rtf': value / SAMPLE_RATE, 'n_gpus': n_gpus,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': total_ms / args.steps, 'higher_is_better': True,
@@ -375,6 +464,8 @@ def run_ours(args):
         }
         if e2e is not None:
             line['e2e'] = e2e
+        if strong is not None:
+            line['strong_c3'] = strong
         if world == 1 and not args.no_step_full and args.hparams == 'default_22k':
             try:   # a secondary figure must never cost the headline line
                 line['step_full'] = step_full_point(torch, net, hp, peaks)

@@ -60,7 +60,8 @@ typedef struct wn_config {
     int32_t hop_size;
     int32_t gin_channels;         /* <= 0 disables global conditioning */
     int32_t use_speaker_embedding, n_speakers;
-    int32_t engine;               /* wn_engine; AUTO picks the pipelined persistent kernel when the model fits it */
+    int32_t engine;               /* wn_engine; AUTO: the tensor-core loop engine (WN_ENGINE_TC) for the 128-channel block it is built
+                                     for, else the pipelined fp32 engine when the model fits it, else the generic one */
     int32_t ksplit;               /* fp32 summation order of the out / skip 1x1s: number of contiguous blocks of the gated
                                      channels summed separately and then added up (DESIGN.md "Arithmetic").  0 = the
                                      pipelined engine's CTAs-per-layer (1 when only the generic engine applies).  Both
@@ -80,6 +81,7 @@ typedef struct wn_info {
     int64_t kernel_launches;      /* kernels launched by this handle so far (for the bench's gpu_launches) */
     float last_upsample_ms;       /* CUDA-event duration of the upsampling net in the last completed wn_synthesize (-1: n/a) */
     float last_loop_ms;           /* CUDA-event duration of the loop kernel in the last completed wn_synthesize (-1: n/a) */
+    int32_t aborted;              /* 1: the persistent kernel of the last call gave up waiting (WN_ERR_WATCHDOG); read after a stream sync */
 } wn_info;
 
 typedef struct wn_handle wn_handle;

@@ -319,7 +319,7 @@ class WaveNetOracle(object):
 			c_btc = np.transpose(c_up, [0, 2, 1])	#self.c, wavenet.py:801
 		else:
 			assert time_length is not None
-			B = len(test_inputs) if test_inputs is not None else (len(g) if g is not None else 1)
+			B = len(test_inputs) if test_inputs is not None else (len(g) if g is not None else (np.shape(noise)[1] if noise is not None else 1))
 			c_btc = None
 		if test_inputs is not None:
 			test_inputs = np.asarray(test_inputs)

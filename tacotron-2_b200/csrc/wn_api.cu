@@ -314,10 +314,12 @@ extern "C" int wn_finalize(wn_handle *h) {
         else if (c.engine == WN_ENGINE_PIPELINE) return fail(h, WN_ERR_INVALID, "pipeline engine unavailable: " + h->err);
         else h->err.clear();
     }
-    if (c.engine == WN_ENGINE_TC) {   // the tensor-core loop engine; the fp32 engines stay planned as its fall-back (large batches, WaveNet.step)
+    // the tensor-core loop engine: on request, and AUTO's choice for the block it is built for (parity by tolerance, 1e-3
+    // criterion, instead of bit for bit; the fp32 engines stay planned: WaveNet.step's serial path, explicit requests)
+    if (c.engine == WN_ENGINE_TC || (c.engine == WN_ENGINE_AUTO && wn_tc_supported(h) && !getenv("WN_AUTO_FP32"))) {
         int trc = wn_tc_plan(h);
-        if (trc) return fail(h, WN_ERR_INVALID, "tensor-core engine unavailable: " + h->err);
-        h->engine = WN_ENGINE_TC;
+        if (trc && c.engine == WN_ENGINE_TC) return fail(h, WN_ERR_INVALID, "tensor-core engine unavailable: " + h->err);
+        if (!trc) h->engine = WN_ENGINE_TC; else h->err.clear();
     }
     h->finalized = true;
     return WN_OK;
@@ -382,7 +384,7 @@ extern "C" int wn_synthesize(wn_handle *h, const float *c, const int32_t *g_ids,
     rc = prep_conditioning(h, c, g_ids, B, Tc, c_up_out, &c_up, &g_emb, st);
     if (rc) return rc;
     WN_CUDA_TRY(h, cudaEventRecord(h->ev[1], st));
-    if (h->engine == WN_ENGINE_TC && B <= wn_tc_max_batch(h)) rc = wn_launch_loop_tc(h, c_up, noise, teacher, 0, B, T, audio, raw, st);
+    if (h->engine == WN_ENGINE_TC) rc = wn_launch_loop_tc(h, c_up, noise, teacher, 0, B, T, audio, raw, st);
     else if (h->pipe) rc = wn_launch_loop_pipe(h, c_up, noise, teacher, 0, B, T, audio, raw, st);
     else rc = wn_launch_loop_generic(h, c_up, g_emb, noise, teacher, 0, B, T, audio, raw, st);
     if (rc) return rc;
@@ -480,6 +482,7 @@ extern "C" int wn_query(wn_handle *h, wn_info *info) {
     }
     wn_pipe_fill_info(h, info);
     wn_tc_fill_info(h, info);
+    info->aborted = (wn_tc_check_abort(h) != WN_OK || wn_pipe_check_abort(h) != WN_OK) ? 1 : 0;   // meaningful after a stream sync
     return WN_OK;
 }
 

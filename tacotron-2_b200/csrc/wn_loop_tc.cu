@@ -4,10 +4,10 @@
 // every MMA); a replica is a chain of L + 1 CTAs, one per residual layer plus one head CTA, each alone on its SM:
 //
 //   layer CTA l  (ResidualConv1DGLU.incremental_step, modules.py:468-521)
-//     * the weights every step needs at once stay ON CHIP for the whole launch, as bf16 (hi, lo) pairs:
+//     * the weights every step needs at once stay ON CHIP for the whole launch, as fp16 (hi, lo) pairs:
 //         current-tap rows of the dilated conv (256 x 128) and the residual 1x1 (128 x 128) in TENSOR MEMORY as the A operand
 //         of tcgen05.mma (lane = output channel, one 32-bit column = two consecutive k), the skip 1x1 in shared memory;
-//     * per step: x_l(t) arrives -> bf16 (hi, lo) image in shared memory (the B operand, K-major) -> 48 MMAs
+//     * per step: x_l(t) arrives -> fp16 (hi, lo) image in shared memory (the B operand, K-major) -> 48 MMAs
 //       (M = 128, N = NB, K = 16; two gate halves x 8 k steps x three passes hi*hi + hi*lo + lo*hi) on top of the part of the
 //       pre-activation that does not depend on x_l(t) -> tcgen05.ld -> tanh * sigmoid -> z image -> 24 MMAs (residual
 //       1x1) -> x_{l+1}(t) = (out + b + x_l(t)) * sqrt(0.5) leaves for the next CTA; 24 more MMAs (skip 1x1) -> the skip
@@ -23,9 +23,11 @@
 // separate from the data.  The dilation rings live in global memory (L2); every ring element is written and later read
 // by the same thread.
 //
-// Arithmetic: fp32 accumulation everywhere; products are bf16-split (16 mantissa bits per operand), so results agree
-// with the fp32 engines to ~1e-5 relative, not bit for bit (tests: tests/test_gpu_tc.py, criterion 1e-3 of BASELINE.json).
-#include <cuda_bf16.h>
+// Arithmetic: fp32 accumulation everywhere; every fp32 operand is split into two fp16 numbers (22 significant bits) and a
+// product is three MMA passes, so results agree with the fp32 engines to ~1e-6 relative - the summation order differs, so not
+// bit for bit (tests: tests/test_gpu_tc.py, criterion 1e-3 of BASELINE.json).  Operands must stay inside the fp16 range
+// (|v| < 65504): weights and activations of a WaveNet are orders of magnitude below it.
+#include <cuda_fp16.h>
 
 #include <algorithm>
 #include <cstdlib>
@@ -41,7 +43,7 @@ constexpr int EPI_THREADS = 256;         // 8 epilogue warps: TMEM lane quarter 
 constexpr int MMA_WARP = 8, LOAD_WARP = 9;
 constexpr int TC_THREADS = 320;
 constexpr int KB_TOTAL = 11;             // 32-wide k blocks of the streamed weights: tap0 4, tap1 4, cin 3 (80 + 16 zero)
-constexpr int NCHUNK = 2 * KB_TOTAL;     // (k block, gate half), 16 KB each: A image [4][128][8] bf16 hi, then lo
+constexpr int NCHUNK = 2 * KB_TOTAL;     // (k block, gate half), 16 KB each: A image [4][128][8] fp16 hi, then lo
 constexpr int CHUNK_BYTES = 16384;
 constexpr int CI_K = 96;                 // K of the conditioning image (cin <= 96, zero padded)
 constexpr unsigned long long WATCHDOG_NS = 20ull * 1000 * 1000 * 1000;
@@ -76,6 +78,8 @@ struct TcParams {
     int inputs_mode;
     float *audio, *raw;
     int B, T, NR;
+    int bend;                            // one past the last utterance of this launch
+    int b0;                              // first utterance of this launch in the caller's batch of B (batches above the launch limit run in chunks)
 };
 
 template <int NB>
@@ -187,22 +191,28 @@ __device__ __forceinline__ bool mbar_wait_cluster_wd(uint32_t bar, uint32_t pari
     return false;
 }
 
-// ---- activation images: [K/8][NB][8] bf16, hi plane then lo plane; one thread per channel writes 2-byte elements ---------
-__device__ __forceinline__ void img_put(unsigned char *img, int plane, int lbo, int j, int n, float v) {
-    const uint32_t h = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(v));
-    const float r = __fsub_rn(v, __uint_as_float(h << 16));
-    const uint32_t l = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(r));
-    const int off = (j >> 3) * lbo + n * 16 + (j & 7) * 2;
-    *reinterpret_cast<unsigned short *>(img + off) = (unsigned short)h;
-    *reinterpret_cast<unsigned short *>(img + plane + off) = (unsigned short)l;
+// ---- activation images: [K/8][NB][8] fp16, hi plane then lo plane; one thread per channel writes 2-byte elements ---------
+// v -> (hi, lo) with hi = v rounded to 11 significant bits (what fp16 holds), lo = fp16(v - hi): hi + lo carries 22 bits of v, so
+// the three MMA passes hi*hi + hi*lo + lo*hi reproduce the fp32 product to ~2^-22.  hi is rounded with integer operations
+// (round to nearest even on bit 13): exactly representable in fp16 for |v| in [6.1e-5, 65504], which the conversions below
+// then pack without a second rounding; below that range the absolute error is < 6e-8.
+__device__ __forceinline__ float round11(float v) {
+    const uint32_t u = __float_as_uint(v);
+    return __uint_as_float((u + 0x00000fffu + ((u >> 13) & 1u)) & 0xffffe000u);
 }
-// two neighbouring utterances n, n + 1 of one channel: one packed conversion per plane (float -> bf16 conversions run on the
+__device__ __forceinline__ void img_put(unsigned char *img, int plane, int lbo, int j, int n, float v) {
+    const float hf = round11(v);
+    const int off = (j >> 3) * lbo + n * 16 + (j & 7) * 2;
+    *reinterpret_cast<unsigned short *>(img + off) = __half_as_ushort(__float2half_rn(hf));
+    *reinterpret_cast<unsigned short *>(img + plane + off) = __half_as_ushort(__float2half_rn(__fsub_rn(v, hf)));
+}
+// two neighbouring utterances n, n + 1 of one channel: one packed conversion per plane (float -> half conversions run on the
 // 16-lane special-function pipe, which bounds the epilogues of this kernel)
 __device__ __forceinline__ void img_put2(unsigned char *p /* element (j, n) of the hi plane */, int plane, float v0, float v1) {
+    const float h0 = round11(v0), h1 = round11(v1);
     uint32_t h, l;
-    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(v1), "f"(v0));
-    const float r0 = __fsub_rn(v0, __uint_as_float(h << 16)), r1 = __fsub_rn(v1, __uint_as_float(h & 0xffff0000u));
-    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(l) : "f"(r1), "f"(r0));
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(h1), "f"(h0));
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(l) : "f"(__fsub_rn(v1, h1)), "f"(__fsub_rn(v0, h0)));
     *reinterpret_cast<unsigned short *>(p) = (unsigned short)h;
     *reinterpret_cast<unsigned short *>(p + 16) = (unsigned short)(h >> 16);
     *reinterpret_cast<unsigned short *>(p + plane) = (unsigned short)l;
@@ -315,8 +325,8 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         for (int i = 0; i < CN; ++i) {
             const int e = tid + i * EPI_THREADS;
             const int n = e / cin, k = e - n * cin;
-            const long long b = (long long)r * NB + n;
-            cnd[i] = (n < NB && b < P.B) ? __ldg(P.c_up + (b * T + t) * cin + k) : 0.0f;
+            const long long b = (long long)P.b0 + r * NB + n;
+            cnd[i] = (n < NB && b < P.bend) ? __ldg(P.c_up + (b * T + t) * cin + k) : 0.0f;
         }
     };
     auto prep_store = [&]() {
@@ -461,7 +471,7 @@ template <int NB>
 __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t tmem, Bars &bars) {
     using G = Geo<NB>;
     constexpr int LBO = G::LBO, PLANE = G::PLANE;
-    constexpr uint32_t idesc = umma::idesc_bf16(CH, NB);
+    constexpr uint32_t idesc = umma::idesc_f16(CH, NB);
     const int T = P.T;
     const uint32_t s0 = umma::smem_addr(smem);
     const uint32_t D_A = tmem + COL_ACC, D_B = tmem + COL_ACC + NB, D_O = tmem + COL_ACC + 2 * NB, D_S = tmem + COL_ACC + 3 * NB;
@@ -595,8 +605,8 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
     float *prm = reinterpret_cast<float *>(smem + G::S_PRM);   // [NB][CH]
     const uint32_t bh = umma::smem_addr(&bars.x), bh2 = umma::smem_addr(&bars.z), bh1 = umma::smem_addr(&bars.gate),
                    bo = umma::smem_addr(&bars.out), bprm = umma::smem_addr(&bars.skip);
-    const long long bu = (long long)r * NB + tid;          // utterance of the sampler thread
-    const bool sampler = tid < NB && bu < P.B;
+    const long long bu = (long long)P.b0 + r * NB + tid;   // utterance of the sampler thread
+    const bool sampler = tid < NB && bu < P.bend;
     // initial input (wavenet.py:433-445): raw 0.0, mulaw mulaw(0) = 0.0; WaveNet.step semantics: the first input is x[0]
     if (tid < NB) st_ll1(min_out + tid, (sampler && P.inputs_mode) ? P.teacher[bu * T] : 0.0f, 1u);
     long long st_c[4] = {0, 0, 0, 0};
@@ -660,8 +670,8 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
                 for (int i = 0; i < NH; ++i) {
                     const float y = __fadd_rn(o[i], b2);
                     prm[(n0 + i) * CH + j] = y;
-                    const long long b = (long long)r * NB + n0 + i;
-                    if (P.raw && b < P.B) P.raw[(b * T + t) * O + j] = y;   // wavenet.py:847
+                    const long long b = (long long)P.b0 + r * NB + n0 + i;
+                    if (P.raw && b < P.bend) P.raw[(b * T + t) * O + j] = y;   // wavenet.py:847
                 }
             }
         }
@@ -698,7 +708,7 @@ template <int NB>
 __device__ void head_mma(const TcParams &P, unsigned char *smem, const uint32_t tmem, Bars &bars) {
     using G = Geo<NB>;
     constexpr int LBO = G::LBO, PLANE = G::PLANE;
-    constexpr uint32_t idesc = umma::idesc_bf16(CH, NB);
+    constexpr uint32_t idesc = umma::idesc_f16(CH, NB);
     const uint32_t s0 = umma::smem_addr(smem);
     const uint64_t hi_hi = umma::smem_desc(s0 + G::S_HI, LBO, 128), hi_lo = umma::smem_desc(s0 + G::S_HI + PLANE, LBO, 128);
     const uint64_t h2_hi = umma::smem_desc(s0 + G::S_H2, LBO, 128), h2_lo = umma::smem_desc(s0 + G::S_H2 + PLANE, LBO, 128);
@@ -828,25 +838,14 @@ struct WnTcPlan {
     long long *d_stats = nullptr;
     int stats_ctas = 0;
     int max_replicas = 0;
-    int last_nb = 0, last_nr = 0;
+    int last_nb = 0, last_nr = 0, last_cluster = 1;
 };
 
-static uint16_t bf16_rn_host(float f) {
-    uint32_t u;
-    memcpy(&u, &f, 4);
-    if ((u & 0x7f800000u) == 0x7f800000u) return (uint16_t)(u >> 16);   // inf / nan: truncate
-    const uint32_t r = u + 0x7fffu + ((u >> 16) & 1u);
-    return (uint16_t)(r >> 16);
-}
-static float bf16_f_host(uint16_t h) {
-    const uint32_t u = (uint32_t)h << 16;
-    float f;
-    memcpy(&f, &u, 4);
-    return f;
-}
-static void split_host(float v, uint16_t &hi, uint16_t &lo) {
-    hi = bf16_rn_host(v);
-    lo = bf16_rn_host(v - bf16_f_host(hi));
+static void split_host(float v, uint16_t &hi, uint16_t &lo) {   // fp16 (hi, lo): 22 significant bits of v
+    const __half h = __float2half_rn(v);
+    const __half l = __float2half_rn(v - __half2float(h));
+    memcpy(&hi, &h, 2);
+    memcpy(&lo, &l, 2);
 }
 
 bool wn_tc_supported(const wn_handle *h) {
@@ -985,7 +984,7 @@ int wn_tc_plan(wn_handle *h) {
     return WN_OK;
 }
 
-// largest batch one launch takes (wn_synthesize falls back to the fp32 pipelined engine above it)
+// largest batch one launch takes; larger batches run as several launches
 int wn_tc_max_batch(const wn_handle *h) { return h->tc ? h->tc->max_replicas * 32 : 0; }
 
 void wn_tc_fill_info(wn_handle *h, wn_info *info) {
@@ -1022,18 +1021,14 @@ int wn_tc_check_abort(wn_handle *h) {   // after the stream has been synchronise
     return WN_ERR_WATCHDOG;
 }
 
-int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int inputs_mode, int B, int T,
-                      float *audio, float *raw, cudaStream_t st) {
+static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStream_t st) {
     WnTcPlan *pl = h->tc;
-    if (!pl) { h->err = "tensor-core loop engine not planned"; return WN_ERR_STATE; }
-    TcParams p = pl->prm;
-    int nb = (B <= pl->max_replicas * 16) ? 16 : 32;
+    int nb = (nbatch <= pl->max_replicas * 16) ? 16 : 32;
     if (const char *e = getenv("WN_TC_NB")) { const int v = atoi(e); if (v == 16 || v == 32) nb = v; }
-    const int nr = (B + nb - 1) / nb;
+    const int nr = (nbatch + nb - 1) / nb;
     if (nr > pl->max_replicas) { h->err = "tensor-core loop engine: batch too large for one launch"; return WN_ERR_INVALID; }
     pl->last_nb = nb; pl->last_nr = nr;
-    p.B = B; p.T = T; p.NR = nr;
-    p.c_up = c_up; p.noise = noise; p.teacher = teacher; p.inputs_mode = inputs_mode; p.audio = audio; p.raw = raw;
+    p.NR = nr; p.b0 = b0; p.bend = b0 + nbatch;
     const int L = p.L;
     // mailboxes: x [NR][L][2][128*NB] | skip [NR][L][2][128*NB] | in [NR][2][NB], 8-byte {value, tag} words, zeroed (tag 0 = empty)
     const size_t mailw = (size_t)CH * nb;
@@ -1057,7 +1052,6 @@ int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const
     }
     p.ring = pl->d_ring;
     WN_CUDA_TRY(h, cudaMemsetAsync(pl->d_mail, 0, words * 8, st));
-    WN_CUDA_TRY(h, cudaMemsetAsync(pl->d_abort, 0, sizeof(int), st));
     const int grid = nr * (L + 1);
     p.stats = nullptr;
     if (getenv("WN_TC_STATS")) {
@@ -1077,7 +1071,6 @@ int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const
     int csize = 1;
     for (int c = 8; c >= 2; --c) {
         if ((L + 1) % c) continue;
-        cfg.gridDim = dim3(grid);
         at[1].id = cudaLaunchAttributeClusterDimension;
         at[1].val.clusterDim.x = c; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
         cfg.attrs = at + 1; cfg.numAttrs = 1;
@@ -1089,9 +1082,28 @@ int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const
     at[1].id = cudaLaunchAttributeClusterDimension;
     at[1].val.clusterDim.x = csize; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = csize > 1 ? 2 : 1;
+    pl->last_cluster = csize;
     void *args[] = {&p};
     WN_CUDA_TRY(h, cudaLaunchKernelExC(&cfg, kern, args));
     h->launches++;
+    return WN_OK;
+}
+
+// Batches above the launch limit (7 replicas of 32 utterances on 148 SMs) run as consecutive launches over equal chunks.
+int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int inputs_mode, int B, int T,
+                      float *audio, float *raw, cudaStream_t st) {
+    WnTcPlan *pl = h->tc;
+    if (!pl) { h->err = "tensor-core loop engine not planned"; return WN_ERR_STATE; }
+    TcParams p = pl->prm;
+    p.B = B; p.T = T;
+    p.c_up = c_up; p.noise = noise; p.teacher = teacher; p.inputs_mode = inputs_mode; p.audio = audio; p.raw = raw;
+    WN_CUDA_TRY(h, cudaMemsetAsync(pl->d_abort, 0, sizeof(int), st));
+    const int cap = pl->max_replicas * 32;
+    const int nchunks = (B + cap - 1) / cap, per = (B + nchunks - 1) / nchunks;
+    for (int b0 = 0; b0 < B; b0 += per) {
+        const int rc = tc_launch_chunk(h, p, b0, std::min(per, B - b0), st);
+        if (rc) return rc;
+    }
     WN_CUDA_TRY(h, cudaMemcpyAsync(pl->h_abort, pl->d_abort, sizeof(int), cudaMemcpyDeviceToHost, st));
     return WN_OK;
 }

@@ -1,35 +1,44 @@
-"""Run logger with the call contract of the reference's ``infolog.log`` (``code/infolog.py:25-31``):
-one line to stdout, optionally appended to a file opened by ``init``.  The Slack webhook of the
-reference is out of scope."""
+"""Run log with the call contract of the reference's `infolog` (code/infolog.py: `init(filename, run_name, slack_url=None)`,
+`log(msg, end='\\n', slack=False)`): every message goes to stdout and, once `init` has named a file, is appended there with a
+millisecond timestamp.  The reference's Slack webhook is out of scope; `slack` is accepted
+and ignored."""
 import atexit
-from datetime import datetime
+import sys
+import time
 
-_format = '%Y-%m-%d %H:%M:%S.%f'
-_file = None
-_run_name = None
+
+class _RunLog(object):
+	def __init__(self):
+		self.sink = None
+
+	def open(self, filename, run_name):
+		self.close()
+		self.sink = open(filename, 'a', encoding='utf-8')
+		bar = '-' * 65
+		self.sink.write('\n{0}\nStarting new {1} training run\n{0}\n'.format(bar, run_name))
+		self.sink.flush()
+
+	def write(self, msg, end):
+		sys.stdout.write('{}{}'.format(msg, end))
+		if self.sink is not None:
+			now = time.time()
+			stamp = time.strftime('%Y-%m-%d %H:%M:%S', time.localtime(now)) + '.{:03d}'.format(int(now * 1000) % 1000)
+			self.sink.write('[{}]  {}\n'.format(stamp, msg))
+			self.sink.flush()
+
+	def close(self):
+		if self.sink is not None:
+			self.sink.close()
+			self.sink = None
+
+
+_log = _RunLog()
+atexit.register(_log.close)
 
 
 def init(filename, run_name, slack_url=None):
-	global _file, _run_name
-	_close_logfile()
-	_file = open(filename, 'a', encoding='utf-8')
-	_file.write('\n-----------------------------------------------------------------\n')
-	_file.write('Starting new {} training run\n'.format(run_name))
-	_file.write('-----------------------------------------------------------------\n')
-	_run_name = run_name
+	_log.open(filename, run_name)
 
 
 def log(msg, end='\n', slack=False):
-	print(msg, end=end)
-	if _file is not None:
-		_file.write('[%s]  %s\n' % (datetime.now().strftime(_format)[:-3], msg))
-
-
-def _close_logfile():
-	global _file
-	if _file is not None:
-		_file.close()
-		_file = None
-
-
-atexit.register(_close_logfile)
+	_log.write(msg, end)

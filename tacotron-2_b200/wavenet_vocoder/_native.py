@@ -50,7 +50,7 @@ class WnInfo(C.Structure):
 		('bytes_per_sample', C.c_int64), ('weight_bytes', C.c_int64), ('engine', C.c_int32), ('ksplit', C.c_int32),
 		('pipeline_ctas', C.c_int32), ('pipeline_ctas_per_layer', C.c_int32), ('pipeline_group_size', C.c_int32),
 		('sm_count', C.c_int32), ('kernel_launches', C.c_int64),
-		('last_upsample_ms', C.c_float), ('last_loop_ms', C.c_float)]
+		('last_upsample_ms', C.c_float), ('last_loop_ms', C.c_float), ('aborted', C.c_int32)]
 
 
 _lib = None

@@ -32,6 +32,22 @@ def make_noise(hp, T, B, rng):
 	return rng.uniform(0., 1., (T, B, 1)).astype(np.float32)
 
 
+class _LazyTower(object):
+	"""A one-tower list whose element is produced on first access."""
+	def __init__(self, make):
+		self._make, self._val, self._done = make, None, False
+	def __len__(self):
+		return 1
+	def __getitem__(self, i):
+		if i not in (0, -1):
+			raise IndexError(i)
+		if not self._done:
+			self._val, self._done = self._make(), True
+		return self._val
+	def __iter__(self):
+		yield self[0]
+
+
 class WaveNet(object):
 	"""Tacotron-2 Wavenet Vocoder model (synthesis path)."""
 
@@ -61,6 +77,7 @@ class WaveNet(object):
 	# ---- weights ("restore") ------------------------------------------------------------------------
 	def load_weights(self, weights):
 		"""weights: dict name -> array in TF layouts (wavenet_vocoder/weights.py).  Uploads to the current CUDA device."""
+		weights = wn_weights.fold_weight_norm(self._hparams, weights)	#modules.py:44-181 at synthesis time (row H4e)
 		wn_weights.check_weights(self._hparams, weights)
 		if self._native is not None:
 			self._native.close()
@@ -94,13 +111,27 @@ class WaveNet(object):
 		if y is not None or x is not None:
 			raise NotImplementedError('training / evaluation towers are out of scope (disabled in the reference fork)')
 		if c is None:
-			raise NotImplementedError('synthesis without local conditioning needs synthesis_length; use incremental()')
-		c = np.asarray(c, np.float32)
-		if c.ndim != 3:
-			raise ValueError('Expected 3 dimension shape [batch_size(1), time_length, {}] for local condition features '
-				'but found {}'.format(hp.cin_channels, c.shape))	#wavenet.py:414-417
-		B, Tc, _ = c.shape
-		T = Tc * get_hop_size(hp)	#wavenet.py:419-423
+			#wavenet.py:409-411: without local conditioning the length comes from synthesis_length
+			if synthesis_length is None:
+				raise AssertionError('synthesis_length is required when c is None (wavenet.py:410)')
+			if hp.cin_channels > 0:
+				raise ValueError('this model was built with local conditioning (cin_channels > 0): c is required')
+			T = int(synthesis_length)
+			if noise is not None:
+				B = np.asarray(noise).shape[1]
+			elif g is not None:
+				B = np.asarray(g).shape[0]
+			elif test_inputs is not None:
+				B = np.asarray(test_inputs).shape[0]
+			else:
+				B = 1
+		else:
+			c = np.asarray(c, np.float32)
+			if c.ndim != 3:
+				raise ValueError('Expected 3 dimension shape [batch_size(1), time_length, {}] for local condition features '
+					'but found {}'.format(hp.cin_channels, c.shape))	#wavenet.py:414-417
+			B, Tc, _ = c.shape
+			T = Tc * get_hop_size(hp)	#wavenet.py:419-423
 		teacher = None
 		if test_inputs is not None:
 			teacher = np.asarray(test_inputs, np.float32).reshape(B, -1)
@@ -115,7 +146,8 @@ class WaveNet(object):
 		if raw is not None:
 			#scalar input: [B, O, T]; mulaw-quantize: [B, T, C]  (wavenet.py:904-908)
 			self.tower_y_hat_eval = [raw if is_mulaw_quantize(hp.input_type) else np.transpose(raw, [0, 2, 1])]
-		self.tower_synth_upsampled_local_features = [None]	#materialised on request by upsample()
+		#wavenet.py:458-459: [B, cin, T], 80 x the audio and only ever plotted -> computed when somebody reads it
+		self.tower_synth_upsampled_local_features = _LazyTower((lambda: self.upsample(c)) if c is not None else (lambda: None))
 		return audio
 
 	def upsample(self, c):
@@ -131,20 +163,44 @@ class WaveNet(object):
 		torch.cuda.synchronize()
 		return out.permute(0, 2, 1).contiguous().cpu().numpy()
 
-	def incremental(self, initial_input=None, c=None, g=None, time_length=100, test_inputs=None, softmax=True,
-			quantize=True, log_scale_min=-7.0, log_scale_min_gauss=-7.0, noise=None):
-		"""Reference signature (wavenet.py:724).  c here is [B, cin, Tc] (channels first, as the reference passes it);
-		returns generated samples [B, C, T] (scalar input: C=1; mulaw-quantize: one-hot C=quantize_channels).
-		initial_input / softmax / log_scale_* are accepted for signature compatibility: the start frame is the
-		reference's silence frame and the scale floors come from hparams, exactly as initialize() passes them."""
+	def incremental(self, initial_input=None, c=None, g=None, time_length=100, test_inputs=None, softmax=False,
+			quantize=True, log_scale_min=None, log_scale_min_gauss=None, noise=None):
+		"""Reference signature (wavenet.py:724).  c is [B, cin, Tc] (channels first, as the reference passes it) or None with
+		time_length steps (models built with cin_channels <= 0); returns the generated samples [B, C, T] (scalar input: C = 1,
+		the value fed back, i.e. still mu-law companded for input_type 'mulaw'; mulaw-quantize: one-hot of the sampled class).
+		The kernels implement what initialize() asks of this function (wavenet.py:447-448): start from the silence frame,
+		softmax=False, quantize=True, scale floors from hparams.  Other argument values are rejected, not ignored."""
 		hp = self._hparams
+		if softmax and not self.scalar_input:
+			raise NotImplementedError('softmax=True re-normalises the logits before tf.multinomial (wavenet.py:861-865); '
+				'initialize() passes softmax=False and so does this build')
+		if not quantize and not self.scalar_input:
+			raise NotImplementedError('quantize=False (feeding back the un-sampled distribution) is not built')
+		for name, val, ref in (('log_scale_min', log_scale_min, hp.log_scale_min),
+				('log_scale_min_gauss', log_scale_min_gauss, hp.log_scale_min_gauss)):
+			if val is not None and abs(float(val) - float(ref)) > 1e-6 * max(1.0, abs(float(ref))):
+				raise ValueError('{}={} differs from hparams.{}={}: the scale floors are fixed when the model is created'.format(
+					name, val, name, ref))
+		if initial_input is not None:
+			ii = np.asarray(initial_input, np.float32)
+			if self.scalar_input:
+				ok = np.all(ii == 0.0)	#raw 0.0 / mulaw(0.0) = 0.0 (wavenet.py:433-445)
+			else:
+				ok = np.all(np.argmax(ii.reshape(ii.shape[0], -1), axis=-1) == util.mulaw_quantize(0, hp.quantize_channels))
+			if not ok:
+				raise NotImplementedError('only the reference silence start frame is supported as initial_input (wavenet.py:433-445)')
 		if c is None:
-			raise NotImplementedError('local conditioning is required by this build (both shipped configs use it)')
-		c_btc = np.ascontiguousarray(np.transpose(np.asarray(c, np.float32), [0, 2, 1]))
-		audio = self.initialize(None, c_btc, g, None, test_inputs=test_inputs, noise=noise)
+			audio = self.initialize(None, None, g, None, synthesis_length=time_length, test_inputs=test_inputs, noise=noise)
+		else:
+			c_btc = np.ascontiguousarray(np.transpose(np.asarray(c, np.float32), [0, 2, 1]))
+			audio = self.initialize(None, c_btc, g, None, test_inputs=test_inputs, noise=noise)
 		B = audio.shape[0]
 		if is_mulaw_quantize(hp.input_type):
-			cls = util.mulaw_quantize(audio, hp.quantize_channels)
+			#the kernel decoded class k to inv_mulaw_quantize(k): recover k by nearest table entry (re-quantising the decoded
+			#value is NOT the identity: truncation moves 77 of the 256 classes by one)
+			table = util.inv_mulaw_quantize(np.arange(hp.quantize_channels), hp.quantize_channels).astype(np.float64)
+			pos = np.clip(np.searchsorted(table, audio.astype(np.float64)), 1, len(table) - 1)
+			cls = np.where(np.abs(audio - table[pos - 1]) <= np.abs(audio - table[pos]), pos - 1, pos)
 			return np.transpose(np.eye(hp.quantize_channels, dtype=np.float32)[cls], [0, 2, 1])
 		if is_mulaw(hp.input_type):
 			return util.mulaw(audio, hp.quantize_channels).astype(np.float32).reshape(B, 1, -1)
@@ -158,13 +214,18 @@ class WaveNet(object):
 		x = np.asarray(x, np.float32)
 		B, Cin, T = x.shape
 		xin = x[:, 0, :] if self.scalar_input else np.argmax(x, axis=1).astype(np.float32)
-		c_btc = np.ascontiguousarray(np.transpose(np.asarray(c, np.float32), [0, 2, 1]))
-		Tc = c_btc.shape[1]
-		if Tc * get_hop_size(hp) != T:
-			raise ValueError('upsampled conditioning length {} != input length {} (wavenet.py:697)'.format(
-				Tc * get_hop_size(hp), T))
+		if c is None:
+			if hp.cin_channels > 0:
+				raise ValueError('this model was built with local conditioning (cin_channels > 0): c is required')
+			Tc, dc = T, None
+		else:
+			c_btc = np.ascontiguousarray(np.transpose(np.asarray(c, np.float32), [0, 2, 1]))
+			Tc = c_btc.shape[1]
+			if Tc * get_hop_size(hp) != T:
+				raise ValueError('upsampled conditioning length {} != input length {} (wavenet.py:697)'.format(
+					Tc * get_hop_size(hp), T))
+			dc = torch.from_numpy(c_btc).cuda()
 		dx = torch.from_numpy(np.ascontiguousarray(xin)).cuda()
-		dc = torch.from_numpy(c_btc).cuda()
 		dg = None if g is None else torch.from_numpy(np.asarray(g, np.int32).reshape(B)).cuda()
 		raw = torch.empty((B, T, hp.out_channels), dtype=torch.float32, device='cuda')
 		self.native.step_full(dx, dc, B, Tc, raw, g_ids=dg, stream=torch.cuda.current_stream().cuda_stream)

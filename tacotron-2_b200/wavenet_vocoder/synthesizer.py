@@ -47,15 +47,56 @@ def resolve_weights(checkpoint_path, hparams):
 
 
 class Synthesizer:
+	"""Multi-GPU (reference: in-graph towers over a tf.split of the batch, wavenet.py:227-239, lists flattened on the host,
+	synthesizer.py:100-101).  Utterances never interact, so they are sharded, with wavenet_vocoder.sharding:
+	  * under torchrun (torch.distributed initialised, one rank per GPU): every rank calls synthesize() with the same batch,
+	    synthesises its shard and rank 0 gathers the audio (the only collective of the path) and writes the files;
+	  * in one process with hparams.wavenet_num_gpus > 1: one model per visible device, one host thread per device
+	    (the library call releases the GIL), results merged in utterance order.
+	The draws of an utterance depend on the seed and on its index in the batch only, never on the number of GPUs."""
+
 	def load(self, checkpoint_path, hparams, model_name='WaveNet', engine='auto'):
 		log('Constructing model: {}'.format(model_name))
 		self._hparams = hparams
 		self.synth_debug = hparams.wavenet_synth_debug
-		self.model = create_model(model_name, hparams, engine=engine)
+		weights = resolve_weights(checkpoint_path, hparams)
 		log('Loading checkpoint: {}'.format(checkpoint_path))
-		self.model.load_weights(resolve_weights(checkpoint_path, hparams))
+		self.models = []
+		n_towers = self._tower_count()
+		if n_towers > 1:
+			import torch
+			keep = torch.cuda.current_device()
+			for d in range(n_towers):
+				torch.cuda.set_device(d)	#wn_create binds the handle to the current device
+				self.models.append(create_model(model_name, hparams, engine=engine).load_weights(weights))
+			torch.cuda.set_device(keep)
+		else:
+			self.models.append(create_model(model_name, hparams, engine=engine).load_weights(weights))
+		self.model = self.models[0]
 		self._rng = np.random.default_rng(hparams.get('wavenet_synthesis_seed'))
 		return self
+
+	def _tower_count(self):
+		n = int(self._hparams.get('wavenet_num_gpus') or 1)
+		if n <= 1 or self._dist()[1] > 1:
+			return 1
+		import torch
+		return max(1, min(n, torch.cuda.device_count()))
+
+	@staticmethod
+	def _dist():
+		"""(rank, world size) of the torch.distributed job this process belongs to, (0, 1) outside one."""
+		try:
+			import torch.distributed as dist
+			if dist.is_available() and dist.is_initialized():
+				return dist.get_rank(), dist.get_world_size()
+		except ImportError:
+			pass
+		return 0, 1
+
+	@property
+	def is_writer(self):
+		return self._dist()[0] == 0
 
 	def prepare_batch(self, mel_spectrograms):
 		"""synthesizer.py:56-70: true lengths, clip, pad with the range minimum, stack, rescale to [0, 1]."""
@@ -74,8 +115,15 @@ class Synthesizer:
 			return_wavs=False):
 		hp = self._hparams
 		local_cond, global_cond = self._check_conditions()
-		if not local_cond:
-			raise NotImplementedError('synthesis without local conditioning is not wired (both shipped configs use mels)')
+		if not local_cond:	#synthesizer.py:76-77: a fixed 100 samples per utterance, no mels
+			B = len(mel_spectrograms)
+			rng = self._rng if seed is None else np.random.default_rng(seed)
+			nz = make_noise(hp, 100, B, rng) if noise is None else noise
+			g = None if (speaker_ids is None or not global_cond) else np.asarray(speaker_ids, dtype=np.int32).reshape(B, 1)
+			wavs = list(self.model.initialize(None, None, g, None, synthesis_length=100, noise=nz, want_raw=False))
+			if return_wavs:
+				return wavs
+			return self._write(wavs, basenames, out_dir)
 
 		if self.synth_debug:	#synthesizer.py:51-53
 			assert len(hp.wavenet_debug_mels) == len(hp.wavenet_debug_wavs)
@@ -97,11 +145,16 @@ class Synthesizer:
 			noise = make_noise(hp, T, B, rng)
 
 		#Generate wavs and clip extra padding to select Real speech parts  (synthesizer.py:97-104)
-		generated = self.model.initialize(None, c_batch, g, None, test_inputs=teacher, noise=noise, want_raw=False)
-		generated_wavs = [wav[:length] for wav, length in zip(generated, audio_lengths)]
+		generated_wavs = self._run_sharded(c_batch, g, teacher, noise, audio_lengths)
+		if generated_wavs is None:	#a non-writing rank of a torch.distributed job
+			return []
 		if return_wavs:
 			return generated_wavs
 
+		return self._write(generated_wavs, basenames, out_dir)
+
+	def _write(self, generated_wavs, basenames, out_dir):
+		hp = self._hparams
 		audio_filenames = []
 		for i, generated_wav in enumerate(generated_wavs):
 			#Save wav to disk (plots of the reference, :115-125, are out of scope)
@@ -109,6 +162,45 @@ class Synthesizer:
 			save_wavenet_wav(generated_wav, audio_filename, sr=hp.sample_rate, inv_preemphasize=hp.preemphasize, k=hp.preemphasis)
 			audio_filenames.append(audio_filename)
 		return audio_filenames
+
+	def _run_sharded(self, c_batch, g, teacher, noise, audio_lengths):
+		"""The session.run of the reference (:97) over however many GPUs take part; returns the cropped wavs in utterance
+		order (None on the ranks of a distributed job that do not hold the result)."""
+		from wavenet_vocoder import sharding
+		rank, world = self._dist()
+		models = getattr(self, 'models', None) or [self.model]
+		towers = len(models)
+
+		def run(model, idx):
+			if not idx:
+				return []
+			sel = np.asarray(idx)
+			frames = max(audio_lengths[i] for i in idx) // get_hop_size(self._hparams)   # a shard stops at its own longest utterance
+			T = frames * get_hop_size(self._hparams)
+			out = model.initialize(None, np.ascontiguousarray(c_batch[sel, :frames]), None if g is None else g[sel], None,
+				test_inputs=None if teacher is None else teacher[sel], noise=np.ascontiguousarray(noise[:T, sel]), want_raw=False)
+			return [out[k, :audio_lengths[i]] for k, i in enumerate(idx)]
+
+		if world > 1:
+			shards = sharding.shard_utterances(audio_lengths, world)
+			local = run(self.model, shards[rank])
+			return sharding.gather_wavs(local, shards[rank], len(audio_lengths))
+		if towers > 1:
+			import torch
+			from concurrent.futures import ThreadPoolExecutor
+			shards = sharding.shard_utterances(audio_lengths, towers)
+
+			def tower(d):
+				torch.cuda.set_device(d)
+				return run(models[d], shards[d])
+			with ThreadPoolExecutor(max_workers=towers) as pool:
+				parts = list(pool.map(tower, range(towers)))
+			wavs = [None] * len(audio_lengths)
+			for d in range(towers):
+				for i, w in zip(shards[d], parts[d]):
+					wavs[i] = w
+			return wavs
+		return run(self.model, list(range(len(audio_lengths))))
 
 	def _check_conditions(self):
 		local_condition = self._hparams.cin_channels > 0

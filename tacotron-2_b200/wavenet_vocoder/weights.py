@@ -165,6 +165,31 @@ def init_weights(hp, seed=5339, kind='stress'):
 	return w
 
 
+def fold_weight_norm(hp, weights):
+	"""What `wavenet_weight_normalization=True` means at synthesis time in the reference (modules.py:44-181).
+
+	WeightNorm keeps the layer's `kernel` variable as the direction v plus a gain g, but re-assigns g := ||v|| under a
+	control dependency every time the effective kernel is computed (:162-164), so the effective kernel is
+	l2_normalize(v) * ||v|| = v up to rounding, whatever g a checkpoint holds.  The incremental convolutions do not even do
+	that: CausalConv1D reads `self.layer.kernel`, which on the wrapper is the raw v captured before normalisation
+	(:151, :245).  Hence: residual / input / final convolutions use `kernel` as stored; the upsampling layers, which run
+	through WeightNorm.call, use l2_normalize(v) * ||v|| in float32 (TF: x * rsqrt(max(sum x^2, 1e-12)); norm over all axes
+	but the last); `g` tensors are ignored.  Returns a new table."""
+	if not getattr(hp, 'wavenet_weight_normalization', False):
+		return weights
+	out = OrderedDict()
+	for name, arr in weights.items():
+		if name.endswith('/g'):
+			continue
+		a = np.asarray(arr, np.float32)
+		if name.startswith('local_conditioning_upsampling_') and name.endswith('/kernel'):
+			sq = np.sum(np.square(a, dtype=np.float32), axis=tuple(range(a.ndim - 1)), keepdims=True, dtype=np.float32)
+			unit = a * (np.float32(1.0) / np.sqrt(np.maximum(sq, np.float32(1e-12)))).astype(np.float32)
+			a = (unit * np.sqrt(sq).astype(np.float32)).astype(np.float32)
+		out[name] = a
+	return out
+
+
 def check_weights(hp, weights):
 	"""Raise ValueError unless `weights` holds exactly the tensors of weight_specs(hp) with those shapes."""
 	specs = weight_specs(hp)

@@ -148,6 +148,8 @@ def test_auto_engine_picks_pipeline_and_falls_back():
     from wavenet_vocoder._native import NativeWaveNet
     hp = common.small()
     assert NativeWaveNet(hp, common.weights_for(hp), engine='auto').info()['engine'] == 'pipeline'
+    hd = common.default_22k()   # the 128-channel block: the tensor-core loop engine
+    assert NativeWaveNet(hd, common.weights_for(hd), engine='auto').info()['engine'] == 'tc'
     hq = common.small_variants()['mulaw_quantize']
     assert NativeWaveNet(hq, common.weights_for(hq), engine='auto').info()['engine'] == 'generic'
     hp_paper = common.paper()  # fp32 weights of the paper config do not fit shared memory -> generic

@@ -1,0 +1,129 @@
+"""The tensor-core loop engine (csrc/wn_loop_tc.cu: tcgen05.mma inside the autoregressive loop, weights resident in tensor
+memory / shared memory) through the C ABI.
+
+Every fp32 operand is split into two fp16 numbers (22 significant bits) and a product is three tensor-core passes
+(hi*hi + hi*lo + lo*hi, fp32 accumulation in tensor memory); the summation order differs from the fixed-order fp32 C oracle,
+so it is not bit-identical.  The criteria, stated here as BASELINE.json asks:
+  * teacher-forced per-step distribution parameters: |a - b| <= 1e-3 * max(|b|, 1e-2) against the C oracle and against the
+    op-for-op numpy oracle (observed ~3e-6; a bf16 split, tried first, gave ~3e-5 and 1.3e-3 on stacks without the sqrt(0.5)
+    scalings);
+  * free-running audio under identical draws: within 1e-3 absolute of the C oracle, sample for sample, over the stated prefix
+    = the whole test utterance (550 .. 1100 samples; observed ~6e-7: no divergence inside the prefix).
+"""
+import os
+
+import numpy as np
+import pytest
+
+import common
+from oracle import wavenet_oracle as O
+from oracle.c_oracle import COracle
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
+PREFIX_ATOL = 1e-3
+
+
+def _net(hp, w, **env):
+    from wavenet_vocoder._native import NativeWaveNet
+    old = {k: os.environ.get(k) for k in env}
+    try:
+        for k, val in env.items():
+            os.environ[k] = str(val)
+        net = NativeWaveNet(hp, w, engine='tc')
+    finally:
+        for k, val in old.items():
+            if val is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = val
+    assert net.info()['engine'] == 'tc'
+    return net
+
+
+def _check(net, hp, w, B, Tc, free=True, **env):
+    T = Tc * hp.hop_size
+    c, nz = common.cond_for(hp, B, Tc), common.noise_for(hp, T, B)
+    teacher = common.teacher_for(hp, B, T)
+    co = COracle(hp, w)
+    old = {k: os.environ.get(k) for k in env}
+    try:
+        for k, val in env.items():
+            os.environ[k] = str(val)
+        audio_t, raw_t = net.synthesize_host(c, nz, teacher=teacher, want_raw=True)
+        if free:
+            audio, raw = net.synthesize_host(c, nz, want_raw=True)
+    finally:
+        for k, val in old.items():
+            if val is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = val
+    a_c, _, raw_c, _ = co.synthesize(c, noise=nz, teacher=teacher)
+    assert np.isfinite(raw_t).all()
+    assert np.all(common.rel_close(raw_t, raw_c)), 'teacher forced: max rel err {:.3e}'.format(common.max_rel(raw_t, raw_c))
+    assert float(np.max(np.abs(audio_t - a_c))) <= PREFIX_ATOL
+    if free:
+        a_f, _, raw_f, _ = co.synthesize(c, noise=nz)
+        assert float(np.max(np.abs(audio - a_f))) <= PREFIX_ATOL, 'free-running audio leaves the oracle inside the prefix'
+        assert np.all(common.rel_close(raw[:, :64], raw_f[:, :64]))
+    return raw_t
+
+
+def test_tc_default_block_small_batch_vs_both_oracles():
+    hp = common.default_22k()
+    w = common.weights_for(hp)
+    net = _net(hp, w)
+    raw_t = _check(net, hp, w, 5, 2)
+    info = net.info()
+    assert info['pipeline_group_size'] == 16 and info['pipeline_ctas'] == hp.layers + 1
+    # the op-for-op numpy oracle (numpy matmul order) on one utterance
+    T = 2 * hp.hop_size
+    c, nz, teacher = common.cond_for(hp, 5, 2), common.noise_for(hp, T, 5), common.teacher_for(hp, 5, T)
+    _, raw_np = O.WaveNetOracle(hp, w).incremental(c=c[:1], noise=nz[:, :1], test_inputs=teacher[:1])
+    assert np.all(common.rel_close(raw_t[0], raw_np[0].T))
+
+
+@pytest.mark.parametrize('B,Tc', [(20, 2), (64, 1), (33, 1)])
+def test_tc_several_replicas(B, Tc):
+    """More than 16 utterances run as several replicas of the layer chain (the last one partly filled)."""
+    hp = common.default_22k()
+    w = common.weights_for(hp)
+    net = _net(hp, w)
+    _check(net, hp, w, B, Tc)
+    assert net.info()['pipeline_ctas'] == ((B + 15) // 16) * (hp.layers + 1)
+
+
+def test_tc_groups_of_32_and_cluster_sizes():
+    """N = 32 replicas (what batches above 7 x 16 use) and every hand-off mix: all through L2 (cluster of 1), clusters of 3 and 7."""
+    hp = common.default_22k()
+    w = common.weights_for(hp)
+    net = _net(hp, w)
+    _check(net, hp, w, 40, 1, WN_TC_NB=32)
+    assert net.info()['pipeline_group_size'] == 32
+    for cs in (1, 3, 7):
+        _check(net, hp, w, 7, 1, free=False, WN_TC_CLUSTER=cs)
+
+
+def test_tc_heads_input_types_and_scalings():
+    """Mixture-of-logistics head, mu-law scalar input, legacy / residual_legacy off - on the 128-channel block."""
+    base = common.default_22k()
+    for hp in (base.override(out_channels=30, legacy=False, residual_legacy=False, log_scale_min=-7.0),
+               base.override(input_type='mulaw', quantize_channels=256, layers=8, stacks=2)):
+        w = common.weights_for(hp)
+        _check(_net(hp, w), hp, w, 3, 1)
+
+
+def test_tc_repeated_calls_and_long_dilation_history():
+    """Two calls on one handle (mailboxes re-armed, rings reused) and T > receptive field, so every ring wraps; teacher forced."""
+    hp = common.default_22k()
+    w = common.weights_for(hp)
+    net = _net(hp, w)
+    _check(net, hp, w, 3, 17, free=False)   # 4675 steps > 4093
+    _check(net, hp, w, 3, 1)
+
+
+def test_tc_rejects_what_it_does_not_cover():
+    from wavenet_vocoder._native import NativeWaveNet
+    hp = common.small()   # 32 residual channels
+    with pytest.raises(ValueError, match='tensor-core engine unavailable'):
+        NativeWaveNet(hp, common.weights_for(hp), engine='tc')

@@ -148,3 +148,72 @@ def test_run_synthesis_batches_and_map_file(tmp_path, monkeypatch):
     assert [len(b) for b in batches] == [2, 2, 1]
     rows = open(os.path.join(out, 'wavs', 'map.txt')).read().strip().split('\n')
     assert len(rows) == 5 and all(r.split('|')[1].endswith('.wav') and os.path.exists(r.split('|')[1]) for r in rows)
+
+
+def test_resolve_checkpoint_forms(tmp_path):
+    """random / .npz / TF prefix / directory with a TF `checkpoint` state file / directory of weight tables
+    (reference wavenet_vocoder/synthesize.py:69-78 asks tf.train.get_checkpoint_state)."""
+    from wavenet_vocoder import synthesize as drv
+    assert drv.resolve_checkpoint('random:3') == 'random:3'
+    assert drv.resolve_checkpoint(None) is None
+    npz = tmp_path / 'w.npz'
+    npz.write_bytes(b'x')
+    assert drv.resolve_checkpoint(str(npz)) == str(npz)
+    d = tmp_path / 'logs'
+    d.mkdir()
+    assert drv.resolve_checkpoint(str(d)) is None
+    (d / 'model.ckpt-500.index').write_bytes(b'')
+    (d / 'model.ckpt-1000.index').write_bytes(b'')
+    os.utime(str(d / 'model.ckpt-500.index'), (1, 1))
+    assert drv.resolve_checkpoint(str(d / 'model.ckpt-500')) == str(d / 'model.ckpt-500')      # a prefix
+    assert drv.resolve_checkpoint(str(d)) == str(d / 'model.ckpt-1000')                        # newest prefix of the directory
+    (d / 'checkpoint').write_text('model_checkpoint_path: "model.ckpt-500"\nall_model_checkpoint_paths: "model.ckpt-500"\n')
+    assert drv.resolve_checkpoint(str(d)) == str(d / 'model.ckpt-500')                         # the TF state file wins
+
+    class Args:
+        output_dir = 'o'
+    with pytest.raises(RuntimeError, match='Failed to load checkpoint'):
+        drv.wavenet_synthesize(Args, common.small(), str(tmp_path / 'missing'))
+
+
+def test_tf_checkpoint_prefix_reaches_the_weight_table(tmp_path):
+    """A TF V2 checkpoint written under EMA names, found through a `checkpoint` state file, loads into the weight table."""
+    from wavenet_vocoder import synthesize as drv
+    from wavenet_vocoder import tf_checkpoint as T
+    hp = common.small()
+    w = common.weights_for(hp)
+    tensors = {}
+    for name, arr in w.items():
+        parts = name.split('/')
+        if parts[0].startswith('ResidualConv1DGLU_'):
+            role = parts[1].replace('residual_block_', '')
+            tf_name = 'WaveNet_model/inference/{0}/residual_block_{1}_{0}/{2}'.format(parts[0], role, parts[2])
+        else:
+            tf_name = 'WaveNet_model/inference/' + name
+        tensors[tf_name + '/ExponentialMovingAverage'] = arr
+    prefix = str(tmp_path / 'wavenet_model.ckpt-7')
+    T.write_bundle(prefix, tensors)
+    (tmp_path / 'checkpoint').write_text('model_checkpoint_path: "wavenet_model.ckpt-7"\n')
+    path = drv.resolve_checkpoint(str(tmp_path))
+    assert path == prefix
+    w2 = S.resolve_weights(path, hp)
+    assert list(w2) == list(w) and all(np.array_equal(w[k], w2[k]) for k in w)
+
+
+def test_weight_norm_fold_is_what_the_reference_computes_at_synthesis():
+    """wavenet_weight_normalization=True (modules.py:44-181): g is re-assigned to ||v|| before every use, so the effective
+    upsampling kernel is l2_normalize(v) * ||v|| (= v to a few ulp) and the incremental convolutions read v itself."""
+    from wavenet_vocoder import weights as W
+    hp = common.small(wavenet_weight_normalization=True)
+    w = common.weights_for(hp)
+    w_g = dict(w)
+    w_g['ResidualConv1DGLU_0/residual_block_causal_conv/g'] = np.full(hp.gate_channels, 3.0, np.float32)   # a stale gain
+    folded = W.fold_weight_norm(hp, w_g)
+    assert not any(k.endswith('/g') for k in folded)
+    W.check_weights(hp, folded)
+    for k in w:
+        if k.startswith('local_conditioning_upsampling_') and k.endswith('/kernel'):
+            assert np.allclose(folded[k], w[k], rtol=3e-7, atol=0)
+        else:
+            assert np.array_equal(folded[k], w[k])
+    assert W.fold_weight_norm(common.small(), w) is w
