@@ -78,6 +78,7 @@ struct TcParams {
     int inputs_mode;
     float *audio, *raw;
     int B, T, NR;
+    int NA;                              // utterances a replica really holds (multiple of 4, <= the MMA's N): the epilogues skip the rest
     int bend;                            // one past the last utterance of this launch
     int b0;                              // first utterance of this launch in the caller's batch of B (batches above the launch limit run in chunks)
 };
@@ -86,7 +87,6 @@ template <int NB>
 struct Geo {
     static constexpr int NH = NB / 2;            // utterances per epilogue thread
     static constexpr int NU = NH / 2;            // 16-byte units of two {value, tag} words
-    static constexpr int NQ = NH / 4;            // 16-byte units of four floats (ring)
     static constexpr int LBO = NB * 16 + 16;     // k-chunk stride of the activation images (16 B of padding: conflict-free stores)
     static constexpr int PLANE = 16 * LBO;       // 128 channels
     static constexpr int IMG = 2 * PLANE;        // hi, lo
@@ -135,20 +135,25 @@ struct Watch {
         return false;
     }
 };
-// NU units of two words, `stride` words apart; returns true if the watchdog fired
+// the first `nu` of NU units of two words, `stride` words apart (the others read as 0); true if the watchdog fired
 template <int NU>
-__device__ __forceinline__ bool poll_units(const unsigned long long *p, long long stride, unsigned tag, float *v, int *abort_flag) {
+__device__ __forceinline__ bool poll_units(const unsigned long long *p, long long stride, unsigned tag, float *v, int nu, int *abort_flag) {
     Watch wd{abort_flag};
     for (;;) {
         unsigned long long w[2 * NU];
 #pragma unroll
-        for (int u = 0; u < NU; ++u) ld_ll2(p + u * stride, w[2 * u], w[2 * u + 1]);
+        for (int u = 0; u < NU; ++u)
+            if (u < nu) ld_ll2(p + u * stride, w[2 * u], w[2 * u + 1]);
         bool ok = true;
 #pragma unroll
-        for (int i = 0; i < 2 * NU; ++i) ok = ok && ((unsigned)(w[i] >> 32) == tag);
+        for (int u = 0; u < NU; ++u)
+            if (u < nu) ok = ok && ((unsigned)(w[2 * u] >> 32) == tag) && ((unsigned)(w[2 * u + 1] >> 32) == tag);
         if (ok) {
 #pragma unroll
-            for (int i = 0; i < 2 * NU; ++i) v[i] = __uint_as_float((unsigned)(w[i] & 0xffffffffu));
+            for (int u = 0; u < NU; ++u) {
+                v[2 * u] = u < nu ? __uint_as_float((unsigned)(w[2 * u] & 0xffffffffu)) : 0.0f;
+                v[2 * u + 1] = u < nu ? __uint_as_float((unsigned)(w[2 * u + 1] & 0xffffffffu)) : 0.0f;
+            }
             return false;
         }
         if (wd.expired()) return true;
@@ -170,9 +175,9 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
     return r;
 }
-__device__ __forceinline__ void st_async4(uint32_t raddr, float4 v, uint32_t rmbar) {
-    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%1, %2, %3, %4}, [%5];"
-                 ::"r"(raddr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(rmbar) : "memory");
+__device__ __forceinline__ void st_async2(uint32_t raddr, float v0, float v1, uint32_t rmbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];"
+                 ::"r"(raddr), "f"(v0), "f"(v1), "r"(rmbar) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_cluster(uint32_t bar, uint32_t parity) {
     uint32_t ok;
@@ -274,12 +279,13 @@ struct Bars {
 // =========================================================================================================================
 // layer CTA
 // =========================================================================================================================
-template <int NB, bool STATS>
+template <int NB, int NAH, bool STATS>
 __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsigned char *smem, const uint32_t tmem, Bars &bars) {
     using G = Geo<NB>;
-    constexpr int NH = G::NH, NU = G::NU, NQ = G::NQ, LBO = G::LBO, PLANE = G::PLANE;
+    constexpr int NH = G::NH, NU = G::NU, LBO = G::LBO, PLANE = G::PLANE;
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, q = w & 3, hh = w >> 2;
-    const int j = 32 * q + lane, n0 = hh * NH;
+    constexpr int nah = NAH, nu = NAH / 2, NA = 2 * NAH;   // utterances / two-utterance units this thread really handles (of NH / NU)
+    const int j = 32 * q + lane, n0 = hh * nah;
     const uint32_t lane_addr = tmem + ((uint32_t)(32 * q) << 16);
     const int L = P.L, T = P.T, cin = P.cin;
     const unsigned char *blob = P.layer_blobs + (long long)l * LAYER_BLOB_BYTES;
@@ -294,7 +300,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     unsigned long long *mx_out = P.mail_x + (long long)(r * L + l + 1) * 2 * G::MAILW + unit0;
     unsigned long long *ms_out = P.mail_skip + (long long)(r * L + l) * 2 * G::MAILW + unit0;
     const unsigned long long *min_in = P.mail_in + (long long)r * 2 * NB + n0;
-    float *ring = P.ring + ((long long)r * P.ring_slots + P.ring_off[l]) * G::MAILW + ((long long)(hh * NQ) * CH + j) * 4;
+    float *ring = P.ring + ((long long)r * P.ring_slots + P.ring_off[l]) * G::MAILW + ((long long)(hh * NU) * CH + j) * 2;   // [half][unit][channel][2]
     unsigned char *XI = smem + G::S_XI, *ZI = smem + G::S_ZI, *TAP = smem + G::S_TAP, *CI = smem + G::S_CI;
     const uint32_t bx = umma::smem_addr(&bars.x), bz = umma::smem_addr(&bars.z), bp = umma::smem_addr(&bars.p),
                    bgate = umma::smem_addr(&bars.gate), bout = umma::smem_addr(&bars.out), bskip = umma::smem_addr(&bars.skip);
@@ -302,10 +308,10 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     // through the L2 mailboxes
     const uint32_t crank = cluster_ctarank(), csize = cluster_nctarank();
     const bool in_dsmem = l > 0 && crank > 0, out_dsmem = l + 1 < L && crank + 1 < csize;
-    float *XF = reinterpret_cast<float *>(smem + G::S_XF) + ((hh * NQ) * CH + j) * 4;     // [half][unit][channel][4 utterances]
+    float *XF = reinterpret_cast<float *>(smem + G::S_XF) + ((hh * NU) * CH + j) * 2;     // [half][unit][channel][2 utterances]
     const uint32_t bxf = umma::smem_addr(&bars.xf);
     const uint32_t r_xf = mapa_u32(umma::smem_addr(XF), out_dsmem ? crank + 1 : crank), r_bxf = mapa_u32(bxf, out_dsmem ? crank + 1 : crank);
-    constexpr int CN = (CI_K * NB + EPI_THREADS - 1) / EPI_THREADS;   // conditioning elements per thread (upper bound)
+    constexpr int CN = (CI_K * NA + EPI_THREADS - 1) / EPI_THREADS;   // conditioning elements per thread (upper bound)
     long long st_c[6] = {0, 0, 0, 0, 0, 0};
     const bool do_stats = STATS && P.stats != nullptr && tid == 0;
 
@@ -314,32 +320,34 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     auto prep_load = [&](int t) {
         const int t0 = t - 2 * d, t1 = t - d;
 #pragma unroll
-        for (int u = 0; u < NQ; ++u) {
-            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-            if (t0 >= 0) a = *reinterpret_cast<const float4 *>(ring + (long long)(t0 & qmask) * G::MAILW + (long long)u * CH * 4);
-            if (t1 >= 0) b = *reinterpret_cast<const float4 *>(ring + (long long)(t1 & qmask) * G::MAILW + (long long)u * CH * 4);
-            tp0[4 * u] = a.x; tp0[4 * u + 1] = a.y; tp0[4 * u + 2] = a.z; tp0[4 * u + 3] = a.w;
-            tp1[4 * u] = b.x; tp1[4 * u + 1] = b.y; tp1[4 * u + 2] = b.z; tp1[4 * u + 3] = b.w;
+        for (int u = 0; u < NU; ++u) {
+            float2 a = make_float2(0.f, 0.f), b = a;
+            if (u < nu && t0 >= 0) a = *reinterpret_cast<const float2 *>(ring + (long long)(t0 & qmask) * G::MAILW + (long long)u * CH * 2);
+            if (u < nu && t1 >= 0) b = *reinterpret_cast<const float2 *>(ring + (long long)(t1 & qmask) * G::MAILW + (long long)u * CH * 2);
+            tp0[2 * u] = a.x; tp0[2 * u + 1] = a.y;
+            tp1[2 * u] = b.x; tp1[2 * u + 1] = b.y;
         }
 #pragma unroll
         for (int i = 0; i < CN; ++i) {
             const int e = tid + i * EPI_THREADS;
             const int n = e / cin, k = e - n * cin;
-            const long long b = (long long)P.b0 + r * NB + n;
-            cnd[i] = (n < NB && b < P.bend) ? __ldg(P.c_up + (b * T + t) * cin + k) : 0.0f;
+            const long long b = (long long)P.b0 + r * NA + n;
+            cnd[i] = (n < NA && b < P.bend) ? __ldg(P.c_up + (b * T + t) * cin + k) : 0.0f;
         }
     };
     auto prep_store = [&]() {
 #pragma unroll
         for (int i = 0; i < NH; i += 2) {
-            img_put2(TAP + joff + i * 16, PLANE, tp0[i], tp0[i + 1]);
-            img_put2(TAP + G::IMG + joff + i * 16, PLANE, tp1[i], tp1[i + 1]);
+            if (i < nah) {
+                img_put2(TAP + joff + i * 16, PLANE, tp0[i], tp0[i + 1]);
+                img_put2(TAP + G::IMG + joff + i * 16, PLANE, tp1[i], tp1[i + 1]);
+            }
         }
 #pragma unroll
         for (int i = 0; i < CN; ++i) {
             const int e = tid + i * EPI_THREADS;
             const int n = e / cin, k = e - n * cin;
-            if (n < NB) img_put(CI, G::CI_PLANE, LBO, k, n, cnd[i]);
+            if (n < NA) img_put(CI, G::CI_PLANE, LBO, k, n, cnd[i]);
         }
         umma::fence_proxy_async();
         umma::fence_before_sync();
@@ -358,34 +366,35 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         float xin[NH];
         if (l == 0) {
             float s[NH];
-            if (poll_units<NU>(min_in + par * NB, 2, tag, s, P.abort_flag)) return;
+            if (poll_units<NU>(min_in + par * NB, 2, tag, s, nu, P.abort_flag)) return;
 #pragma unroll
             for (int i = 0; i < NH; ++i) xin[i] = __fmaf_rn(s[i], wf, bf);
         } else if (in_dsmem) {
-            if (tid == 0) umma::mbar_expect_tx(bxf, CH * NB * 4);
+            if (tid == 0) umma::mbar_expect_tx(bxf, CH * NA * 4);
             if (mbar_wait_cluster_wd(bxf, par, P.abort_flag)) return;
 #pragma unroll
-            for (int u = 0; u < NQ; ++u) {
-                const float4 v = *reinterpret_cast<const float4 *>(XF + u * CH * 4);
-                xin[4 * u] = v.x; xin[4 * u + 1] = v.y; xin[4 * u + 2] = v.z; xin[4 * u + 3] = v.w;
+            for (int u = 0; u < NU; ++u) {
+                const float2 v = u < nu ? *reinterpret_cast<const float2 *>(XF + u * CH * 2) : make_float2(0.f, 0.f);
+                xin[2 * u] = v.x; xin[2 * u + 1] = v.y;
             }
         } else {
-            if (poll_units<NU>(mx_in + (long long)par * G::MAILW, (long long)CH * 2, tag, xin, P.abort_flag)) return;
+            if (poll_units<NU>(mx_in + (long long)par * G::MAILW, (long long)CH * 2, tag, xin, nu, P.abort_flag)) return;
         }
         const long long c1 = do_stats ? clock64() : 0;
         unsigned char *xi = XI + par * G::IMG;
         {
             unsigned char *px = xi + joff;
 #pragma unroll
-            for (int i = 0; i < NH; i += 2) img_put2(px + i * 16, PLANE, xin[i], xin[i + 1]);
+            for (int i = 0; i < NH; i += 2)
+                if (i < nah) img_put2(px + i * 16, PLANE, xin[i], xin[i + 1]);
         }
         umma::fence_proxy_async();
         __syncwarp();
         if (lane == 0) umma::mbar_arrive(bx);
 #pragma unroll
-        for (int u = 0; u < NQ; ++u)
-            *reinterpret_cast<float4 *>(ring + (long long)(t & qmask) * G::MAILW + (long long)u * CH * 4) =
-                make_float4(xin[4 * u], xin[4 * u + 1], xin[4 * u + 2], xin[4 * u + 3]);
+        for (int u = 0; u < NU; ++u)
+            if (u < nu)
+                *reinterpret_cast<float2 *>(ring + (long long)(t & qmask) * G::MAILW + (long long)u * CH * 2) = make_float2(xin[2 * u], xin[2 * u + 1]);
         // ---- gate (modules.py:494-510) ----------------------------------------------------------------------------------------
         if (mbar_wait_wd(bgate, par, P.abort_flag)) return;
         umma::fence_after_sync();
@@ -402,8 +411,9 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
             umma::tmem_ld_wait();
 #pragma unroll
             for (int i = 0; i < NH; i += 2)
-                img_put2(ZI + joff + i * 16, PLANE, gate_fast(__fadd_rn(a[i], ba), __fadd_rn(b[i], bb)),
-                         gate_fast(__fadd_rn(a[i + 1], ba), __fadd_rn(b[i + 1], bb)));
+                if (i < nah)
+                    img_put2(ZI + joff + i * 16, PLANE, gate_fast(__fadd_rn(a[i], ba), __fadd_rn(b[i], bb)),
+                             gate_fast(__fadd_rn(a[i + 1], ba), __fadd_rn(b[i + 1], bb)));
         }
         umma::fence_proxy_async();
         umma::fence_before_sync();
@@ -419,22 +429,15 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
             if constexpr (NH == 8) umma::tmem_ld8(lane_addr + COL_ACC + 2 * NB + n0, reinterpret_cast<float(&)[8]>(o));
             else umma::tmem_ld16(lane_addr + COL_ACC + 2 * NB + n0, reinterpret_cast<float(&)[16]>(o));
             umma::tmem_ld_wait();
-            if (out_dsmem) {
-#pragma unroll
-                for (int u = 0; u < NQ; ++u) {
-                    float4 v;
-                    v.x = __fmul_rn(__fadd_rn(__fadd_rn(o[4 * u], bo), xin[4 * u]), cres);
-                    v.y = __fmul_rn(__fadd_rn(__fadd_rn(o[4 * u + 1], bo), xin[4 * u + 1]), cres);
-                    v.z = __fmul_rn(__fadd_rn(__fadd_rn(o[4 * u + 2], bo), xin[4 * u + 2]), cres);
-                    v.w = __fmul_rn(__fadd_rn(__fadd_rn(o[4 * u + 3], bo), xin[4 * u + 3]), cres);
-                    st_async4(r_xf + u * CH * 16, v, r_bxf);
-                }
-            } else if (l + 1 < L) {
+            if (l + 1 < L) {
 #pragma unroll
                 for (int u = 0; u < NU; ++u) {
-                    const float v0 = __fmul_rn(__fadd_rn(__fadd_rn(o[2 * u], bo), xin[2 * u]), cres);
-                    const float v1 = __fmul_rn(__fadd_rn(__fadd_rn(o[2 * u + 1], bo), xin[2 * u + 1]), cres);
-                    st_ll2(mx_out + (long long)par * G::MAILW + (long long)u * CH * 2, v0, v1, tag);
+                    if (u < nu) {
+                        const float v0 = __fmul_rn(__fadd_rn(__fadd_rn(o[2 * u], bo), xin[2 * u]), cres);
+                        const float v1 = __fmul_rn(__fadd_rn(__fadd_rn(o[2 * u + 1], bo), xin[2 * u + 1]), cres);
+                        if (out_dsmem) st_async2(r_xf + u * CH * 8, v0, v1, r_bxf);
+                        else st_ll2(mx_out + (long long)par * G::MAILW + (long long)u * CH * 2, v0, v1, tag);
+                    }
                 }
             }
         }
@@ -448,7 +451,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
             umma::tmem_ld_wait();
 #pragma unroll
             for (int u = 0; u < NU; ++u)
-                st_ll2(ms_out + (long long)par * G::MAILW + (long long)u * CH * 2, __fadd_rn(s[2 * u], bs), __fadd_rn(s[2 * u + 1], bs), tag);
+                if (u < nu) st_ll2(ms_out + (long long)par * G::MAILW + (long long)u * CH * 2, __fadd_rn(s[2 * u], bs), __fadd_rn(s[2 * u + 1], bs), tag);
         }
         // ---- off the critical path: operands of the x-independent part of the next step ---------------------------------------
         if (t + 1 < T) {
@@ -586,12 +589,13 @@ __device__ void layer_loader(const TcParams &P, const int l, unsigned char *smem
 // =========================================================================================================================
 // head CTA
 // =========================================================================================================================
-template <int NB, bool STATS>
+template <int NB, int NAH, bool STATS>
 __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *smem, const uint32_t tmem, Bars &bars) {
     using G = Geo<NB>;
     constexpr int NH = G::NH, NU = G::NU, LBO = G::LBO, PLANE = G::PLANE;
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, q = w & 3, hh = w >> 2;
-    const int j = 32 * q + lane, n0 = hh * NH;
+    constexpr int nah = NAH, nu = NAH / 2, NA = 2 * NAH;
+    const int j = 32 * q + lane, n0 = hh * nah;
     const uint32_t lane_addr = tmem + ((uint32_t)(32 * q) << 16);
     const int L = P.L, T = P.T, O = P.O;
     const float *hb = reinterpret_cast<const float *>(P.head_blob + 4 * 32768);
@@ -605,8 +609,8 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
     float *prm = reinterpret_cast<float *>(smem + G::S_PRM);   // [NB][CH]
     const uint32_t bh = umma::smem_addr(&bars.x), bh2 = umma::smem_addr(&bars.z), bh1 = umma::smem_addr(&bars.gate),
                    bo = umma::smem_addr(&bars.out), bprm = umma::smem_addr(&bars.skip);
-    const long long bu = (long long)P.b0 + r * NB + tid;   // utterance of the sampler thread
-    const bool sampler = tid < NB && bu < P.bend;
+    const long long bu = (long long)P.b0 + r * NA + tid;   // utterance of the sampler thread
+    const bool sampler = tid < NA && bu < P.bend;
     // initial input (wavenet.py:433-445): raw 0.0, mulaw mulaw(0) = 0.0; WaveNet.step semantics: the first input is x[0]
     if (tid < NB) st_ll1(min_out + tid, (sampler && P.inputs_mode) ? P.teacher[bu * T] : 0.0f, 1u);
     long long st_c[4] = {0, 0, 0, 0};
@@ -625,7 +629,7 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
         float S[NH];
         for (int l = 0; l < L; ++l) {
             float s[NH];
-            if (poll_units<NU>(ms_in + ((long long)l * 2 + par) * G::MAILW, (long long)CH * 2, tag, s, P.abort_flag)) return;
+            if (poll_units<NU>(ms_in + ((long long)l * 2 + par) * G::MAILW, (long long)CH * 2, tag, s, nu, P.abort_flag)) return;
 #pragma unroll
             for (int i = 0; i < NH; ++i) {
                 if (l == 0) S[i] = s[i];
@@ -635,7 +639,7 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
         const long long c1 = do_stats ? clock64() : 0;
 #pragma unroll
         for (int i = 0; i < NH; i += 2)   // relu (wavenet.py:840)
-            img_put2(HI + joff + i * 16, PLANE, S[i] > 0.0f ? S[i] : 0.0f, S[i + 1] > 0.0f ? S[i + 1] : 0.0f);
+            if (i < nah) img_put2(HI + joff + i * 16, PLANE, S[i] > 0.0f ? S[i] : 0.0f, S[i + 1] > 0.0f ? S[i + 1] : 0.0f);
         umma::fence_proxy_async();
         umma::fence_before_sync();
         __syncwarp();
@@ -650,7 +654,7 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
 #pragma unroll
             for (int i = 0; i < NH; i += 2) {
                 const float y0 = __fadd_rn(h[i], b1), y1 = __fadd_rn(h[i + 1], b1);
-                img_put2(H2 + joff + i * 16, PLANE, y0 > 0.0f ? y0 : 0.0f, y1 > 0.0f ? y1 : 0.0f);
+                if (i < nah) img_put2(H2 + joff + i * 16, PLANE, y0 > 0.0f ? y0 : 0.0f, y1 > 0.0f ? y1 : 0.0f);
             }
         }
         umma::fence_proxy_async();
@@ -668,10 +672,12 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
             if (j < O) {
 #pragma unroll
                 for (int i = 0; i < NH; ++i) {
-                    const float y = __fadd_rn(o[i], b2);
-                    prm[(n0 + i) * CH + j] = y;
-                    const long long b = (long long)P.b0 + r * NB + n0 + i;
-                    if (P.raw && b < P.bend) P.raw[(b * T + t) * O + j] = y;   // wavenet.py:847
+                    if (i < nah) {
+                        const float y = __fadd_rn(o[i], b2);
+                        prm[(n0 + i) * CH + j] = y;
+                        const long long b = (long long)P.b0 + r * NA + n0 + i;
+                        if (P.raw && b < P.bend) P.raw[(b * T + t) * O + j] = y;   // wavenet.py:847
+                    }
                 }
             }
         }
@@ -764,7 +770,7 @@ __device__ void load_tmem_weights(const unsigned char *src, int nmat, uint32_t t
     umma::tmem_st_wait();
 }
 
-template <int NB, bool STATS>
+template <int NB, int NAH, bool STATS>
 __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParams P) {
     using G = Geo<NB>;
     extern __shared__ __align__(128) unsigned char tc_smem[];
@@ -807,10 +813,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
     umma::fence_after_sync();
     cluster_sync_all();   // the peers' mbarriers exist before anything is sent to them
     if (head) {
-        if (warp < 8) head_epilogue<NB, STATS>(P, r, tc_smem, tmem, bars);
+        if (warp < 8) head_epilogue<NB, NAH, STATS>(P, r, tc_smem, tmem, bars);
         else if (warp == MMA_WARP) head_mma<NB>(P, tc_smem, tmem, bars);
     } else {
-        if (warp < 8) layer_epilogue<NB, STATS>(P, r, l, tc_smem, tmem, bars);
+        if (warp < 8) layer_epilogue<NB, NAH, STATS>(P, r, l, tc_smem, tmem, bars);
         else if (warp == MMA_WARP) layer_mma<NB>(P, tc_smem, tmem, bars);
         else layer_loader(P, l, tc_smem, bars, G::S_WST);
     }
@@ -870,9 +876,14 @@ void wn_tc_free(wn_handle *h) {
     h->tc = nullptr;
 }
 
-template <int NB>
-static const void *tc_kernel(bool stats) {
-    return stats ? (const void *)wn_loop_tc_kernel<NB, true> : (const void *)wn_loop_tc_kernel<NB, false>;
+// kernel for N = nb and na = 2 * NAH utterances per replica (na a multiple of 4, nb - 12 <= na <= nb)
+static const void *tc_kernel(int nb, int na, bool stats) {
+#define WN_TC_K(NB_, NAH_) (stats ? (const void *)wn_loop_tc_kernel<NB_, NAH_, true> : (const void *)wn_loop_tc_kernel<NB_, NAH_, false>)
+    if (nb == 16) {
+        switch (na) { case 4: return WN_TC_K(16, 2); case 8: return WN_TC_K(16, 4); case 12: return WN_TC_K(16, 6); default: return WN_TC_K(16, 8); }
+    }
+    switch (na) { case 20: return WN_TC_K(32, 10); case 24: return WN_TC_K(32, 12); case 28: return WN_TC_K(32, 14); default: return WN_TC_K(32, 16); }
+#undef WN_TC_K
 }
 
 // Packs the weights (TF layouts) into the per-CTA blobs described at the top of this file.
@@ -973,13 +984,12 @@ int wn_tc_plan(wn_handle *h) {
     p.ring_slots = slots;
     p.layer_blobs = pl->d_layer_blobs; p.head_blob = pl->d_head_blob; p.first_wb = pl->d_first; p.abort_flag = pl->d_abort;
     pl->max_replicas = h->sm_count / (L + 1);
-    for (int nb : {16, 32}) {
-        const void *k0 = nb == 16 ? tc_kernel<16>(false) : tc_kernel<32>(false), *k1 = nb == 16 ? tc_kernel<16>(true) : tc_kernel<32>(true);
-        const int smem = nb == 16 ? Geo<16>::SMEM : Geo<32>::SMEM;
-        if (cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess ||
-            cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
-            return bail("tensor-core loop engine: shared memory attribute");
-    }
+    for (int nb : {16, 32})
+        for (int na = nb - 12; na <= nb; na += 4)
+            for (int st = 0; st < 2; ++st)
+                if (cudaFuncSetAttribute(tc_kernel(nb, na, st != 0), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         nb == 16 ? Geo<16>::SMEM : Geo<32>::SMEM) != cudaSuccess)
+                    return bail("tensor-core loop engine: shared memory attribute");
     if (pl->max_replicas < 1) return bail("tensor-core loop engine: fewer SMs than layers + 1");
     return WN_OK;
 }
@@ -1025,10 +1035,16 @@ static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStr
     WnTcPlan *pl = h->tc;
     int nb = (nbatch <= pl->max_replicas * 16) ? 16 : 32;
     if (const char *e = getenv("WN_TC_NB")) { const int v = atoi(e); if (v == 16 || v == 32) nb = v; }
-    const int nr = (nbatch + nb - 1) / nb;
+    // the step time of a replica grows with the utterances it holds (epilogue work, hand-off bytes) while idle SMs cost nothing:
+    // spread the batch over as many replicas as fit, in multiples of 4 utterances
+    int na = nb;
+    for (int a = nb - 12; a <= nb; a += 4)
+        if ((nbatch + a - 1) / a <= pl->max_replicas) { na = a; break; }
+    if (const char *e = getenv("WN_TC_NA")) { const int v = atoi(e); if (v >= nb - 12 && v <= nb && v % 4 == 0) na = v; }
+    const int nr = (nbatch + na - 1) / na;
     if (nr > pl->max_replicas) { h->err = "tensor-core loop engine: batch too large for one launch"; return WN_ERR_INVALID; }
-    pl->last_nb = nb; pl->last_nr = nr;
-    p.NR = nr; p.b0 = b0; p.bend = b0 + nbatch;
+    pl->last_nb = na; pl->last_nr = nr;
+    p.NR = nr; p.NA = na; p.b0 = b0; p.bend = b0 + nbatch;
     const int L = p.L;
     // mailboxes: x [NR][L][2][128*NB] | skip [NR][L][2][128*NB] | in [NR][2][NB], 8-byte {value, tag} words, zeroed (tag 0 = empty)
     const size_t mailw = (size_t)CH * nb;
@@ -1062,7 +1078,7 @@ static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStr
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(TC_THREADS); cfg.stream = st;
     cfg.dynamicSmemBytes = nb == 16 ? Geo<16>::SMEM : Geo<32>::SMEM;
-    const void *kern = nb == 16 ? tc_kernel<16>(p.stats != nullptr) : tc_kernel<32>(p.stats != nullptr);
+    const void *kern = tc_kernel(nb, na, p.stats != nullptr);
     cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeCooperative;
     at[0].val.cooperative = 1;

@@ -74,8 +74,8 @@ def test_tc_default_block_small_batch_vs_both_oracles():
     w = common.weights_for(hp)
     net = _net(hp, w)
     raw_t = _check(net, hp, w, 5, 2)
-    info = net.info()
-    assert info['pipeline_group_size'] == 16 and info['pipeline_ctas'] == hp.layers + 1
+    info = net.info()   # 5 utterances: two replicas of 4 (the batch is spread over as many layer chains as fit)
+    assert info['pipeline_group_size'] == 4 and info['pipeline_ctas'] == 2 * (hp.layers + 1)
     # the op-for-op numpy oracle (numpy matmul order) on one utterance
     T = 2 * hp.hop_size
     c, nz, teacher = common.cond_for(hp, 5, 2), common.noise_for(hp, T, 5), common.teacher_for(hp, 5, T)
@@ -83,14 +83,17 @@ def test_tc_default_block_small_batch_vs_both_oracles():
     assert np.all(common.rel_close(raw_t[0], raw_np[0].T))
 
 
-@pytest.mark.parametrize('B,Tc', [(20, 2), (64, 1), (33, 1)])
-def test_tc_several_replicas(B, Tc):
-    """More than 16 utterances run as several replicas of the layer chain (the last one partly filled)."""
+@pytest.mark.parametrize('B,Tc,group', [(20, 2, 4), (64, 1, 12), (33, 1, 8), (112, 1, 16)])
+def test_tc_several_replicas(B, Tc, group):
+    """The batch runs as up to 7 replicas of the layer chain, `group` utterances each (a multiple of 4; the last replica
+    partly filled): 64 utterances = configs[1], 33 ~ the per-GPU share of configs[2] on 8 GPUs."""
     hp = common.default_22k()
     w = common.weights_for(hp)
     net = _net(hp, w)
     _check(net, hp, w, B, Tc)
-    assert net.info()['pipeline_ctas'] == ((B + 15) // 16) * (hp.layers + 1)
+    info = net.info()
+    assert info['pipeline_group_size'] == group
+    assert info['pipeline_ctas'] == ((B + group - 1) // group) * (hp.layers + 1)
 
 
 def test_tc_groups_of_32_and_cluster_sizes():
@@ -98,8 +101,11 @@ def test_tc_groups_of_32_and_cluster_sizes():
     hp = common.default_22k()
     w = common.weights_for(hp)
     net = _net(hp, w)
-    _check(net, hp, w, 40, 1, WN_TC_NB=32)
+    _check(net, hp, w, 40, 1, WN_TC_NB=32, WN_TC_NA=32)
     assert net.info()['pipeline_group_size'] == 32
+    _check(net, hp, w, 130, 1, free=False)            # 7 replicas of 20, N = 32
+    assert net.info()['pipeline_group_size'] == 20
+    _check(net, hp, w, 9, 1, free=False, WN_TC_NA=16)   # one full-width replica
     for cs in (1, 3, 7):
         _check(net, hp, w, 7, 1, free=False, WN_TC_CLUSTER=cs)
 
