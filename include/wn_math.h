@@ -7,7 +7,7 @@
  * explicit rounding intrinsics on the device (never contracted or re-associated by nvcc) and plain C on the
  * host (compile the host side with -ffp-contract=off -mfma), therefore device and host results are bit-identical.
  *
- * Accuracy (vs. float64 libm, measured in tests/test_wn_math.py): expf/tanhf/sigmoid/logf within 2 ulp over the
+ * Accuracy (vs. float64 libm, measured in tests/test_c_oracle.py): expf/tanhf/sigmoid/logf within 2 ulp over the
  * ranges the path uses.  The reference computes the same quantities with tf.nn.tanh / tf.nn.sigmoid / tf.exp /
  * tf.log (modules.py:510, gaussian.py:47, mixture.py:92,105), i.e. Eigen or CUDA libm at a few ulp as well.
  */

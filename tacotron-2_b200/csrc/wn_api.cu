@@ -329,6 +329,10 @@ static int check_ready(wn_handle *h, int B, int Tc) {
     if (!h) return WN_ERR_INVALID;
     if (!h->finalized) return fail(h, WN_ERR_STATE, "model not finalized (call wn_load_weights for every tensor, then wn_finalize)");
     if (B <= 0 || Tc <= 0) return fail(h, WN_ERR_INVALID, "batch and frame count must be positive");
+    // a handle lives on the device that was current at wn_create: make it current for this call (a caller thread that serves
+    // several handles, or another library, may have switched devices in between)
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev != h->device) WN_CUDA_TRY(h, cudaSetDevice(h->device));
     return WN_OK;
 }
 

@@ -46,7 +46,7 @@ constexpr int KB_TOTAL = 11;             // 32-wide k blocks of the streamed wei
 constexpr int NCHUNK = 2 * KB_TOTAL;     // (k block, gate half), 16 KB each: A image [4][128][8] fp16 hi, then lo
 constexpr int CHUNK_BYTES = 16384;
 constexpr int CI_K = 96;                 // K of the conditioning image (cin <= 96, zero padded)
-constexpr unsigned long long WATCHDOG_NS = 20ull * 1000 * 1000 * 1000;
+constexpr unsigned long long WATCHDOG_NS_DEFAULT = 20ull * 1000 * 1000 * 1000;   // WN_WATCHDOG_MS overrides it (tests)
 
 // layer blob (bytes)
 constexpr int OFF_TMEM = 0;                       // 6 x [128 rows][64 words]: Wcur a hi, a lo, b hi, b lo, Wout hi, lo
@@ -72,14 +72,16 @@ struct TcParams {
     const float *first_wb;               // input 1x1: w[128], b[128]
     unsigned long long *mail_x, *mail_skip, *mail_in;
     float *ring;
-    int *abort_flag;
+    int *abort_flag;              // [0] set by the first waiter that gives up; [1..2] = the wall-clock limit in ns (lo, hi words)
     long long *stats;
     const float *c_up, *noise, *teacher;
     int inputs_mode;
     float *audio, *raw;
     int B, T, NR;
-    int NA;                              // utterances a replica really holds (multiple of 4, <= the MMA's N): the epilogues skip the rest
+    int NG;                              // utterance groups that travel through a replica's chain one after the other (1 or 2)
+    int NA;                              // utterances a group really holds (multiple of 4, <= the MMA's N): the epilogues skip the rest
     int bend;                            // one past the last utterance of this launch
+    int test_stall_step;                 // development / tests: the head stops feeding samples back at this step (-1: never)
     int b0;                              // first utterance of this launch in the caller's batch of B (batches above the launch limit run in chunks)
 };
 
@@ -94,9 +96,13 @@ struct Geo {
     // shared memory of a layer CTA
     static constexpr int S_WS = 0, S_WST = 65536, S_XI = S_WST + 2 * CHUNK_BYTES, S_ZI = S_XI + 2 * IMG, S_TAP = S_ZI + IMG,
                          S_CI = S_TAP + 2 * IMG, S_XF = S_CI + 2 * CI_PLANE, S_END = S_XF + CH * NB * 4;   // S_XF: fp32 inbox of x
+    // [S_XI, S_END) is the state of ONE utterance group; a second group (NB = 16 only) repeats it GRP bytes further
+    static constexpr int GRP = S_END - S_XI, NG_MAX = (S_END + GRP <= 227 * 1024 - 1024 && 384 + 8 * NB <= 512) ? 2 : 1;
+    static constexpr int ACC = 4 * NB;           // tensor-memory columns of one group's accumulators
     // head CTA
     static constexpr int S_HI = 0, S_H2 = IMG, S_PRM = 2 * IMG, S_HEND = S_PRM + NB * CH * 4;
-    static constexpr int SMEM = S_END > S_HEND ? S_END : S_HEND;
+    static constexpr int SMEM = (S_END + (NG_MAX - 1) * GRP) > S_HEND ? (S_END + (NG_MAX - 1) * GRP) : S_HEND;
+    static constexpr int smem_for(int ng) { return (S_END + (ng - 1) * GRP) > S_HEND ? (S_END + (ng - 1) * GRP) : S_HEND; }
     static constexpr int MAILW = CH * NB;        // words of one mailbox buffer (and floats of one ring slot)
 };
 
@@ -131,7 +137,7 @@ struct Watch {
         if (*(volatile int *)flag) return true;
         const unsigned long long now = global_timer_ns();
         if (t0 == 0) t0 = now;
-        else if (now - t0 > WATCHDOG_NS) { atomicExch(flag, 1); return true; }
+        else if (now - t0 > *reinterpret_cast<const volatile unsigned long long *>(flag + 2)) { atomicExch(flag, 1); return true; }
         return false;
     }
 };
@@ -272,8 +278,12 @@ __device__ float tc_sample_mol(const TcParams &P, const float *out, const float 
 }
 
 // mbarriers of a CTA
+struct GBars {   // per utterance group: every barrier completes once per step of its group
+    unsigned long long x, z, gate, out, skip, p, xf;
+};
 struct Bars {
-    unsigned long long x, z, gate, out, skip, p, wfull[2], wempty[2], xf;
+    GBars g[2];
+    unsigned long long wfull[2], wempty[2];
 };
 
 // =========================================================================================================================
@@ -287,7 +297,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     constexpr int nah = NAH, nu = NAH / 2, NA = 2 * NAH;   // utterances / two-utterance units this thread really handles (of NH / NU)
     const int j = 32 * q + lane, n0 = hh * nah;
     const uint32_t lane_addr = tmem + ((uint32_t)(32 * q) << 16);
-    const int L = P.L, T = P.T, cin = P.cin;
+    const int L = P.L, T = P.T, cin = P.cin, NG = P.NG;
     const unsigned char *blob = P.layer_blobs + (long long)l * LAYER_BLOB_BYTES;
     const float *bias = reinterpret_cast<const float *>(blob + OFF_BIAS);
     const float ba = __ldg(bias + j), bb = __ldg(bias + CH + j), bo = __ldg(bias + 2 * CH + j), bs = __ldg(bias + 3 * CH + j);
@@ -296,24 +306,38 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     const int d = P.dil[l], qmask = 2 * d - 1;
     const int joff = (j >> 3) * LBO + n0 * 16 + (j & 7) * 2;            // element (j, n0) inside an image plane
     const long long unit0 = ((long long)(hh * NU) * CH + j) * 2;      // word offset of this thread's first unit inside a mailbox buffer
-    const unsigned long long *mx_in = P.mail_x + (long long)(r * L + l) * 2 * G::MAILW + unit0;
-    unsigned long long *mx_out = P.mail_x + (long long)(r * L + l + 1) * 2 * G::MAILW + unit0;
-    unsigned long long *ms_out = P.mail_skip + (long long)(r * L + l) * 2 * G::MAILW + unit0;
-    const unsigned long long *min_in = P.mail_in + (long long)r * 2 * NB + n0;
-    float *ring = P.ring + ((long long)r * P.ring_slots + P.ring_off[l]) * G::MAILW + ((long long)(hh * NU) * CH + j) * 2;   // [half][unit][channel][2]
-    unsigned char *XI = smem + G::S_XI, *ZI = smem + G::S_ZI, *TAP = smem + G::S_TAP, *CI = smem + G::S_CI;
-    const uint32_t bx = umma::smem_addr(&bars.x), bz = umma::smem_addr(&bars.z), bp = umma::smem_addr(&bars.p),
-                   bgate = umma::smem_addr(&bars.gate), bout = umma::smem_addr(&bars.out), bskip = umma::smem_addr(&bars.skip);
     // x arrives / leaves through distributed shared memory when the neighbouring stage shares this CTA's cluster, else
     // through the L2 mailboxes
     const uint32_t crank = cluster_ctarank(), csize = cluster_nctarank();
     const bool in_dsmem = l > 0 && crank > 0, out_dsmem = l + 1 < L && crank + 1 < csize;
-    float *XF = reinterpret_cast<float *>(smem + G::S_XF) + ((hh * NU) * CH + j) * 2;     // [half][unit][channel][2 utterances]
-    const uint32_t bxf = umma::smem_addr(&bars.xf);
-    const uint32_t r_xf = mapa_u32(umma::smem_addr(XF), out_dsmem ? crank + 1 : crank), r_bxf = mapa_u32(bxf, out_dsmem ? crank + 1 : crank);
     constexpr int CN = (CI_K * NA + EPI_THREADS - 1) / EPI_THREADS;   // conditioning elements per thread (upper bound)
     long long st_c[6] = {0, 0, 0, 0, 0, 0};
     const bool do_stats = STATS && P.stats != nullptr && tid == 0;
+
+    // ---- the state of utterance group g of this replica (set by setg) -----------------------------------------------------------
+    int rg = 0;                                   // index of the group among all groups of the launch
+    const unsigned long long *mx_in = nullptr, *min_in = nullptr;
+    unsigned long long *mx_out = nullptr, *ms_out = nullptr;
+    float *ring = nullptr, *XF = nullptr;
+    unsigned char *XI = nullptr, *ZI = nullptr, *TAP = nullptr, *CI = nullptr;
+    uint32_t bx = 0, bz = 0, bp = 0, bgate = 0, bout = 0, bskip = 0, bxf = 0, r_xf = 0, r_bxf = 0, acc = 0;
+    auto setg = [&](int g) {
+        rg = r * NG + g;
+        mx_in = P.mail_x + (long long)(rg * L + l) * 2 * G::MAILW + unit0;
+        mx_out = P.mail_x + (long long)(rg * L + l + 1) * 2 * G::MAILW + unit0;
+        ms_out = P.mail_skip + (long long)(rg * L + l) * 2 * G::MAILW + unit0;
+        min_in = P.mail_in + (long long)rg * 2 * NB + n0;
+        ring = P.ring + ((long long)rg * P.ring_slots + P.ring_off[l]) * G::MAILW + ((long long)(hh * NU) * CH + j) * 2;   // [half][unit][channel][2]
+        unsigned char *base = smem + g * G::GRP;
+        XI = base + G::S_XI; ZI = base + G::S_ZI; TAP = base + G::S_TAP; CI = base + G::S_CI;
+        XF = reinterpret_cast<float *>(base + G::S_XF) + ((hh * NU) * CH + j) * 2;        // [half][unit][channel][2 utterances]
+        GBars &gb = bars.g[g];
+        bx = umma::smem_addr(&gb.x); bz = umma::smem_addr(&gb.z); bp = umma::smem_addr(&gb.p); bgate = umma::smem_addr(&gb.gate);
+        bout = umma::smem_addr(&gb.out); bskip = umma::smem_addr(&gb.skip); bxf = umma::smem_addr(&gb.xf);
+        r_xf = mapa_u32(umma::smem_addr(XF), out_dsmem ? crank + 1 : crank);
+        r_bxf = mapa_u32(bxf, out_dsmem ? crank + 1 : crank);
+        acc = lane_addr + COL_ACC + g * G::ACC;
+    };
 
     // operands of the x-independent part of step t: the two older taps from the ring and the conditioning column c(t)
     float tp0[NH], tp1[NH], cnd[CN];
@@ -331,7 +355,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         for (int i = 0; i < CN; ++i) {
             const int e = tid + i * EPI_THREADS;
             const int n = e / cin, k = e - n * cin;
-            const long long b = (long long)P.b0 + r * NA + n;
+            const long long b = (long long)P.b0 + rg * NA + n;
             cnd[i] = (n < NA && b < P.bend) ? __ldg(P.c_up + (b * T + t) * cin + k) : 0.0f;
         }
     };
@@ -354,11 +378,18 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         __syncwarp();
         if (lane == 0) umma::mbar_arrive(bp);
     };
-    prep_load(0);
-    prep_store();
+    for (int g = 0; g < NG; ++g) {
+        setg(g);
+        prep_load(0);
+        prep_store();
+    }
 
     const long long st_begin = clock64();
+    // The groups of a replica follow each other through the chain: group 1 enters a stage when group 0 has left it, so every
+    // role simply alternates between them; a group's own step latency is unchanged and the chain is busy twice as often.
     for (int t = 0; t < T; ++t) {
+      for (int g = 0; g < NG; ++g) {
+        setg(g);
         const int par = t & 1;
         const unsigned tag = (unsigned)t + 1u;
         const long long c0 = do_stats ? clock64() : 0;
@@ -402,11 +433,11 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         {
             float a[NH], b[NH];
             if constexpr (NH == 8) {
-                umma::tmem_ld8(lane_addr + COL_ACC + n0, reinterpret_cast<float(&)[8]>(a));
-                umma::tmem_ld8(lane_addr + COL_ACC + NB + n0, reinterpret_cast<float(&)[8]>(b));
+                umma::tmem_ld8(acc + n0, reinterpret_cast<float(&)[8]>(a));
+                umma::tmem_ld8(acc + NB + n0, reinterpret_cast<float(&)[8]>(b));
             } else {
-                umma::tmem_ld16(lane_addr + COL_ACC + n0, reinterpret_cast<float(&)[16]>(a));
-                umma::tmem_ld16(lane_addr + COL_ACC + NB + n0, reinterpret_cast<float(&)[16]>(b));
+                umma::tmem_ld16(acc + n0, reinterpret_cast<float(&)[16]>(a));
+                umma::tmem_ld16(acc + NB + n0, reinterpret_cast<float(&)[16]>(b));
             }
             umma::tmem_ld_wait();
 #pragma unroll
@@ -426,8 +457,8 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         const long long c4 = do_stats ? clock64() : 0;
         {
             float o[NH];
-            if constexpr (NH == 8) umma::tmem_ld8(lane_addr + COL_ACC + 2 * NB + n0, reinterpret_cast<float(&)[8]>(o));
-            else umma::tmem_ld16(lane_addr + COL_ACC + 2 * NB + n0, reinterpret_cast<float(&)[16]>(o));
+            if constexpr (NH == 8) umma::tmem_ld8(acc + 2 * NB + n0, reinterpret_cast<float(&)[8]>(o));
+            else umma::tmem_ld16(acc + 2 * NB + n0, reinterpret_cast<float(&)[16]>(o));
             umma::tmem_ld_wait();
             if (l + 1 < L) {
 #pragma unroll
@@ -446,14 +477,14 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         umma::fence_after_sync();
         {
             float s[NH];
-            if constexpr (NH == 8) umma::tmem_ld8(lane_addr + COL_ACC + 3 * NB + n0, reinterpret_cast<float(&)[8]>(s));
-            else umma::tmem_ld16(lane_addr + COL_ACC + 3 * NB + n0, reinterpret_cast<float(&)[16]>(s));
+            if constexpr (NH == 8) umma::tmem_ld8(acc + 3 * NB + n0, reinterpret_cast<float(&)[8]>(s));
+            else umma::tmem_ld16(acc + 3 * NB + n0, reinterpret_cast<float(&)[16]>(s));
             umma::tmem_ld_wait();
 #pragma unroll
             for (int u = 0; u < NU; ++u)
                 if (u < nu) st_ll2(ms_out + (long long)par * G::MAILW + (long long)u * CH * 2, __fadd_rn(s[2 * u], bs), __fadd_rn(s[2 * u + 1], bs), tag);
         }
-        // ---- off the critical path: operands of the x-independent part of the next step ---------------------------------------
+        // ---- off the critical path: operands of the x-independent part of this group's next step ------------------------------
         if (t + 1 < T) {
             prep_load(t + 1);
             prep_store();
@@ -462,11 +493,12 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
             const long long c5 = clock64();
             st_c[0] += c1 - c0; st_c[1] += c2 - c1; st_c[2] += c3 - c2; st_c[3] += c4 - c3; st_c[4] += c5 - c4;
         }
+      }
     }
     if (do_stats) {
         long long *o = P.stats + (long long)blockIdx.x * 16;
         for (int i = 0; i < 5; ++i) o[i] = st_c[i];
-        o[14] = clock64() - st_begin; o[15] = T;
+        o[14] = clock64() - st_begin; o[15] = (long long)T * NG;
     }
 }
 
@@ -475,31 +507,31 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
     using G = Geo<NB>;
     constexpr int LBO = G::LBO, PLANE = G::PLANE;
     constexpr uint32_t idesc = umma::idesc_f16(CH, NB);
-    const int T = P.T;
+    const int T = P.T, NG = P.NG;
     const uint32_t s0 = umma::smem_addr(smem);
-    const uint32_t D_A = tmem + COL_ACC, D_B = tmem + COL_ACC + NB, D_O = tmem + COL_ACC + 2 * NB, D_S = tmem + COL_ACC + 3 * NB;
-    const uint64_t zi_hi = umma::smem_desc(s0 + G::S_ZI, LBO, 128), zi_lo = umma::smem_desc(s0 + G::S_ZI + PLANE, LBO, 128);
     const uint64_t ws_hi = umma::smem_desc(s0 + G::S_WS, CH * 16, 128), ws_lo = umma::smem_desc(s0 + G::S_WS + 32768, CH * 16, 128);
     const uint64_t st_hi[2] = {umma::smem_desc(s0 + G::S_WST, CH * 16, 128), umma::smem_desc(s0 + G::S_WST + CHUNK_BYTES, CH * 16, 128)};
     const uint64_t st_lo[2] = {umma::smem_desc(s0 + G::S_WST + 8192, CH * 16, 128), umma::smem_desc(s0 + G::S_WST + CHUNK_BYTES + 8192, CH * 16, 128)};
-    const uint64_t tap_hi[3] = {umma::smem_desc(s0 + G::S_TAP, LBO, 128), umma::smem_desc(s0 + G::S_TAP + G::IMG, LBO, 128),
-                                umma::smem_desc(s0 + G::S_CI, LBO, 128)};
-    const uint64_t tap_lo[3] = {umma::smem_desc(s0 + G::S_TAP + PLANE, LBO, 128), umma::smem_desc(s0 + G::S_TAP + G::IMG + PLANE, LBO, 128),
-                                umma::smem_desc(s0 + G::S_CI + G::CI_PLANE, LBO, 128)};
     constexpr uint64_t KS_B = (uint64_t)((2 * LBO) >> 4);        // descriptor step per k step (16 k) of an activation image
     constexpr uint64_t KS_A = (uint64_t)((2 * CH * 16) >> 4);    // ... of a 128-row weight image
-    const uint32_t bgate = umma::smem_addr(&bars.gate), bout = umma::smem_addr(&bars.out), bskip = umma::smem_addr(&bars.skip),
-                   bp = umma::smem_addr(&bars.p);
+    constexpr uint64_t GRP_D = (uint64_t)(G::GRP >> 4);          // ... from one utterance group's images to the next group's
 
-    // the x-independent part of step tp, accumulated from scratch into the gate accumulators
-    auto p_phase = [&](int tp) -> bool {
-        if (mbar_wait_wd(bp, tp & 1, P.abort_flag)) return true;
+    // the x-independent part of step tp of group g, accumulated from scratch into that group's gate accumulators
+    auto p_phase = [&](int tp, int g) -> bool {
+        if (mbar_wait_wd(umma::smem_addr(&bars.g[g].p), tp & 1, P.abort_flag)) return true;
         umma::fence_after_sync();
+        const uint32_t D_A = tmem + COL_ACC + g * G::ACC, D_B = D_A + NB;
+        const uint64_t gd = g * GRP_D;
+        const uint64_t tap_hi[3] = {umma::smem_desc(s0 + G::S_TAP, LBO, 128) + gd, umma::smem_desc(s0 + G::S_TAP + G::IMG, LBO, 128) + gd,
+                                    umma::smem_desc(s0 + G::S_CI, LBO, 128) + gd};
+        const uint64_t tap_lo[3] = {umma::smem_desc(s0 + G::S_TAP + PLANE, LBO, 128) + gd, umma::smem_desc(s0 + G::S_TAP + G::IMG + PLANE, LBO, 128) + gd,
+                                    umma::smem_desc(s0 + G::S_CI + G::CI_PLANE, LBO, 128) + gd};
+        const uint32_t pass = (uint32_t)(tp * NG + g);   // passes over the weight stream so far
 #pragma unroll
         for (int kb = 0; kb < KB_TOTAL; ++kb) {
 #pragma unroll
             for (int half = 0; half < 2; ++half) {
-                const uint32_t use = (uint32_t)(KB_TOTAL * tp + kb);
+                const uint32_t use = (uint32_t)KB_TOTAL * pass + kb;
                 if (mbar_wait_wd(umma::smem_addr(&bars.wfull[half]), use & 1, P.abort_flag)) return true;
                 umma::fence_after_sync();
                 if (umma::elect_one()) {
@@ -520,13 +552,19 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
         }
         return false;
     };
-    if (p_phase(0)) return;
+    for (int g = 0; g < NG; ++g)
+        if (p_phase(0, g)) return;
     for (int t = 0; t < T; ++t) {
+      for (int g = 0; g < NG; ++g) {
         const int par = t & 1;
-        const uint64_t xi_hi = umma::smem_desc(s0 + G::S_XI + par * G::IMG, LBO, 128),
-                       xi_lo = umma::smem_desc(s0 + G::S_XI + par * G::IMG + PLANE, LBO, 128);
+        GBars &gb = bars.g[g];
+        const uint32_t D_A = tmem + COL_ACC + g * G::ACC, D_B = D_A + NB, D_O = D_A + 2 * NB, D_S = D_A + 3 * NB;
+        const uint32_t sg = s0 + g * G::GRP;
+        const uint64_t xi_hi = umma::smem_desc(sg + G::S_XI + par * G::IMG, LBO, 128),
+                       xi_lo = umma::smem_desc(sg + G::S_XI + par * G::IMG + PLANE, LBO, 128);
+        const uint64_t zi_hi = umma::smem_desc(sg + G::S_ZI, LBO, 128), zi_lo = umma::smem_desc(sg + G::S_ZI + PLANE, LBO, 128);
         // current tap of the dilated conv (modules.py:294-297) on top of the x-independent part
-        if (mbar_wait_wd(umma::smem_addr(&bars.x), par, P.abort_flag)) return;
+        if (mbar_wait_wd(umma::smem_addr(&gb.x), par, P.abort_flag)) return;
         umma::fence_after_sync();
         if (umma::elect_one()) {
 #pragma unroll
@@ -539,11 +577,11 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
                 umma::mma_bf16_ts(D_A, tmem + COL_WCUR + 64 + ks * 8, bh, idesc, 1);
                 umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 192 + ks * 8, bh, idesc, 1);
             }
-            umma::mma_commit(bgate);
+            umma::mma_commit(umma::smem_addr(&gb.gate));
         }
         __syncwarp();
         // residual 1x1 on z (modules.py:515)
-        if (mbar_wait_wd(umma::smem_addr(&bars.z), par, P.abort_flag)) return;
+        if (mbar_wait_wd(umma::smem_addr(&gb.z), par, P.abort_flag)) return;
         umma::fence_after_sync();
         if (umma::elect_one()) {
 #pragma unroll
@@ -552,7 +590,7 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
                 umma::mma_bf16_ts(D_O, tmem + COL_WOUT + ks * 8, zi_lo + ks * KS_B, idesc, 1);
                 umma::mma_bf16_ts(D_O, tmem + COL_WOUT + 64 + ks * 8, zi_hi + ks * KS_B, idesc, 1);
             }
-            umma::mma_commit(bout);
+            umma::mma_commit(umma::smem_addr(&gb.out));
         }
         __syncwarp();
         // skip 1x1 on z (modules.py:512), weights in shared memory
@@ -563,22 +601,24 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
                 umma::mma_bf16(D_S, ws_hi + ks * KS_A, zi_lo + ks * KS_B, idesc, 1);
                 umma::mma_bf16(D_S, ws_lo + ks * KS_A, zi_hi + ks * KS_B, idesc, 1);
             }
-            umma::mma_commit(bskip);
+            umma::mma_commit(umma::smem_addr(&gb.skip));
         }
         __syncwarp();
-        if (t + 1 < T && p_phase(t + 1)) return;
+        if (t + 1 < T && p_phase(t + 1, g)) return;
+      }
     }
 }
 
-// streams the [tap0 | tap1 | cin] weights of the layer, NCHUNK chunks per step, through the two stages
+// streams the [tap0 | tap1 | cin] weights of the layer, NCHUNK chunks per step and utterance group, through the two stages
 __device__ void layer_loader(const TcParams &P, const int l, unsigned char *smem, Bars &bars, int wst_off) {
     if ((threadIdx.x & 31) != 0) return;
     const unsigned char *stream = P.layer_blobs + (long long)l * LAYER_BLOB_BYTES + OFF_STREAM;
     const uint32_t dst0 = umma::smem_addr(smem + wst_off);
-    for (int tp = 0; tp < P.T; ++tp)
+    const int passes = P.T * P.NG;
+    for (int pass = 0; pass < passes; ++pass)
         for (int kb = 0; kb < KB_TOTAL; ++kb)
             for (int half = 0; half < 2; ++half) {
-                const uint32_t use = (uint32_t)(KB_TOTAL * tp + kb);
+                const uint32_t use = (uint32_t)(KB_TOTAL * pass + kb);
                 if (mbar_wait_wd(umma::smem_addr(&bars.wempty[half]), (use & 1) ^ 1, P.abort_flag)) return;
                 const uint32_t full = umma::smem_addr(&bars.wfull[half]);
                 umma::mbar_expect_tx(full, CHUNK_BYTES);
@@ -597,27 +637,34 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
     constexpr int nah = NAH, nu = NAH / 2, NA = 2 * NAH;
     const int j = 32 * q + lane, n0 = hh * nah;
     const uint32_t lane_addr = tmem + ((uint32_t)(32 * q) << 16);
-    const int L = P.L, T = P.T, O = P.O;
+    const int L = P.L, T = P.T, O = P.O, NG = P.NG;
     const float *hb = reinterpret_cast<const float *>(P.head_blob + 4 * 32768);
     const float b1 = __ldg(hb + j), b2 = __ldg(hb + CH + j);
     const float cskip = 0.70710677f;
     const int joff = (j >> 3) * LBO + n0 * 16 + (j & 7) * 2;
     const long long unit0 = ((long long)(hh * NU) * CH + j) * 2;
-    const unsigned long long *ms_in = P.mail_skip + (long long)r * L * 2 * G::MAILW + unit0;
-    unsigned long long *min_out = P.mail_in + (long long)r * 2 * NB;
+
     unsigned char *HI = smem + G::S_HI, *H2 = smem + G::S_H2;
     float *prm = reinterpret_cast<float *>(smem + G::S_PRM);   // [NB][CH]
-    const uint32_t bh = umma::smem_addr(&bars.x), bh2 = umma::smem_addr(&bars.z), bh1 = umma::smem_addr(&bars.gate),
-                   bo = umma::smem_addr(&bars.out), bprm = umma::smem_addr(&bars.skip);
-    const long long bu = (long long)P.b0 + r * NA + tid;   // utterance of the sampler thread
-    const bool sampler = tid < NA && bu < P.bend;
+    const uint32_t bh = umma::smem_addr(&bars.g[0].x), bh2 = umma::smem_addr(&bars.g[0].z), bh1 = umma::smem_addr(&bars.g[0].gate),
+                   bo = umma::smem_addr(&bars.g[0].out), bprm = umma::smem_addr(&bars.g[0].skip);
     // initial input (wavenet.py:433-445): raw 0.0, mulaw mulaw(0) = 0.0; WaveNet.step semantics: the first input is x[0]
-    if (tid < NB) st_ll1(min_out + tid, (sampler && P.inputs_mode) ? P.teacher[bu * T] : 0.0f, 1u);
+    for (int g = 0; g < NG; ++g) {
+        const long long b = (long long)P.b0 + (long long)(r * NG + g) * NA + tid;
+        if (tid < NB) st_ll1(P.mail_in + (long long)(r * NG + g) * 2 * NB + tid, (tid < NA && b < P.bend && P.inputs_mode) ? P.teacher[b * T] : 0.0f, 1u);
+    }
     long long st_c[4] = {0, 0, 0, 0};
     const bool do_stats = STATS && P.stats != nullptr && tid == 0;
     const long long st_begin = clock64();
     for (int t = 0; t < T; ++t) {
-        const int par = t & 1;
+      for (int g = 0; g < NG; ++g) {   // the groups of the replica arrive one after the other
+        const int rg = r * NG + g;
+        const unsigned long long *ms_in = P.mail_skip + (long long)rg * L * 2 * G::MAILW + unit0;
+        unsigned long long *min_out = P.mail_in + (long long)rg * 2 * NB;
+        const long long bu = (long long)P.b0 + (long long)rg * NA + tid;   // utterance of the sampler thread
+        const bool sampler = tid < NA && bu < P.bend;
+        const int par = t & 1;                      // mailbox buffer of the step
+        const int bpar = (t * NG + g) & 1;          // phase of this CTA's barriers (one completion per group and step)
         const unsigned tag = (unsigned)t + 1u;
         const long long c0 = do_stats ? clock64() : 0;
         float nz0 = 0.0f, tch = 0.0f;
@@ -644,7 +691,7 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
         umma::fence_before_sync();
         __syncwarp();
         if (lane == 0) umma::mbar_arrive(bh);
-        if (mbar_wait_wd(bh1, par, P.abort_flag)) return;
+        if (mbar_wait_wd(bh1, bpar, P.abort_flag)) return;
         umma::fence_after_sync();
         {
             float h[NH];
@@ -661,7 +708,7 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
         umma::fence_before_sync();
         __syncwarp();
         if (lane == 0) umma::mbar_arrive(bh2);
-        if (mbar_wait_wd(bo, par, P.abort_flag)) return;
+        if (mbar_wait_wd(bo, bpar, P.abort_flag)) return;
         umma::fence_after_sync();
         const long long c2 = do_stats ? clock64() : 0;
         {
@@ -675,7 +722,7 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
                     if (i < nah) {
                         const float y = __fadd_rn(o[i], b2);
                         prm[(n0 + i) * CH + j] = y;
-                        const long long b = (long long)P.b0 + r * NA + n0 + i;
+                        const long long b = (long long)P.b0 + (long long)rg * NA + n0 + i;
                         if (P.raw && b < P.bend) P.raw[(b * T + t) * O + j] = y;   // wavenet.py:847
                     }
                 }
@@ -684,7 +731,8 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
         umma::fence_before_sync();
         __syncwarp();
         if (lane == 0) umma::mbar_arrive(bprm);
-        if (mbar_wait_wd(bprm, par, P.abort_flag)) return;   // all parameters of the step are in shared memory
+        if (mbar_wait_wd(bprm, bpar, P.abort_flag)) return;   // all parameters of the step are in shared memory
+        if (t == P.test_stall_step) return;   // test hook: the chain starves and every waiter must time out (WN_ERR_WATCHDOG)
         // sampling + feedback (wavenet.py:850-878)
         if (tid < NB) {
             float nxt = 0.0f;
@@ -702,11 +750,12 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
             const long long c3 = clock64();
             st_c[0] += c1 - c0; st_c[1] += c2 - c1; st_c[2] += c3 - c2;
         }
+      }
     }
     if (do_stats) {
         long long *o = P.stats + (long long)blockIdx.x * 16;
         for (int i = 0; i < 3; ++i) o[i] = st_c[i];
-        o[14] = clock64() - st_begin; o[15] = T;
+        o[14] = clock64() - st_begin; o[15] = (long long)T * NG;
     }
 }
 
@@ -720,10 +769,11 @@ __device__ void head_mma(const TcParams &P, unsigned char *smem, const uint32_t 
     const uint64_t h2_hi = umma::smem_desc(s0 + G::S_H2, LBO, 128), h2_lo = umma::smem_desc(s0 + G::S_H2 + PLANE, LBO, 128);
     constexpr uint64_t KS_B = (uint64_t)((2 * LBO) >> 4);
     const uint32_t D_H = tmem + COL_HACC, D_O = tmem + COL_HACC + NB;
-    const uint32_t bh1 = umma::smem_addr(&bars.gate), bo = umma::smem_addr(&bars.out);
-    for (int t = 0; t < P.T; ++t) {
-        const int par = t & 1;
-        if (mbar_wait_wd(umma::smem_addr(&bars.x), par, P.abort_flag)) return;   // final_convolution_1 (wavenet.py:841)
+    const uint32_t bh1 = umma::smem_addr(&bars.g[0].gate), bo = umma::smem_addr(&bars.g[0].out);
+    const int steps = P.T * P.NG;   // one pass per step and utterance group
+    for (int k = 0; k < steps; ++k) {
+        const int par = k & 1;
+        if (mbar_wait_wd(umma::smem_addr(&bars.g[0].x), par, P.abort_flag)) return;   // final_convolution_1 (wavenet.py:841)
         umma::fence_after_sync();
         if (umma::elect_one()) {
 #pragma unroll
@@ -735,7 +785,7 @@ __device__ void head_mma(const TcParams &P, unsigned char *smem, const uint32_t 
             umma::mma_commit(bh1);
         }
         __syncwarp();
-        if (mbar_wait_wd(umma::smem_addr(&bars.z), par, P.abort_flag)) return;   // final_convolution_2 (wavenet.py:843), rows >= O zero
+        if (mbar_wait_wd(umma::smem_addr(&bars.g[0].z), par, P.abort_flag)) return;   // final_convolution_2 (wavenet.py:843), rows >= O zero
         umma::fence_after_sync();
         if (umma::elect_one()) {
 #pragma unroll
@@ -781,14 +831,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
     const int r = blockIdx.x / stages, l = blockIdx.x - r * stages;
     const bool head = l == P.L;
     if (tid == 0) {
-        umma::mbar_init(umma::smem_addr(&bars.x), EPI_THREADS / 32);
-        umma::mbar_init(umma::smem_addr(&bars.z), EPI_THREADS / 32);
-        umma::mbar_init(umma::smem_addr(&bars.gate), 1);
-        umma::mbar_init(umma::smem_addr(&bars.out), 1);
-        umma::mbar_init(umma::smem_addr(&bars.skip), head ? EPI_THREADS / 32 : 1);   // head: "parameters written" barrier
-        umma::mbar_init(umma::smem_addr(&bars.p), EPI_THREADS / 32);
+        for (int g = 0; g < 2; ++g) {
+            GBars &gb = bars.g[g];
+            umma::mbar_init(umma::smem_addr(&gb.x), EPI_THREADS / 32);
+            umma::mbar_init(umma::smem_addr(&gb.z), EPI_THREADS / 32);
+            umma::mbar_init(umma::smem_addr(&gb.gate), 1);
+            umma::mbar_init(umma::smem_addr(&gb.out), 1);
+            umma::mbar_init(umma::smem_addr(&gb.skip), head ? EPI_THREADS / 32 : 1);   // head: "parameters written" barrier
+            umma::mbar_init(umma::smem_addr(&gb.p), EPI_THREADS / 32);
+            umma::mbar_init(umma::smem_addr(&gb.xf), 1);
+        }
         for (int i = 0; i < 2; ++i) { umma::mbar_init(umma::smem_addr(&bars.wfull[i]), 1); umma::mbar_init(umma::smem_addr(&bars.wempty[i]), 1); }
-        umma::mbar_init(umma::smem_addr(&bars.xf), 1);
         umma::mbar_fence_init();
     }
     if (warp == 0) umma::tmem_alloc(umma::smem_addr(&tmem_base_s), 512);
@@ -805,7 +858,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
         load_tmem_weights(blob + OFF_TMEM, 6, tmem, COL_WCUR);
         const uint4 *ws = reinterpret_cast<const uint4 *>(blob + OFF_WS);
         for (int i = tid; i < 65536 / 16; i += TC_THREADS) reinterpret_cast<uint4 *>(tc_smem + G::S_WS)[i] = __ldg(ws + i);
-        for (int i = tid; i < (G::S_END - G::S_XI) / 16; i += TC_THREADS) reinterpret_cast<uint4 *>(tc_smem + G::S_XI)[i] = make_uint4(0, 0, 0, 0);
+        for (int i = tid; i < P.NG * G::GRP / 16; i += TC_THREADS) reinterpret_cast<uint4 *>(tc_smem + G::S_XI)[i] = make_uint4(0, 0, 0, 0);
     }
     umma::fence_proxy_async();
     umma::fence_before_sync();
@@ -841,10 +894,11 @@ struct WnTcPlan {
     float *d_ring = nullptr;
     size_t ring_floats = 0;
     int *d_abort = nullptr, *h_abort = nullptr;
+    int h_abort_init[4] = {0, 0, 0, 0};
     long long *d_stats = nullptr;
     int stats_ctas = 0;
     int max_replicas = 0;
-    int last_nb = 0, last_nr = 0, last_cluster = 1;
+    int last_nb = 0, last_nr = 0, last_ng = 1, last_cluster = 1;
 };
 
 static void split_host(float v, uint16_t &hi, uint16_t &lo) {   // fp16 (hi, lo): 22 significant bits of v
@@ -969,7 +1023,7 @@ int wn_tc_plan(wn_handle *h) {
     if (cudaMalloc((void **)&pl->d_layer_blobs, blobs.size()) != cudaSuccess) return bail("tensor-core loop engine: cudaMalloc(layer blobs)");
     if (cudaMalloc((void **)&pl->d_head_blob, hb.size()) != cudaSuccess) return bail("tensor-core loop engine: cudaMalloc(head blob)");
     if (cudaMalloc((void **)&pl->d_first, first.size() * 4) != cudaSuccess) return bail("tensor-core loop engine: cudaMalloc(first conv)");
-    if (cudaMalloc((void **)&pl->d_abort, sizeof(int)) != cudaSuccess) return bail("tensor-core loop engine: cudaMalloc(abort flag)");
+    if (cudaMalloc((void **)&pl->d_abort, 4 * sizeof(int)) != cudaSuccess) return bail("tensor-core loop engine: cudaMalloc(abort flag)");
     if (cudaMallocHost((void **)&pl->h_abort, sizeof(int)) != cudaSuccess) return bail("tensor-core loop engine: cudaMallocHost(abort flag)");
     *pl->h_abort = 0;
     cudaMemcpy(pl->d_layer_blobs, blobs.data(), blobs.size(), cudaMemcpyHostToDevice);
@@ -1033,22 +1087,40 @@ int wn_tc_check_abort(wn_handle *h) {   // after the stream has been synchronise
 
 static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStream_t st) {
     WnTcPlan *pl = h->tc;
-    int nb = (nbatch <= pl->max_replicas * 16) ? 16 : 32;
+    // How the batch is laid over the chip.  A replica is a chain of L + 1 CTAs; NG utterance groups of NA utterances follow each
+    // other through it.  Measured: the step time of a group grows with NA (epilogue work, hand-off bytes:
+    // 25.4 / 30.2 / 33.8 / 37.5 us at 4 / 8 / 12 / 16), a second group in the chain costs ~1 us, more than 5 replicas lose the
+    // clusters of 7 (+1.5 us); idle SMs cost nothing.  The cheapest feasible (NA, NG, NR) wins.
+    int nb = 16, na = 16, ng = 1, nr = 0;
+    {
+        static const float base[4] = {25.4f, 30.2f, 33.8f, 37.5f};
+        float best = 1e30f;
+        for (int a = 4; a <= 16; a += 4)
+            for (int g = 1; g <= Geo<16>::NG_MAX; ++g) {
+                const int groups = (nbatch + a - 1) / a, r = (groups + g - 1) / g;
+                if (r > pl->max_replicas) continue;
+                const float cost = base[a / 4 - 1] + (g > 1 ? 1.0f : 0.0f) + (r > 5 ? 1.5f : 0.0f) + 0.01f * r * g;
+                if (cost < best) { best = cost; na = a; ng = g; nr = r; }
+            }
+    }
     if (const char *e = getenv("WN_TC_NB")) { const int v = atoi(e); if (v == 16 || v == 32) nb = v; }
-    // the step time of a replica grows with the utterances it holds (epilogue work, hand-off bytes) while idle SMs cost nothing:
-    // spread the batch over as many replicas as fit, in multiples of 4 utterances
-    int na = nb;
-    for (int a = nb - 12; a <= nb; a += 4)
-        if ((nbatch + a - 1) / a <= pl->max_replicas) { na = a; break; }
+    if (nr == 0) nb = 32;   // more than 14 groups of 16: 32-wide MMAs, one group per chain
+    if (nb == 32) {
+        ng = 1; na = 32;
+        for (int a = 20; a <= 32; a += 4)
+            if ((nbatch + a - 1) / a <= pl->max_replicas) { na = a; break; }
+    }
     if (const char *e = getenv("WN_TC_NA")) { const int v = atoi(e); if (v >= nb - 12 && v <= nb && v % 4 == 0) na = v; }
-    const int nr = (nbatch + na - 1) / na;
+    if (const char *e = getenv("WN_TC_NG")) { const int v = atoi(e); if (v >= 1 && v <= (nb == 16 ? Geo<16>::NG_MAX : 1)) ng = v; }
+    nr = ((nbatch + na - 1) / na + ng - 1) / ng;
     if (nr > pl->max_replicas) { h->err = "tensor-core loop engine: batch too large for one launch"; return WN_ERR_INVALID; }
-    pl->last_nb = na; pl->last_nr = nr;
-    p.NR = nr; p.NA = na; p.b0 = b0; p.bend = b0 + nbatch;
+    pl->last_nb = na; pl->last_nr = nr; pl->last_ng = ng;
+    p.NR = nr; p.NG = ng; p.NA = na; p.b0 = b0; p.bend = b0 + nbatch;
     const int L = p.L;
-    // mailboxes: x [NR][L][2][128*NB] | skip [NR][L][2][128*NB] | in [NR][2][NB], 8-byte {value, tag} words, zeroed (tag 0 = empty)
+    // mailboxes, per utterance group: x [groups][L][2][128*NB] | skip [groups][L][2][128*NB] | in [groups][2][NB], 8-byte {value, tag} words, zeroed (tag 0 = empty)
     const size_t mailw = (size_t)CH * nb;
-    const size_t words = 2 * (size_t)nr * L * 2 * mailw + (size_t)nr * 2 * nb;
+    const size_t ngt = (size_t)nr * ng;   // utterance groups of the launch
+    const size_t words = 2 * ngt * L * 2 * mailw + ngt * 2 * nb;
     if (pl->mail_words < words) {
         if (pl->d_mail) cudaFree(pl->d_mail);
         pl->d_mail = nullptr; pl->mail_words = 0;
@@ -1056,10 +1128,10 @@ static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStr
         pl->mail_words = words;
     }
     p.mail_x = pl->d_mail;
-    p.mail_skip = p.mail_x + (size_t)nr * L * 2 * mailw;
-    p.mail_in = p.mail_skip + (size_t)nr * L * 2 * mailw;
+    p.mail_skip = p.mail_x + ngt * L * 2 * mailw;
+    p.mail_in = p.mail_skip + ngt * L * 2 * mailw;
     // dilation rings [NR][sum 2d][128*NB] floats: every slot is written before it is read (steps before 0 read zeros instead)
-    const size_t ring_floats = (size_t)nr * p.ring_slots * mailw;
+    const size_t ring_floats = ngt * p.ring_slots * mailw;
     if (pl->ring_floats < ring_floats) {
         if (pl->d_ring) cudaFree(pl->d_ring);
         pl->d_ring = nullptr; pl->ring_floats = 0;
@@ -1077,7 +1149,7 @@ static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStr
     // all CTAs wait for each other: they must be co-resident -> cooperative launch (one CTA per SM, grid <= SM count)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(TC_THREADS); cfg.stream = st;
-    cfg.dynamicSmemBytes = nb == 16 ? Geo<16>::SMEM : Geo<32>::SMEM;
+    cfg.dynamicSmemBytes = nb == 16 ? Geo<16>::smem_for(ng) : Geo<32>::smem_for(1);
     const void *kern = tc_kernel(nb, na, p.stats != nullptr);
     cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeCooperative;
@@ -1113,8 +1185,16 @@ int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const
     TcParams p = pl->prm;
     p.B = B; p.T = T;
     p.c_up = c_up; p.noise = noise; p.teacher = teacher; p.inputs_mode = inputs_mode; p.audio = audio; p.raw = raw;
-    WN_CUDA_TRY(h, cudaMemsetAsync(pl->d_abort, 0, sizeof(int), st));
-    const int cap = pl->max_replicas * 32;
+    {   // abort flag + the watchdog's wall-clock limit
+        unsigned long long limit = WATCHDOG_NS_DEFAULT;
+        if (const char *e = getenv("WN_WATCHDOG_MS")) { const long long v = atoll(e); if (v > 0) limit = (unsigned long long)v * 1000000ull; }
+        pl->h_abort_init[0] = 0; pl->h_abort_init[1] = 0;
+        memcpy(&pl->h_abort_init[2], &limit, 8);
+        WN_CUDA_TRY(h, cudaMemcpyAsync(pl->d_abort, pl->h_abort_init, 4 * sizeof(int), cudaMemcpyHostToDevice, st));
+    }
+    p.test_stall_step = -1;
+    if (const char *e = getenv("WN_TC_TEST_STALL")) p.test_stall_step = atoi(e);
+    const int cap = pl->max_replicas * 32;   // = 2 groups x 16 utterances per chain with N = 16 MMAs
     const int nchunks = (B + cap - 1) / cap, per = (B + nchunks - 1) / nchunks;
     for (int b0 = 0; b0 < B; b0 += per) {
         const int rc = tc_launch_chunk(h, p, b0, std::min(per, B - b0), st);

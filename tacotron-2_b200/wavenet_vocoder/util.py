@@ -1,7 +1,7 @@
 """input_type predicates and mu-law helpers (reference ``code/wavenet_vocoder/util.py:13-129``).
 
 numpy only: in the reference these functions are numpy-or-TF polymorphic; the in-graph (TF) uses
-of the synthesis path are done on the device by the CUDA epilogue (csrc/wn_kernels.cu), the numpy
+of the synthesis path are done on the device by the head of the loop kernels (csrc/wn_loop_tc.cu, wn_loop_pipe.cu, wn_loop_generic.cu), the numpy
 uses stay here.  ``mu`` is hard-wired to 255 whatever is passed, exactly like the reference
 (:48, :67, :99, :127)."""
 import numpy as np

@@ -83,17 +83,24 @@ def test_tc_default_block_small_batch_vs_both_oracles():
     assert np.all(common.rel_close(raw_t[0], raw_np[0].T))
 
 
-@pytest.mark.parametrize('B,Tc,group', [(20, 2, 4), (64, 1, 12), (33, 1, 8), (112, 1, 16)])
-def test_tc_several_replicas(B, Tc, group):
-    """The batch runs as up to 7 replicas of the layer chain, `group` utterances each (a multiple of 4; the last replica
-    partly filled): 64 utterances = configs[1], 33 ~ the per-GPU share of configs[2] on 8 GPUs."""
+@pytest.mark.parametrize('B,Tc,group,replicas', [(20, 2, 4, 5), (64, 1, 8, 4), (33, 1, 4, 5), (112, 1, 8, 7), (224, 1, 16, 7)])
+def test_tc_replicas_and_groups(B, Tc, group, replicas):
+    """The batch is cut into groups of `group` utterances (a multiple of 4; the last one partly filled); up to 7 replicas of
+    the layer chain run side by side and up to two groups follow each other through one chain: 64 utterances = configs[1]
+    (4 chains x 2 groups x 8), 33 ~ the per-GPU share of configs[2] on 8 GPUs, 224 = the most one launch takes."""
     hp = common.default_22k()
     w = common.weights_for(hp)
     net = _net(hp, w)
     _check(net, hp, w, B, Tc)
     info = net.info()
     assert info['pipeline_group_size'] == group
-    assert info['pipeline_ctas'] == ((B + group - 1) // group) * (hp.layers + 1)
+    assert info['pipeline_ctas'] == replicas * (hp.layers + 1)
+
+
+def test_tc_batch_above_one_launch_runs_in_chunks():
+    hp = common.default_22k()
+    w = common.weights_for(hp)
+    _check(_net(hp, w), hp, w, 230, 1, free=False)
 
 
 def test_tc_groups_of_32_and_cluster_sizes():
@@ -103,9 +110,10 @@ def test_tc_groups_of_32_and_cluster_sizes():
     net = _net(hp, w)
     _check(net, hp, w, 40, 1, WN_TC_NB=32, WN_TC_NA=32)
     assert net.info()['pipeline_group_size'] == 32
-    _check(net, hp, w, 130, 1, free=False)            # 7 replicas of 20, N = 32
+    _check(net, hp, w, 130, 1, free=False, WN_TC_NB=32)   # 7 replicas of 20, N = 32
     assert net.info()['pipeline_group_size'] == 20
-    _check(net, hp, w, 9, 1, free=False, WN_TC_NA=16)   # one full-width replica
+    _check(net, hp, w, 9, 1, free=False, WN_TC_NA=16, WN_TC_NG=1)   # one full-width replica
+    _check(net, hp, w, 20, 1, free=False, WN_TC_NA=12, WN_TC_NG=2)  # two groups in one chain, the second partly filled
     for cs in (1, 3, 7):
         _check(net, hp, w, 7, 1, free=False, WN_TC_CLUSTER=cs)
 
@@ -133,3 +141,24 @@ def test_tc_rejects_what_it_does_not_cover():
     hp = common.small()   # 32 residual channels
     with pytest.raises(ValueError, match='tensor-core engine unavailable'):
         NativeWaveNet(hp, common.weights_for(hp), engine='tc')
+
+
+def test_tc_watchdog_reports_a_starved_chain_and_the_handle_survives():
+    """WN_ERR_WATCHDOG: with the head's feedback cut after step 5 (test hook) every CTA waits in vain; with the limit shortened
+    to 300 ms the launch ends by itself, the host-buffer call raises and wn_info.aborted is set; the next call is clean."""
+    hp = common.default_22k()
+    w = common.weights_for(hp)
+    net = _net(hp, w)
+    B, Tc = 4, 1
+    T = Tc * hp.hop_size
+    c, nz = common.cond_for(hp, B, Tc), common.noise_for(hp, T, B)
+    os.environ['WN_WATCHDOG_MS'], os.environ['WN_TC_TEST_STALL'] = '300', '5'
+    try:
+        with pytest.raises(RuntimeError, match='watchdog'):
+            net.synthesize_host(c, nz)
+        assert net.info()['aborted'] == 1
+    finally:
+        del os.environ['WN_WATCHDOG_MS'], os.environ['WN_TC_TEST_STALL']
+    a = net.synthesize_host(c, nz)
+    assert net.info()['aborted'] == 0
+    assert float(np.max(np.abs(a - COracle(hp, w).synthesize(c, noise=nz)[0]))) <= PREFIX_ATOL
