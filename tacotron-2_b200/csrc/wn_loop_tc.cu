@@ -211,23 +211,60 @@ __device__ __forceinline__ float round11(float v) {
     const uint32_t u = __float_as_uint(v);
     return __uint_as_float((u + 0x00000fffu + ((u >> 13) & 1u)) & 0xffffe000u);
 }
+// WIDE images (groups of <= 8 utterances with N = 16 MMAs): the unused half of the columns carries the lo parts, i.e. plane 0 holds
+// hi at column n and lo at column n + 8, plane 1 holds hi at column n (columns 8.. stay zero).  One MMA of A_hi with plane 0 then
+// yields A_hi x_hi (columns 0..7) AND A_hi x_lo (columns 8..15), a second one of A_lo with plane 1 adds A_lo x_hi: two MMAs per k
+// step instead of three; the epilogue adds column n + 8 to column n.
+template <bool WIDE>
 __device__ __forceinline__ void img_put(unsigned char *img, int plane, int lbo, int j, int n, float v) {
     const float hf = round11(v);
     const int off = (j >> 3) * lbo + n * 16 + (j & 7) * 2;
-    *reinterpret_cast<unsigned short *>(img + off) = __half_as_ushort(__float2half_rn(hf));
-    *reinterpret_cast<unsigned short *>(img + plane + off) = __half_as_ushort(__float2half_rn(__fsub_rn(v, hf)));
+    const unsigned short h = __half_as_ushort(__float2half_rn(hf)), l = __half_as_ushort(__float2half_rn(__fsub_rn(v, hf)));
+    *reinterpret_cast<unsigned short *>(img + off) = h;
+    if (WIDE) {
+        *reinterpret_cast<unsigned short *>(img + off + 8 * 16) = l;
+        *reinterpret_cast<unsigned short *>(img + plane + off) = h;
+    } else {
+        *reinterpret_cast<unsigned short *>(img + plane + off) = l;
+    }
 }
 // two neighbouring utterances n, n + 1 of one channel: one packed conversion per plane (float -> half conversions run on the
 // 16-lane special-function pipe, which bounds the epilogues of this kernel)
-__device__ __forceinline__ void img_put2(unsigned char *p /* element (j, n) of the hi plane */, int plane, float v0, float v1) {
+template <bool WIDE>
+__device__ __forceinline__ void img_put2(unsigned char *p /* element (j, n) of plane 0 */, int plane, float v0, float v1) {
     const float h0 = round11(v0), h1 = round11(v1);
     uint32_t h, l;
     asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(h1), "f"(h0));
     asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(l) : "f"(__fsub_rn(v1, h1)), "f"(__fsub_rn(v0, h0)));
     *reinterpret_cast<unsigned short *>(p) = (unsigned short)h;
     *reinterpret_cast<unsigned short *>(p + 16) = (unsigned short)(h >> 16);
-    *reinterpret_cast<unsigned short *>(p + plane) = (unsigned short)l;
-    *reinterpret_cast<unsigned short *>(p + plane + 16) = (unsigned short)(l >> 16);
+    if (WIDE) {
+        *reinterpret_cast<unsigned short *>(p + 8 * 16) = (unsigned short)l;
+        *reinterpret_cast<unsigned short *>(p + 9 * 16) = (unsigned short)(l >> 16);
+        *reinterpret_cast<unsigned short *>(p + plane) = (unsigned short)h;
+        *reinterpret_cast<unsigned short *>(p + plane + 16) = (unsigned short)(h >> 16);
+    } else {
+        *reinterpret_cast<unsigned short *>(p + plane) = (unsigned short)l;
+        *reinterpret_cast<unsigned short *>(p + plane + 16) = (unsigned short)(l >> 16);
+    }
+}
+// NH accumulator columns of this thread's lane from column `taddr` on; WIDE: plus the partial sums 8 columns further
+template <int NH, bool WIDE>
+__device__ __forceinline__ void acc_load(uint32_t taddr, float (&v)[NH]) {
+    if constexpr (NH == 8) {
+        umma::tmem_ld8(taddr, v);
+        if constexpr (WIDE) {   // at most 4 utterances per thread: 4 columns (a wider load could leave the allocation)
+            float w[4];
+            umma::tmem_ld4(taddr + 8, w);
+            umma::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 4; ++i) v[i] = __fadd_rn(v[i], w[i]);
+            return;
+        }
+    } else {
+        umma::tmem_ld16(taddr, v);
+    }
+    umma::tmem_ld_wait();
 }
 
 // tanh(t) * sigmoid(s) (modules.py:510) with ex2.approx / rcp.approx; same form as wn_step_umma.cu
@@ -295,6 +332,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     constexpr int NH = G::NH, NU = G::NU, LBO = G::LBO, PLANE = G::PLANE;
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, q = w & 3, hh = w >> 2;
     constexpr int nah = NAH, nu = NAH / 2, NA = 2 * NAH;   // utterances / two-utterance units this thread really handles (of NH / NU)
+    constexpr bool WIDE = NB == 16 && NA <= 8;             // hi | lo side by side in the 16 columns (see img_put)
     const int j = 32 * q + lane, n0 = hh * nah;
     const uint32_t lane_addr = tmem + ((uint32_t)(32 * q) << 16);
     const int L = P.L, T = P.T, cin = P.cin, NG = P.NG;
@@ -363,15 +401,15 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
 #pragma unroll
         for (int i = 0; i < NH; i += 2) {
             if (i < nah) {
-                img_put2(TAP + joff + i * 16, PLANE, tp0[i], tp0[i + 1]);
-                img_put2(TAP + G::IMG + joff + i * 16, PLANE, tp1[i], tp1[i + 1]);
+                img_put2<WIDE>(TAP + joff + i * 16, PLANE, tp0[i], tp0[i + 1]);
+                img_put2<WIDE>(TAP + G::IMG + joff + i * 16, PLANE, tp1[i], tp1[i + 1]);
             }
         }
 #pragma unroll
         for (int i = 0; i < CN; ++i) {
             const int e = tid + i * EPI_THREADS;
             const int n = e / cin, k = e - n * cin;
-            if (n < NA) img_put(CI, G::CI_PLANE, LBO, k, n, cnd[i]);
+            if (n < NA) img_put<WIDE>(CI, G::CI_PLANE, LBO, k, n, cnd[i]);
         }
         umma::fence_proxy_async();
         umma::fence_before_sync();
@@ -417,7 +455,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
             unsigned char *px = xi + joff;
 #pragma unroll
             for (int i = 0; i < NH; i += 2)
-                if (i < nah) img_put2(px + i * 16, PLANE, xin[i], xin[i + 1]);
+                if (i < nah) img_put2<WIDE>(px + i * 16, PLANE, xin[i], xin[i + 1]);
         }
         umma::fence_proxy_async();
         __syncwarp();
@@ -432,18 +470,12 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         const long long c2 = do_stats ? clock64() : 0;
         {
             float a[NH], b[NH];
-            if constexpr (NH == 8) {
-                umma::tmem_ld8(acc + n0, reinterpret_cast<float(&)[8]>(a));
-                umma::tmem_ld8(acc + NB + n0, reinterpret_cast<float(&)[8]>(b));
-            } else {
-                umma::tmem_ld16(acc + n0, reinterpret_cast<float(&)[16]>(a));
-                umma::tmem_ld16(acc + NB + n0, reinterpret_cast<float(&)[16]>(b));
-            }
-            umma::tmem_ld_wait();
+            acc_load<NH, WIDE>(acc + n0, a);
+            acc_load<NH, WIDE>(acc + NB + n0, b);
 #pragma unroll
             for (int i = 0; i < NH; i += 2)
                 if (i < nah)
-                    img_put2(ZI + joff + i * 16, PLANE, gate_fast(__fadd_rn(a[i], ba), __fadd_rn(b[i], bb)),
+                    img_put2<WIDE>(ZI + joff + i * 16, PLANE, gate_fast(__fadd_rn(a[i], ba), __fadd_rn(b[i], bb)),
                              gate_fast(__fadd_rn(a[i + 1], ba), __fadd_rn(b[i + 1], bb)));
         }
         umma::fence_proxy_async();
@@ -457,9 +489,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         const long long c4 = do_stats ? clock64() : 0;
         {
             float o[NH];
-            if constexpr (NH == 8) umma::tmem_ld8(acc + 2 * NB + n0, reinterpret_cast<float(&)[8]>(o));
-            else umma::tmem_ld16(acc + 2 * NB + n0, reinterpret_cast<float(&)[16]>(o));
-            umma::tmem_ld_wait();
+            acc_load<NH, WIDE>(acc + 2 * NB + n0, o);
             if (l + 1 < L) {
 #pragma unroll
                 for (int u = 0; u < NU; ++u) {
@@ -477,9 +507,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         umma::fence_after_sync();
         {
             float s[NH];
-            if constexpr (NH == 8) umma::tmem_ld8(acc + 3 * NB + n0, reinterpret_cast<float(&)[8]>(s));
-            else umma::tmem_ld16(acc + 3 * NB + n0, reinterpret_cast<float(&)[16]>(s));
-            umma::tmem_ld_wait();
+            acc_load<NH, WIDE>(acc + 3 * NB + n0, s);
 #pragma unroll
             for (int u = 0; u < NU; ++u)
                 if (u < nu) st_ll2(ms_out + (long long)par * G::MAILW + (long long)u * CH * 2, __fadd_rn(s[2 * u], bs), __fadd_rn(s[2 * u + 1], bs), tag);
@@ -502,7 +530,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     }
 }
 
-template <int NB>
+template <int NB, bool WIDE>
 __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t tmem, Bars &bars) {
     using G = Geo<NB>;
     constexpr int LBO = G::LBO, PLANE = G::PLANE;
@@ -541,9 +569,9 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
                         const uint64_t ah = st_hi[half] + kk * KS_A, al = st_lo[half] + kk * KS_A;
                         const uint64_t bh = tap_hi[src] + (kin + kk) * KS_B, bl = tap_lo[src] + (kin + kk) * KS_B;
                         const uint32_t dd = half ? D_B : D_A;
-                        umma::mma_bf16(dd, ah, bh, idesc, (kb | kk) != 0);
-                        umma::mma_bf16(dd, ah, bl, idesc, 1);
-                        umma::mma_bf16(dd, al, bh, idesc, 1);
+                        umma::mma_bf16(dd, ah, bh, idesc, (kb | kk) != 0);      // WIDE: plane 0 = hi | lo, plane 1 = hi
+                        if (!WIDE) umma::mma_bf16(dd, ah, bl, idesc, 1);
+                        umma::mma_bf16(dd, al, WIDE ? bl : bh, idesc, 1);
                     }
                     umma::mma_commit(umma::smem_addr(&bars.wempty[half]));
                 }
@@ -572,10 +600,12 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
                 const uint64_t bh = xi_hi + ks * KS_B, bl = xi_lo + ks * KS_B;
                 umma::mma_bf16_ts(D_A, tmem + COL_WCUR + ks * 8, bh, idesc, 1);
                 umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 128 + ks * 8, bh, idesc, 1);
-                umma::mma_bf16_ts(D_A, tmem + COL_WCUR + ks * 8, bl, idesc, 1);
-                umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 128 + ks * 8, bl, idesc, 1);
-                umma::mma_bf16_ts(D_A, tmem + COL_WCUR + 64 + ks * 8, bh, idesc, 1);
-                umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 192 + ks * 8, bh, idesc, 1);
+                if (!WIDE) {
+                    umma::mma_bf16_ts(D_A, tmem + COL_WCUR + ks * 8, bl, idesc, 1);
+                    umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 128 + ks * 8, bl, idesc, 1);
+                }
+                umma::mma_bf16_ts(D_A, tmem + COL_WCUR + 64 + ks * 8, WIDE ? bl : bh, idesc, 1);
+                umma::mma_bf16_ts(D_B, tmem + COL_WCUR + 192 + ks * 8, WIDE ? bl : bh, idesc, 1);
             }
             umma::mma_commit(umma::smem_addr(&gb.gate));
         }
@@ -587,8 +617,8 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
 #pragma unroll
             for (int ks = 0; ks < 8; ++ks) {
                 umma::mma_bf16_ts(D_O, tmem + COL_WOUT + ks * 8, zi_hi + ks * KS_B, idesc, ks != 0);
-                umma::mma_bf16_ts(D_O, tmem + COL_WOUT + ks * 8, zi_lo + ks * KS_B, idesc, 1);
-                umma::mma_bf16_ts(D_O, tmem + COL_WOUT + 64 + ks * 8, zi_hi + ks * KS_B, idesc, 1);
+                if (!WIDE) umma::mma_bf16_ts(D_O, tmem + COL_WOUT + ks * 8, zi_lo + ks * KS_B, idesc, 1);
+                umma::mma_bf16_ts(D_O, tmem + COL_WOUT + 64 + ks * 8, (WIDE ? zi_lo : zi_hi) + ks * KS_B, idesc, 1);
             }
             umma::mma_commit(umma::smem_addr(&gb.out));
         }
@@ -598,8 +628,8 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
 #pragma unroll
             for (int ks = 0; ks < 8; ++ks) {
                 umma::mma_bf16(D_S, ws_hi + ks * KS_A, zi_hi + ks * KS_B, idesc, ks != 0);
-                umma::mma_bf16(D_S, ws_hi + ks * KS_A, zi_lo + ks * KS_B, idesc, 1);
-                umma::mma_bf16(D_S, ws_lo + ks * KS_A, zi_hi + ks * KS_B, idesc, 1);
+                if (!WIDE) umma::mma_bf16(D_S, ws_hi + ks * KS_A, zi_lo + ks * KS_B, idesc, 1);
+                umma::mma_bf16(D_S, ws_lo + ks * KS_A, (WIDE ? zi_lo : zi_hi) + ks * KS_B, idesc, 1);
             }
             umma::mma_commit(umma::smem_addr(&gb.skip));
         }
@@ -635,6 +665,7 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
     constexpr int NH = G::NH, NU = G::NU, LBO = G::LBO, PLANE = G::PLANE;
     const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31, q = w & 3, hh = w >> 2;
     constexpr int nah = NAH, nu = NAH / 2, NA = 2 * NAH;
+    constexpr bool WIDE = NB == 16 && NA <= 8;
     const int j = 32 * q + lane, n0 = hh * nah;
     const uint32_t lane_addr = tmem + ((uint32_t)(32 * q) << 16);
     const int L = P.L, T = P.T, O = P.O, NG = P.NG;
@@ -686,7 +717,7 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
         const long long c1 = do_stats ? clock64() : 0;
 #pragma unroll
         for (int i = 0; i < NH; i += 2)   // relu (wavenet.py:840)
-            if (i < nah) img_put2(HI + joff + i * 16, PLANE, S[i] > 0.0f ? S[i] : 0.0f, S[i + 1] > 0.0f ? S[i + 1] : 0.0f);
+            if (i < nah) img_put2<WIDE>(HI + joff + i * 16, PLANE, S[i] > 0.0f ? S[i] : 0.0f, S[i + 1] > 0.0f ? S[i + 1] : 0.0f);
         umma::fence_proxy_async();
         umma::fence_before_sync();
         __syncwarp();
@@ -695,13 +726,11 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
         umma::fence_after_sync();
         {
             float h[NH];
-            if constexpr (NH == 8) umma::tmem_ld8(lane_addr + COL_HACC + n0, reinterpret_cast<float(&)[8]>(h));
-            else umma::tmem_ld16(lane_addr + COL_HACC + n0, reinterpret_cast<float(&)[16]>(h));
-            umma::tmem_ld_wait();
+            acc_load<NH, WIDE>(lane_addr + COL_HACC + n0, h);
 #pragma unroll
             for (int i = 0; i < NH; i += 2) {
                 const float y0 = __fadd_rn(h[i], b1), y1 = __fadd_rn(h[i + 1], b1);
-                if (i < nah) img_put2(H2 + joff + i * 16, PLANE, y0 > 0.0f ? y0 : 0.0f, y1 > 0.0f ? y1 : 0.0f);
+                if (i < nah) img_put2<WIDE>(H2 + joff + i * 16, PLANE, y0 > 0.0f ? y0 : 0.0f, y1 > 0.0f ? y1 : 0.0f);
             }
         }
         umma::fence_proxy_async();
@@ -713,9 +742,7 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
         const long long c2 = do_stats ? clock64() : 0;
         {
             float o[NH];
-            if constexpr (NH == 8) umma::tmem_ld8(lane_addr + COL_HACC + NB + n0, reinterpret_cast<float(&)[8]>(o));
-            else umma::tmem_ld16(lane_addr + COL_HACC + NB + n0, reinterpret_cast<float(&)[16]>(o));
-            umma::tmem_ld_wait();
+            acc_load<NH, WIDE>(lane_addr + COL_HACC + NB + n0, o);
             if (j < O) {
 #pragma unroll
                 for (int i = 0; i < NH; ++i) {
@@ -759,7 +786,7 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
     }
 }
 
-template <int NB>
+template <int NB, bool WIDE>
 __device__ void head_mma(const TcParams &P, unsigned char *smem, const uint32_t tmem, Bars &bars) {
     using G = Geo<NB>;
     constexpr int LBO = G::LBO, PLANE = G::PLANE;
@@ -779,8 +806,8 @@ __device__ void head_mma(const TcParams &P, unsigned char *smem, const uint32_t 
 #pragma unroll
             for (int ks = 0; ks < 8; ++ks) {
                 umma::mma_bf16_ts(D_H, tmem + COL_W1 + ks * 8, hi_hi + ks * KS_B, idesc, ks != 0);
-                umma::mma_bf16_ts(D_H, tmem + COL_W1 + ks * 8, hi_lo + ks * KS_B, idesc, 1);
-                umma::mma_bf16_ts(D_H, tmem + COL_W1 + 64 + ks * 8, hi_hi + ks * KS_B, idesc, 1);
+                if (!WIDE) umma::mma_bf16_ts(D_H, tmem + COL_W1 + ks * 8, hi_lo + ks * KS_B, idesc, 1);
+                umma::mma_bf16_ts(D_H, tmem + COL_W1 + 64 + ks * 8, (WIDE ? hi_lo : hi_hi) + ks * KS_B, idesc, 1);
             }
             umma::mma_commit(bh1);
         }
@@ -791,8 +818,8 @@ __device__ void head_mma(const TcParams &P, unsigned char *smem, const uint32_t 
 #pragma unroll
             for (int ks = 0; ks < 8; ++ks) {
                 umma::mma_bf16_ts(D_O, tmem + COL_W2 + ks * 8, h2_hi + ks * KS_B, idesc, ks != 0);
-                umma::mma_bf16_ts(D_O, tmem + COL_W2 + ks * 8, h2_lo + ks * KS_B, idesc, 1);
-                umma::mma_bf16_ts(D_O, tmem + COL_W2 + 64 + ks * 8, h2_hi + ks * KS_B, idesc, 1);
+                if (!WIDE) umma::mma_bf16_ts(D_O, tmem + COL_W2 + ks * 8, h2_lo + ks * KS_B, idesc, 1);
+                umma::mma_bf16_ts(D_O, tmem + COL_W2 + 64 + ks * 8, (WIDE ? h2_lo : h2_hi) + ks * KS_B, idesc, 1);
             }
             umma::mma_commit(bo);
         }
@@ -867,10 +894,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
     cluster_sync_all();   // the peers' mbarriers exist before anything is sent to them
     if (head) {
         if (warp < 8) head_epilogue<NB, NAH, STATS>(P, r, tc_smem, tmem, bars);
-        else if (warp == MMA_WARP) head_mma<NB>(P, tc_smem, tmem, bars);
+        else if (warp == MMA_WARP) head_mma<NB, (NB == 16 && NAH <= 4)>(P, tc_smem, tmem, bars);
     } else {
         if (warp < 8) layer_epilogue<NB, NAH, STATS>(P, r, l, tc_smem, tmem, bars);
-        else if (warp == MMA_WARP) layer_mma<NB>(P, tc_smem, tmem, bars);
+        else if (warp == MMA_WARP) layer_mma<NB, (NB == 16 && NAH <= 4)>(P, tc_smem, tmem, bars);
         else layer_loader(P, l, tc_smem, bars, G::S_WST);
     }
     // every role returns when the sequence is done (or the watchdog fired): release tensor memory
