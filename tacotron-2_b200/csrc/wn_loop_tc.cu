@@ -78,7 +78,7 @@ struct TcParams {
     int inputs_mode;
     float *audio, *raw;
     int B, T, NR;
-    int NG;                              // utterance groups that travel through a replica's chain one after the other (1 or 2)
+    int NG;                              // utterance groups that travel through a replica's chain one after the other (1 .. 3)
     int NA;                              // utterances a group really holds (multiple of 4, <= the MMA's N): the epilogues skip the rest
     int bend;                            // one past the last utterance of this launch
     int test_stall_step;                 // development / tests: the head stops feeding samples back at this step (-1: never)
@@ -93,16 +93,19 @@ struct Geo {
     static constexpr int PLANE = 16 * LBO;       // 128 channels
     static constexpr int IMG = 2 * PLANE;        // hi, lo
     static constexpr int CI_PLANE = (CI_K / 8) * LBO;
-    // shared memory of a layer CTA
-    static constexpr int S_WS = 0, S_WST = 65536, S_XI = S_WST + 2 * CHUNK_BYTES, S_ZI = S_XI + 2 * IMG, S_TAP = S_ZI + IMG,
-                         S_CI = S_TAP + 2 * IMG, S_XF = S_CI + 2 * CI_PLANE, S_END = S_XF + CH * NB * 4;   // S_XF: fp32 inbox of x
-    // [S_XI, S_END) is the state of ONE utterance group; a second group (NB = 16 only) repeats it GRP bytes further
-    static constexpr int GRP = S_END - S_XI, NG_MAX = (S_END + GRP <= 227 * 1024 - 1024 && 384 + 8 * NB <= 512) ? 2 : 1;
-    static constexpr int ACC = 4 * NB;           // tensor-memory columns of one group's accumulators
+    // shared memory of a layer CTA: the weights, the images every utterance group rebuilds inside its own turn (z, taps,
+    // conditioning), then per group what arrives or lives across turns (x image, double buffered, and the fp32 inbox of x)
+    static constexpr int S_WS = 0, S_WST = 65536, S_ZI = S_WST + 2 * CHUNK_BYTES, S_TAP = S_ZI + IMG, S_CI = S_TAP + 2 * IMG,
+                         S_G0 = S_CI + 2 * CI_PLANE, G_XI = 0, G_XF = 2 * IMG, GRP = 2 * IMG + CH * NB * 4;
+    // tensor memory: gate accumulators per group from COL_ACC, the out | skip accumulators (used inside a turn only) at the end
+    static constexpr int COL_OS = 512 - 2 * NB;
+    static constexpr int NG_TMEM = (COL_OS - 384) / (2 * NB), NG_SMEM = (226 * 1024 - S_G0) / GRP;
+    static constexpr int NG_MAX = NG_TMEM < NG_SMEM ? (NG_TMEM < 3 ? NG_TMEM : 3) : (NG_SMEM < 3 ? NG_SMEM : 3);
+    static constexpr int S_END = S_G0 + NG_MAX * GRP;
     // head CTA
     static constexpr int S_HI = 0, S_H2 = IMG, S_PRM = 2 * IMG, S_HEND = S_PRM + NB * CH * 4;
-    static constexpr int SMEM = (S_END + (NG_MAX - 1) * GRP) > S_HEND ? (S_END + (NG_MAX - 1) * GRP) : S_HEND;
-    static constexpr int smem_for(int ng) { return (S_END + (ng - 1) * GRP) > S_HEND ? (S_END + (ng - 1) * GRP) : S_HEND; }
+    static constexpr int SMEM = S_END > S_HEND ? S_END : S_HEND;
+    static constexpr int smem_for(int ng) { return (S_G0 + ng * GRP) > S_HEND ? (S_G0 + ng * GRP) : S_HEND; }
     static constexpr int MAILW = CH * NB;        // words of one mailbox buffer (and floats of one ring slot)
 };
 
@@ -319,8 +322,9 @@ struct GBars {   // per utterance group: every barrier completes once per step o
     unsigned long long x, z, gate, out, skip, p, xf;
 };
 struct Bars {
-    GBars g[2];
+    GBars g[3];
     unsigned long long wfull[2], wempty[2];
+    unsigned long long pdone;   // prologue only: the x-independent part of step 0 of a group has been read from the shared images
 };
 
 // =========================================================================================================================
@@ -359,6 +363,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     float *ring = nullptr, *XF = nullptr;
     unsigned char *XI = nullptr, *ZI = nullptr, *TAP = nullptr, *CI = nullptr;
     uint32_t bx = 0, bz = 0, bp = 0, bgate = 0, bout = 0, bskip = 0, bxf = 0, r_xf = 0, r_bxf = 0, acc = 0;
+    const uint32_t acc_os = lane_addr + G::COL_OS;   // out | skip accumulators, shared by the groups
     auto setg = [&](int g) {
         rg = r * NG + g;
         mx_in = P.mail_x + (long long)(rg * L + l) * 2 * G::MAILW + unit0;
@@ -366,15 +371,15 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         ms_out = P.mail_skip + (long long)(rg * L + l) * 2 * G::MAILW + unit0;
         min_in = P.mail_in + (long long)rg * 2 * NB + n0;
         ring = P.ring + ((long long)rg * P.ring_slots + P.ring_off[l]) * G::MAILW + ((long long)(hh * NU) * CH + j) * 2;   // [half][unit][channel][2]
-        unsigned char *base = smem + g * G::GRP;
-        XI = base + G::S_XI; ZI = base + G::S_ZI; TAP = base + G::S_TAP; CI = base + G::S_CI;
-        XF = reinterpret_cast<float *>(base + G::S_XF) + ((hh * NU) * CH + j) * 2;        // [half][unit][channel][2 utterances]
+        unsigned char *base = smem + G::S_G0 + g * G::GRP;
+        XI = base + G::G_XI; ZI = smem + G::S_ZI; TAP = smem + G::S_TAP; CI = smem + G::S_CI;
+        XF = reinterpret_cast<float *>(base + G::G_XF) + ((hh * NU) * CH + j) * 2;        // [half][unit][channel][2 utterances]
         GBars &gb = bars.g[g];
         bx = umma::smem_addr(&gb.x); bz = umma::smem_addr(&gb.z); bp = umma::smem_addr(&gb.p); bgate = umma::smem_addr(&gb.gate);
         bout = umma::smem_addr(&gb.out); bskip = umma::smem_addr(&gb.skip); bxf = umma::smem_addr(&gb.xf);
         r_xf = mapa_u32(umma::smem_addr(XF), out_dsmem ? crank + 1 : crank);
         r_bxf = mapa_u32(bxf, out_dsmem ? crank + 1 : crank);
-        acc = lane_addr + COL_ACC + g * G::ACC;
+        acc = lane_addr + COL_ACC + g * 2 * NB;   // gate a | gate b of the group
     };
 
     // operands of the x-independent part of step t: the two older taps from the ring and the conditioning column c(t)
@@ -416,10 +421,11 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         __syncwarp();
         if (lane == 0) umma::mbar_arrive(bp);
     };
-    for (int g = 0; g < NG; ++g) {
+    for (int g = 0; g < NG; ++g) {   // the tap / conditioning images are shared by the groups: one group at a time
         setg(g);
         prep_load(0);
         prep_store();
+        if (g + 1 < NG && mbar_wait_wd(umma::smem_addr(&bars.pdone), g & 1, P.abort_flag)) return;
     }
 
     const long long st_begin = clock64();
@@ -489,7 +495,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         const long long c4 = do_stats ? clock64() : 0;
         {
             float o[NH];
-            acc_load<NH, WIDE>(acc + 2 * NB + n0, o);
+            acc_load<NH, WIDE>(acc_os + n0, o);
             if (l + 1 < L) {
 #pragma unroll
                 for (int u = 0; u < NU; ++u) {
@@ -507,7 +513,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         umma::fence_after_sync();
         {
             float s[NH];
-            acc_load<NH, WIDE>(acc + 3 * NB + n0, s);
+            acc_load<NH, WIDE>(acc_os + NB + n0, s);
 #pragma unroll
             for (int u = 0; u < NU; ++u)
                 if (u < nu) st_ll2(ms_out + (long long)par * G::MAILW + (long long)u * CH * 2, __fadd_rn(s[2 * u], bs), __fadd_rn(s[2 * u + 1], bs), tag);
@@ -542,18 +548,16 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
     const uint64_t st_lo[2] = {umma::smem_desc(s0 + G::S_WST + 8192, CH * 16, 128), umma::smem_desc(s0 + G::S_WST + CHUNK_BYTES + 8192, CH * 16, 128)};
     constexpr uint64_t KS_B = (uint64_t)((2 * LBO) >> 4);        // descriptor step per k step (16 k) of an activation image
     constexpr uint64_t KS_A = (uint64_t)((2 * CH * 16) >> 4);    // ... of a 128-row weight image
-    constexpr uint64_t GRP_D = (uint64_t)(G::GRP >> 4);          // ... from one utterance group's images to the next group's
 
     // the x-independent part of step tp of group g, accumulated from scratch into that group's gate accumulators
     auto p_phase = [&](int tp, int g) -> bool {
         if (mbar_wait_wd(umma::smem_addr(&bars.g[g].p), tp & 1, P.abort_flag)) return true;
         umma::fence_after_sync();
-        const uint32_t D_A = tmem + COL_ACC + g * G::ACC, D_B = D_A + NB;
-        const uint64_t gd = g * GRP_D;
-        const uint64_t tap_hi[3] = {umma::smem_desc(s0 + G::S_TAP, LBO, 128) + gd, umma::smem_desc(s0 + G::S_TAP + G::IMG, LBO, 128) + gd,
-                                    umma::smem_desc(s0 + G::S_CI, LBO, 128) + gd};
-        const uint64_t tap_lo[3] = {umma::smem_desc(s0 + G::S_TAP + PLANE, LBO, 128) + gd, umma::smem_desc(s0 + G::S_TAP + G::IMG + PLANE, LBO, 128) + gd,
-                                    umma::smem_desc(s0 + G::S_CI + G::CI_PLANE, LBO, 128) + gd};
+        const uint32_t D_A = tmem + COL_ACC + g * 2 * NB, D_B = D_A + NB;
+        const uint64_t tap_hi[3] = {umma::smem_desc(s0 + G::S_TAP, LBO, 128), umma::smem_desc(s0 + G::S_TAP + G::IMG, LBO, 128),
+                                    umma::smem_desc(s0 + G::S_CI, LBO, 128)};
+        const uint64_t tap_lo[3] = {umma::smem_desc(s0 + G::S_TAP + PLANE, LBO, 128), umma::smem_desc(s0 + G::S_TAP + G::IMG + PLANE, LBO, 128),
+                                    umma::smem_desc(s0 + G::S_CI + G::CI_PLANE, LBO, 128)};
         const uint32_t pass = (uint32_t)(tp * NG + g);   // passes over the weight stream so far
 #pragma unroll
         for (int kb = 0; kb < KB_TOTAL; ++kb) {
@@ -580,17 +584,20 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
         }
         return false;
     };
-    for (int g = 0; g < NG; ++g)
+    for (int g = 0; g < NG; ++g) {
         if (p_phase(0, g)) return;
+        if (umma::elect_one()) umma::mma_commit(umma::smem_addr(&bars.pdone));
+        __syncwarp();
+    }
     for (int t = 0; t < T; ++t) {
       for (int g = 0; g < NG; ++g) {
         const int par = t & 1;
         GBars &gb = bars.g[g];
-        const uint32_t D_A = tmem + COL_ACC + g * G::ACC, D_B = D_A + NB, D_O = D_A + 2 * NB, D_S = D_A + 3 * NB;
-        const uint32_t sg = s0 + g * G::GRP;
-        const uint64_t xi_hi = umma::smem_desc(sg + G::S_XI + par * G::IMG, LBO, 128),
-                       xi_lo = umma::smem_desc(sg + G::S_XI + par * G::IMG + PLANE, LBO, 128);
-        const uint64_t zi_hi = umma::smem_desc(sg + G::S_ZI, LBO, 128), zi_lo = umma::smem_desc(sg + G::S_ZI + PLANE, LBO, 128);
+        const uint32_t D_A = tmem + COL_ACC + g * 2 * NB, D_B = D_A + NB, D_O = tmem + G::COL_OS, D_S = D_O + NB;
+        const uint32_t sg = s0 + G::S_G0 + g * G::GRP;
+        const uint64_t xi_hi = umma::smem_desc(sg + G::G_XI + par * G::IMG, LBO, 128),
+                       xi_lo = umma::smem_desc(sg + G::G_XI + par * G::IMG + PLANE, LBO, 128);
+        const uint64_t zi_hi = umma::smem_desc(s0 + G::S_ZI, LBO, 128), zi_lo = umma::smem_desc(s0 + G::S_ZI + PLANE, LBO, 128);
         // current tap of the dilated conv (modules.py:294-297) on top of the x-independent part
         if (mbar_wait_wd(umma::smem_addr(&gb.x), par, P.abort_flag)) return;
         umma::fence_after_sync();
@@ -678,7 +685,7 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
     unsigned char *HI = smem + G::S_HI, *H2 = smem + G::S_H2;
     float *prm = reinterpret_cast<float *>(smem + G::S_PRM);   // [NB][CH]
     const uint32_t bh = umma::smem_addr(&bars.g[0].x), bh2 = umma::smem_addr(&bars.g[0].z), bh1 = umma::smem_addr(&bars.g[0].gate),
-                   bo = umma::smem_addr(&bars.g[0].out), bprm = umma::smem_addr(&bars.g[0].skip);
+                   bo = umma::smem_addr(&bars.g[0].out);
     // initial input (wavenet.py:433-445): raw 0.0, mulaw mulaw(0) = 0.0; WaveNet.step semantics: the first input is x[0]
     for (int g = 0; g < NG; ++g) {
         const long long b = (long long)P.b0 + (long long)(r * NG + g) * NA + tid;
@@ -692,8 +699,11 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
         const int rg = r * NG + g;
         const unsigned long long *ms_in = P.mail_skip + (long long)rg * L * 2 * G::MAILW + unit0;
         unsigned long long *min_out = P.mail_in + (long long)rg * 2 * NB;
-        const long long bu = (long long)P.b0 + (long long)rg * NA + tid;   // utterance of the sampler thread
-        const bool sampler = tid < NA && bu < P.bend;
+        // the O <= 32 output rows live in lane quarter 0: warp 0 (first half of the utterances) and warp 4 (second half) hold
+        // every parameter of their utterances, so lane i of those warps samples utterance n0 + i without a CTA-wide barrier
+        const int ns = n0 + lane;                                              // utterance (inside the group) of a sampler lane
+        const long long bu = (long long)P.b0 + (long long)rg * NA + ns;
+        const bool slane = q == 0 && lane < nah, sampler = slane && bu < P.bend;
         const int par = t & 1;                      // mailbox buffer of the step
         const int bpar = (t * NG + g) & 1;          // phase of this CTA's barriers (one completion per group and step)
         const unsigned tag = (unsigned)t + 1u;
@@ -757,22 +767,21 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
         }
         umma::fence_before_sync();
         __syncwarp();
-        if (lane == 0) umma::mbar_arrive(bprm);
-        if (mbar_wait_wd(bprm, bpar, P.abort_flag)) return;   // all parameters of the step are in shared memory
         if (t == P.test_stall_step) return;   // test hook: the chain starves and every waiter must time out (WN_ERR_WATCHDOG)
         // sampling + feedback (wavenet.py:850-878)
-        if (tid < NB) {
+        if (slane) {
             float nxt = 0.0f;
             if (sampler && P.inputs_mode) {
                 nxt = tch;
             } else if (sampler) {
-                const float smp = (O == 2) ? tc_sample_gaussian(P, prm + tid * CH, nz0)
-                                           : tc_sample_mol(P, prm + tid * CH, P.noise + ((long long)t * P.B + bu) * P.NZ);
+                const float smp = (O == 2) ? tc_sample_gaussian(P, prm + ns * CH, nz0)
+                                           : tc_sample_mol(P, prm + ns * CH, P.noise + ((long long)t * P.B + bu) * P.NZ);
                 P.audio[bu * T + t] = P.input_type == WN_INPUT_MULAW ? wn_inv_mulawf(smp) : smp;
                 nxt = P.teacher ? tch : smp;
             }
-            if (t + 1 < T) st_ll1(min_out + ((t + 1) & 1) * NB + tid, nxt, tag + 1u);
+            if (t + 1 < T) st_ll1(min_out + ((t + 1) & 1) * NB + ns, nxt, tag + 1u);
         }
+        __syncwarp();   // the parameters are overwritten by the same warp in its next turn
         if (do_stats) {
             const long long c3 = clock64();
             st_c[0] += c1 - c0; st_c[1] += c2 - c1; st_c[2] += c3 - c2;
@@ -858,7 +867,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
     const int r = blockIdx.x / stages, l = blockIdx.x - r * stages;
     const bool head = l == P.L;
     if (tid == 0) {
-        for (int g = 0; g < 2; ++g) {
+        for (int g = 0; g < 3; ++g) {
             GBars &gb = bars.g[g];
             umma::mbar_init(umma::smem_addr(&gb.x), EPI_THREADS / 32);
             umma::mbar_init(umma::smem_addr(&gb.z), EPI_THREADS / 32);
@@ -869,6 +878,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
             umma::mbar_init(umma::smem_addr(&gb.xf), 1);
         }
         for (int i = 0; i < 2; ++i) { umma::mbar_init(umma::smem_addr(&bars.wfull[i]), 1); umma::mbar_init(umma::smem_addr(&bars.wempty[i]), 1); }
+        umma::mbar_init(umma::smem_addr(&bars.pdone), 1);
         umma::mbar_fence_init();
     }
     if (warp == 0) umma::tmem_alloc(umma::smem_addr(&tmem_base_s), 512);
@@ -885,7 +895,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
         load_tmem_weights(blob + OFF_TMEM, 6, tmem, COL_WCUR);
         const uint4 *ws = reinterpret_cast<const uint4 *>(blob + OFF_WS);
         for (int i = tid; i < 65536 / 16; i += TC_THREADS) reinterpret_cast<uint4 *>(tc_smem + G::S_WS)[i] = __ldg(ws + i);
-        for (int i = tid; i < P.NG * G::GRP / 16; i += TC_THREADS) reinterpret_cast<uint4 *>(tc_smem + G::S_XI)[i] = make_uint4(0, 0, 0, 0);
+        for (int i = tid; i < (G::S_G0 - G::S_ZI + P.NG * G::GRP) / 16; i += TC_THREADS) reinterpret_cast<uint4 *>(tc_smem + G::S_ZI)[i] = make_uint4(0, 0, 0, 0);
     }
     umma::fence_proxy_async();
     umma::fence_before_sync();
@@ -939,7 +949,7 @@ bool wn_tc_supported(const wn_handle *h) {
     const wn_config &c = h->cfg;
     return c.residual_channels == CH && c.gate_channels == 2 * CH && c.skip_out_channels == CH && c.kernel_size == 3 &&
            c.input_type != WN_INPUT_MULAW_QUANTIZE && c.gin_channels <= 0 && c.cin_channels > 0 && c.cin_channels <= CI_K &&
-           c.out_channels <= CH && c.layers >= 1 && c.layers / c.stacks <= 16;
+           c.out_channels <= 32 && c.layers >= 1 && c.layers / c.stacks <= 16;   // <= 32 output rows: one TMEM lane quarter (head sampler)
 }
 
 void wn_tc_free(wn_handle *h) {
@@ -1076,7 +1086,7 @@ int wn_tc_plan(wn_handle *h) {
 }
 
 // largest batch one launch takes; larger batches run as several launches
-int wn_tc_max_batch(const wn_handle *h) { return h->tc ? h->tc->max_replicas * 32 : 0; }
+int wn_tc_max_batch(const wn_handle *h) { return h->tc ? h->tc->max_replicas * Geo<16>::NG_MAX * 16 : 0; }
 
 void wn_tc_fill_info(wn_handle *h, wn_info *info) {
     if (!h->tc || h->engine != WN_ENGINE_TC) return;
@@ -1116,17 +1126,17 @@ static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStr
     WnTcPlan *pl = h->tc;
     // How the batch is laid over the chip.  A replica is a chain of L + 1 CTAs; NG utterance groups of NA utterances follow each
     // other through it.  Measured: the step time of a group grows with NA (epilogue work, hand-off bytes:
-    // 25.4 / 30.2 / 33.8 / 37.5 us at 4 / 8 / 12 / 16), a second group in the chain costs ~1 us, more than 5 replicas lose the
+    // 23.3 / 28.7 / 33.8 / 37.5 us at 4 / 8 / 12 / 16), every further group in the chain costs ~1 us, more than 5 replicas lose the
     // clusters of 7 (+1.5 us); idle SMs cost nothing.  The cheapest feasible (NA, NG, NR) wins.
     int nb = 16, na = 16, ng = 1, nr = 0;
     {
-        static const float base[4] = {25.4f, 30.2f, 33.8f, 37.5f};
+        static const float base[4] = {23.3f, 28.7f, 33.8f, 37.5f};
         float best = 1e30f;
         for (int a = 4; a <= 16; a += 4)
             for (int g = 1; g <= Geo<16>::NG_MAX; ++g) {
                 const int groups = (nbatch + a - 1) / a, r = (groups + g - 1) / g;
                 if (r > pl->max_replicas) continue;
-                const float cost = base[a / 4 - 1] + (g > 1 ? 1.0f : 0.0f) + (r > 5 ? 1.5f : 0.0f) + 0.01f * r * g;
+                const float cost = base[a / 4 - 1] + 1.0f * (g - 1) + (r > 5 ? 1.5f : 0.0f) + 0.01f * r * g;
                 if (cost < best) { best = cost; na = a; ng = g; nr = r; }
             }
     }
@@ -1221,7 +1231,7 @@ int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const
     }
     p.test_stall_step = -1;
     if (const char *e = getenv("WN_TC_TEST_STALL")) p.test_stall_step = atoi(e);
-    const int cap = pl->max_replicas * 32;   // = 2 groups x 16 utterances per chain with N = 16 MMAs
+    const int cap = pl->max_replicas * Geo<16>::NG_MAX * 16;   // groups of 16 utterances in every chain
     const int nchunks = (B + cap - 1) / cap, per = (B + nchunks - 1) / nchunks;
     for (int b0 = 0; b0 < B; b0 += per) {
         const int rc = tc_launch_chunk(h, p, b0, std::min(per, B - b0), st);
