@@ -292,8 +292,8 @@ def strong_c3_point(torch, dist, net, hp, world, rank):
                         'with sharding.shard_utterances, final gather with sharding.gather_wavs included'.format(world),
             'scaling': 'strong', 'value': v, 'unit': UNIT, 'rtf': v / SAMPLE_RATE, 'rtf_target': 1000.0, 'seconds': dt, 'n_gpus': world,
             'utterances_per_gpu': len(mine), 'engine': info['engine'], 'loop_ms_rank0': info['last_loop_ms'],
-            'us_per_step_rank0': 1e3 * info['last_loop_ms'] / T * (1 if len(mine) <= 224 else 0.5),
-            'replicas': info['pipeline_ctas_per_layer'], 'utterances_per_replica': info['pipeline_group_size'],
+            'us_per_step_rank0': 1e3 * info['last_loop_ms'] / T / max(1, -(-len(mine) // 336)),   # per launch: one launch takes 336 utterances
+            'layer_chains': info['pipeline_ctas_per_layer'], 'utterances_per_group': info['pipeline_group_size'],
             'limiter': 'serial stage latency of the layer chain (us_per_step x 220 550 steps); no collective on the data path',
             'api': 'wn_synthesize_host per rank (host buffers) + one gather'}
 
@@ -446,11 +446,11 @@ def run_ours(args):
         }
         if info['engine'] == 'tc':
             # tcgen05 engine: a batched step is tensor work (north_star); the fraction is on ALGORITHMIC flops against the
-            # measured sustained bf16 GEMM rate; the kernel executes 3 bf16 MMA passes per fp32 product
+            # measured sustained bf16 GEMM rate (fp16 MMAs run at the same rate); the kernel executes 2-3 fp16 MMA passes per fp32 product
             t_peak = peaks.get('bf16_tflops_sustained', peaks.get('bf16_tflops', 1590.0))
             roofline = dict(common_fields, bound='tensor', achieved=alg_tflops, peak=t_peak, unit='TFLOP/s', frac=alg_tflops / t_peak,
                             traffic=None, traffic_source='not captured on the timed shape (see profiles/ for the range capture)',
-                            executed_bf16_tflops=3 * alg_tflops, replicas=info['pipeline_ctas_per_layer'], utterances_per_replica=info['pipeline_group_size'])
+                            executed_fp16_tflops=3 * alg_tflops, layer_chains=info['pipeline_ctas_per_layer'], utterances_per_group=info['pipeline_group_size'])
         else:
             roofline = dict(common_fields, bound='hbm', achieved=achieved, peak=hbm_peak, unit='GB/s', frac=achieved / hbm_peak,
                             traffic=traffic, traffic_source=None if traffic is None else 'EXTRAPOLATED, not measured on this launch: ' + traffic_src,
