@@ -8,7 +8,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, '..', 'wavenet_vocoder', 'libwavenet_b200.so')
-SOURCES = ['wn_api.cu', 'wn_upsample.cu', 'wn_loop_generic.cu', 'wn_loop_pipe.cu', 'wn_loop_tc.cu', 'wn_step_full.cu', 'wn_step_gemm.cu', 'wn_step_umma.cu']
+SOURCES = ['wn_api.cu', 'wn_upsample.cu', 'wn_loop_generic.cu', 'wn_loop_pipe.cu', 'wn_loop_tc.cu', 'wn_loop_tc2.cu', 'wn_step_full.cu', 'wn_step_gemm.cu', 'wn_step_umma.cu']
 
 
 def build(force=False, verbose=False):

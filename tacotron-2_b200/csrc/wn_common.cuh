@@ -52,6 +52,7 @@ struct WnPipePlan;  // wn_loop_pipe.cu
 struct WnGemmPlan;  // wn_step_gemm.cu
 struct WnUmmaPlan;  // wn_step_umma.cu
 struct WnTcPlan;    // wn_loop_tc.cu
+struct WnTc2Plan;   // wn_loop_tc2.cu
 
 struct wn_handle {
     wn_config cfg;
@@ -78,6 +79,7 @@ struct wn_handle {
     WnGemmPlan *gemm = nullptr;
     WnUmmaPlan *umma = nullptr;
     WnTcPlan *tc = nullptr;
+    WnTc2Plan *tc2 = nullptr;
     int engine = WN_ENGINE_GENERIC;
     int64_t launches = 0;
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};  // before upsample / before loop / after loop
@@ -118,6 +120,15 @@ void wn_tc_fill_info(wn_handle *h, wn_info *info);
 int wn_tc_check_abort(wn_handle *h);
 int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int inputs_mode, int B, int T,
                       float *audio, float *raw, cudaStream_t st);
+// the same for the 256-channel block of paper_hparams.py (wn_loop_tc2.cu: four CTAs per layer); reached through the wn_tc_* entry
+// points above, which hand over to these when the model is that block
+bool wn_tc2_supported(const wn_handle *h);
+int wn_tc2_plan(wn_handle *h);
+void wn_tc2_free(wn_handle *h);
+void wn_tc2_fill_info(wn_handle *h, wn_info *info);
+int wn_tc2_check_abort(wn_handle *h);
+int wn_launch_loop_tc2(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int inputs_mode, int B, int T,
+                       float *audio, float *raw, cudaStream_t st);
 
 // time-parallel WaveNet.step (wn_step_gemm.cu)
 bool wn_gemm_supported(const wn_handle *h);

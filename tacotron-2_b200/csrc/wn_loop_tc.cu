@@ -46,7 +46,6 @@ constexpr int KB_TOTAL = 11;             // 32-wide k blocks of the streamed wei
 constexpr int NCHUNK = 2 * KB_TOTAL;     // (k block, gate half), 16 KB each: A image [4][128][8] fp16 hi, then lo
 constexpr int CHUNK_BYTES = 16384;
 constexpr int CI_K = 96;                 // K of the conditioning image (cin <= 96, zero padded)
-constexpr unsigned long long WATCHDOG_NS_DEFAULT = 20ull * 1000 * 1000 * 1000;   // WN_WATCHDOG_MS overrides it (tests)
 
 // layer blob (bytes)
 constexpr int OFF_TMEM = 0;                       // 6 x [128 rows][64 words]: Wcur a hi, a lo, b hi, b lo, Wout hi, lo
@@ -109,215 +108,8 @@ struct Geo {
     static constexpr int MAILW = CH * NB;        // words of one mailbox buffer (and floats of one ring slot)
 };
 
-// ---- {value, tag} words -----------------------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned long long pack_ll(float v, unsigned tag) {
-    return ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v);
-}
-__device__ __forceinline__ void st_ll2(unsigned long long *p, float v0, float v1, unsigned tag) {
-    const unsigned long long a = pack_ll(v0, tag), b = pack_ll(v1, tag);
-    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
-}
-__device__ __forceinline__ void st_ll1(unsigned long long *p, float v, unsigned tag) {
-    const unsigned long long a = pack_ll(v, tag);
-    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(a) : "memory");
-}
-__device__ __forceinline__ void ld_ll2(const unsigned long long *p, unsigned long long &a, unsigned long long &b) {
-    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
-}
-__device__ __forceinline__ unsigned long long global_timer_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-// shared watchdog of every wait in this kernel: a waiter that sees the abort flag, or that has waited WATCHDOG_NS of wall
-// clock, gives up (and tells everybody else); the launch then ends with wrong output and WN_ERR_WATCHDOG instead of a hang
-struct Watch {
-    int *flag;
-    unsigned spins = 0;
-    unsigned long long t0 = 0;
-    __device__ __forceinline__ bool expired() {
-        if ((++spins & 0x3ffu) != 0) return false;
-        if (*(volatile int *)flag) return true;
-        const unsigned long long now = global_timer_ns();
-        if (t0 == 0) t0 = now;
-        else if (now - t0 > *reinterpret_cast<const volatile unsigned long long *>(flag + 2)) { atomicExch(flag, 1); return true; }
-        return false;
-    }
-};
-// the first `nu` of NU units of two words, `stride` words apart (the others read as 0); true if the watchdog fired
-template <int NU>
-__device__ __forceinline__ bool poll_units(const unsigned long long *p, long long stride, unsigned tag, float *v, int nu, int *abort_flag) {
-    Watch wd{abort_flag};
-    for (;;) {
-        unsigned long long w[2 * NU];
-#pragma unroll
-        for (int u = 0; u < NU; ++u)
-            if (u < nu) ld_ll2(p + u * stride, w[2 * u], w[2 * u + 1]);
-        bool ok = true;
-#pragma unroll
-        for (int u = 0; u < NU; ++u)
-            if (u < nu) ok = ok && ((unsigned)(w[2 * u] >> 32) == tag) && ((unsigned)(w[2 * u + 1] >> 32) == tag);
-        if (ok) {
-#pragma unroll
-            for (int u = 0; u < NU; ++u) {
-                v[2 * u] = u < nu ? __uint_as_float((unsigned)(w[2 * u] & 0xffffffffu)) : 0.0f;
-                v[2 * u + 1] = u < nu ? __uint_as_float((unsigned)(w[2 * u + 1] & 0xffffffffu)) : 0.0f;
-            }
-            return false;
-        }
-        if (wd.expired()) return true;
-    }
-}
-__device__ __forceinline__ bool mbar_wait_wd(uint32_t bar, uint32_t parity, int *abort_flag) {
-    Watch wd{abort_flag};
-    while (!umma::mbar_try(bar, parity))
-        if (wd.expired()) return true;
-    return false;
-}
+#include "wn_tc_common.cuh"
 
-// ---- thread-block cluster / distributed shared memory: consecutive stages of a replica that share a cluster hand x over
-// with st.async straight into the next CTA's shared memory (counted in bytes on that CTA's mbarrier) ----------------------
-__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
-__device__ __forceinline__ uint32_t cluster_nctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
-__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
-    uint32_t r;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
-    return r;
-}
-__device__ __forceinline__ void st_async2(uint32_t raddr, float v0, float v1, uint32_t rmbar) {
-    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];"
-                 ::"r"(raddr), "f"(v0), "f"(v1), "r"(rmbar) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_cluster(uint32_t bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-    return ok != 0;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-
-__device__ __forceinline__ bool mbar_wait_cluster_wd(uint32_t bar, uint32_t parity, int *abort_flag) {
-    Watch wd{abort_flag};
-    while (!mbar_try_cluster(bar, parity))
-        if (wd.expired()) return true;
-    return false;
-}
-
-// ---- activation images: [K/8][NB][8] fp16, hi plane then lo plane; one thread per channel writes 2-byte elements ---------
-// v -> (hi, lo) with hi = v rounded to 11 significant bits (what fp16 holds), lo = fp16(v - hi): hi + lo carries 22 bits of v, so
-// the three MMA passes hi*hi + hi*lo + lo*hi reproduce the fp32 product to ~2^-22.  hi is rounded with integer operations
-// (round to nearest even on bit 13): exactly representable in fp16 for |v| in [6.1e-5, 65504], which the conversions below
-// then pack without a second rounding; below that range the absolute error is < 6e-8.
-__device__ __forceinline__ float round11(float v) {
-    const uint32_t u = __float_as_uint(v);
-    return __uint_as_float((u + 0x00000fffu + ((u >> 13) & 1u)) & 0xffffe000u);
-}
-// WIDE images (groups of <= 8 utterances with N = 16 MMAs): the unused half of the columns carries the lo parts, i.e. plane 0 holds
-// hi at column n and lo at column n + 8, plane 1 holds hi at column n (columns 8.. stay zero).  One MMA of A_hi with plane 0 then
-// yields A_hi x_hi (columns 0..7) AND A_hi x_lo (columns 8..15), a second one of A_lo with plane 1 adds A_lo x_hi: two MMAs per k
-// step instead of three; the epilogue adds column n + 8 to column n.
-template <bool WIDE>
-__device__ __forceinline__ void img_put(unsigned char *img, int plane, int lbo, int j, int n, float v) {
-    const float hf = round11(v);
-    const int off = (j >> 3) * lbo + n * 16 + (j & 7) * 2;
-    const unsigned short h = __half_as_ushort(__float2half_rn(hf)), l = __half_as_ushort(__float2half_rn(__fsub_rn(v, hf)));
-    *reinterpret_cast<unsigned short *>(img + off) = h;
-    if (WIDE) {
-        *reinterpret_cast<unsigned short *>(img + off + 8 * 16) = l;
-        *reinterpret_cast<unsigned short *>(img + plane + off) = h;
-    } else {
-        *reinterpret_cast<unsigned short *>(img + plane + off) = l;
-    }
-}
-// two neighbouring utterances n, n + 1 of one channel: one packed conversion per plane (float -> half conversions run on the
-// 16-lane special-function pipe, which bounds the epilogues of this kernel)
-template <bool WIDE>
-__device__ __forceinline__ void img_put2(unsigned char *p /* element (j, n) of plane 0 */, int plane, float v0, float v1) {
-    const float h0 = round11(v0), h1 = round11(v1);
-    uint32_t h, l;
-    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(h1), "f"(h0));
-    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(l) : "f"(__fsub_rn(v1, h1)), "f"(__fsub_rn(v0, h0)));
-    *reinterpret_cast<unsigned short *>(p) = (unsigned short)h;
-    *reinterpret_cast<unsigned short *>(p + 16) = (unsigned short)(h >> 16);
-    if (WIDE) {
-        *reinterpret_cast<unsigned short *>(p + 8 * 16) = (unsigned short)l;
-        *reinterpret_cast<unsigned short *>(p + 9 * 16) = (unsigned short)(l >> 16);
-        *reinterpret_cast<unsigned short *>(p + plane) = (unsigned short)h;
-        *reinterpret_cast<unsigned short *>(p + plane + 16) = (unsigned short)(h >> 16);
-    } else {
-        *reinterpret_cast<unsigned short *>(p + plane) = (unsigned short)l;
-        *reinterpret_cast<unsigned short *>(p + plane + 16) = (unsigned short)(l >> 16);
-    }
-}
-// NH accumulator columns of this thread's lane from column `taddr` on; WIDE: plus the partial sums 8 columns further
-template <int NH, bool WIDE>
-__device__ __forceinline__ void acc_load(uint32_t taddr, float (&v)[NH]) {
-    if constexpr (NH == 8) {
-        umma::tmem_ld8(taddr, v);
-        if constexpr (WIDE) {   // at most 4 utterances per thread: 4 columns (a wider load could leave the allocation)
-            float w[4];
-            umma::tmem_ld4(taddr + 8, w);
-            umma::tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 4; ++i) v[i] = __fadd_rn(v[i], w[i]);
-            return;
-        }
-    } else {
-        umma::tmem_ld16(taddr, v);
-    }
-    umma::tmem_ld_wait();
-}
-
-// tanh(t) * sigmoid(s) (modules.py:510) with ex2.approx / rcp.approx; same form as wn_step_umma.cu
-__device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
-__device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
-__device__ __forceinline__ float gate_fast(float t, float s) {
-    // tanh(t) * sigmoid(s) = sign(t) (1 - E) / ((1 + E)(1 + F)), E = exp(-2|t|) in (0, 1], F = exp(-s): two ex2 and ONE rcp per
-    // element (the MUFU pipe, 16 lanes per clock and SM, bounds this epilogue); F = inf gives rcp(inf) = 0, the right limit
-    constexpr float LOG2E = 1.4426950408889634f;
-    const float at = fabsf(t);
-    const float E = ex2_approx(__fmul_rn(-2.0f * LOG2E, at)), F = ex2_approx(__fmul_rn(-LOG2E, s));
-    const float den = __fmul_rn(__fadd_rn(1.0f, E), __fadd_rn(1.0f, F));
-    const float r = rcp_approx(den);
-    // 1 - E cancels for small |t|: tanh(|t|) (1 + E) from the polynomial of wn_tanhf instead (select, no branch)
-    const float z = __fmul_rn(at, at);
-    float p = -5.70498872745e-3f;
-    p = __fmaf_rn(p, z, 2.06390887954e-2f);
-    p = __fmaf_rn(p, z, -5.37397155531e-2f);
-    p = __fmaf_rn(p, z, 1.33314422036e-1f);
-    p = __fmaf_rn(p, z, -3.33332819422e-1f);
-    const float small = __fmul_rn(__fmaf_rn(__fmul_rn(p, z), at, at), __fadd_rn(1.0f, E));
-    const float num = at < 0.625f ? small : __fsub_rn(1.0f, E);
-    return copysignf(__fmul_rn(num, r), t);
-}
-
-__device__ __forceinline__ float tc_sample_gaussian(const TcParams &P, const float *out, float eps) {   // gaussian.py:39-52
-    const float mean = out[0];
-    const float ls = out[1] > P.log_scale_min_gauss ? out[1] : P.log_scale_min_gauss;
-    float x = __fadd_rn(mean, __fmul_rn(wn_expf(ls), eps));
-    x = x > -1.0f ? x : -1.0f;
-    return x < 1.0f ? x : 1.0f;
-}
-__device__ float tc_sample_mol(const TcParams &P, const float *out, const float *u) {   // mixture.py:76-107
-    const int K = P.O / 3;
-    int best = 0;
-    float bestv = 0.0f;
-    for (int k = 0; k < K; ++k) {
-        const float v = __fsub_rn(out[k], wn_logf(-wn_logf(u[k])));
-        if (k == 0 || v > bestv) { bestv = v; best = k; }
-    }
-    const float mean = out[K + best], lsr = out[2 * K + best];
-    const float ls = lsr > P.log_scale_min ? lsr : P.log_scale_min;
-    const float u2 = u[K];
-    const float lg = __fsub_rn(wn_logf(u2), wn_logf(__fsub_rn(1.0f, u2)));
-    float x = __fadd_rn(mean, __fmul_rn(wn_expf(ls), lg));
-    x = x > -1.0f ? x : -1.0f;
-    return x < 1.0f ? x : 1.0f;
-}
-
-// mbarriers of a CTA
 struct GBars {   // per utterance group: every barrier completes once per step of its group
     unsigned long long x, z, gate, out, skip, p, xf;
 };
@@ -774,8 +566,8 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
             if (sampler && P.inputs_mode) {
                 nxt = tch;
             } else if (sampler) {
-                const float smp = (O == 2) ? tc_sample_gaussian(P, prm + ns * CH, nz0)
-                                           : tc_sample_mol(P, prm + ns * CH, P.noise + ((long long)t * P.B + bu) * P.NZ);
+                const float smp = (O == 2) ? tc_sample_gaussian(P.log_scale_min_gauss, prm + ns * CH, nz0)
+                                           : tc_sample_mol(P.log_scale_min, O, prm + ns * CH, P.noise + ((long long)t * P.B + bu) * P.NZ);
                 P.audio[bu * T + t] = P.input_type == WN_INPUT_MULAW ? wn_inv_mulawf(smp) : smp;
                 nxt = P.teacher ? tch : smp;
             }
@@ -945,14 +737,17 @@ static void split_host(float v, uint16_t &hi, uint16_t &lo) {   // fp16 (hi, lo)
     memcpy(&lo, &l, 2);
 }
 
-bool wn_tc_supported(const wn_handle *h) {
+static bool tc1_supported(const wn_handle *h) {
     const wn_config &c = h->cfg;
     return c.residual_channels == CH && c.gate_channels == 2 * CH && c.skip_out_channels == CH && c.kernel_size == 3 &&
            c.input_type != WN_INPUT_MULAW_QUANTIZE && c.gin_channels <= 0 && c.cin_channels > 0 && c.cin_channels <= CI_K &&
            c.out_channels <= 32 && c.layers >= 1 && c.layers / c.stacks <= 16;   // <= 32 output rows: one TMEM lane quarter (head sampler)
 }
 
+bool wn_tc_supported(const wn_handle *h) { return tc1_supported(h) || wn_tc2_supported(h); }
+
 void wn_tc_free(wn_handle *h) {
+    wn_tc2_free(h);
     WnTcPlan *pl = h->tc;
     if (!pl) return;
     if (pl->d_layer_blobs) cudaFree(pl->d_layer_blobs);
@@ -979,7 +774,8 @@ static const void *tc_kernel(int nb, int na, bool stats) {
 
 // Packs the weights (TF layouts) into the per-CTA blobs described at the top of this file.
 int wn_tc_plan(wn_handle *h) {
-    if (!wn_tc_supported(h)) { h->err = "tensor-core loop engine: needs R = G/2 = S = 128, kernel_size 3, scalar input, local conditioning (<= 96 channels), no global conditioning"; return WN_ERR_INVALID; }
+    if (!tc1_supported(h) && wn_tc2_supported(h)) return wn_tc2_plan(h);   // the 256-channel block: wn_loop_tc2.cu
+    if (!tc1_supported(h)) { h->err = "tensor-core loop engine: needs R = G/2 = S = 128, kernel_size 3, scalar input, local conditioning (<= 96 channels), no global conditioning"; return WN_ERR_INVALID; }
     const wn_config &c = h->cfg;
     const int L = c.layers, cin = c.cin_channels, O = c.out_channels, G2 = 2 * CH;
     auto W = [&](const std::string &n) -> const float * {
@@ -1089,6 +885,7 @@ int wn_tc_plan(wn_handle *h) {
 int wn_tc_max_batch(const wn_handle *h) { return h->tc ? h->tc->max_replicas * Geo<16>::NG_MAX * 16 : 0; }
 
 void wn_tc_fill_info(wn_handle *h, wn_info *info) {
+    wn_tc2_fill_info(h, info);
     if (!h->tc || h->engine != WN_ENGINE_TC) return;
     info->pipeline_ctas = h->tc->last_nr * (h->cfg.layers + 1);
     info->pipeline_ctas_per_layer = h->tc->last_nr;
@@ -1096,6 +893,7 @@ void wn_tc_fill_info(wn_handle *h, wn_info *info) {
 }
 
 int wn_tc_check_abort(wn_handle *h) {   // after the stream has been synchronised
+    if (h->tc2) return wn_tc2_check_abort(h);
     WnTcPlan *pl = h->tc;
     if (!pl || !pl->h_abort) return WN_OK;
     if (pl->d_stats && pl->stats_ctas > 0 && getenv("WN_TC_STATS")) {   // development aid
@@ -1217,6 +1015,7 @@ static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStr
 // Batches above the launch limit (7 replicas of 32 utterances on 148 SMs) run as consecutive launches over equal chunks.
 int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int inputs_mode, int B, int T,
                       float *audio, float *raw, cudaStream_t st) {
+    if (h->tc2) return wn_launch_loop_tc2(h, c_up, noise, teacher, inputs_mode, B, T, audio, raw, st);
     WnTcPlan *pl = h->tc;
     if (!pl) { h->err = "tensor-core loop engine not planned"; return WN_ERR_STATE; }
     TcParams p = pl->prm;

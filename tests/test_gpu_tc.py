@@ -137,6 +137,30 @@ def test_tc_repeated_calls_and_long_dilation_history():
     _check(net, hp, w, 3, 1)
 
 
+@pytest.mark.parametrize('B,group', [(3, 8), (16, 16), (11, 16), (19, 16)])
+def test_tc_paper_block_four_ctas_per_layer(B, group):
+    """paper_hparams.py un-shrunk (R 256, G 512, S 256, 24 layers, 10 logistics): csrc/wn_loop_tc2.cu, a layer = four CTAs that
+    all-gather x and z through L2 mailboxes; <= 8 utterances use the two-pass (hi | lo side by side) images, 19 run as two
+    launches of 10 and 9."""
+    hp = common.paper()
+    w = common.weights_for(hp)
+    net = _net(hp, w)
+    _check(net, hp, w, B, 1)
+    info = net.info()
+    assert info['pipeline_ctas'] == 4 * hp.layers + 1 and info['pipeline_ctas_per_layer'] == 4
+    assert info['pipeline_group_size'] == group
+
+
+def test_tc_paper_block_gaussian_head_and_ring_wrap():
+    """The 256-channel block with the single-Gaussian head and scalings off, T > receptive field (every ring wraps), two calls."""
+    hp = common.paper().override(out_channels=2, legacy=False, residual_legacy=False, layers=12, stacks=2)
+    w = common.weights_for(hp)
+    net = _net(hp, w)
+    Tc = 2 + (2 * 63 * 2 + 1) // hp.hop_size
+    _check(net, hp, w, 5, Tc, free=False)
+    _check(net, hp, w, 9, 1)
+
+
 def test_tc_rejects_what_it_does_not_cover():
     from wavenet_vocoder._native import NativeWaveNet
     hp = common.small()   # 32 residual channels

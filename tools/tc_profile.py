@@ -12,7 +12,7 @@ from wavenet_vocoder._native import NativeWaveNet
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
 Tc = int(sys.argv[2]) if len(sys.argv) > 2 else 4
 engine = sys.argv[3] if len(sys.argv) > 3 else 'tc'
-hp = common.default_22k()
+hp = common.paper() if (len(sys.argv) > 4 and sys.argv[4] == 'paper') else common.default_22k()   # argv[4]: 'paper' = the 256-channel block
 net = NativeWaveNet(hp, common.weights_for(hp, kind='tf-init'), engine=engine)
 T = Tc * hp.hop_size
 d_c = torch.from_numpy(common.cond_for(hp, B, Tc)).cuda()
