@@ -137,7 +137,7 @@ def test_tc_repeated_calls_and_long_dilation_history():
     _check(net, hp, w, 3, 1)
 
 
-@pytest.mark.parametrize('B,group', [(3, 8), (16, 16), (11, 16), (19, 16)])
+@pytest.mark.parametrize('B,group', [(3, 8), (16, 8), (11, 8), (19, 8), (40, 16)])
 def test_tc_paper_block_four_ctas_per_layer(B, group):
     """paper_hparams.py un-shrunk (R 256, G 512, S 256, 24 layers, 10 logistics): csrc/wn_loop_tc2.cu, a layer = four CTAs that
     all-gather x and z through L2 mailboxes; <= 8 utterances use the two-pass (hi | lo side by side) images, 19 run as two
