@@ -3,7 +3,7 @@ group / cluster choices are the production ones), plus the boundary cases of the
 
   configs[1]  default_22k, 64 utterances on one GPU: 16 groups of 4 in flight over all layer clusters
   configs[2]  128 / 32 utterances per GPU (2 and 8 GPUs): groups of 8 at the production threshold, small batch
-  configs[3]  un-shrunk paper() hparams, 16 and 14 utterances on the generic engine (both cluster branches)
+  configs[3]  un-shrunk paper() hparams, 16 and 14 utterances on the generic fp32 engine (both cluster branches)
   configs[4]  WaveNet.step on default_22k through the fused tcgen05 kernel, against WaveNetOracle.step itself
 The fp32 engines are compared BIT FOR BIT with the fixed-order C oracle; the tensor-core paths by the 1e-3 criterion.
 """
@@ -54,10 +54,14 @@ def test_config3_per_gpu_shares_pipelined_engine(B, group):
 @pytest.mark.parametrize('B', [16, 14])
 def test_config4_paper_hparams_generic_engine(B):
     """paper_hparams.py un-shrunk (R 256, G 512, S 256, 24 layers, 10 logistics, ConvTranspose2D [5, 5, 11]): 16 utterances
-    take the two-CTAs-per-SM kernel variant, 14 the clusters of 8 with one CTA per SM."""
+    take the two-CTAs-per-SM kernel variant, 14 the clusters of 8 with one CTA per SM.  (AUTO picks the tensor-core engine for
+    this block - tests/test_gpu_tc.py - so the fp32 engine is asked for by name.)"""
+    from wavenet_vocoder._native import NativeWaveNet
     hp = common.paper()
     assert (hp.residual_channels, hp.gate_channels, hp.layers, hp.out_channels) == (256, 512, 24, 30)
-    _bit_exact('auto', hp, B, 1, expect={'engine': 'generic'})
+    _bit_exact('generic', hp, B, 1, expect={'engine': 'generic'})
+    if B == 16:
+        assert NativeWaveNet(hp, common.weights_for(hp), engine='auto').info()['engine'] == 'tc'
 
 
 def test_config5_step_tensor_core_kernel_vs_numpy_oracle_step():
