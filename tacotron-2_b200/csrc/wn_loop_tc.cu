@@ -77,6 +77,7 @@ struct TcParams {
     int inputs_mode;
     float *audio, *raw;
     int B, T, NR;
+    int stride;                          // CTAs per replica in the grid: L + 1, or padded so that larger clusters divide it (idle CTAs at the end)
     int NG;                              // utterance groups that travel through a replica's chain one after the other (1 .. 3)
     int NA;                              // utterances a group really holds (multiple of 4, <= the MMA's N): the epilogues skip the rest
     int bend;                            // one past the last utterance of this launch
@@ -655,9 +656,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
     __shared__ Bars bars;
     __shared__ uint32_t tmem_base_s;
     const int tid = threadIdx.x, warp = tid >> 5;
-    const int stages = P.L + 1;
-    const int r = blockIdx.x / stages, l = blockIdx.x - r * stages;
+    const int r = blockIdx.x / P.stride, l = blockIdx.x - r * P.stride;
     const bool head = l == P.L;
+    if (l > P.L) {   // padding CTA (the replica's slots are rounded up to a multiple of the cluster size): only the cluster's barriers
+        cluster_sync_all();
+        cluster_sync_all();
+        return;
+    }
     if (tid == 0) {
         for (int g = 0; g < 3; ++g) {
             GBars &gb = bars.g[g];
@@ -727,7 +732,7 @@ struct WnTcPlan {
     long long *d_stats = nullptr;
     int stats_ctas = 0;
     int max_replicas = 0;
-    int last_nb = 0, last_nr = 0, last_ng = 1, last_cluster = 1;
+    int last_nb = 0, last_nr = 0, last_ng = 1, last_cluster = 1, last_stride = 1;
 };
 
 static void split_host(float v, uint16_t &hi, uint16_t &lo) {   // fp16 (hi, lo): 22 significant bits of v
@@ -901,12 +906,12 @@ int wn_tc_check_abort(wn_handle *h) {   // after the stream has been synchronise
         if (cudaMemcpy(st.data(), pl->d_stats, st.size() * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess) {
             FILE *f = fopen(getenv("WN_TC_STATS"), "a");
             if (f) {
-                fprintf(f, "# tc stats: L=%d NB=%d NR=%d; cols: cta stage  layer: poll image+arrive->gate gate-epilogue->z z->out out+skip | head: skip-polls 1x1s sampler ; total steps\n",
-                        pl->prm.L, pl->last_nb, pl->last_nr);
+                fprintf(f, "# tc stats: L=%d NB=%d NR=%d cluster=%d; cols: cta stage  layer: poll image+arrive->gate gate-epilogue->z z->out out+skip | head: skip-polls 1x1s sampler ; total steps\n",
+                        pl->prm.L, pl->last_nb, pl->last_nr, pl->last_cluster);
                 for (int i = 0; i < pl->stats_ctas; ++i) {
                     const long long *o = st.data() + (size_t)i * 16;
                     if (o[15] == 0) continue;
-                    fprintf(f, "%d %d", i, i % (pl->prm.L + 1));
+                    fprintf(f, "%d %d", i, i % pl->last_stride);
                     for (int k = 0; k < 5; ++k) fprintf(f, " %.0f", (double)o[k] / (double)o[15]);
                     fprintf(f, " | %.0f %lld\n", (double)o[14] / (double)o[15], o[15]);
                 }
@@ -924,8 +929,8 @@ static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStr
     WnTcPlan *pl = h->tc;
     // How the batch is laid over the chip.  A replica is a chain of L + 1 CTAs; NG utterance groups of NA utterances follow each
     // other through it.  Measured: the step time of a group grows with NA (epilogue work, hand-off bytes:
-    // 23.3 / 28.7 / 33.8 / 37.5 us at 4 / 8 / 12 / 16), every further group in the chain costs ~1 us, more than 5 replicas lose the
-    // clusters of 7 (+1.5 us); idle SMs cost nothing.  The cheapest feasible (NA, NG, NR) wins.
+    // 23.3 / 28.7 / 33.8 / 37.5 us at 4 / 8 / 12 / 16), every further group in the chain costs 0.5 - 0.75 us, more than 5 replicas
+    // lose the clusters of 8 (+0.6 .. 0.8 us); idle SMs cost nothing.  The cheapest feasible (NA, NG, NR) wins.
     int nb = 16, na = 16, ng = 1, nr = 0;
     {
         static const float base[4] = {23.3f, 28.7f, 33.8f, 37.5f};
@@ -934,7 +939,7 @@ static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStr
             for (int g = 1; g <= Geo<16>::NG_MAX; ++g) {
                 const int groups = (nbatch + a - 1) / a, r = (groups + g - 1) / g;
                 if (r > pl->max_replicas) continue;
-                const float cost = base[a / 4 - 1] + 1.0f * (g - 1) + (r > 5 ? 1.5f : 0.0f) + 0.01f * r * g;
+                const float cost = base[a / 4 - 1] + 0.7f * (g - 1) + (r > 5 ? 0.8f : 0.0f) + 0.01f * r * g;
                 if (cost < best) { best = cost; na = a; ng = g; nr = r; }
             }
     }
@@ -975,37 +980,52 @@ static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStr
     }
     p.ring = pl->d_ring;
     WN_CUDA_TRY(h, cudaMemsetAsync(pl->d_mail, 0, words * 8, st));
-    const int grid = nr * (L + 1);
     p.stats = nullptr;
     if (getenv("WN_TC_STATS")) {
         if (!pl->d_stats) cudaMalloc((void **)&pl->d_stats, sizeof(long long) * 16 * 256);
-        if (pl->d_stats) { cudaMemsetAsync(pl->d_stats, 0, sizeof(long long) * 16 * 256, st); p.stats = pl->d_stats; pl->stats_ctas = grid; }
+        if (pl->d_stats) { cudaMemsetAsync(pl->d_stats, 0, sizeof(long long) * 16 * 256, st); p.stats = pl->d_stats; pl->stats_ctas = 256; }
     }
     // all CTAs wait for each other: they must be co-resident -> cooperative launch (one CTA per SM, grid <= SM count)
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(TC_THREADS); cfg.stream = st;
+    cfg.blockDim = dim3(TC_THREADS); cfg.stream = st;
     cfg.dynamicSmemBytes = nb == 16 ? Geo<16>::smem_for(ng) : Geo<32>::smem_for(1);
     const void *kern = tc_kernel(nb, na, p.stats != nullptr);
     cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeCooperative;
     at[0].val.cooperative = 1;
-    // consecutive stages of a replica share a thread-block cluster (a divisor of L + 1, at most 8): inside a cluster x is
-    // handed over through distributed shared memory.  The largest size whose clusters are all co-resident is used.
-    int csize = 1;
-    for (int c = 8; c >= 2; --c) {
-        if ((L + 1) % c) continue;
+    // Consecutive stages of a replica share a thread-block cluster: inside a cluster x is handed over through distributed shared
+    // memory (~0.33 us cheaper per hop than an L2 mailbox).  A replica occupies `stride` consecutive CTAs, L + 1 of them working:
+    // padding the 21 stages of the default stack to 24 lets clusters of 12 (one L2 hop inside a replica; one such cluster fits a
+    // GPC: up to 4 replicas), 8 (two hops, 5 replicas) and 6 (three hops, 6 replicas) divide it; unpadded, the divisors of L + 1
+    // remain (7 replicas: clusters of 3).  The candidate with the fewest L2 hops whose clusters are all co-resident is used.
+    struct Cand { int stride, csize, hops; };
+    std::vector<Cand> cands;
+    const int pad = ((L + 1 + 11) / 12) * 12;
+    for (int c : {12, 8, 6, 4}) cands.push_back({pad, c, (L + c - 1) / c - 1});
+    for (int c = 8; c >= 2; --c)
+        if ((L + 1) % c == 0) cands.push_back({L + 1, c, (L + c - 1) / c - 1});
+    std::stable_sort(cands.begin(), cands.end(), [](const Cand &a, const Cand &b) { return a.hops < b.hops; });
+    int csize = 1, stride = L + 1;
+    const char *ecl = getenv("WN_TC_CLUSTER");
+    const int want = ecl ? atoi(ecl) : 0;
+    for (const Cand &cd : cands) {
+        if (want > 0 && cd.csize != want) continue;
+        if (nr * cd.stride > h->sm_count) continue;
+        if (cd.csize > 8 && cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); continue; }
+        cfg.gridDim = dim3(nr * cd.stride);
         at[1].id = cudaLaunchAttributeClusterDimension;
-        at[1].val.clusterDim.x = c; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+        at[1].val.clusterDim.x = cd.csize; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
         cfg.attrs = at + 1; cfg.numAttrs = 1;
         int ncl = 0;
-        if (cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg) == cudaSuccess && ncl * c >= grid) { csize = c; break; }
+        if (cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg) == cudaSuccess && ncl * cd.csize >= nr * cd.stride) { csize = cd.csize; stride = cd.stride; break; }
         cudaGetLastError();
     }
-    if (const char *e = getenv("WN_TC_CLUSTER")) { const int v = atoi(e); if (v >= 1 && v <= 8 && (L + 1) % v == 0) csize = v; }
+    p.stride = stride;
+    cfg.gridDim = dim3(nr * stride);
     at[1].id = cudaLaunchAttributeClusterDimension;
     at[1].val.clusterDim.x = csize; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = csize > 1 ? 2 : 1;
-    pl->last_cluster = csize;
+    pl->last_cluster = csize; pl->last_stride = stride;
     void *args[] = {&p};
     WN_CUDA_TRY(h, cudaLaunchKernelExC(&cfg, kern, args));
     h->launches++;
