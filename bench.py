@@ -11,7 +11,9 @@ PER GPU (weak scaling: utterances are independent, every rank synthesises its ow
 
 One JSON line on stdout (rank 0).  `value` is device-resident (inputs in HBM before the timed region, CUDA events on
 the launch stream, max over ranks); `e2e` goes through the host-buffer C-ABI call wn_synthesize_host (pinned host
-buffers, H2D + D2H inside the timed region).
+buffers, H2D + D2H inside the timed region).  Secondary objects on the same line, each measured outside the headline's timed
+region: `strong_c3` (configs[2], 256 x 10 s over the ranks, host buffers + gather, at every N), and at N = 1 `step_full`
+(configs[4], WaveNet.step on 8 x 10 s) and `c4_paper` (configs[3], paper_hparams, 16 utterances, 2 s sample).
 """
 import argparse
 import json
@@ -61,6 +63,7 @@ def parse_args():
     ap.add_argument('--no-step-full', action='store_true', help='skip the secondary WaveNet.step (configs[4]) figure')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-c4', action='store_true', help='skip the configs[3] figure (paper_hparams, 16 utterances, 2 s sample)')
     ap.add_argument('--no-strong-c3', action='store_true', help='skip the configs[2] strong-scaling pass (256 x 10 s over the ranks)')
     return ap.parse_args()
 
@@ -254,6 +257,36 @@ def step_full_point(torch, net, hp, peaks):
                          'frac': flops / (best / 1e3) / 1e12 / peak, 'executed_bf16_tflops': tensor_tflops, 'executed_frac': tensor_tflops / peak,
                          'peak_source': 'measured burst (MEASURED_PEAKS.json)' if 'bf16_tflops' in peaks else 'fallback (B200_PROFILING.md)',
                          'note': 'three bf16 passes (hi*hi, hi*lo, lo*hi) per fp32 product; see DESIGN.md 4.5'}}
+
+
+def c4_point(torch):
+    """BASELINE.json configs[3]: paper_hparams (R 256, G 512, S 256, 24 layers, 10 logistics, ConvTranspose2D [5, 5, 11]), 16
+    utterances, on a 2 s sample of its 30 s (the step time does not depend on the length; the full-length pass is
+    profiles/r2_c4_full_run.txt).  Its own model object (AUTO: csrc/wn_loop_tc2.cu), device-resident buffers, one warm-up call,
+    one timed call; loop time from the library's CUDA events.  A secondary figure outside the headline's timed region."""
+    from wavenet_vocoder._native import NativeWaveNet
+    from wavenet_vocoder import weights as W
+    hp = get_hparams('paper')
+    B, frames = 16, 161
+    T = frames * hp.hop_size
+    net = NativeWaveNet(hp, W.init_weights(hp, seed=5339, kind='tf-init'))
+    c_np, noise_np = synth_inputs(hp, list(range(B)), frames)
+    d_c, d_noise = torch.from_numpy(c_np).cuda(), torch.from_numpy(noise_np).cuda()
+    d_audio = torch.empty((B, T), dtype=torch.float32, device='cuda')
+    sp = torch.cuda.current_stream().cuda_stream
+    for _ in range(2):
+        net.synthesize(d_c, B, frames, d_noise, d_audio, stream=sp)
+        torch.cuda.synchronize()
+    info = net.info()
+    assert bool(torch.isfinite(d_audio).all()) and not info['aborted']
+    ms = info['last_loop_ms'] + info['last_upsample_ms']
+    v = B * T / (ms / 1e3)
+    out = {'workload': 'configs[3]: paper_hparams, 16 utterances, 2 s sample of 30 s ({} frames -> {} samples each)'.format(frames, T),
+           'value': v, 'unit': UNIT, 'rtf': v / hp.sample_rate, 'ms': ms, 'us_per_step': 1e3 * info['last_loop_ms'] / T,
+           'engine': info['engine'], 'ctas': info['pipeline_ctas'], 'utterances_per_group': info['pipeline_group_size'],
+           'round1_us_per_step': 329.5}
+    net.close()
+    return out
 
 
 def strong_c3_point(torch, dist, net, hp, world, rank):
@@ -471,6 +504,11 @@ def run_ours(args):
                 line['step_full'] = step_full_point(torch, net, hp, peaks)
             except Exception as e:
                 line['step_full'] = {'error': '{}: {}'.format(type(e).__name__, e)}
+        if world == 1 and not args.no_c4 and args.workload == 'c2' and args.hparams == 'default_22k':
+            try:
+                line['c4_paper'] = c4_point(torch)
+            except Exception as e:
+                line['c4_paper'] = {'error': '{}: {}'.format(type(e).__name__, e)}
         if not args.no_cpu_baseline and world == 1:
             cores = os.cpu_count() or 1
             n, dt = cpu_sample(hp, weights, cores)

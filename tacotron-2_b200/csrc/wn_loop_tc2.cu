@@ -102,6 +102,7 @@ struct Tc2Params {
     int inputs_mode;
     float *audio, *raw;
     int B, T, b0, bend;
+    int test_stall_step;                 // test hook (WN_TC_TEST_STALL): the head stops feeding back after this step
 };
 
 struct Bars2 {
@@ -562,6 +563,7 @@ __device__ void head2_epilogue(const Tc2Params &P, unsigned char *smem, const ui
         if (lane == 0) umma::mbar_arrive(bprm);
         if (mbar_wait_wd(bprm, par, P.abort_flag)) return;
         WN_CK(6);
+        if (t == P.test_stall_step) return;   // test hook: the chain starves and every waiter must time out (WN_ERR_WATCHDOG)
         // sampling + feedback (wavenet.py:850-878)
         if (slane) {
             float nxt = 0.0f;
@@ -922,6 +924,8 @@ int wn_launch_loop_tc2(wn_handle *h, const float *c_up, const float *noise, cons
         memcpy(&pl->h_abort_init[2], &limit, 8);
         WN_CUDA_TRY(h, cudaMemcpyAsync(pl->d_abort, pl->h_abort_init, 4 * sizeof(int), cudaMemcpyHostToDevice, st));
     }
+    p.test_stall_step = -1;
+    if (const char *e = getenv("WN_TC_TEST_STALL")) p.test_stall_step = atoi(e);
     const int cap = NG_MAX * NB;
     const int nchunks = (B + cap - 1) / cap, per = (B + nchunks - 1) / nchunks;
     for (int b0 = 0; b0 < B; b0 += per) {

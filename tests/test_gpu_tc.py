@@ -187,3 +187,22 @@ def test_tc_watchdog_reports_a_starved_chain_and_the_handle_survives():
     a = net.synthesize_host(c, nz)
     assert net.info()['aborted'] == 0
     assert float(np.max(np.abs(a - COracle(hp, w).synthesize(c, noise=nz)[0]))) <= PREFIX_ATOL
+
+
+def test_tc_paper_block_watchdog():
+    """The same starvation test on the four-CTAs-per-layer engine (97 CTAs that all wait for each other)."""
+    hp = common.paper()
+    w = common.weights_for(hp)
+    net = _net(hp, w)
+    B, Tc = 9, 1
+    T = Tc * hp.hop_size
+    c, nz = common.cond_for(hp, B, Tc), common.noise_for(hp, T, B)
+    os.environ['WN_WATCHDOG_MS'], os.environ['WN_TC_TEST_STALL'] = '300', '5'
+    try:
+        with pytest.raises(RuntimeError, match='watchdog'):
+            net.synthesize_host(c, nz)
+        assert net.info()['aborted'] == 1
+    finally:
+        del os.environ['WN_WATCHDOG_MS'], os.environ['WN_TC_TEST_STALL']
+    a = net.synthesize_host(c, nz)
+    assert net.info()['aborted'] == 0 and np.isfinite(a).all()
