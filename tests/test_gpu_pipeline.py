@@ -152,7 +152,9 @@ def test_auto_engine_picks_pipeline_and_falls_back():
     assert NativeWaveNet(hd, common.weights_for(hd), engine='auto').info()['engine'] == 'tc'
     hq = common.small_variants()['mulaw_quantize']
     assert NativeWaveNet(hq, common.weights_for(hq), engine='auto').info()['engine'] == 'generic'
-    hp_paper = common.paper()  # fp32 weights of the paper config do not fit shared memory -> generic
-    assert NativeWaveNet(hp_paper, common.weights_for(hp_paper), engine='auto').info()['engine'] == 'generic'
+    hp_paper = common.paper()  # the 256-channel block: the four-CTAs-per-layer tensor-core engine; with global conditioning (which
+    assert NativeWaveNet(hp_paper, common.weights_for(hp_paper), engine='auto').info()['engine'] == 'tc'   # no fast engine covers) the
+    hg = hp_paper.override(gin_channels=16, n_speakers=4, use_speaker_embedding=True)   # fp32 weights do not fit shared memory either -> generic
+    assert NativeWaveNet(hg, common.weights_for(hg), engine='auto').info()['engine'] == 'generic'
     with pytest.raises(ValueError, match='pipeline engine unavailable'):
         NativeWaveNet(hq, common.weights_for(hq), engine='pipeline')
