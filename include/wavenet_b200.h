@@ -60,8 +60,9 @@ typedef struct wn_config {
     int32_t hop_size;
     int32_t gin_channels;         /* <= 0 disables global conditioning */
     int32_t use_speaker_embedding, n_speakers;
-    int32_t engine;               /* wn_engine; AUTO: the tensor-core loop engine (WN_ENGINE_TC) for the 128-channel block it is built
-                                     for, else the pipelined fp32 engine when the model fits it, else the generic one */
+    int32_t engine;               /* wn_engine; AUTO: the tensor-core loop engine (WN_ENGINE_TC) for the blocks it is built for
+                                     (R = S = G/2 = 128 or 256, kernel_size 3, scalar input, local conditioning only), else the
+                                     pipelined fp32 engine when the model fits it, else the generic one */
     int32_t ksplit;               /* fp32 summation order of the out / skip 1x1s: number of contiguous blocks of the gated
                                      channels summed separately and then added up (DESIGN.md "Arithmetic").  0 = the
                                      pipelined engine's CTAs-per-layer (1 when only the generic engine applies).  Both
