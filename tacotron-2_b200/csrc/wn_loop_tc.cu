@@ -14,7 +14,7 @@
 //       contribution leaves for the head CTA;
 //     * between two steps (the CTA idles ~95 % of a step): the x-independent part of the NEXT step, W[tap0 | tap1 | cin]
 //       * [x_l(t+1-2d) ; x_l(t+1-d) ; c(t+1)], is accumulated straight into the gate accumulator in tensor memory; its
-//       weights (344 KB per layer) are streamed from L2 through two 16 KB shared-memory stages with cp.async.bulk.
+//       weights (344 KB per layer) are streamed from L2 through four 16 KB shared-memory stages with cp.async.bulk.
 //   head CTA  (wavenet.py:828-878): running skip sum in the reference's order, relu, 1x1, relu, 1x1 (both on the tensor
 //     cores), the sampler (gaussian.py:39-52 / mixture.py:76-107) from the caller's noise buffer, audio / raw outputs,
 //     and the sample fed back to layer 0.
@@ -40,11 +40,13 @@ namespace {
 
 constexpr int CH = 128;                  // residual = gate / 2 = skip channels of the block this engine is built for
 constexpr int EPI_THREADS = 256;         // 8 epilogue warps: TMEM lane quarter = warp % 4, utterance half = warp / 4
-constexpr int MMA_WARP = 8, LOAD_WARP = 9;
+constexpr int MMA_WARP = 8;              // warp 9 streams the weights
 constexpr int TC_THREADS = 320;
 constexpr int KB_TOTAL = 11;             // 32-wide k blocks of the streamed weights: tap0 4, tap1 4, cin 3 (80 + 16 zero)
 constexpr int NCHUNK = 2 * KB_TOTAL;     // (k block, gate half), 16 KB each: A image [4][128][8] fp16 hi, then lo
 constexpr int CHUNK_BYTES = 16384;
+constexpr int NSTG = 4;                  // chunks in flight between L2 and the tensor cores: a pass over the stream takes 9.6 k cycles with 2
+                                         // stages, 6.5 k with 4 (the L2 -> SM bandwidth bound is 5.6 k) - the MMA warp is busy that long per group
 constexpr int CI_K = 96;                 // K of the conditioning image (cin <= 96, zero padded)
 
 // layer blob (bytes)
@@ -78,12 +80,14 @@ struct TcParams {
     float *audio, *raw;
     int B, T, NR;
     int stride;                          // CTAs per replica in the grid: L + 1, or padded so that larger clusters divide it (idle CTAs at the end)
-    int NG;                              // utterance groups that travel through a replica's chain one after the other (1 .. 3)
+    int NG;                              // utterance groups that travel through a replica's chain one after the other (1 .. 4)
     int NA;                              // utterances a group really holds (multiple of 4, <= the MMA's N): the epilogues skip the rest
     int bend;                            // one past the last utterance of this launch
     int test_stall_step;                 // development / tests: the head stops feeding samples back at this step (-1: never)
     int b0;                              // first utterance of this launch in the caller's batch of B (batches above the launch limit run in chunks)
 };
+
+constexpr int NG_CAP = 4;                // utterance groups per chain (barrier sets)
 
 template <int NB>
 struct Geo {
@@ -94,13 +98,14 @@ struct Geo {
     static constexpr int IMG = 2 * PLANE;        // hi, lo
     static constexpr int CI_PLANE = (CI_K / 8) * LBO;
     // shared memory of a layer CTA: the weights, the images every utterance group rebuilds inside its own turn (z, taps,
-    // conditioning), then per group what arrives or lives across turns (x image, double buffered, and the fp32 inbox of x)
-    static constexpr int S_WS = 0, S_WST = 65536, S_ZI = S_WST + 2 * CHUNK_BYTES, S_TAP = S_ZI + IMG, S_CI = S_TAP + 2 * IMG,
-                         S_G0 = S_CI + 2 * CI_PLANE, G_XI = 0, G_XF = 2 * IMG, GRP = 2 * IMG + CH * NB * 4;
-    // tensor memory: gate accumulators per group from COL_ACC, the out | skip accumulators (used inside a turn only) at the end
-    static constexpr int COL_OS = 512 - 2 * NB;
-    static constexpr int NG_TMEM = (COL_OS - 384) / (2 * NB), NG_SMEM = (226 * 1024 - S_G0) / GRP;
-    static constexpr int NG_MAX = NG_TMEM < NG_SMEM ? (NG_TMEM < 3 ? NG_TMEM : 3) : (NG_SMEM < 3 ? NG_SMEM : 3);
+    // conditioning), then per group what arrives or lives across turns (x image and the fp32 inbox of x)
+    static constexpr int S_WS = 0, S_WST = 65536, S_ZI = S_WST + NSTG * CHUNK_BYTES, S_TAP = S_ZI + IMG, S_CI = S_TAP + 2 * IMG,
+                         S_G0 = S_CI + 2 * CI_PLANE, G_XI = 0, G_XF = IMG, GRP = IMG + CH * NB * 4;
+    // tensor memory: gate accumulators a | b per group from COL_ACC.  The out | skip accumulators of a group's turn are the SAME columns:
+    // the gate epilogue has read them before the out / skip MMAs are issued (z barrier), and the next x-independent part overwrites
+    // them only after the out / skip epilogues (p barrier)
+    static constexpr int NG_TMEM = (512 - 384) / (2 * NB), NG_SMEM = (226 * 1024 - S_G0) / GRP;
+    static constexpr int NG_MAX = NG_TMEM < NG_SMEM ? (NG_TMEM < NG_CAP ? NG_TMEM : NG_CAP) : (NG_SMEM < NG_CAP ? NG_SMEM : NG_CAP);
     static constexpr int S_END = S_G0 + NG_MAX * GRP;
     // head CTA
     static constexpr int S_HI = 0, S_H2 = IMG, S_PRM = 2 * IMG, S_HEND = S_PRM + NB * CH * 4;
@@ -115,8 +120,8 @@ struct GBars {   // per utterance group: every barrier completes once per step o
     unsigned long long x, z, gate, out, skip, p, xf;
 };
 struct Bars {
-    GBars g[3];
-    unsigned long long wfull[2], wempty[2];
+    GBars g[NG_CAP];
+    unsigned long long wfull[NSTG], wempty[NSTG];
     unsigned long long pdone;   // prologue only: the x-independent part of step 0 of a group has been read from the shared images
 };
 
@@ -155,8 +160,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     unsigned long long *mx_out = nullptr, *ms_out = nullptr;
     float *ring = nullptr, *XF = nullptr;
     unsigned char *XI = nullptr, *ZI = nullptr, *TAP = nullptr, *CI = nullptr;
-    uint32_t bx = 0, bz = 0, bp = 0, bgate = 0, bout = 0, bskip = 0, bxf = 0, r_xf = 0, r_bxf = 0, acc = 0;
-    const uint32_t acc_os = lane_addr + G::COL_OS;   // out | skip accumulators, shared by the groups
+    uint32_t bx = 0, bz = 0, bp = 0, bgate = 0, bout = 0, bskip = 0, bxf = 0, r_xf = 0, r_bxf = 0, acc = 0, acc_os = 0;
     auto setg = [&](int g) {
         rg = r * NG + g;
         mx_in = P.mail_x + (long long)(rg * L + l) * 2 * G::MAILW + unit0;
@@ -173,6 +177,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         r_xf = mapa_u32(umma::smem_addr(XF), out_dsmem ? crank + 1 : crank);
         r_bxf = mapa_u32(bxf, out_dsmem ? crank + 1 : crank);
         acc = lane_addr + COL_ACC + g * 2 * NB;   // gate a | gate b of the group
+        acc_os = acc;                             // ... and, later in the turn, its out | skip accumulators
     };
 
     // operands of the x-independent part of step t: the two older taps from the ring and the conditioning column c(t)
@@ -249,7 +254,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
             if (poll_units<NU>(mx_in + (long long)par * G::MAILW, (long long)CH * 2, tag, xin, nu, P.abort_flag)) return;
         }
         const long long c1 = do_stats ? clock64() : 0;
-        unsigned char *xi = XI + par * G::IMG;
+        unsigned char *xi = XI;
         {
             unsigned char *px = xi + joff;
 #pragma unroll
@@ -337,15 +342,19 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
     const int T = P.T, NG = P.NG;
     const uint32_t s0 = umma::smem_addr(smem);
     const uint64_t ws_hi = umma::smem_desc(s0 + G::S_WS, CH * 16, 128), ws_lo = umma::smem_desc(s0 + G::S_WS + 32768, CH * 16, 128);
-    const uint64_t st_hi[2] = {umma::smem_desc(s0 + G::S_WST, CH * 16, 128), umma::smem_desc(s0 + G::S_WST + CHUNK_BYTES, CH * 16, 128)};
-    const uint64_t st_lo[2] = {umma::smem_desc(s0 + G::S_WST + 8192, CH * 16, 128), umma::smem_desc(s0 + G::S_WST + CHUNK_BYTES + 8192, CH * 16, 128)};
+    const uint64_t st_hi0 = umma::smem_desc(s0 + G::S_WST, CH * 16, 128), st_lo0 = umma::smem_desc(s0 + G::S_WST + 8192, CH * 16, 128);   // stage 0
+    const uint32_t wfull0 = umma::smem_addr(&bars.wfull[0]), wempty0 = umma::smem_addr(&bars.wempty[0]);
     constexpr uint64_t KS_B = (uint64_t)((2 * LBO) >> 4);        // descriptor step per k step (16 k) of an activation image
     constexpr uint64_t KS_A = (uint64_t)((2 * CH * 16) >> 4);    // ... of a 128-row weight image
 
     // the x-independent part of step tp of group g, accumulated from scratch into that group's gate accumulators
+    long long pst[3] = {0, 0, 0};
     auto p_phase = [&](int tp, int g) -> bool {
+        const long long q0 = P.stats ? clock64() : 0;
         if (mbar_wait_wd(umma::smem_addr(&bars.g[g].p), tp & 1, P.abort_flag)) return true;
         umma::fence_after_sync();
+        const long long q1 = P.stats ? clock64() : 0;
+        pst[0] += q1 - q0;
         const uint32_t D_A = tmem + COL_ACC + g * 2 * NB, D_B = D_A + NB;
         const uint64_t tap_hi[3] = {umma::smem_desc(s0 + G::S_TAP, LBO, 128), umma::smem_desc(s0 + G::S_TAP + G::IMG, LBO, 128),
                                     umma::smem_desc(s0 + G::S_CI, LBO, 128)};
@@ -356,25 +365,26 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
         for (int kb = 0; kb < KB_TOTAL; ++kb) {
 #pragma unroll
             for (int half = 0; half < 2; ++half) {
-                const uint32_t use = (uint32_t)KB_TOTAL * pass + kb;
-                if (mbar_wait_wd(umma::smem_addr(&bars.wfull[half]), use & 1, P.abort_flag)) return true;
+                const uint32_t c = (uint32_t)NCHUNK * pass + 2 * kb + half, stage = c % NSTG, use = c / NSTG;   // chunk number -> stage, turn
+                if (mbar_wait_wd(wfull0 + stage * 8, use & 1, P.abort_flag)) return true;
                 umma::fence_after_sync();
                 if (umma::elect_one()) {
                     const int src = kb / 4, kin = (kb % 4) * 2;   // image (tap0, tap1, cin) and first k step inside it
 #pragma unroll
                     for (int kk = 0; kk < 2; ++kk) {
-                        const uint64_t ah = st_hi[half] + kk * KS_A, al = st_lo[half] + kk * KS_A;
+                        const uint64_t ah = st_hi0 + stage * (CHUNK_BYTES >> 4) + kk * KS_A, al = st_lo0 + stage * (CHUNK_BYTES >> 4) + kk * KS_A;
                         const uint64_t bh = tap_hi[src] + (kin + kk) * KS_B, bl = tap_lo[src] + (kin + kk) * KS_B;
                         const uint32_t dd = half ? D_B : D_A;
                         umma::mma_bf16(dd, ah, bh, idesc, (kb | kk) != 0);      // WIDE: plane 0 = hi | lo, plane 1 = hi
                         if (!WIDE) umma::mma_bf16(dd, ah, bl, idesc, 1);
                         umma::mma_bf16(dd, al, WIDE ? bl : bh, idesc, 1);
                     }
-                    umma::mma_commit(umma::smem_addr(&bars.wempty[half]));
+                    umma::mma_commit(wempty0 + stage * 8);
                 }
                 __syncwarp();
             }
         }
+        if (P.stats) { pst[1] += clock64() - q1; pst[2] += 1; }
         return false;
     };
     for (int g = 0; g < NG; ++g) {
@@ -386,10 +396,9 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
       for (int g = 0; g < NG; ++g) {
         const int par = t & 1;
         GBars &gb = bars.g[g];
-        const uint32_t D_A = tmem + COL_ACC + g * 2 * NB, D_B = D_A + NB, D_O = tmem + G::COL_OS, D_S = D_O + NB;
+        const uint32_t D_A = tmem + COL_ACC + g * 2 * NB, D_B = D_A + NB, D_O = D_A, D_S = D_B;   // out | skip reuse the gate columns
         const uint32_t sg = s0 + G::S_G0 + g * G::GRP;
-        const uint64_t xi_hi = umma::smem_desc(sg + G::G_XI + par * G::IMG, LBO, 128),
-                       xi_lo = umma::smem_desc(sg + G::G_XI + par * G::IMG + PLANE, LBO, 128);
+        const uint64_t xi_hi = umma::smem_desc(sg + G::G_XI, LBO, 128), xi_lo = umma::smem_desc(sg + G::G_XI + PLANE, LBO, 128);
         const uint64_t zi_hi = umma::smem_desc(s0 + G::S_ZI, LBO, 128), zi_lo = umma::smem_desc(s0 + G::S_ZI + PLANE, LBO, 128);
         // current tap of the dilated conv (modules.py:294-297) on top of the x-independent part
         if (mbar_wait_wd(umma::smem_addr(&gb.x), par, P.abort_flag)) return;
@@ -437,9 +446,13 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
         if (t + 1 < T && p_phase(t + 1, g)) return;
       }
     }
+    if (P.stats && (threadIdx.x & 31) == 0) {
+        long long *o = P.stats + (long long)blockIdx.x * 16;
+        o[8] = pst[0]; o[9] = pst[1]; o[10] = pst[2];
+    }
 }
 
-// streams the [tap0 | tap1 | cin] weights of the layer, NCHUNK chunks per step and utterance group, through the two stages
+// streams the [tap0 | tap1 | cin] weights of the layer, NCHUNK chunks per step and utterance group, through the NSTG stages
 __device__ void layer_loader(const TcParams &P, const int l, unsigned char *smem, Bars &bars, int wst_off) {
     if ((threadIdx.x & 31) != 0) return;
     const unsigned char *stream = P.layer_blobs + (long long)l * LAYER_BLOB_BYTES + OFF_STREAM;
@@ -448,11 +461,11 @@ __device__ void layer_loader(const TcParams &P, const int l, unsigned char *smem
     for (int pass = 0; pass < passes; ++pass)
         for (int kb = 0; kb < KB_TOTAL; ++kb)
             for (int half = 0; half < 2; ++half) {
-                const uint32_t use = (uint32_t)(KB_TOTAL * pass + kb);
-                if (mbar_wait_wd(umma::smem_addr(&bars.wempty[half]), (use & 1) ^ 1, P.abort_flag)) return;
-                const uint32_t full = umma::smem_addr(&bars.wfull[half]);
+                const uint32_t c = (uint32_t)(NCHUNK * pass + 2 * kb + half), stage = c % NSTG, use = c / NSTG;
+                if (mbar_wait_wd(umma::smem_addr(&bars.wempty[stage]), (use & 1) ^ 1, P.abort_flag)) return;
+                const uint32_t full = umma::smem_addr(&bars.wfull[stage]);
                 umma::mbar_expect_tx(full, CHUNK_BYTES);
-                umma::bulk_g2s(dst0 + half * CHUNK_BYTES, stream + (size_t)(kb * 2 + half) * CHUNK_BYTES, CHUNK_BYTES, full);
+                umma::bulk_g2s(dst0 + stage * CHUNK_BYTES, stream + (size_t)(kb * 2 + half) * CHUNK_BYTES, CHUNK_BYTES, full);
             }
 }
 
@@ -507,14 +520,40 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
             if (P.teacher) tch = P.inputs_mode ? (t + 1 < T ? __ldg(P.teacher + bu * T + t + 1) : 0.0f) : __ldg(P.teacher + bu * T + t);
         }
         // running skip sum in the reference's order (wavenet.py:833-836)
+        // One L2 round trip per layer would make the head the slowest stage for the groups that arrive behind the first one of a
+        // step (their skip outputs are there already; 20 round trips = 14.7 k cycles per group: a chain could not carry more than
+        // three).  Polling many mailboxes at once while the chain is still working, on the other hand, slows the chain (+0.75 us
+        // per step).  So: layer by layer while the words have to be waited for; as soon as a mailbox is complete at the first look
+        // the head is behind, and it looks at LB mailboxes at a time (all loads in flight together) until it has caught up.
+        constexpr int LB = nu <= 1 ? 5 : nu <= 2 ? 4 : 2;
         float S[NH];
-        for (int l = 0; l < L; ++l) {
-            float s[NH];
-            if (poll_units<NU>(ms_in + ((long long)l * 2 + par) * G::MAILW, (long long)CH * 2, tag, s, nu, P.abort_flag)) return;
+        auto add_layer = [&](int l, const float *s) {
 #pragma unroll
             for (int i = 0; i < NH; ++i) {
                 if (l == 0) S[i] = s[i];
                 else S[i] = P.legacy ? __fmul_rn(__fadd_rn(S[i], s[i]), cskip) : __fadd_rn(S[i], s[i]);
+            }
+        };
+        {
+            bool behind = false;
+            int l = 0;
+            while (l < L) {
+                const unsigned long long *box = ms_in + ((long long)l * 2 + par) * G::MAILW;
+                if (!behind || nu > 4) {
+                    float s[NH];
+                    if (poll_units_first<NU>(box, (long long)CH * 2, tag, s, nu, P.abort_flag, behind)) return;
+                    add_layer(l, s);
+                    ++l;
+                } else {
+                    float s[LB][NH];
+                    const int nl = L - l < LB ? L - l : LB;
+                    const int m = look_boxes<NU, LB>(box, 2LL * G::MAILW, (long long)CH * 2, tag, s, nu, nl);
+#pragma unroll
+                    for (int b = 0; b < LB; ++b)
+                        if (b < m) add_layer(l + b, s[b]);
+                    l += m;
+                    behind = m == nl;
+                }
             }
         }
         const long long c1 = do_stats ? clock64() : 0;
@@ -664,7 +703,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
         return;
     }
     if (tid == 0) {
-        for (int g = 0; g < 3; ++g) {
+        for (int g = 0; g < NG_CAP; ++g) {
             GBars &gb = bars.g[g];
             umma::mbar_init(umma::smem_addr(&gb.x), EPI_THREADS / 32);
             umma::mbar_init(umma::smem_addr(&gb.z), EPI_THREADS / 32);
@@ -674,7 +713,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
             umma::mbar_init(umma::smem_addr(&gb.p), EPI_THREADS / 32);
             umma::mbar_init(umma::smem_addr(&gb.xf), 1);
         }
-        for (int i = 0; i < 2; ++i) { umma::mbar_init(umma::smem_addr(&bars.wfull[i]), 1); umma::mbar_init(umma::smem_addr(&bars.wempty[i]), 1); }
+        for (int i = 0; i < NSTG; ++i) { umma::mbar_init(umma::smem_addr(&bars.wfull[i]), 1); umma::mbar_init(umma::smem_addr(&bars.wempty[i]), 1); }
         umma::mbar_init(umma::smem_addr(&bars.pdone), 1);
         umma::mbar_fence_init();
     }
@@ -913,6 +952,7 @@ int wn_tc_check_abort(wn_handle *h) {   // after the stream has been synchronise
                     if (o[15] == 0) continue;
                     fprintf(f, "%d %d", i, i % pl->last_stride);
                     for (int k = 0; k < 5; ++k) fprintf(f, " %.0f", (double)o[k] / (double)o[15]);
+                    if (o[10]) fprintf(f, " [x-independent part: wait for operands %.0f, stream + MMAs %.0f]", (double)o[8] / (double)o[10], (double)o[9] / (double)o[10]);
                     fprintf(f, " | %.0f %lld\n", (double)o[14] / (double)o[15], o[15]);
                 }
                 fclose(f);
@@ -929,8 +969,9 @@ static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStr
     WnTcPlan *pl = h->tc;
     // How the batch is laid over the chip.  A replica is a chain of L + 1 CTAs; NG utterance groups of NA utterances follow each
     // other through it.  Measured: the step time of a group grows with NA (epilogue work, hand-off bytes:
-    // 23.3 / 28.7 / 33.8 / 37.5 us at 4 / 8 / 12 / 16), every further group in the chain costs 0.5 - 0.75 us, more than 5 replicas
-    // lose the clusters of 8 (+0.6 .. 0.8 us); idle SMs cost nothing.  The cheapest feasible (NA, NG, NR) wins.
+    // 23.3 / 28.7 / 33.8 / 37.5 us at 4 / 8 / 12 / 16), every further group in the chain costs 0.2 - 0.7 us, more than 5 replicas
+    // lose the clusters of 8 (6 replicas: +1.9 us, 7: +4.3 us at one group of 4); idle SMs cost nothing.  The cheapest feasible
+    // (NA, NG, NR) wins.
     int nb = 16, na = 16, ng = 1, nr = 0;
     {
         static const float base[4] = {23.3f, 28.7f, 33.8f, 37.5f};
@@ -939,7 +980,7 @@ static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStr
             for (int g = 1; g <= Geo<16>::NG_MAX; ++g) {
                 const int groups = (nbatch + a - 1) / a, r = (groups + g - 1) / g;
                 if (r > pl->max_replicas) continue;
-                const float cost = base[a / 4 - 1] + 0.7f * (g - 1) + (r > 5 ? 0.8f : 0.0f) + 0.01f * r * g;
+                const float cost = base[a / 4 - 1] + 0.4f * (g - 1) + (r > 6 ? 4.3f : r > 5 ? 1.9f : 0.0f) + 0.01f * r * g;
                 if (cost < best) { best = cost; na = a; ng = g; nr = r; }
             }
     }

@@ -65,6 +65,61 @@ __device__ __forceinline__ bool poll_units(const unsigned long long *p, long lon
         if (wd.expired()) return true;
     }
 }
+// poll_units that also says whether the words were there at the first look (the reader is behind the writer)
+template <int NU>
+__device__ __forceinline__ bool poll_units_first(const unsigned long long *p, long long stride, unsigned tag, float *v, int nu, int *abort_flag, bool &first) {
+    Watch wd{abort_flag};
+    first = true;
+    for (;;) {
+        unsigned long long w[2 * NU];
+#pragma unroll
+        for (int u = 0; u < NU; ++u)
+            if (u < nu) ld_ll2(p + u * stride, w[2 * u], w[2 * u + 1]);
+        bool ok = true;
+#pragma unroll
+        for (int u = 0; u < NU; ++u)
+            if (u < nu) ok = ok && ((unsigned)(w[2 * u] >> 32) == tag) && ((unsigned)(w[2 * u + 1] >> 32) == tag);
+        if (ok) {
+#pragma unroll
+            for (int u = 0; u < NU; ++u) {
+                v[2 * u] = u < nu ? __uint_as_float((unsigned)(w[2 * u] & 0xffffffffu)) : 0.0f;
+                v[2 * u + 1] = u < nu ? __uint_as_float((unsigned)(w[2 * u + 1] & 0xffffffffu)) : 0.0f;
+            }
+            return false;
+        }
+        first = false;
+        if (wd.expired()) return true;
+    }
+}
+// ONE look at LB mailboxes `box_stride` words apart (the first `nl` of them), all loads in flight together: returns how many
+// leading mailboxes were complete (their values in v).  A reader that is behind pays one L2 round trip per LB layers this way.
+template <int NU, int LB>
+__device__ __forceinline__ int look_boxes(const unsigned long long *p, long long box_stride, long long stride, unsigned tag, float (&v)[LB][2 * NU],
+                                          int nu, int nl) {
+    unsigned long long w[LB][2 * NU];
+#pragma unroll
+    for (int b = 0; b < LB; ++b)
+#pragma unroll
+        for (int u = 0; u < NU; ++u)
+            if (b < nl && u < nu) ld_ll2(p + b * box_stride + u * stride, w[b][2 * u], w[b][2 * u + 1]);
+    int m = 0;
+    bool run = true;
+#pragma unroll
+    for (int b = 0; b < LB; ++b) {
+        bool ok = b < nl;
+#pragma unroll
+        for (int u = 0; u < NU; ++u)
+            if (b < nl && u < nu) ok = ok && ((unsigned)(w[b][2 * u] >> 32) == tag) && ((unsigned)(w[b][2 * u + 1] >> 32) == tag);
+        run = run && ok;
+        m += run ? 1 : 0;
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+            v[b][2 * u] = (b < nl && u < nu) ? __uint_as_float((unsigned)(w[b][2 * u] & 0xffffffffu)) : 0.0f;
+            v[b][2 * u + 1] = (b < nl && u < nu) ? __uint_as_float((unsigned)(w[b][2 * u + 1] & 0xffffffffu)) : 0.0f;
+        }
+    }
+    return m;
+}
 __device__ __forceinline__ bool mbar_wait_wd(uint32_t bar, uint32_t parity, int *abort_flag) {
     Watch wd{abort_flag};
     while (!umma::mbar_try(bar, parity))

@@ -83,11 +83,11 @@ def test_tc_default_block_small_batch_vs_both_oracles():
     assert np.all(common.rel_close(raw_t[0], raw_np[0].T))
 
 
-@pytest.mark.parametrize('B,Tc,group,replicas', [(20, 2, 4, 5), (64, 1, 4, 6), (33, 1, 4, 5), (112, 1, 8, 5), (224, 1, 12, 7), (336, 1, 16, 7)])
+@pytest.mark.parametrize('B,Tc,group,replicas', [(20, 2, 4, 5), (64, 1, 4, 4), (33, 1, 4, 5), (112, 1, 4, 7), (224, 1, 8, 7), (336, 1, 12, 7), (448, 1, 16, 7)])
 def test_tc_replicas_and_groups(B, Tc, group, replicas):
     """The batch is cut into groups of `group` utterances (a multiple of 4; the last one partly filled); up to 7 replicas of
-    the layer chain run side by side and up to three groups follow each other through one chain: 64 utterances = configs[1]
-    (6 chains x 3 groups x 4), 33 ~ the per-GPU share of configs[2] on 8 GPUs, 336 = the most one launch takes."""
+    the layer chain run side by side and up to four groups follow each other through one chain: 64 utterances = configs[1]
+    (4 chains x 4 groups x 4), 33 ~ the per-GPU share of configs[2] on 8 GPUs, 448 = the most one launch takes."""
     hp = common.default_22k()
     w = common.weights_for(hp)
     net = _net(hp, w)
@@ -100,7 +100,7 @@ def test_tc_replicas_and_groups(B, Tc, group, replicas):
 def test_tc_batch_above_one_launch_runs_in_chunks():
     hp = common.default_22k()
     w = common.weights_for(hp)
-    _check(_net(hp, w), hp, w, 340, 1, free=False)
+    _check(_net(hp, w), hp, w, 452, 1, free=False)
 
 
 def test_tc_groups_of_32_and_cluster_sizes():
@@ -115,6 +115,7 @@ def test_tc_groups_of_32_and_cluster_sizes():
     _check(net, hp, w, 9, 1, free=False, WN_TC_NA=16, WN_TC_NG=1)   # one full-width replica
     _check(net, hp, w, 20, 1, free=False, WN_TC_NA=12, WN_TC_NG=2)  # two groups in one chain, the second partly filled
     _check(net, hp, w, 40, 1, free=False, WN_TC_NA=16, WN_TC_NG=3)  # three groups of 16 in one chain
+    _check(net, hp, w, 13, 1, free=False, WN_TC_NA=4, WN_TC_NG=4)   # four groups of 4 in one chain, the last one with a single utterance
     for cs in (1, 3, 7):
         _check(net, hp, w, 7, 1, free=False, WN_TC_CLUSTER=cs)
 
