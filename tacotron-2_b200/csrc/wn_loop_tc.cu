@@ -541,9 +541,11 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
                 const unsigned long long *box = ms_in + ((long long)l * 2 + par) * G::MAILW;
                 if (!behind || nu > 4) {
                     float s[NH];
-                    if (poll_units_first<NU>(box, (long long)CH * 2, tag, s, nu, P.abort_flag, behind)) return;
+                    bool first;
+                    if (poll_units_first<NU>(box, (long long)CH * 2, tag, s, nu, P.abort_flag, first)) return;
                     add_layer(l, s);
                     ++l;
+                    behind = first && NG >= 3;   // one or two groups: the head keeps up anyway (and 0.2 us per step is lost otherwise)
                 } else {
                     float s[LB][NH];
                     const int nl = L - l < LB ? L - l : LB;
