@@ -49,7 +49,8 @@ constexpr int OFF_TMEM = 0;                          // 3 x [128 rows][128 words
 constexpr int OFF_OSLO = 3 * 65536;                  // out/skip lo: A image [32][128][8]
 constexpr int OFF_STREAM = OFF_OSLO + 65536;         // KB_TOTAL chunks
 constexpr int OFF_BIAS = OFF_STREAM + KB_TOTAL * CHUNK_BYTES;   // gate rows [128], out/skip rows [128]
-constexpr int QUARTER_BLOB_BYTES = OFF_BIAS + 2 * 128 * 4;
+constexpr int OFF_OSLO_T = OFF_BIAS + 2 * 128 * 4;              // out/skip lo, k < 128, as tensor-memory rows [128][64 words] (two-pass kernels)
+constexpr int QUARTER_BLOB_BYTES = OFF_OSLO_T + 32768;
 // head blob: W1 hi 2 x [128][128 words] | W1 lo 2 x A image [32][128][8] | W2 fp32 [32][256] | b1 [256] | b2 [32] | first conv w [256], b [256]
 constexpr int HOFF_W1HI = 0, HOFF_W1LO = 2 * 65536, HOFF_W2 = 4 * 65536, HOFF_B1 = HOFF_W2 + 32 * C2 * 4, HOFF_B2 = HOFF_B1 + C2 * 4,
               HOFF_FIRST = HOFF_B2 + 32 * 4, HEAD_BLOB_BYTES = HOFF_FIRST + 2 * C2 * 4;
@@ -62,6 +63,9 @@ constexpr int ACCW = 2 * NB;
 constexpr int COL_WG = 0, COL_WOS = 256, COL_AG = 384, COL_AOS = COL_AG + NG_MAX * ACCW;   // layer quarter: gate accumulators per group
 constexpr int COL_W1 = 0, COL_H0 = 384, COL_H1 = COL_H0 + ACCW;              // head
 static_assert(COL_AOS + ACCW <= 512, "tensor memory");
+// two-pass kernels (groups of <= 8) use only the first NB columns of every accumulator: the other halves hold the out/skip lo weights of
+// k < 128 (two k steps per 16-column piece), so that only 8 of the 16 lo * hi MMAs of the second GEMM read A from shared memory
+__host__ __device__ constexpr int col_oslo(int ks) { return COL_AG + (ks / 2) * ACCW + NB + (ks % 2) * 8; }
 
 // NH = 8 accumulator columns of this thread's lane: main + cross terms (WIDE: both inside the first NB columns, see img_put2)
 template <bool WIDE>
@@ -399,7 +403,8 @@ __device__ void quarter_mma(const Tc2Params &P, unsigned char *smem, const uint3
             for (int ks = 0; ks < 16; ++ks) {
                 umma::mma_bf16_ts(D_OS, tmem + COL_WOS + ks * 8, zi_hi + ks * KS_B, idesc, ks != 0);
                 if (!WIDE) umma::mma_bf16_ts(D_OS + NB, tmem + COL_WOS + ks * 8, zi_lo + ks * KS_B, idesc, ks != 0);
-                umma::mma_bf16(WIDE ? D_OS : D_OS + NB, oslo + ks * KS_A, (WIDE ? zi_lo : zi_hi) + ks * KS_B, idesc, 1);
+                if (WIDE && ks < 8) umma::mma_bf16_ts(D_OS, tmem + col_oslo(ks), zi_lo + ks * KS_B, idesc, 1);
+                else umma::mma_bf16(WIDE ? D_OS : D_OS + NB, oslo + ks * KS_A, (WIDE ? zi_lo : zi_hi) + ks * KS_B, idesc, 1);
             }
             umma::mma_commit(umma::smem_addr(&bars.os));
         }
@@ -696,6 +701,20 @@ __global__ void __launch_bounds__(T2_THREADS, 1) wn_loop_tc2_kernel(const Tc2Par
     } else {
         const unsigned char *blob = P.blobs + (long long)blockIdx.x * QUARTER_BLOB_BYTES;
         load_tmem_weights2(blob + OFF_TMEM, 3, tmem, COL_WG);
+        if (NA <= 8 && tid < 128) {   // out/skip lo, k < 128, into the unused accumulator halves
+            const uint32_t lane_addr = tmem + ((uint32_t)(tid & ~31) << 16);
+            const uint4 *row = reinterpret_cast<const uint4 *>(blob + OFF_OSLO_T + (size_t)tid * 256);
+            for (int pc = 0; pc < 4; ++pc) {
+                uint32_t r[16];
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    const uint4 x = __ldg(row + pc * 4 + v);
+                    r[4 * v] = x.x; r[4 * v + 1] = x.y; r[4 * v + 2] = x.z; r[4 * v + 3] = x.w;
+                }
+                umma::tmem_st16(lane_addr + col_oslo(2 * pc), r);
+            }
+            umma::tmem_st_wait();
+        }
         const uint4 *src = reinterpret_cast<const uint4 *>(blob + OFF_OSLO);
         for (int i = tid; i < 65536 / 16; i += T2_THREADS) reinterpret_cast<uint4 *>(tc_smem + S_OSLO)[i] = __ldg(src + i);
         for (int i = tid; i < (S_G0 + P.NG * GRP - S_ZI) / 16; i += T2_THREADS) reinterpret_cast<uint4 *>(tc_smem + S_ZI)[i] = make_uint4(0, 0, 0, 0);
@@ -814,6 +833,11 @@ int wn_tc2_plan(wn_handle *h) {
                     const float osv = row < 64 ? ow[(size_t)k * C2 + j] : sw[(size_t)k * C2 + j];
                     put_tmem(b + OFF_TMEM + 2 * 65536, nullptr, row, k, osv);
                     put_img(nullptr, b + OFF_OSLO, row, k, osv);
+                    if (k < 128) {   // the same lo halves as tensor-memory rows [128][64 words]
+                        uint16_t hi16, lo16;
+                        split_host2(osv, hi16, lo16);
+                        reinterpret_cast<uint16_t *>(b + OFF_OSLO_T)[(size_t)row * 128 + k] = lo16;
+                    }
                 }
                 for (int k = 0; k < KB_TOTAL * 32; ++k) {
                     float v = 0.0f;
