@@ -1070,12 +1070,21 @@ static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStr
     cfg.attrs = at; cfg.numAttrs = csize > 1 ? 2 : 1;
     pl->last_cluster = csize; pl->last_stride = stride;
     void *args[] = {&p};
-    WN_CUDA_TRY(h, cudaLaunchKernelExC(&cfg, kern, args));
+    cudaError_t le = cudaLaunchKernelExC(&cfg, kern, args);
+    if (le != cudaSuccess && csize > 1) {   // the occupancy query was optimistic (another context on the GPU, ...): every hand-off through L2
+        cudaGetLastError();
+        p.stride = L + 1;
+        cfg.gridDim = dim3(nr * (L + 1));
+        cfg.numAttrs = 1;
+        pl->last_cluster = 1; pl->last_stride = L + 1;
+        le = cudaLaunchKernelExC(&cfg, kern, args);
+    }
+    WN_CUDA_TRY(h, le);
     h->launches++;
     return WN_OK;
 }
 
-// Batches above the launch limit (7 replicas of 32 utterances on 148 SMs) run as consecutive launches over equal chunks.
+// Batches above the launch limit (7 replicas x 4 groups x 16 utterances on 148 SMs) run as consecutive launches over equal chunks.
 int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const float *teacher, int inputs_mode, int B, int T,
                       float *audio, float *raw, cudaStream_t st) {
     if (h->tc2) return wn_launch_loop_tc2(h, c_up, noise, teacher, inputs_mode, B, T, audio, raw, st);

@@ -49,8 +49,8 @@ constexpr int OFF_TMEM = 0;                          // 3 x [128 rows][128 words
 constexpr int OFF_OSLO = 3 * 65536;                  // out/skip lo: A image [32][128][8]
 constexpr int OFF_STREAM = OFF_OSLO + 65536;         // KB_TOTAL chunks
 constexpr int OFF_BIAS = OFF_STREAM + KB_TOTAL * CHUNK_BYTES;   // gate rows [128], out/skip rows [128]
-constexpr int OFF_OSLO_T = OFF_BIAS + 2 * 128 * 4;              // out/skip lo, k < 128, as tensor-memory rows [128][64 words] (two-pass kernels)
-constexpr int QUARTER_BLOB_BYTES = OFF_OSLO_T + 32768;
+constexpr int OFF_OSLO_T = OFF_BIAS + 2 * 128 * 4;              // out/skip lo once more, as tensor-memory rows [128][128 words]
+constexpr int QUARTER_BLOB_BYTES = OFF_OSLO_T + 65536;
 // head blob: W1 hi 2 x [128][128 words] | W1 lo 2 x A image [32][128][8] | W2 fp32 [32][256] | b1 [256] | b2 [32] | first conv w [256], b [256]
 constexpr int HOFF_W1HI = 0, HOFF_W1LO = 2 * 65536, HOFF_W2 = 4 * 65536, HOFF_B1 = HOFF_W2 + 32 * C2 * 4, HOFF_B2 = HOFF_B1 + C2 * 4,
               HOFF_FIRST = HOFF_B2 + 32 * 4, HEAD_BLOB_BYTES = HOFF_FIRST + 2 * C2 * 4;
@@ -60,12 +60,17 @@ constexpr int NG_MAX = 3;                                                    // 
 // every accumulator is 2 NB columns: the main terms (hi * hi) | the cross terms (hi * lo + lo * hi), added in the epilogue - the
 // tensor core truncates an addend when it aligns it to the accumulator, so the small cross terms accumulate among themselves
 constexpr int ACCW = 2 * NB;
-constexpr int COL_WG = 0, COL_WOS = 256, COL_AG = 384, COL_AOS = COL_AG + NG_MAX * ACCW;   // layer quarter: gate accumulators per group
+constexpr int COL_WG = 0, COL_WOS = 256, COL_AG = 384;                       // layer quarter: weights, then the accumulators of the groups
 constexpr int COL_W1 = 0, COL_H0 = 384, COL_H1 = COL_H0 + ACCW;              // head
-static_assert(COL_AOS + ACCW <= 512, "tensor memory");
-// two-pass kernels (groups of <= 8) use only the first NB columns of every accumulator: the other halves hold the out/skip lo weights of
-// k < 128 (two k steps per 16-column piece), so that only 8 of the 16 lo * hi MMAs of the second GEMM read A from shared memory
-__host__ __device__ constexpr int col_oslo(int ks) { return COL_AG + (ks / 2) * ACCW + NB + (ks % 2) * 8; }
+// Layer quarter, columns from COL_AG on, for a kernel built for NGT groups: one accumulator per group - two-pass kernels (groups of
+// <= 8: main | cross inside NB columns) NB columns, three-pass kernels 2 NB - which holds the gate pre-activations and, later in the
+// group's turn, the out | skip rows (the gate epilogue has read it before the z barrier; the next x-independent part overwrites it
+// only after the p barrier).  Everything behind the last accumulator holds out/skip LO weights, 8 columns per k step: those k
+// steps of the lo * hi pass read A from tensor memory (~10 cycles per MMA), the rest from shared memory (~60).
+__host__ __device__ constexpr int acc_w(bool wide) { return wide ? NB : 2 * NB; }
+__host__ __device__ constexpr int col_acc(bool wide, int g) { return COL_AG + g * acc_w(wide); }
+__host__ __device__ constexpr int nks_tmem(bool wide, int ngt) { return (512 - col_acc(wide, ngt)) / 8 < 16 ? (512 - col_acc(wide, ngt)) / 8 : 16; }
+__host__ __device__ constexpr int col_oslo(bool wide, int ngt, int ks) { return col_acc(wide, ngt) + 8 * ks; }
 
 // NH = 8 accumulator columns of this thread's lane: main + cross terms (WIDE: both inside the first NB columns, see img_put2)
 template <bool WIDE>
@@ -122,7 +127,7 @@ __device__ __forceinline__ bool poll_channel(const unsigned long long *p, unsign
 // ---------------------------------------------------------------------------------------------------------------------
 // layer quarter
 // ---------------------------------------------------------------------------------------------------------------------
-template <int NA, bool STATS>
+template <int NA, int NGT, bool STATS>
 __device__ void quarter_epilogue(const Tc2Params &P, const int l, const int q, unsigned char *smem, const uint32_t tmem, Bars2 &bars) {
     constexpr bool WIDE = NA <= 8;
     constexpr int nah = NA / 2, NH = 8;
@@ -247,7 +252,7 @@ __device__ void quarter_epilogue(const Tc2Params &P, const int l, const int q, u
         WN_CK(3);
         {
             float a[NH];
-            acc_load2<WIDE>(lane_addr + COL_AG + g * ACCW + n0, a);
+            acc_load2<WIDE>(lane_addr + col_acc(WIDE, g) + n0, a);
             umma::fence_before_sync();
             if (q4 >= 2) {   // sigmoid rows: hand the pre-activations to the warps that hold the tanh rows
 #pragma unroll
@@ -285,7 +290,7 @@ __device__ void quarter_epilogue(const Tc2Params &P, const int l, const int q, u
         WN_CK(7);
         {
             float o[NH];
-            acc_load2<WIDE>(lane_addr + COL_AOS + n0, o);
+            acc_load2<WIDE>(lane_addr + col_acc(WIDE, g) + n0, o);
             umma::fence_before_sync();
             if (q4 < 2) {
                 if (l + 1 < L) {
@@ -325,7 +330,7 @@ __device__ void quarter_epilogue(const Tc2Params &P, const int l, const int q, u
     }
 }
 
-template <bool WIDE>
+template <bool WIDE, int NGT>
 __device__ void quarter_mma(const Tc2Params &P, unsigned char *smem, const uint32_t tmem, Bars2 &bars) {
     constexpr uint32_t idesc = umma::idesc_f16(128, NB);
     const int T = P.T, NG = P.NG;
@@ -335,7 +340,7 @@ __device__ void quarter_mma(const Tc2Params &P, unsigned char *smem, const uint3
     const uint64_t st_lo0 = umma::smem_desc(s0 + S_WST + 8192, 128 * 16, 128), st_lo1 = umma::smem_desc(s0 + S_WST + CHUNK_BYTES + 8192, 128 * 16, 128);
     constexpr uint64_t KS_B = (uint64_t)((2 * LBO) >> 4);        // descriptor step per k step (16 k) of an activation image
     constexpr uint64_t KS_A = (uint64_t)((2 * 128 * 16) >> 4);   // ... of a 128-row weight image
-    const uint32_t D_OS = tmem + COL_AOS;
+    constexpr int NKS_T = nks_tmem(WIDE, NGT);   // k steps of the out/skip lo weights that are resident in tensor memory
     const uint64_t tap_hi[3] = {umma::smem_desc(s0 + S_TAP, LBO, 128), umma::smem_desc(s0 + S_TAP + IMG, LBO, 128), umma::smem_desc(s0 + S_CI, LBO, 128)};
     const uint64_t tap_lo[3] = {umma::smem_desc(s0 + S_TAP + PLANE, LBO, 128), umma::smem_desc(s0 + S_TAP + IMG + PLANE, LBO, 128),
                                 umma::smem_desc(s0 + S_CI + CI_PLANE, LBO, 128)};
@@ -345,7 +350,7 @@ __device__ void quarter_mma(const Tc2Params &P, unsigned char *smem, const uint3
     // group's gate accumulator
     auto p_phase = [&](int tp, int g) -> bool {
         const uint32_t m = (uint32_t)(tp * NG + g);
-        const uint32_t D_G = tmem + COL_AG + g * ACCW;
+        const uint32_t D_G = tmem + col_acc(WIDE, g);
         if (mbar_wait_wd(umma::smem_addr(&bars.p), m & 1u, P.abort_flag)) return true;
         umma::fence_after_sync();
 #pragma unroll
@@ -378,7 +383,7 @@ __device__ void quarter_mma(const Tc2Params &P, unsigned char *smem, const uint3
     for (int t = 0; t < T; ++t) {
       for (int g = 0; g < NG; ++g) {
         const int par = (t * NG + g) & 1;
-        const uint32_t D_G = tmem + COL_AG + g * ACCW;
+        const uint32_t D_G = tmem + col_acc(WIDE, g), D_OS = D_G;   // the out | skip accumulator of the turn = the group's gate columns
         const uint32_t xi = s0 + S_G0 + g * GRP + G_XI;
         const uint64_t xi_hi = umma::smem_desc(xi, LBO, 128), xi_lo = umma::smem_desc(xi + PLANE, LBO, 128);
         // current tap of the dilated conv (modules.py:294-297) on top of the x-independent part
@@ -403,7 +408,7 @@ __device__ void quarter_mma(const Tc2Params &P, unsigned char *smem, const uint3
             for (int ks = 0; ks < 16; ++ks) {
                 umma::mma_bf16_ts(D_OS, tmem + COL_WOS + ks * 8, zi_hi + ks * KS_B, idesc, ks != 0);
                 if (!WIDE) umma::mma_bf16_ts(D_OS + NB, tmem + COL_WOS + ks * 8, zi_lo + ks * KS_B, idesc, ks != 0);
-                if (WIDE && ks < 8) umma::mma_bf16_ts(D_OS, tmem + col_oslo(ks), zi_lo + ks * KS_B, idesc, 1);
+                if (ks < NKS_T) umma::mma_bf16_ts(WIDE ? D_OS : D_OS + NB, tmem + col_oslo(WIDE, NGT, ks), (WIDE ? zi_lo : zi_hi) + ks * KS_B, idesc, 1);
                 else umma::mma_bf16(WIDE ? D_OS : D_OS + NB, oslo + ks * KS_A, (WIDE ? zi_lo : zi_hi) + ks * KS_B, idesc, 1);
             }
             umma::mma_commit(umma::smem_addr(&bars.os));
@@ -665,7 +670,7 @@ __device__ void load_tmem_weights2(const unsigned char *src, int nmat, uint32_t 
     umma::tmem_st_wait();
 }
 
-template <int NA, bool STATS>
+template <int NA, int NGT, bool STATS>
 __global__ void __launch_bounds__(T2_THREADS, 1) wn_loop_tc2_kernel(const Tc2Params P) {
     extern __shared__ __align__(128) unsigned char tc_smem[];
     __shared__ Bars2 bars;
@@ -701,17 +706,19 @@ __global__ void __launch_bounds__(T2_THREADS, 1) wn_loop_tc2_kernel(const Tc2Par
     } else {
         const unsigned char *blob = P.blobs + (long long)blockIdx.x * QUARTER_BLOB_BYTES;
         load_tmem_weights2(blob + OFF_TMEM, 3, tmem, COL_WG);
-        if (NA <= 8 && tid < 128) {   // out/skip lo, k < 128, into the unused accumulator halves
+        if (tid < 128) {   // the leading k steps of the out/skip lo weights behind the accumulators
+            constexpr bool WIDE = NA <= 8;
+            constexpr int NKS_T = nks_tmem(WIDE, NGT);
             const uint32_t lane_addr = tmem + ((uint32_t)(tid & ~31) << 16);
-            const uint4 *row = reinterpret_cast<const uint4 *>(blob + OFF_OSLO_T + (size_t)tid * 256);
-            for (int pc = 0; pc < 4; ++pc) {
+            const uint4 *row = reinterpret_cast<const uint4 *>(blob + OFF_OSLO_T + (size_t)tid * 512);
+            for (int pc = 0; pc < NKS_T / 2; ++pc) {   // 16 columns = two k steps at a time
                 uint32_t r[16];
 #pragma unroll
                 for (int v = 0; v < 4; ++v) {
                     const uint4 x = __ldg(row + pc * 4 + v);
                     r[4 * v] = x.x; r[4 * v + 1] = x.y; r[4 * v + 2] = x.z; r[4 * v + 3] = x.w;
                 }
-                umma::tmem_st16(lane_addr + col_oslo(2 * pc), r);
+                umma::tmem_st16(lane_addr + col_oslo(WIDE, NGT, 2 * pc), r);
             }
             umma::tmem_st_wait();
         }
@@ -727,8 +734,8 @@ __global__ void __launch_bounds__(T2_THREADS, 1) wn_loop_tc2_kernel(const Tc2Par
         if (warp < 8) head2_epilogue<NA, STATS>(P, tc_smem, tmem, bars);
         else if (warp == MMA_WARP) head2_mma<(NA <= 8)>(P, tc_smem, tmem, bars);
     } else {
-        if (warp < 8) quarter_epilogue<NA, STATS>(P, l, q, tc_smem, tmem, bars);
-        else if (warp == MMA_WARP) quarter_mma<(NA <= 8)>(P, tc_smem, tmem, bars);
+        if (warp < 8) quarter_epilogue<NA, NGT, STATS>(P, l, q, tc_smem, tmem, bars);
+        else if (warp == MMA_WARP) quarter_mma<(NA <= 8), NGT>(P, tc_smem, tmem, bars);
         else quarter_loader(P, l, q, tc_smem, bars);
     }
     // every role returns when the sequence is done (or the watchdog fired): release tensor memory
@@ -784,9 +791,12 @@ void wn_tc2_free(wn_handle *h) {
     h->tc2 = nullptr;
 }
 
-static const void *tc2_kernel(int na, bool stats) {
-    if (stats) return na <= 8 ? (const void *)wn_loop_tc2_kernel<8, true> : (const void *)wn_loop_tc2_kernel<16, true>;
-    return na <= 8 ? (const void *)wn_loop_tc2_kernel<8, false> : (const void *)wn_loop_tc2_kernel<16, false>;
+// kernel for groups of na (8: two-pass images, 16) utterances and ng groups per chain (the tensor-memory layout depends on both)
+static const void *tc2_kernel(int na, int ng, bool stats) {
+#define WN_TC2_K(NA_, NG_) (stats ? (const void *)wn_loop_tc2_kernel<NA_, NG_, true> : (const void *)wn_loop_tc2_kernel<NA_, NG_, false>)
+    if (na <= 8) return ng <= 1 ? WN_TC2_K(8, 1) : ng == 2 ? WN_TC2_K(8, 2) : WN_TC2_K(8, 3);
+    return ng <= 1 ? WN_TC2_K(16, 1) : ng == 2 ? WN_TC2_K(16, 2) : WN_TC2_K(16, 3);
+#undef WN_TC2_K
 }
 
 // Packs the weights (TF layouts) into the per-CTA blobs described at the top of this file.
@@ -833,10 +843,10 @@ int wn_tc2_plan(wn_handle *h) {
                     const float osv = row < 64 ? ow[(size_t)k * C2 + j] : sw[(size_t)k * C2 + j];
                     put_tmem(b + OFF_TMEM + 2 * 65536, nullptr, row, k, osv);
                     put_img(nullptr, b + OFF_OSLO, row, k, osv);
-                    if (k < 128) {   // the same lo halves as tensor-memory rows [128][64 words]
+                    {   // the same lo halves as tensor-memory rows [128][128 words]
                         uint16_t hi16, lo16;
                         split_host2(osv, hi16, lo16);
-                        reinterpret_cast<uint16_t *>(b + OFF_OSLO_T)[(size_t)row * 128 + k] = lo16;
+                        reinterpret_cast<uint16_t *>(b + OFF_OSLO_T)[(size_t)row * 256 + k] = lo16;
                     }
                 }
                 for (int k = 0; k < KB_TOTAL * 32; ++k) {
@@ -893,9 +903,10 @@ int wn_tc2_plan(wn_handle *h) {
     cudaMemcpy(pl->d_head_blob, hb.data(), hb.size(), cudaMemcpyHostToDevice);
     p.blobs = pl->d_blobs; p.head_blob = pl->d_head_blob; p.abort_flag = pl->d_abort;
     for (int na : {8, 16})
-        for (int st = 0; st < 2; ++st)
-            if (cudaFuncSetAttribute(tc2_kernel(na, st != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, smem_for(NG_MAX)) != cudaSuccess)
-                return bail("tensor-core loop engine: shared memory attribute");
+        for (int ng = 1; ng <= NG_MAX; ++ng)
+            for (int st = 0; st < 2; ++st)
+                if (cudaFuncSetAttribute(tc2_kernel(na, ng, st != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, smem_for(NG_MAX)) != cudaSuccess)
+                    return bail("tensor-core loop engine: shared memory attribute");
     return WN_OK;
 }
 
@@ -995,7 +1006,7 @@ int wn_launch_loop_tc2(wn_handle *h, const float *c_up, const float *noise, cons
             if (pl->d_stats) { cudaMemsetAsync(pl->d_stats, 0, sizeof(long long) * 16 * 160, st); p.stats = pl->d_stats; pl->stats_ctas = 4 * p.L + 1; }
         }
         void *args[] = {&p};
-        WN_CUDA_TRY(h, cudaLaunchKernelExC(&cfg, tc2_kernel(na, p.stats != nullptr), args));
+        WN_CUDA_TRY(h, cudaLaunchKernelExC(&cfg, tc2_kernel(na, ng, p.stats != nullptr), args));
         h->launches++;
     }
     WN_CUDA_TRY(h, cudaMemcpyAsync(pl->h_abort, pl->d_abort, sizeof(int), cudaMemcpyDeviceToHost, st));
