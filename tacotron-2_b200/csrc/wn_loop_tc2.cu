@@ -53,7 +53,8 @@ constexpr int OFF_OSLO_T = OFF_BIAS + 2 * 128 * 4;              // out/skip lo o
 constexpr int QUARTER_BLOB_BYTES = OFF_OSLO_T + 65536;
 // head blob: W1 hi 2 x [128][128 words] | W1 lo 2 x A image [32][128][8] | W2 fp32 [32][256] | b1 [256] | b2 [32] | first conv w [256], b [256]
 constexpr int HOFF_W1HI = 0, HOFF_W1LO = 2 * 65536, HOFF_W2 = 4 * 65536, HOFF_B1 = HOFF_W2 + 32 * C2 * 4, HOFF_B2 = HOFF_B1 + C2 * 4,
-              HOFF_FIRST = HOFF_B2 + 32 * 4, HEAD_BLOB_BYTES = HOFF_FIRST + 2 * C2 * 4;
+              HOFF_FIRST = HOFF_B2 + 32 * 4, HOFF_W1LO_T = HOFF_FIRST + 2 * C2 * 4 /* W1 lo once more, as tensor-memory rows 2 x [128][128 words] */,
+              HEAD_BLOB_BYTES = HOFF_W1LO_T + 2 * 65536;
 
 // tensor memory columns
 constexpr int NG_MAX = 3;                                                    // utterance groups that follow each other through the chain
@@ -61,7 +62,8 @@ constexpr int NG_MAX = 3;                                                    // 
 // tensor core truncates an addend when it aligns it to the accumulator, so the small cross terms accumulate among themselves
 constexpr int ACCW = 2 * NB;
 constexpr int COL_WG = 0, COL_WOS = 256, COL_AG = 384;                       // layer quarter: weights, then the accumulators of the groups
-constexpr int COL_W1 = 0, COL_H0 = 384, COL_H1 = COL_H0 + ACCW;              // head
+constexpr int COL_W1 = 0, COL_H0 = 384, COL_H1 = COL_H0 + ACCW;              // head: W1 hi (two tiles) | W1 lo of tile 0 | accumulators | W1 lo of tile 1, k < 128
+constexpr int COL_W1LO0 = 256, COL_W1LO1 = COL_H1 + ACCW, HEAD_NKS1 = (512 - COL_W1LO1) / 8;   // 8 of tile 1's 16 lo k steps fit
 // Layer quarter, columns from COL_AG on, for a kernel built for NGT groups: one accumulator per group - two-pass kernels (groups of
 // <= 8: main | cross inside NB columns) NB columns, three-pass kernels 2 NB - which holds the gate pre-activations and, later in the
 // group's turn, the out | skip rows (the gate epilogue has read it before the z barrier; the next x-independent part overwrites it
@@ -641,7 +643,9 @@ __device__ void head2_mma(const Tc2Params &P, unsigned char *smem, const uint32_
                 for (int ks = 0; ks < 16; ++ks) {
                     umma::mma_bf16_ts(D, tmem + COL_W1 + tile * 128 + ks * 8, hi_hi + ks * KS_B, idesc, ks != 0);
                     if (!WIDE) umma::mma_bf16_ts(D + NB, tmem + COL_W1 + tile * 128 + ks * 8, hi_lo + ks * KS_B, idesc, ks != 0);
-                    umma::mma_bf16(WIDE ? D : D + NB, w1lo[tile] + ks * KS_A, (WIDE ? hi_lo : hi_hi) + ks * KS_B, idesc, 1);
+                    if (tile == 0 || ks < HEAD_NKS1)   // lo weights resident in tensor memory
+                        umma::mma_bf16_ts(WIDE ? D : D + NB, tmem + (tile ? COL_W1LO1 : COL_W1LO0) + ks * 8, (WIDE ? hi_lo : hi_hi) + ks * KS_B, idesc, 1);
+                    else umma::mma_bf16(WIDE ? D : D + NB, w1lo[tile] + ks * KS_A, (WIDE ? hi_lo : hi_hi) + ks * KS_B, idesc, 1);
                 }
             }
             umma::mma_commit(umma::smem_addr(&bars.gate));
@@ -700,6 +704,21 @@ __global__ void __launch_bounds__(T2_THREADS, 1) wn_loop_tc2_kernel(const Tc2Par
     // resident weights; zero the activation images (the padding rows / columns of the images are never written again)
     if (head) {
         load_tmem_weights2(P.head_blob + HOFF_W1HI, 2, tmem, COL_W1);
+        load_tmem_weights2(P.head_blob + HOFF_W1LO_T, 1, tmem, COL_W1LO0);
+        if (tid < 128) {   // tile 1: the leading k steps
+            const uint32_t lane_addr = tmem + ((uint32_t)(tid & ~31) << 16);
+            const uint4 *row = reinterpret_cast<const uint4 *>(P.head_blob + HOFF_W1LO_T + 65536 + (size_t)tid * 512);
+            for (int pc = 0; pc < HEAD_NKS1 / 2; ++pc) {
+                uint32_t r[16];
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    const uint4 x = __ldg(row + pc * 4 + v);
+                    r[4 * v] = x.x; r[4 * v + 1] = x.y; r[4 * v + 2] = x.z; r[4 * v + 3] = x.w;
+                }
+                umma::tmem_st16(lane_addr + COL_W1LO1 + 16 * pc, r);
+            }
+            umma::tmem_st_wait();
+        }
         const uint4 *src = reinterpret_cast<const uint4 *>(P.head_blob + HOFF_W1LO);
         for (int i = tid; i < (S_W2 - S_W1LO) / 16; i += T2_THREADS) reinterpret_cast<uint4 *>(tc_smem + S_W1LO)[i] = __ldg(src + i);   // W1 lo
         for (int i = tid; i < (S_HEND - S_HI) / 16; i += T2_THREADS) reinterpret_cast<uint4 *>(tc_smem + S_HI)[i] = make_uint4(0, 0, 0, 0);
@@ -875,6 +894,11 @@ int wn_tc2_plan(wn_handle *h) {
                 const float v = w1[(size_t)k * C2 + j];
                 put_tmem(hb.data() + HOFF_W1HI + tile * 65536, nullptr, row, k, v);
                 put_img(nullptr, hb.data() + HOFF_W1LO + tile * 65536, row, k, v);
+                {
+                    uint16_t hi16, lo16;
+                    split_host2(v, hi16, lo16);
+                    reinterpret_cast<uint16_t *>(hb.data() + HOFF_W1LO_T + tile * 65536)[(size_t)row * 256 + k] = lo16;
+                }
             }
             b1s[j] = b1 ? b1[j] : 0.0f;
             first[j] = fw[j];
