@@ -334,7 +334,9 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     }
 }
 
-template <int NB, bool WIDE>
+// LAST: the last layer has no residual output - the tensor-memory slot of W_out holds its skip weights (wn_tc_plan), the same
+// MMAs go into the skip accumulator and the shared-memory-operand skip MMAs (~60 cycles each, on the step's critical path there) fall away
+template <int NB, bool WIDE, bool LAST>
 __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t tmem, Bars &bars) {
     using G = Geo<NB>;
     constexpr int LBO = G::LBO, PLANE = G::PLANE;
@@ -425,15 +427,16 @@ __device__ void layer_mma(const TcParams &P, unsigned char *smem, const uint32_t
         if (umma::elect_one()) {
 #pragma unroll
             for (int ks = 0; ks < 8; ++ks) {
-                umma::mma_bf16_ts(D_O, tmem + COL_WOUT + ks * 8, zi_hi + ks * KS_B, idesc, ks != 0);
-                if (!WIDE) umma::mma_bf16_ts(D_O, tmem + COL_WOUT + ks * 8, zi_lo + ks * KS_B, idesc, 1);
-                umma::mma_bf16_ts(D_O, tmem + COL_WOUT + 64 + ks * 8, (WIDE ? zi_lo : zi_hi) + ks * KS_B, idesc, 1);
+                umma::mma_bf16_ts(LAST ? D_S : D_O, tmem + COL_WOUT + ks * 8, zi_hi + ks * KS_B, idesc, ks != 0);
+                if (!WIDE) umma::mma_bf16_ts(LAST ? D_S : D_O, tmem + COL_WOUT + ks * 8, zi_lo + ks * KS_B, idesc, 1);
+                umma::mma_bf16_ts(LAST ? D_S : D_O, tmem + COL_WOUT + 64 + ks * 8, (WIDE ? zi_lo : zi_hi) + ks * KS_B, idesc, 1);
             }
             umma::mma_commit(umma::smem_addr(&gb.out));
+            if (LAST) umma::mma_commit(umma::smem_addr(&gb.skip));
         }
         __syncwarp();
         // skip 1x1 on z (modules.py:512), weights in shared memory
-        if (umma::elect_one()) {
+        if (!LAST && umma::elect_one()) {
 #pragma unroll
             for (int ks = 0; ks < 8; ++ks) {
                 umma::mma_bf16(D_S, ws_hi + ks * KS_A, zi_hi + ks * KS_B, idesc, ks != 0);
@@ -745,7 +748,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
         else if (warp == MMA_WARP) head_mma<NB, (NB == 16 && NAH <= 4)>(P, tc_smem, tmem, bars);
     } else {
         if (warp < 8) layer_epilogue<NB, NAH, STATS>(P, r, l, tc_smem, tmem, bars);
-        else if (warp == MMA_WARP) layer_mma<NB, (NB == 16 && NAH <= 4)>(P, tc_smem, tmem, bars);
+        else if (warp == MMA_WARP) {
+            if (l + 1 == P.L) layer_mma<NB, (NB == 16 && NAH <= 4), true>(P, tc_smem, tmem, bars);
+            else layer_mma<NB, (NB == 16 && NAH <= 4), false>(P, tc_smem, tmem, bars);
+        }
         else layer_loader(P, l, tc_smem, bars, G::S_WST);
     }
     // every role returns when the sequence is done (or the watchdog fired): release tensor memory
@@ -856,7 +862,8 @@ int wn_tc_plan(wn_handle *h) {
                 // current tap = tap 2 of the [3][R][G] kernel (modules.py:238-251: row = tap * R + ci, tap 0 oldest)
                 put_tmem(b + OFF_TMEM, b + OFF_TMEM + 32768, j, k, cw[((size_t)2 * CH + k) * G2 + j]);
                 put_tmem(b + OFF_TMEM + 2 * 32768, b + OFF_TMEM + 3 * 32768, j, k, cw[((size_t)2 * CH + k) * G2 + CH + j]);
-                put_tmem(b + OFF_TMEM + 4 * 32768, b + OFF_TMEM + 5 * 32768, j, k, ow[(size_t)k * CH + j]);
+                // the last layer has no residual output (wavenet.py:833: only its skip is used): the slot holds its skip weights instead
+                put_tmem(b + OFF_TMEM + 4 * 32768, b + OFF_TMEM + 5 * 32768, j, k, l + 1 == L ? sw[(size_t)k * CH + j] : ow[(size_t)k * CH + j]);
                 put_img(b + OFF_WS, b + OFF_WS + 32768, j, k, sw[(size_t)k * CH + j]);
             }
         for (int kb = 0; kb < KB_TOTAL; ++kb)
