@@ -6,8 +6,9 @@
 //
 //   quarter q owns the gate channels [64q, 64q + 64) - one M = 128 tile = their 64 tanh rows + their 64 sigmoid rows over
 //   K = 256 - and one M = 128 tile of the second GEMM = 64 residual-out rows + 64 skip rows over K = 256 (the gated channels).
-//   Tensor memory: gate tile hi | lo (256 columns), out/skip tile hi (128), accumulators (32); the out/skip lo half (64 KB)
-//   and the two stages of the weight stream sit in shared memory.
+//   Tensor memory: gate tile hi | lo (256 columns), out/skip tile hi (128), one accumulator per utterance group, and behind them the
+//   out/skip lo weights of as many k steps as fit; the out/skip lo half (64 KB, used for the remaining k steps) and the two stages
+//   of the weight stream sit in shared memory.
 //
 //   Both GEMMs need ALL 256 channels of their input, produced 64 per quarter: the all-gather is a shared mailbox in L2 -
 //   every quarter writes its 64 channels as {value, tag} words, every quarter polls all 256.  Per layer and step:
