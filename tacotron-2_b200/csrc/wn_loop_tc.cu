@@ -79,6 +79,7 @@ struct TcParams {
     int inputs_mode;
     float *audio, *raw;
     int B, T, NR;
+    int no_fb;                           // ablation (WN_TC_NOFB): the fed-back sample through the L2 mailbox even inside a cluster
     int stride;                          // CTAs per replica in the grid: L + 1, or padded so that larger clusters divide it (idle CTAs at the end)
     int NG;                              // utterance groups that travel through a replica's chain one after the other (1 .. 4)
     int NA;                              // utterances a group really holds (multiple of 4, <= the MMA's N): the epilogues skip the rest
@@ -150,6 +151,7 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
     // through the L2 mailboxes
     const uint32_t crank = cluster_ctarank(), csize = cluster_nctarank();
     const bool in_dsmem = l > 0 && crank > 0, out_dsmem = l + 1 < L && crank + 1 < csize;
+    const bool fb_dsmem = l == 0 && crank > 0 && !P.no_fb;   // layer 0: the head is the previous CTA of the cluster
     constexpr int CN = (CI_K * NA + EPI_THREADS - 1) / EPI_THREADS;   // conditioning elements per thread (upper bound)
     long long st_c[6] = {0, 0, 0, 0, 0, 0};
     const bool do_stats = STATS && P.stats != nullptr && tid == 0;
@@ -239,7 +241,13 @@ __device__ void layer_epilogue(const TcParams &P, const int r, const int l, unsi
         float xin[NH];
         if (l == 0) {
             float s[NH];
-            if (poll_units<NU>(min_in + par * NB, 2, tag, s, nu, P.abort_flag)) return;
+            if (fb_dsmem) {   // the group's inbox holds the NA fed-back samples (4 bytes each, counted on the inbox barrier)
+                if (tid == 0) umma::mbar_expect_tx(bxf, NA * 4);
+                if (mbar_wait_cluster_wd(bxf, par, P.abort_flag)) return;
+                const float *fb = reinterpret_cast<const float *>(smem + G::S_G0 + g * G::GRP + G::G_XF);
+#pragma unroll
+                for (int i = 0; i < NH; ++i) s[i] = i < nah ? fb[n0 + i] : 0.0f;
+            } else if (poll_units<NU>(min_in + par * NB, 2, tag, s, nu, P.abort_flag)) return;
 #pragma unroll
             for (int i = 0; i < NH; ++i) xin[i] = __fmaf_rn(s[i], wf, bf);
         } else if (in_dsmem) {
@@ -495,10 +503,16 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
     float *prm = reinterpret_cast<float *>(smem + G::S_PRM);   // [NB][CH]
     const uint32_t bh = umma::smem_addr(&bars.g[0].x), bh2 = umma::smem_addr(&bars.g[0].z), bh1 = umma::smem_addr(&bars.g[0].gate),
                    bo = umma::smem_addr(&bars.g[0].out);
+    // layer 0 is the next CTA of the head's cluster (if there are clusters): the samples go into its per-group inbox with st.async
+    const bool fb_dsmem = cluster_nctarank() > 1 && !P.no_fb;
+    auto r_fb = [&](int g) { return mapa_u32(umma::smem_addr(smem + G::S_G0 + g * G::GRP + G::G_XF), 1); };
+    auto r_bfb = [&](int g) { return mapa_u32(umma::smem_addr(&bars.g[g].xf), 1); };
     // initial input (wavenet.py:433-445): raw 0.0, mulaw mulaw(0) = 0.0; WaveNet.step semantics: the first input is x[0]
     for (int g = 0; g < NG; ++g) {
         const long long b = (long long)P.b0 + (long long)(r * NG + g) * NA + tid;
-        if (tid < NB) st_ll1(P.mail_in + (long long)(r * NG + g) * 2 * NB + tid, (tid < NA && b < P.bend && P.inputs_mode) ? P.teacher[b * T] : 0.0f, 1u);
+        const float v0 = (tid < NA && b < P.bend && P.inputs_mode) ? P.teacher[b * T] : 0.0f;
+        if (fb_dsmem) { if (tid < NA) st_async_b32(r_fb(g) + tid * 4, __float_as_uint(v0), r_bfb(g)); }
+        else if (tid < NB) st_ll1(P.mail_in + (long long)(r * NG + g) * 2 * NB + tid, v0, 1u);
     }
     long long st_c[4] = {0, 0, 0, 0};
     const bool do_stats = STATS && P.stats != nullptr && tid == 0;
@@ -616,7 +630,10 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
                 P.audio[bu * T + t] = P.input_type == WN_INPUT_MULAW ? wn_inv_mulawf(smp) : smp;
                 nxt = P.teacher ? tch : smp;
             }
-            if (t + 1 < T) st_ll1(min_out + ((t + 1) & 1) * NB + ns, nxt, tag + 1u);
+            if (t + 1 < T) {
+                if (fb_dsmem) st_async_b32(r_fb(g) + ns * 4, __float_as_uint(nxt), r_bfb(g));
+                else st_ll1(min_out + ((t + 1) & 1) * NB + ns, nxt, tag + 1u);
+            }
         }
         __syncwarp();   // the parameters are overwritten by the same warp in its next turn
         if (do_stats) {
@@ -700,9 +717,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) wn_loop_tc_kernel(const TcParam
     __shared__ Bars bars;
     __shared__ uint32_t tmem_base_s;
     const int tid = threadIdx.x, warp = tid >> 5;
-    const int r = blockIdx.x / P.stride, l = blockIdx.x - r * P.stride;
-    const bool head = l == P.L;
-    if (l > P.L) {   // padding CTA (the replica's slots are rounded up to a multiple of the cluster size): only the cluster's barriers
+    // slots of a replica in the grid: 0 = the head (so that it shares layer 0's cluster: the fed-back sample travels through
+    // distributed shared memory), 1 .. L = the layers, beyond = padding
+    const int r = blockIdx.x / P.stride, slot = blockIdx.x - r * P.stride;
+    const bool head = slot == 0;
+    const int l = head ? P.L : slot - 1;
+    if (slot > P.L) {   // padding CTA (the replica's slots are rounded up to a multiple of the cluster size): only the cluster's barriers
         cluster_sync_all();
         cluster_sync_all();
         return;
@@ -1051,9 +1071,9 @@ static int tc_launch_chunk(wn_handle *h, TcParams p, int b0, int nbatch, cudaStr
     struct Cand { int stride, csize, hops; };
     std::vector<Cand> cands;
     const int pad = ((L + 1 + 11) / 12) * 12;
-    for (int c : {12, 8, 6, 4}) cands.push_back({pad, c, (L + c - 1) / c - 1});
+    for (int c : {12, 8, 6, 4}) cands.push_back({pad, c, L / c});   // layer l sits in slot l + 1: its x crosses a cluster boundary when c divides l + 1
     for (int c = 8; c >= 2; --c)
-        if ((L + 1) % c == 0) cands.push_back({L + 1, c, (L + c - 1) / c - 1});
+        if ((L + 1) % c == 0) cands.push_back({L + 1, c, L / c});
     std::stable_sort(cands.begin(), cands.end(), [](const Cand &a, const Cand &b) { return a.hops < b.hops; });
     int csize = 1, stride = L + 1;
     const char *ecl = getenv("WN_TC_CLUSTER");
@@ -1109,6 +1129,7 @@ int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const
     }
     p.test_stall_step = -1;
     if (const char *e = getenv("WN_TC_TEST_STALL")) p.test_stall_step = atoi(e);
+    p.no_fb = getenv("WN_TC_NOFB") ? 1 : 0;
     const int cap = pl->max_replicas * Geo<16>::NG_MAX * 16;   // groups of 16 utterances in every chain
     const int nchunks = (B + cap - 1) / cap, per = (B + nchunks - 1) / nchunks;
     for (int b0 = 0; b0 < B; b0 += per) {

@@ -140,6 +140,9 @@ __device__ __forceinline__ void st_async2(uint32_t raddr, float v0, float v1, ui
     asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];"
                  ::"r"(raddr), "f"(v0), "f"(v1), "r"(rmbar) : "memory");
 }
+__device__ __forceinline__ void st_async_b32(uint32_t raddr, uint32_t v, uint32_t rmbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(raddr), "r"(v), "r"(rmbar) : "memory");
+}
 __device__ __forceinline__ bool mbar_try_cluster(uint32_t bar, uint32_t parity) {
     uint32_t ok;
     asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
