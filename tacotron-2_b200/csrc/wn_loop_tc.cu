@@ -56,7 +56,7 @@ constexpr int OFF_STREAM = OFF_WS + 65536;        // NCHUNK chunks
 constexpr int OFF_BIAS = OFF_STREAM + NCHUNK * CHUNK_BYTES;   // gate a, gate b, out, skip: 4 x 128 floats
 constexpr int LAYER_BLOB_BYTES = OFF_BIAS + 4 * CH * 4;
 // head blob: 4 x [128][64] words (W1 hi, lo, W2 hi, lo; W2 rows >= O zero), then b1[128], b2[128]
-constexpr int HEAD_BLOB_BYTES = 4 * 32768 + 2 * CH * 4;
+constexpr int HEAD_BLOB_BYTES = 4 * 32768 + 4 * CH * 4;   // W1, W2 as tensor-memory rows (hi, lo) | b1, b2 | rows 0, 1 of W2 in fp32
 
 // tensor memory columns of a layer CTA
 constexpr int COL_WCUR = 0, COL_WOUT = 256, COL_ACC = 384;   // accumulators: gate a | gate b | out | skip, NB columns each
@@ -79,6 +79,7 @@ struct TcParams {
     int inputs_mode;
     float *audio, *raw;
     int B, T, NR;
+    int no_w2c;                          // ablation (WN_TC_NOW2C): the single-Gaussian head's second 1x1 on the tensor cores too
     int no_fb;                           // ablation (WN_TC_NOFB): the fed-back sample through the L2 mailbox even inside a cluster
     int stride;                          // CTAs per replica in the grid: L + 1, or padded so that larger clusters divide it (idle CTAs at the end)
     int NG;                              // utterance groups that travel through a replica's chain one after the other (1 .. 4)
@@ -495,6 +496,12 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
     const int L = P.L, T = P.T, O = P.O, NG = P.NG;
     const float *hb = reinterpret_cast<const float *>(P.head_blob + 4 * 32768);
     const float b1 = __ldg(hb + j), b2 = __ldg(hb + CH + j);
+    // single-Gaussian head (O = 2): the second 1x1 has two output rows - fp32 dot products on the CUDA cores (this thread's channel,
+    // warp-shuffle tree, the four warps of a utterance half through shared memory) instead of another image -> MMA -> epilogue round trip
+    const bool w2_cuda = O == 2 && !P.no_w2c;
+    const float w20 = __ldg(hb + 2 * CH + j), w21 = __ldg(hb + 3 * CH + j), b20 = __ldg(hb + CH), b21 = __ldg(hb + CH + 1);
+    float *part = reinterpret_cast<float *>(smem + G::S_H2);   // [4 lane quarters][2 rows][NB]   (the image of the MMA path is not used then)
+    const uint32_t bpart = umma::smem_addr(&bars.g[1].x);      // 8 warp arrivals per turn
     const float cskip = 0.70710677f;
     const int joff = (j >> 3) * LBO + n0 * 16 + (j & 7) * 2;
     const long long unit0 = ((long long)(hh * NU) * CH + j) * 2;
@@ -585,6 +592,46 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
         if (lane == 0) umma::mbar_arrive(bh);
         if (mbar_wait_wd(bh1, bpar, P.abort_flag)) return;
         umma::fence_after_sync();
+        float out2[2] = {0.0f, 0.0f};   // the two parameters of this sampler lane's utterance (w2_cuda)
+        if (w2_cuda) {
+            float h[NH];
+            acc_load<NH, WIDE>(lane_addr + COL_HACC + n0, h);
+            float pa[NH], pb[NH];
+#pragma unroll
+            for (int i = 0; i < NH; ++i) {
+                const float y = __fadd_rn(h[i], b1), yr = y > 0.0f ? y : 0.0f;   // relu (wavenet.py:842)
+                pa[i] = i < nah ? __fmul_rn(w20, yr) : 0.0f;
+                pb[i] = i < nah ? __fmul_rn(w21, yr) : 0.0f;
+            }
+#pragma unroll
+            for (int i = 0; i < NH; ++i) {
+                if (i < nah) {
+#pragma unroll
+                    for (int m = 16; m >= 1; m >>= 1) {
+                        pa[i] = __fadd_rn(pa[i], __shfl_xor_sync(0xffffffffu, pa[i], m));
+                        pb[i] = __fadd_rn(pb[i], __shfl_xor_sync(0xffffffffu, pb[i], m));
+                    }
+                    if (lane == 0) {
+                        part[(q * 2 + 0) * NB + n0 + i] = pa[i];
+                        part[(q * 2 + 1) * NB + n0 + i] = pb[i];
+                    }
+                }
+            }
+            umma::fence_before_sync();
+            __syncwarp();
+            if (lane == 0) umma::mbar_arrive(bpart);
+            if (q == 0) {   // the sampler warps
+                if (mbar_wait_wd(bpart, bpar, P.abort_flag)) return;
+                if (slane) {
+                    out2[0] = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(part[0 * NB + ns], part[2 * NB + ns]), part[4 * NB + ns]), part[6 * NB + ns]), b20);
+                    out2[1] = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(part[1 * NB + ns], part[3 * NB + ns]), part[5 * NB + ns]), part[7 * NB + ns]), b21);
+                    if (P.raw && bu < P.bend) {   // wavenet.py:847
+                        P.raw[(bu * T + t) * 2] = out2[0];
+                        P.raw[(bu * T + t) * 2 + 1] = out2[1];
+                    }
+                }
+            }
+        } else {
         {
             float h[NH];
             acc_load<NH, WIDE>(lane_addr + COL_HACC + n0, h);
@@ -600,7 +647,6 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
         if (lane == 0) umma::mbar_arrive(bh2);
         if (mbar_wait_wd(bo, bpar, P.abort_flag)) return;
         umma::fence_after_sync();
-        const long long c2 = do_stats ? clock64() : 0;
         {
             float o[NH];
             acc_load<NH, WIDE>(lane_addr + COL_HACC + NB + n0, o);
@@ -616,6 +662,8 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
                 }
             }
         }
+        }
+        const long long c2 = do_stats ? clock64() : 0;
         umma::fence_before_sync();
         __syncwarp();
         if (t == P.test_stall_step) return;   // test hook: the chain starves and every waiter must time out (WN_ERR_WATCHDOG)
@@ -625,7 +673,7 @@ __device__ void head_epilogue(const TcParams &P, const int r, unsigned char *sme
             if (sampler && P.inputs_mode) {
                 nxt = tch;
             } else if (sampler) {
-                const float smp = (O == 2) ? tc_sample_gaussian(P.log_scale_min_gauss, prm + ns * CH, nz0)
+                const float smp = (O == 2) ? tc_sample_gaussian(P.log_scale_min_gauss, out2, nz0)
                                            : tc_sample_mol(P.log_scale_min, O, prm + ns * CH, P.noise + ((long long)t * P.B + bu) * P.NZ);
                 P.audio[bu * T + t] = P.input_type == WN_INPUT_MULAW ? wn_inv_mulawf(smp) : smp;
                 nxt = P.teacher ? tch : smp;
@@ -675,6 +723,7 @@ __device__ void head_mma(const TcParams &P, unsigned char *smem, const uint32_t 
             umma::mma_commit(bh1);
         }
         __syncwarp();
+        if (P.O == 2 && !P.no_w2c) continue;   // single Gaussian: the second 1x1 runs on the CUDA cores (head_epilogue)
         if (mbar_wait_wd(umma::smem_addr(&bars.g[0].z), par, P.abort_flag)) return;   // final_convolution_2 (wavenet.py:843), rows >= O zero
         umma::fence_after_sync();
         if (umma::elect_one()) {
@@ -916,7 +965,10 @@ int wn_tc_plan(wn_handle *h) {
                 put_tmem(hb.data() + 2 * 32768, hb.data() + 3 * 32768, j, k, j < O ? w2[(size_t)k * O + j] : 0.0f);
             }
         float *bias = reinterpret_cast<float *>(hb.data() + 4 * 32768);
-        for (int j = 0; j < CH; ++j) { bias[j] = b1 ? b1[j] : 0.0f; bias[CH + j] = (b2 && j < O) ? b2[j] : 0.0f; }
+        for (int j = 0; j < CH; ++j) {
+            bias[j] = b1 ? b1[j] : 0.0f; bias[CH + j] = (b2 && j < O) ? b2[j] : 0.0f;
+            bias[2 * CH + j] = w2[(size_t)j * O]; bias[3 * CH + j] = O > 1 ? w2[(size_t)j * O + 1] : 0.0f;
+        }
     }
     std::vector<float> first(2 * CH, 0.0f);
     {
@@ -1130,6 +1182,7 @@ int wn_launch_loop_tc(wn_handle *h, const float *c_up, const float *noise, const
     p.test_stall_step = -1;
     if (const char *e = getenv("WN_TC_TEST_STALL")) p.test_stall_step = atoi(e);
     p.no_fb = getenv("WN_TC_NOFB") ? 1 : 0;
+    p.no_w2c = getenv("WN_TC_NOW2C") ? 1 : 0;
     const int cap = pl->max_replicas * Geo<16>::NG_MAX * 16;   // groups of 16 utterances in every chain
     const int nchunks = (B + cap - 1) / cap, per = (B + nchunks - 1) / nchunks;
     for (int b0 = 0; b0 < B; b0 += per) {
