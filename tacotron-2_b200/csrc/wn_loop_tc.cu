@@ -1,7 +1,8 @@
 // wn_loop_tc.cu - the autoregressive loop of WaveNet.incremental (wavenet.py:805-911) on the sm_100a tensor cores.
 //
-// ONE cooperative launch runs all T steps.  The batch is cut into NR "replicas" of NB utterances (NB = 16 or 32 = the N of
-// every MMA); a replica is a chain of L + 1 CTAs, one per residual layer plus one head CTA, each alone on its SM:
+// ONE cooperative launch runs all T steps.  The batch is cut into groups of NA utterances (a multiple of 4, at most NB = 16 or 32 =
+// the N of every MMA); a "replica" is a chain of L + 1 CTAs, the head CTA and one per residual layer, each alone on its SM; up to 7
+// replicas run side by side and up to 4 groups follow each other through one chain:
 //
 //   layer CTA l  (ResidualConv1DGLU.incremental_step, modules.py:468-521)
 //     * the weights every step needs at once stay ON CHIP for the whole launch, as fp16 (hi, lo) pairs:
@@ -19,9 +20,11 @@
 //     cores), the sampler (gaussian.py:39-52 / mixture.py:76-107) from the caller's noise buffer, audio / raw outputs,
 //     and the sample fed back to layer 0.
 //
-// Hand-offs between CTAs are {value, tag} words in L2 (tag = step + 1, double buffered on t & 1): no fence, no flag
-// separate from the data.  The dilation rings live in global memory (L2); every ring element is written and later read
-// by the same thread.
+// Hand-offs: consecutive CTAs of a replica share a thread-block cluster where they can (tc_launch_chunk) and pass x - and the head
+// the fed-back sample - with st.async into the next CTA's shared memory, counted in bytes on its mbarrier; across cluster
+// boundaries and for the skip outputs they are {value, tag} words in L2 (tag = step + 1, double buffered on t & 1): no fence, no
+// flag separate from the data.  The dilation rings live in global memory (L2); every ring element is written and later read
+// by the same thread.  Groups of <= 8 utterances use two MMA passes instead of three (img_put2 in wn_tc_common.cuh).
 //
 // Arithmetic: fp32 accumulation everywhere; every fp32 operand is split into two fp16 numbers (22 significant bits) and a
 // product is three MMA passes, so results agree with the fp32 engines to ~1e-6 relative - the summation order differs, so not
